@@ -1,0 +1,221 @@
+/*
+ * plc.h — C ABI of the B200-native point-cloud path ("plc") that replaces the data-parallel
+ * bodies of three reference ROS2 nodes.  POD only, no exceptions, no C++/torch types.
+ *
+ * The reference (YamaguchiAtsushi/pointcloud_processor) has no FFI or plugin interface: its hot
+ * path sits in private member functions of rclcpp::Node subclasses.  Each entry point below names
+ * the reference lines whose body it replaces; INTEGRATION.md shows the call sites a maintainer
+ * adds to the three nodes.
+ *
+ * Conventions
+ *   - every function returns plc_status (0 = OK, negative = error); plc_strerror() names it.
+ *   - the caller owns every host pointer; the library copies in during the call and never keeps
+ *     caller memory.  Output buffers are caller-allocated with a capacity; too small a capacity
+ *     is PLC_E_CAPACITY and nothing is written.
+ *   - a plc_ctx is bound to one CUDA device and one stream, is NOT thread-safe, and every call is
+ *     synchronous unless its name ends in _async.
+ *   - there is no CPU fallback: without a usable device plc_ctx_create fails with PLC_E_CUDA.
+ *   - point clouds cross the boundary in sensor_msgs/PointCloud2 wire layout: a byte buffer,
+ *     a point_step, and the byte offsets of the FLOAT32 x/y/z fields (plc_cloud_view).
+ */
+#ifndef PLC_H_
+#define PLC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PLC_ABI_VERSION 1
+
+typedef enum plc_status {
+    PLC_OK = 0,
+    PLC_E_INVALID_ARG = -1,
+    PLC_E_NO_TERRAIN = -2,   /* sweep asked for before plc_vl_set_terrain (reference: runOptimization guard, virtual_lidar.cpp:455) */
+    PLC_E_NO_CELLS = -3,     /* sweep asked for before plc_vl_set_cells (virtual_lidar.cpp:455) */
+    PLC_E_CAPACITY = -4,
+    PLC_E_CUDA = -5,
+    PLC_E_NCCL = -6,
+    PLC_E_OOM = -7,
+    PLC_E_NO_CANDIDATES = -8
+} plc_status;
+
+typedef struct plc_ctx plc_ctx;
+
+/* ---------------------------------------------------------------- PODs ---------------------- */
+
+/* A view of PointCloud2 `data`.  Offsets are byte offsets of FLOAT32 fields. */
+typedef struct plc_cloud_view {
+    const void* data;
+    uint64_t n_points;      /* width*height */
+    uint32_t point_step;
+    uint32_t off_x, off_y, off_z;
+} plc_cloud_view;
+
+/* Evaluation target; mirrors the fields of `struct GridCell` the sweep reads
+ * (virtual_lidar.cpp:20-44): double centre, float32 unit normal (pcl::Normal). 40 bytes. */
+typedef struct plc_cell {
+    double x, y, z;
+    float nx, ny, nz;
+    uint32_t pad;
+} plc_cell;
+
+/* Sensor pose; mirrors `struct LidarPosition` (virtual_lidar.cpp:46-51). 40 bytes. */
+typedef struct plc_pose {
+    double x, y, z, pitch, yaw;
+} plc_pose;
+
+/* Every ROS parameter and every `static constexpr` of the sweep (virtual_lidar.cpp:66-71,100-114)
+ * as a runtime field, so the un-built `virtual_lidar_memo.cpp` parameterisation is testable too. */
+typedef struct plc_params {
+    double max_distance;          /* param "max_distance" = 15.0            (:69, :662) */
+    double min_distance;          /* MIN_DISTANCE = 0.5                      (:102, :662) */
+    double ray_step;              /* RAY_STEP_SIZE = 0.3                     (:111, :796) */
+    double ray_start;             /* start_offset = 0.5                      (:765)       */
+    double vis_radius;            /* VISIBILITY_RADIUS = 0.08; end margin    (:112, :767) */
+    double block_radius_scale;    /* 0.7: search radius = vis_radius*0.7     (:782)       */
+    double observed_radius_scale; /* 3.0: fixed-sensor lookup radius scale   (:743)       */
+    double fov_vertical;          /* 180.0*M_PI/180.0 (full angle)           (:711-713)   */
+    double fov_horizontal;        /* < 0: no azimuth test (built node); memo variant: 180.0*M_PI/180.0 */
+    double alpha, beta;           /* ALPHA = BETA = 1.0                      (:100-101, :698) */
+    int32_t fixed_mode;           /* 0: built node (:716-752)  1: memo variant (virtual_lidar_memo.cpp:699-726) */
+    int32_t reserved;
+} plc_params;
+
+/* Defaults of the built node. */
+void plc_params_default(plc_params* p);
+/* Defaults of virtual_lidar_memo.cpp (constants :102-113, FOV :684-697). */
+void plc_params_memo(plc_params* p);
+
+/* Per-cell flag bits, same meaning as the GridCell bools (virtual_lidar.cpp:26-31). */
+enum {
+    PLC_FLAG_RANGE_FIXED = 1u << 0,
+    PLC_FLAG_FOV_FIXED = 1u << 1,
+    PLC_FLAG_VIS_FIXED = 1u << 2,
+    PLC_FLAG_RANGE_MOBILE = 1u << 3,
+    PLC_FLAG_FOV_MOBILE = 1u << 4,
+    PLC_FLAG_VIS_MOBILE = 1u << 5
+};
+
+/* Counters echoed by the sweep so that both sides compute the same algorithmic bytes
+ * (SURVEY §8 D4). All refer to mobile-sensor rays of the candidates this ctx evaluated. */
+typedef struct plc_counters {
+    uint64_t rays;            /* candidates evaluated * cells */
+    uint64_t rays_gated_in;   /* rays that passed range and FOV */
+    uint64_t rays_visible;    /* rays with the visibility bit set */
+    uint64_t samples;         /* sample positions the reference would evaluate (up to and incl. first blocked) */
+    uint64_t fixed_samples;   /* same, for the hoisted fixed-sensor pass (M rays) */
+    uint64_t exact_tests;     /* samples that needed the exact point test (implementation detail, informational) */
+} plc_counters;
+
+typedef struct plc_sweep_out {
+    /* scalars, always written */
+    int64_t best_index;       /* global candidate index of the first maximum; -1 if no candidates (Q5) */
+    double best_score;        /* -inf if no candidates */
+    int32_t best_covered;     /* covered_cells of the best candidate */
+    int32_t n_cells;
+    double fixed_total;       /* "Total Score (ZX120 only)" (virtual_lidar.cpp:384-386) */
+    plc_counters counters;
+    /* optional arrays, may be NULL; indexed by LOCAL candidate (cand_begin..cand_end) */
+    double* scores;           /* [n_local] total_score per candidate (:647) */
+    int32_t* covered;         /* [n_local] covered_cells (:648) */
+    uint32_t* mask;           /* [n_local * mask_words] bit j of word w = mobile ray to cell 32w+j passed range, FOV and occlusion */
+    uint64_t mask_words;      /* ceil(n_cells/32), written by the library */
+    uint8_t* cell_flags;      /* [n_cells] PLC_FLAG_* with the reference's carry-over rule */
+    double* fixed_scores;     /* [n_cells] score_zx120 per cell (:377) */
+} plc_sweep_out;
+
+/* ---------------------------------------------------------------- context ------------------- */
+
+/* Binds a context to `device`.  `stream` is a cudaStream_t (as void*) the library launches on, or
+ * NULL to let the context create its own non-blocking stream. */
+plc_status plc_ctx_create(int device, void* stream, plc_ctx** out);
+void plc_ctx_destroy(plc_ctx* ctx);
+const char* plc_strerror(int status);
+/* Last CUDA/NCCL error text seen by this context ("" if none). */
+const char* plc_last_error(const plc_ctx* ctx);
+/* Number of kernels this context has launched since creation (bench.py "gpu_launches"). */
+uint64_t plc_launch_count(const plc_ctx* ctx);
+int plc_abi_version(void);
+/* Blocks until everything queued on the context's stream has finished. */
+plc_status plc_ctx_sync(plc_ctx* ctx);
+
+/* ---------------------------------------------------------------- virtual_lidar ------------- */
+
+/* Replaces the KD-tree build of terrainCallback (virtual_lidar.cpp:180-192): voxelises the
+ * /excavated_terrain cloud into the occupancy grid the sweep traverses.  Non-finite points are
+ * dropped, as KdTreeFLANN::setInputCloud does.  n_points == 0 leaves "no terrain" (every ray
+ * visible, :727), matching the reference's empty-cloud guard (:184). */
+plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* cloud);
+/* Replaces zx120PointsCallback (virtual_lidar.cpp:194-207): the cloud observed by the fixed sensor. */
+plc_status plc_vl_set_observed(plc_ctx* ctx, const plc_cloud_view* cloud);
+/* Hands over excavation_grid_3d_ (built by generateExcavationGrid3D, :236-287). Resets cell flags. */
+plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint64_t n_cells);
+
+/* Replaces runOptimization lines 460-475: evaluateZX120Only + the candidate loop + argmax.
+ * `cands[0..n_cands)` is the full candidate list; this context evaluates [cand_begin, cand_end)
+ * (pass 0, n_cands for a single GPU).  best_index is a GLOBAL index. */
+plc_status plc_vl_sweep(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
+                        const plc_pose* cands, uint64_t n_cands,
+                        uint64_t cand_begin, uint64_t cand_end, plc_sweep_out* out);
+
+/* The same sweep split so that a caller can keep inputs resident in HBM and time the device part:
+ *   upload (H2D of params + poses)  ->  run_async (kernels only)  ->  fetch (D2H of results). */
+plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
+                                    const plc_pose* cands, uint64_t n_cands,
+                                    uint64_t cand_begin, uint64_t cand_end);
+plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_flags);
+plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out);
+/* Device address of this context's {double best_score; int64 best_global_index} pair (16 bytes),
+ * valid after plc_vl_run_async; the multi-GPU exchange all-gathers it. */
+plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr);
+
+/* Grid facts for roofline accounting: bytes of the occupancy structure the sweep reads. */
+typedef struct plc_grid_info {
+    uint64_t n_points;        /* finite points indexed */
+    uint64_t n_voxels;        /* coarse voxels */
+    uint64_t grid_bytes;      /* mask bricks + voxel ranges + sorted float4 points */
+    int32_t dim[3];
+    double origin[3];
+    double voxel;             /* coarse voxel edge (m) */
+} plc_grid_info;
+plc_status plc_vl_grid_info(const plc_ctx* ctx, plc_grid_info* terrain, plc_grid_info* observed);
+
+/* ---------------------------------------------------------------- pointcloud_filter --------- */
+
+/* cropFrontArea bounds (pointcloud_filter.cpp:111-113); all six comparisons strict. */
+typedef struct plc_crop_box {
+    double x_min, x_max;   /* 0.0, front_range  */
+    double y_min, y_max;   /* -side, +side      */
+    double z_min, z_max;   /* -1.5, height      */
+} plc_crop_box;
+
+/* Replaces processCloudSimple's crop + VoxelGrid (pointcloud_filter.cpp:64-85, 87-139).
+ * Output: PointXYZ wire layout, 16 bytes per point: x,y,z and the 1.0f that pcl::PointXYZ keeps in
+ * data[3] and pcl::toROSMsg copies to the wire.
+ * leaf <= 0 skips the downsample (crop only).  An empty crop returns n_out = 0 (Q7). */
+plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const plc_crop_box* box, double leaf,
+                      void* out_xyz16, uint64_t capacity, uint64_t* n_out, uint64_t* n_cropped);
+
+/* ---------------------------------------------------------------- pointcloud_merger --------- */
+
+typedef struct plc_merge_src {
+    plc_cloud_view cloud;
+    double t[3];           /* transform translation map <- velodyne_link */
+    double q[4];           /* transform rotation quaternion x,y,z,w */
+    uint8_t r, g, b, present;   /* present == 0: source skipped (TF failure / no cloud, :389-393) */
+} plc_merge_src;
+
+/* Replaces processRobotCloud x2 + concatenation (pointcloud_merger.cpp:308-394).
+ * out_merged: PointXYZRGB wire layout, 32 bytes per point, sources in the order given.
+ * out_each[i] (may be NULL): the i-th source's coloured cloud, same layout. */
+plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_src,
+                     void* out_merged, uint64_t capacity, uint64_t* n_out,
+                     void* const* out_each, uint64_t* n_each);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLC_H_ */

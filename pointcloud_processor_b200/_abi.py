@@ -1,0 +1,197 @@
+"""ctypes binding of the C ABI in include/plc.h and include/plc_host.h.
+
+This is the headless stand-in for the cgo/JNI-style stub a maintainer would add to the reference's
+ROS2 nodes (INTEGRATION.md shows the C++ call sites).  It loads the in-tree
+``pointcloud_processor_b200/lib/libplc.so`` and fails loudly when it is missing: there is no
+Python or CPU fallback for any plc_* entry point.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "lib" / "libplc.so"
+
+PLC_OK = 0
+PLC_E_INVALID_ARG = -1
+PLC_E_NO_TERRAIN = -2
+PLC_E_NO_CELLS = -3
+PLC_E_CAPACITY = -4
+PLC_E_CUDA = -5
+PLC_E_NCCL = -6
+PLC_E_OOM = -7
+PLC_E_NO_CANDIDATES = -8
+
+FLAG_RANGE_FIXED, FLAG_FOV_FIXED, FLAG_VIS_FIXED = 1, 2, 4
+FLAG_RANGE_MOBILE, FLAG_FOV_MOBILE, FLAG_VIS_MOBILE = 8, 16, 32
+
+
+class CloudView(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("n_points", C.c_uint64), ("point_step", C.c_uint32),
+                ("off_x", C.c_uint32), ("off_y", C.c_uint32), ("off_z", C.c_uint32)]
+
+
+class Params(C.Structure):
+    _fields_ = [("max_distance", C.c_double), ("min_distance", C.c_double), ("ray_step", C.c_double),
+                ("ray_start", C.c_double), ("vis_radius", C.c_double), ("block_radius_scale", C.c_double),
+                ("observed_radius_scale", C.c_double), ("fov_vertical", C.c_double),
+                ("fov_horizontal", C.c_double), ("alpha", C.c_double), ("beta", C.c_double),
+                ("fixed_mode", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Counters(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("rays_gated_in", C.c_uint64), ("rays_visible", C.c_uint64),
+                ("samples", C.c_uint64), ("fixed_samples", C.c_uint64), ("exact_tests", C.c_uint64)]
+
+
+class SweepOut(C.Structure):
+    _fields_ = [("best_index", C.c_int64), ("best_score", C.c_double), ("best_covered", C.c_int32),
+                ("n_cells", C.c_int32), ("fixed_total", C.c_double), ("counters", Counters),
+                ("scores", C.c_void_p), ("covered", C.c_void_p), ("mask", C.c_void_p),
+                ("mask_words", C.c_uint64), ("cell_flags", C.c_void_p), ("fixed_scores", C.c_void_p)]
+
+
+class GridInfo(C.Structure):
+    _fields_ = [("n_points", C.c_uint64), ("n_voxels", C.c_uint64), ("grid_bytes", C.c_uint64),
+                ("dim", C.c_int32 * 3), ("origin", C.c_double * 3), ("voxel", C.c_double)]
+
+
+class CropBox(C.Structure):
+    _fields_ = [("x_min", C.c_double), ("x_max", C.c_double), ("y_min", C.c_double),
+                ("y_max", C.c_double), ("z_min", C.c_double), ("z_max", C.c_double)]
+
+
+class MergeSrc(C.Structure):
+    _fields_ = [("cloud", CloudView), ("t", C.c_double * 3), ("q", C.c_double * 4),
+                ("r", C.c_uint8), ("g", C.c_uint8), ("b", C.c_uint8), ("present", C.c_uint8)]
+
+
+class GridBounds(C.Structure):
+    _fields_ = [("min_x", C.c_double), ("max_x", C.c_double), ("min_y", C.c_double),
+                ("max_y", C.c_double), ("min_z", C.c_double), ("max_z", C.c_double),
+                ("width", C.c_int32), ("height", C.c_int32)]
+
+
+# numpy mirrors of the PODs (same byte layout as plc_cell / plc_pose)
+CELL_DTYPE = np.dtype([("x", "<f8"), ("y", "<f8"), ("z", "<f8"), ("nx", "<f4"), ("ny", "<f4"),
+                       ("nz", "<f4"), ("pad", "<u4")])
+POSE_DTYPE = np.dtype([("x", "<f8"), ("y", "<f8"), ("z", "<f8"), ("pitch", "<f8"), ("yaw", "<f8")])
+assert CELL_DTYPE.itemsize == 40 and POSE_DTYPE.itemsize == 40
+
+# every symbol include/plc.h and include/plc_host.h declare (tests check the library exports them all)
+EXPORTS = [
+    "plc_params_default", "plc_params_memo", "plc_ctx_create", "plc_ctx_destroy", "plc_strerror",
+    "plc_last_error", "plc_launch_count", "plc_abi_version", "plc_ctx_sync",
+    "plc_vl_set_terrain", "plc_vl_set_observed", "plc_vl_set_cells", "plc_vl_sweep",
+    "plc_vl_upload_candidates", "plc_vl_run_async", "plc_vl_fetch", "plc_vl_result_device_ptr",
+    "plc_vl_grid_info", "plc_filter", "plc_merge",
+    "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
+]
+
+_lib = None
+
+
+class PlcError(RuntimeError):
+    def __init__(self, status: int, where: str, detail: str = ""):
+        self.status = status
+        msg = f"{where}: {strerror(status)} ({status})"
+        if detail:
+            msg += f" [{detail}]"
+        super().__init__(msg)
+
+
+def lib() -> C.CDLL:
+    """Loads libplc.so (once).  Missing library is an error, never a fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C pointcloud_processor_b200/csrc`. There is no CPU fallback.")
+    L = C.CDLL(os.fspath(LIB_PATH))
+    vp, u64, i32, dbl = C.c_void_p, C.c_uint64, C.c_int32, C.c_double
+    L.plc_strerror.restype = C.c_char_p
+    L.plc_strerror.argtypes = [C.c_int]
+    L.plc_last_error.restype = C.c_char_p
+    L.plc_last_error.argtypes = [vp]
+    L.plc_launch_count.restype = u64
+    L.plc_launch_count.argtypes = [vp]
+    L.plc_abi_version.restype = C.c_int
+    L.plc_params_default.argtypes = [C.POINTER(Params)]
+    L.plc_params_default.restype = None
+    L.plc_params_memo.argtypes = [C.POINTER(Params)]
+    L.plc_params_memo.restype = None
+    L.plc_ctx_create.argtypes = [C.c_int, vp, C.POINTER(vp)]
+    L.plc_ctx_destroy.argtypes = [vp]
+    L.plc_ctx_destroy.restype = None
+    L.plc_ctx_sync.argtypes = [vp]
+    for name in ("plc_vl_set_terrain", "plc_vl_set_observed"):
+        getattr(L, name).argtypes = [vp, C.POINTER(CloudView)]
+    L.plc_vl_set_cells.argtypes = [vp, vp, u64]
+    L.plc_vl_sweep.argtypes = [vp, C.POINTER(Params), vp, vp, u64, u64, u64, C.POINTER(SweepOut)]
+    L.plc_vl_upload_candidates.argtypes = [vp, C.POINTER(Params), vp, vp, u64, u64, u64]
+    L.plc_vl_run_async.argtypes = [vp, C.c_int, C.c_int]
+    L.plc_vl_fetch.argtypes = [vp, C.POINTER(SweepOut)]
+    L.plc_vl_result_device_ptr.argtypes = [vp, C.POINTER(vp)]
+    L.plc_vl_grid_info.argtypes = [vp, C.POINTER(GridInfo), C.POINTER(GridInfo)]
+    L.plc_filter.argtypes = [vp, C.POINTER(CloudView), C.POINTER(CropBox), dbl, vp, u64,
+                             C.POINTER(u64), C.POINTER(u64)]
+    L.plc_merge.argtypes = [vp, C.POINTER(MergeSrc), C.c_int, vp, u64, C.POINTER(u64),
+                            C.POINTER(vp), C.POINTER(u64)]
+    L.plc_host_generate_cells.argtypes = [C.POINTER(CloudView), vp, dbl, i32, dbl, vp, u64,
+                                          C.POINTER(u64), C.POINTER(GridBounds)]
+    L.plc_host_compute_normals.argtypes = [C.POINTER(CloudView), dbl, vp]
+    L.plc_host_generate_candidates.argtypes = [C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
+                                               dbl, dbl, vp, u64, C.POINTER(u64)]
+    _lib = L
+    return L
+
+
+def strerror(status: int) -> str:
+    return lib().plc_strerror(int(status)).decode()
+
+
+def default_params() -> Params:
+    p = Params()
+    lib().plc_params_default(C.byref(p))
+    return p
+
+
+def memo_params() -> Params:
+    p = Params()
+    lib().plc_params_memo(C.byref(p))
+    return p
+
+
+def cloud_view(buf: np.ndarray, point_step: int | None = None, off=(0, 4, 8)) -> CloudView:
+    """View over a PointCloud2-style buffer.
+
+    ``buf`` is either an (n, k) float32 array whose first three columns are x, y, z (point_step =
+    4k) or a flat uint8 array with an explicit ``point_step``.  The caller keeps ``buf`` alive.
+    """
+    if buf.dtype == np.uint8 and buf.ndim == 1:
+        if not point_step:
+            raise ValueError("point_step required for a byte buffer")
+        n = buf.size // point_step
+    else:
+        if buf.dtype != np.float32 or buf.ndim != 2 or buf.shape[1] < 3:
+            raise ValueError("expected an (n, >=3) float32 array or a uint8 byte buffer")
+        point_step = buf.shape[1] * 4
+        n = buf.shape[0]
+    if not buf.flags["C_CONTIGUOUS"]:
+        raise ValueError("cloud buffer must be C-contiguous")
+    v = CloudView()
+    v.data = buf.ctypes.data if n else None
+    v.n_points = n
+    v.point_step = point_step
+    v.off_x, v.off_y, v.off_z = off
+    return v
+
+
+def ptr(a: np.ndarray | None):
+    return None if a is None else a.ctypes.data

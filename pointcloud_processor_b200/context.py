@@ -1,0 +1,243 @@
+"""Thin object wrapper over the plc_* C ABI (include/plc.h).  No computation happens in Python:
+every method forwards to libplc.so and raises PlcError on a non-zero status."""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _abi as A
+
+
+@dataclass
+class SweepResult:
+    best_index: int
+    best_score: float
+    best_covered: int
+    n_cells: int
+    fixed_total: float
+    counters: dict
+    scores: np.ndarray | None = None
+    covered: np.ndarray | None = None
+    mask: np.ndarray | None = None          # (n_local, mask_words) uint32
+    cell_flags: np.ndarray | None = None    # (n_cells,) uint8
+    fixed_scores: np.ndarray | None = None  # (n_cells,) float64
+    extra: dict = field(default_factory=dict)
+
+    def mask_bits(self) -> np.ndarray:
+        """(n_local, n_cells) bool view of the packed visibility mask."""
+        bits = np.unpackbits(self.mask.view(np.uint8), axis=1, bitorder="little")
+        return bits[:, : self.n_cells].astype(bool)
+
+
+def _counters(c: A.Counters) -> dict:
+    return {k: int(getattr(c, k)) for k, _ in A.Counters._fields_}
+
+
+class Context:
+    """One plc_ctx: one CUDA device, one stream.  Not thread-safe (same contract as the C ABI)."""
+
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self._L = A.lib()
+        h = C.c_void_p()
+        st = self._L.plc_ctx_create(int(device), C.c_void_p(stream) if stream else None, C.byref(h))
+        if st != A.PLC_OK:
+            raise A.PlcError(st, "plc_ctx_create")
+        self._h = h
+        self.device = device
+        self.n_cells = 0
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.plc_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, st: int, where: str):
+        if st != A.PLC_OK:
+            raise A.PlcError(st, where, self._L.plc_last_error(self._h).decode())
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._L.plc_launch_count(self._h))
+
+    def sync(self):
+        self._check(self._L.plc_ctx_sync(self._h), "plc_ctx_sync")
+
+    # ---- virtual_lidar -------------------------------------------------------------------------
+    def set_terrain(self, cloud: np.ndarray, point_step: int | None = None, off=(0, 4, 8)):
+        v = A.cloud_view(cloud, point_step, off)
+        self._check(self._L.plc_vl_set_terrain(self._h, C.byref(v)), "plc_vl_set_terrain")
+
+    def set_observed(self, cloud: np.ndarray, point_step: int | None = None, off=(0, 4, 8)):
+        v = A.cloud_view(cloud, point_step, off)
+        self._check(self._L.plc_vl_set_observed(self._h, C.byref(v)), "plc_vl_set_observed")
+
+    def set_cells(self, cells: np.ndarray):
+        cells = np.ascontiguousarray(cells, dtype=A.CELL_DTYPE)
+        self._check(self._L.plc_vl_set_cells(self._h, A.ptr(cells) if cells.size else None, cells.size),
+                    "plc_vl_set_cells")
+        self.n_cells = int(cells.size)
+
+    def _alloc_out(self, n_local, want_scores, want_mask, want_flags, want_fixed):
+        out = A.SweepOut()
+        arrays = {}
+        words = (self.n_cells + 31) // 32
+        if want_scores:
+            arrays["scores"] = np.zeros(n_local, np.float64)
+            arrays["covered"] = np.zeros(n_local, np.int32)
+        if want_mask:
+            arrays["mask"] = np.zeros((n_local, words), np.uint32)
+        if want_flags:
+            arrays["cell_flags"] = np.zeros(self.n_cells, np.uint8)
+        if want_fixed:
+            arrays["fixed_scores"] = np.zeros(self.n_cells, np.float64)
+        for k, a in arrays.items():
+            setattr(out, k, a.ctypes.data)
+        return out, arrays
+
+    def _result(self, out: A.SweepOut, arrays: dict) -> SweepResult:
+        return SweepResult(int(out.best_index), float(out.best_score), int(out.best_covered),
+                           int(out.n_cells), float(out.fixed_total), _counters(out.counters), **arrays)
+
+    def sweep(self, params: A.Params, fixed: np.ndarray, cands: np.ndarray, begin: int = 0,
+              end: int | None = None, *, scores=True, mask=False, flags=False, fixed_scores=False) -> SweepResult:
+        """plc_vl_sweep: host buffers in, host results out (H2D and D2H inside the call)."""
+        cands = np.ascontiguousarray(cands, dtype=A.POSE_DTYPE)
+        fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
+        end = cands.size if end is None else end
+        out, arrays = self._alloc_out(end - begin, scores, mask, flags, fixed_scores)
+        st = self._L.plc_vl_sweep(self._h, C.byref(params), A.ptr(fixed), A.ptr(cands) if cands.size else None,
+                                  cands.size, begin, end, C.byref(out))
+        self._check(st, "plc_vl_sweep")
+        return self._result(out, arrays)
+
+    def upload_candidates(self, params: A.Params, fixed: np.ndarray, cands: np.ndarray, begin: int = 0,
+                          end: int | None = None):
+        cands = np.ascontiguousarray(cands, dtype=A.POSE_DTYPE)
+        fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
+        end = cands.size if end is None else end
+        self._n_local = end - begin
+        st = self._L.plc_vl_upload_candidates(self._h, C.byref(params), A.ptr(fixed),
+                                              A.ptr(cands) if cands.size else None, cands.size, begin, end)
+        self._check(st, "plc_vl_upload_candidates")
+
+    def run_async(self, want_mask: bool = False, want_flags: bool = False):
+        self._check(self._L.plc_vl_run_async(self._h, int(want_mask), int(want_flags)), "plc_vl_run_async")
+
+    def fetch(self, *, scores=True, mask=False, flags=False, fixed_scores=False) -> SweepResult:
+        out, arrays = self._alloc_out(self._n_local, scores, mask, flags, fixed_scores)
+        self._check(self._L.plc_vl_fetch(self._h, C.byref(out)), "plc_vl_fetch")
+        return self._result(out, arrays)
+
+    def result_device_ptr(self) -> int:
+        p = C.c_void_p()
+        self._check(self._L.plc_vl_result_device_ptr(self._h, C.byref(p)), "plc_vl_result_device_ptr")
+        return int(p.value)
+
+    def grid_info(self):
+        t, o = A.GridInfo(), A.GridInfo()
+        self._check(self._L.plc_vl_grid_info(self._h, C.byref(t), C.byref(o)), "plc_vl_grid_info")
+        conv = lambda g: {"n_points": int(g.n_points), "n_voxels": int(g.n_voxels), "grid_bytes": int(g.grid_bytes),
+                          "dim": list(g.dim), "origin": list(g.origin), "voxel": float(g.voxel)}
+        return conv(t), conv(o)
+
+    # ---- pointcloud_filter / pointcloud_merger -------------------------------------------------
+    def filter(self, cloud: np.ndarray, box: A.CropBox, leaf: float, point_step: int | None = None,
+               off=(0, 4, 8)):
+        """plc_filter: crop box + voxel-grid centroid downsample.  Returns ((n,4) float32, n_cropped)."""
+        v = A.cloud_view(cloud, point_step, off)
+        cap = max(int(v.n_points), 1)
+        out = np.zeros((cap, 4), np.float32)
+        n_out, n_crop = C.c_uint64(0), C.c_uint64(0)
+        st = self._L.plc_filter(self._h, C.byref(v), C.byref(box), float(leaf), out.ctypes.data, cap,
+                                C.byref(n_out), C.byref(n_crop))
+        self._check(st, "plc_filter")
+        return out[: n_out.value], int(n_crop.value)
+
+    def merge(self, sources):
+        """plc_merge.  sources: list of dicts {cloud, t(3), q(4 xyzw), rgb(3), present, point_step?, off?}.
+        Returns (merged (n,32) uint8 as structured bytes, [per-source arrays])."""
+        n = len(sources)
+        arr = (A.MergeSrc * n)()
+        total = 0
+        each = []
+        keep = []
+        for i, s in enumerate(sources):
+            v = A.cloud_view(s["cloud"], s.get("point_step"), s.get("off", (0, 4, 8)))
+            keep.append(s["cloud"])
+            arr[i].cloud = v
+            arr[i].t[:] = list(map(float, s["t"]))
+            arr[i].q[:] = list(map(float, s["q"]))
+            arr[i].r, arr[i].g, arr[i].b = s["rgb"]
+            arr[i].present = 1 if s.get("present", True) else 0
+            cnt = int(v.n_points) if arr[i].present else 0
+            total += cnt
+            each.append(np.zeros((max(cnt, 1), 32), np.uint8))
+        merged = np.zeros((max(total, 1), 32), np.uint8)
+        ptrs = (C.c_void_p * n)(*[e.ctypes.data for e in each])
+        n_each = (C.c_uint64 * n)()
+        n_out = C.c_uint64(0)
+        st = self._L.plc_merge(self._h, arr, n, merged.ctypes.data, max(total, 1), C.byref(n_out), ptrs, n_each)
+        self._check(st, "plc_merge")
+        return merged[: n_out.value], [e[: n_each[i]] for i, e in enumerate(each)]
+
+
+# ---- host-side setup (include/plc_host.h) -------------------------------------------------------
+def host_generate_cells(area: np.ndarray, normals: np.ndarray | None, grid_resolution: float,
+                        vertical_layers: int, normal_search_radius: float = 1.5):
+    L = A.lib()
+    v = A.cloud_view(area)
+    if normals is not None:
+        normals = np.ascontiguousarray(normals, np.float32)
+    b = A.GridBounds()
+    n = C.c_uint64(0)
+    st = L.plc_host_generate_cells(C.byref(v), A.ptr(normals), grid_resolution, vertical_layers,
+                                   normal_search_radius, None, 0, C.byref(n), C.byref(b))
+    if st not in (A.PLC_OK, A.PLC_E_CAPACITY):
+        raise A.PlcError(st, "plc_host_generate_cells")
+    cells = np.zeros(n.value, A.CELL_DTYPE)
+    if n.value:
+        st = L.plc_host_generate_cells(C.byref(v), A.ptr(normals), grid_resolution, vertical_layers,
+                                       normal_search_radius, cells.ctypes.data, cells.size, C.byref(n), C.byref(b))
+        if st != A.PLC_OK:
+            raise A.PlcError(st, "plc_host_generate_cells")
+    return cells, b
+
+
+def host_compute_normals(area: np.ndarray, radius: float = 1.5) -> np.ndarray:
+    L = A.lib()
+    v = A.cloud_view(area)
+    out = np.zeros((area.shape[0], 3), np.float32)
+    st = L.plc_host_compute_normals(C.byref(v), radius, out.ctypes.data)
+    if st != A.PLC_OK:
+        raise A.PlcError(st, "plc_host_compute_normals")
+    return out
+
+
+def host_generate_candidates(terrain: np.ndarray, bounds: A.GridBounds, fixed: np.ndarray,
+                             num_candidates: int, search_radius: float, sensor_height: float) -> np.ndarray:
+    L = A.lib()
+    v = A.cloud_view(terrain)
+    fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
+    side = int(np.ceil(np.sqrt(num_candidates)))
+    out = np.zeros(side * side, A.POSE_DTYPE)
+    n = C.c_uint64(0)
+    st = L.plc_host_generate_candidates(C.byref(v), C.byref(bounds), fixed.ctypes.data, num_candidates,
+                                        search_radius, sensor_height, out.ctypes.data, out.size, C.byref(n))
+    if st != A.PLC_OK:
+        raise A.PlcError(st, "plc_host_generate_candidates")
+    return out[: n.value].copy()

@@ -1,0 +1,105 @@
+// plc_ctx.cu — context lifetime, status text, parameter presets.
+#include <cmath>
+#include <new>
+
+#include "plc_internal.cuh"
+
+extern "C" int plc_abi_version(void) { return PLC_ABI_VERSION; }
+
+extern "C" const char* plc_strerror(int status) {
+    switch (status) {
+        case PLC_OK: return "ok";
+        case PLC_E_INVALID_ARG: return "invalid argument";
+        case PLC_E_NO_TERRAIN: return "no terrain cloud has been set";
+        case PLC_E_NO_CELLS: return "no evaluation cells have been set";
+        case PLC_E_CAPACITY: return "output buffer too small";
+        case PLC_E_CUDA: return "CUDA error (see plc_last_error)";
+        case PLC_E_NCCL: return "NCCL error (see plc_last_error)";
+        case PLC_E_OOM: return "out of device memory";
+        case PLC_E_NO_CANDIDATES: return "no candidates have been uploaded";
+        default: return "unknown status";
+    }
+}
+
+// Built node: virtual_lidar.cpp:66-71 (parameters) and :100-114 (constants).
+extern "C" void plc_params_default(plc_params* p) {
+    if (!p) return;
+    p->max_distance = 15.0;
+    p->min_distance = 0.5;
+    p->ray_step = 0.3;
+    p->ray_start = 0.5;
+    p->vis_radius = 0.08;
+    p->block_radius_scale = 0.7;
+    p->observed_radius_scale = 3.0;
+    p->fov_vertical = 180.0 * M_PI / 180.0;   // formed exactly as :711
+    p->fov_horizontal = -1.0;
+    p->alpha = 1.0;
+    p->beta = 1.0;
+    p->fixed_mode = 0;
+    p->reserved = 0;
+}
+
+// virtual_lidar_memo.cpp:102-113 (constants), :684-697 (FOV), :699-726 (fixed sensor: observed cloud only).
+extern "C" void plc_params_memo(plc_params* p) {
+    if (!p) return;
+    plc_params_default(p);
+    p->min_distance = 1.0;
+    p->ray_step = 0.2;
+    p->vis_radius = 0.05;
+    p->observed_radius_scale = 1.0;
+    p->fov_vertical = 90.0 * M_PI / 180.0;
+    p->fov_horizontal = 180.0 * M_PI / 180.0;
+    p->fixed_mode = 1;
+}
+
+extern "C" plc_status plc_ctx_create(int device, void* stream, plc_ctx** out) {
+    if (!out) return PLC_E_INVALID_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return PLC_E_CUDA;
+    if (cudaSetDevice(device) != cudaSuccess) return PLC_E_CUDA;
+    plc_ctx* c = new (std::nothrow) plc_ctx();
+    if (!c) return PLC_E_OOM;
+    c->device = device;
+    if (stream) {
+        c->stream = static_cast<cudaStream_t>(stream);
+    } else {
+        if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+            delete c;
+            return PLC_E_CUDA;
+        }
+        c->own_stream = true;
+    }
+    if (c->result.reserve(sizeof(plc::SweepResult)) != cudaSuccess || !c->pinned_reserve(1 << 16)) {
+        plc_ctx_destroy(c);
+        return PLC_E_OOM;
+    }
+    *out = c;
+    return PLC_OK;
+}
+
+extern "C" void plc_ctx_destroy(plc_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->terrain.release();
+    c->observed.release();
+    plc::DevBuf* bufs[] = {&c->upload, &c->scratch, &c->cells, &c->cell_flags, &c->fixed_scores, &c->cands,
+                           &c->partial_score, &c->partial_cov, &c->scores, &c->covered, &c->mask, &c->result,
+                           &c->f_keys, &c->f_vals, &c->f_keys2, &c->f_vals2, &c->f_tmp, &c->f_out, &c->f_flags,
+                           &c->m_out};
+    for (plc::DevBuf* b : bufs) b->release();
+    if (c->pinned) cudaFreeHost(c->pinned);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" const char* plc_last_error(const plc_ctx* c) { return c ? c->last_error.c_str() : ""; }
+extern "C" uint64_t plc_launch_count(const plc_ctx* c) { return c ? c->launches : 0; }
+
+extern "C" plc_status plc_ctx_sync(plc_ctx* c) {
+    if (!c) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(c, cudaSetDevice(c->device));
+    PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return PLC_OK;
+}

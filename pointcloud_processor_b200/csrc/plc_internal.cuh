@@ -1,0 +1,163 @@
+// plc_internal.cuh — context, device buffers and the voxel index shared by the plc_* kernels.
+// sm_100a only; there is deliberately no host fallback anywhere behind this header.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "plc.h"
+
+#define PLC_CUDA_TRY(ctx, expr)                                                              \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            (ctx)->set_error(#expr, cudaGetErrorString(e__));                                \
+            return e__ == cudaErrorMemoryAllocation ? PLC_E_OOM : PLC_E_CUDA;                \
+        }                                                                                    \
+    } while (0)
+
+#define PLC_TRY(expr)                          \
+    do {                                       \
+        plc_status s__ = (expr);               \
+        if (s__ != PLC_OK) return s__;         \
+    } while (0)
+
+namespace plc {
+
+// Grow-only device allocation.
+struct DevBuf {
+    void* ptr = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&ptr, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T* as() const { return static_cast<T*>(ptr); }
+};
+
+// Geometry of a voxel index, passed to kernels by value.
+//   coarse voxel edge h (a power of two), fine voxel edge g = h/4, shared origin.
+//   mask32[2*v + ((fz>>1)&1)] bit ((fx&3) | (fy&3)<<2 | (fz&1)<<4): fine voxel may hold a sample that
+//   the radius test accepts (conservative dilation of the points by the query radius).
+//   vstart[v] .. vstart[v+1]: range of the coarse voxel's points in `pts` (x fastest, so voxels
+//   adjacent in x are adjacent in pts).
+struct VoxelGeom {
+    float ox, oy, oz;        // origin (multiple of h, exactly representable)
+    float inv_g;             // 1/g (power of two)
+    float reach;             // float radius + slack used to pick the coarse voxels to scan
+    int dim_x, dim_y, dim_z; // coarse dims
+    int fdim_x, fdim_y, fdim_z;   // fine dims = 4*coarse
+    const uint32_t* __restrict__ mask32;
+    const uint32_t* __restrict__ vstart;
+    const float4* __restrict__ pts;
+    uint32_t n_pts;
+};
+
+struct VoxelIndex {
+    // raw finite points (unsorted) kept so the index can be rebuilt for another radius
+    DevBuf raw;          // float4[n_raw]
+    uint64_t n_raw = 0;
+    uint64_t n_input = 0;
+    float bbox[6] = {0, 0, 0, 0, 0, 0};   // min xyz, max xyz of finite points
+    // built index
+    double built_radius = -1.0;   // query radius (m) the mask was dilated for
+    double h = 0.0;
+    DevBuf mask32, vstart, vfill, pts, scan_tmp;
+    VoxelGeom geom{};
+    uint64_t n_vox = 0;
+    bool has_points() const { return n_raw > 0; }
+    uint64_t bytes() const { return n_vox * 8 + (n_vox + 1) * 4 + n_raw * 16; }
+    void release() {
+        raw.release(); mask32.release(); vstart.release(); vfill.release(); pts.release(); scan_tmp.release();
+    }
+};
+
+}  // namespace plc
+
+struct plc_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    uint64_t launches = 0;
+    std::string last_error;
+
+    // staging
+    plc::DevBuf upload;          // raw PointCloud2 bytes
+    plc::DevBuf scratch;         // small reductions
+    void* pinned = nullptr;      // pinned host scratch for small results
+    size_t pinned_cap = 0;
+
+    // virtual_lidar state
+    plc::VoxelIndex terrain, observed;
+    plc::DevBuf cells;           // plc_cell[n_cells]
+    uint64_t n_cells = 0;
+    plc::DevBuf cell_flags;      // uint8[n_cells], persists across sweeps (Q3)
+    plc::DevBuf fixed_scores;    // double[n_cells]
+    plc::DevBuf cands;           // plc_pose[n_cands] (full list)
+    uint64_t n_cands = 0, cand_begin = 0, cand_end = 0;
+    plc_params prm{};
+    plc_pose fixed{};
+    bool have_job = false;
+    bool ran = false, ran_mask = false, ran_flags = false;
+    plc::DevBuf partial_score, partial_cov;   // per (candidate, tile)
+    plc::DevBuf scores, covered, mask;
+    plc::DevBuf result;          // SweepResult
+    uint64_t mask_words = 0;
+    int tiles = 0;
+
+    // filter / merge scratch
+    plc::DevBuf f_keys, f_vals, f_keys2, f_vals2, f_tmp, f_out, f_flags;
+    plc::DevBuf m_out;
+
+    void set_error(const char* what, const char* why) {
+        last_error = std::string(what) + ": " + why;
+    }
+    void* pinned_reserve(size_t bytes) {
+        if (bytes <= pinned_cap) return pinned;
+        if (pinned) cudaFreeHost(pinned);
+        pinned = nullptr;
+        pinned_cap = 0;
+        if (cudaMallocHost(&pinned, bytes + 4096) != cudaSuccess) return nullptr;
+        pinned_cap = bytes + 4096;
+        return pinned;
+    }
+};
+
+namespace plc {
+
+// Device-side result block of a sweep (first 16 bytes are what the multi-GPU exchange gathers).
+struct SweepResult {
+    double best_score;
+    long long best_index;       // global candidate index
+    int best_covered;
+    int pad;
+    double fixed_total;
+    unsigned long long rays_gated_in, rays_visible, samples, fixed_samples, exact_tests;
+};
+
+plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* cloud);
+plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius);
+
+inline bool cloud_view_ok(const plc_cloud_view* v) {
+    if (!v) return false;
+    if (v->n_points == 0) return true;
+    return v->data && v->point_step >= 12 && v->off_x + 4 <= v->point_step &&
+           v->off_y + 4 <= v->point_step && v->off_z + 4 <= v->point_step;
+}
+
+}  // namespace plc

@@ -1,0 +1,625 @@
+// plc_sweep.cu — K2/K3/K4: the virtual_lidar visibility sweep on one B200.
+//
+// Replaces /root/reference/src/virtual_lidar.cpp:
+//   evaluateZX120Only 360-398        -> k_fixed   (once per sweep; the reference repeats it per candidate, :637)
+//   evaluatePosition 627-654 x C     -> k_sweep   (one thread per (candidate, cell) ray) + k_finalize
+//   evaluateCellScore 656-701, isInFieldOfView 703-714, checkVisibility* 716-800 -> device functions below
+//   argmax 464-475                   -> k_argmax  (first maximum = lowest index)
+//   stale per-cell flags -> k_flags
+//
+// Numerics contract: double geometry exactly as written upstream (no FMA: this file
+// is compiled with -fmad=false and uses explicit _rn intrinsics where the order matters), sample
+// point narrowed to float32, float32 distance test against the voxelised terrain.  The visibility
+// bit of every ray is therefore bit-identical to the CPU restatement; scores differ only by libm
+// round-off in acos/sin.
+//
+// Roofline: the sweep's algorithmic traffic is 32 B per ray + 4 B per evaluated sample (SURVEY
+// §8 D4).  The occupancy bricks and voxel ranges are L2-resident, so the kernel is issue/latency
+// bound; bench.py reports achieved algorithmic GB/s against the measured HBM peak.
+#include <cmath>
+#include <limits>
+
+#include "plc_voxel_query.cuh"
+
+namespace plc {
+
+namespace {
+
+constexpr int kSweepThreads = 128;
+constexpr int kRaysPerThread = 8;
+constexpr int kTileCells = kSweepThreads * kRaysPerThread;
+
+struct SweepDev {
+    VoxelGeom terrain, observed;
+    int have_terrain, have_observed;
+    float thr_block, thr_obs;
+    double max_distance, min_distance, ray_step, ray_start, vis_radius;
+    double half_fov_v, half_fov_h;   // half_fov_h < 0: no azimuth test
+    double alpha, beta;
+    int fixed_mode;
+};
+
+struct RayStats {
+    unsigned samples = 0;
+    unsigned long long exact = 0;
+};
+
+// checkVisibilityWithRaycasting, :754-800
+__device__ __forceinline__ bool ray_clear(const SweepDev& P, double sx, double sy, double sz, double dx,
+                                          double dy, double dz, double L, RayStats& st) {
+    double ux = __ddiv_rn(dx, L), uy = __ddiv_rn(dy, L), uz = __ddiv_rn(dz, L);
+    double s = P.ray_start;
+    double end = __dsub_rn(L, P.vis_radius);
+    while (s < end) {
+        float qx = (float)__dadd_rn(sx, __dmul_rn(ux, s));
+        float qy = (float)__dadd_rn(sy, __dmul_rn(uy, s));
+        float qz = (float)__dadd_rn(sz, __dmul_rn(uz, s));
+        ++st.samples;
+        if (ball_any(P.terrain, qx, qy, qz, P.thr_block, &st.exact)) return false;
+        s = __dadd_rn(s, P.ray_step);
+    }
+    return true;
+}
+
+__device__ __forceinline__ double ray_length(double dx, double dy, double dz) {
+    return __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+}
+
+// isInFieldOfView, :703-714 (+ azimuth of virtual_lidar_memo.cpp:684-697 when enabled)
+__device__ __forceinline__ bool in_fov(const SweepDev& P, double pitch, double yaw, double dx, double dy, double dz) {
+    double elevation = atan2(dz, __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy))));
+    bool ok = fabs(__dsub_rn(elevation, pitch)) <= P.half_fov_v;
+    if (P.half_fov_h >= 0.0) {
+        double az = atan2(dy, dx);
+        double diff = __dsub_rn(fmod(__dadd_rn(__dsub_rn(az, yaw), M_PI), 2 * M_PI), M_PI);
+        ok = (fabs(diff) <= P.half_fov_h) && ok;
+    }
+    return ok;
+}
+
+// incidence + range score, :689-700
+__device__ __forceinline__ double ray_score(const SweepDev& P, double dx, double dy, double dz, double L,
+                                            float nx, float ny, float nz) {
+    double bx = __ddiv_rn(dx, L), by = __ddiv_rn(dy, L), bz = __ddiv_rn(dz, L);
+    double dot = __dadd_rn(__dadd_rn(__dmul_rn(bx, (double)nx), __dmul_rn(by, (double)ny)), __dmul_rn(bz, (double)nz));
+    double theta = acos(fmax(0.0, fmin(1.0, fabs(dot))));
+    double score = __dadd_rn(__dmul_rn(P.alpha, sin(__dsub_rn(M_PI / 2, theta))), __dmul_rn(P.beta, __ddiv_rn(1.0, L)));
+    return fmax(0.0, score);
+}
+
+// Outcome bits of one evaluateCellScore call (which assignments the reference performed and their values)
+enum : unsigned {
+    kRangeVal = 1u, kFovSet = 2u, kFovVal = 4u, kVisSet = 8u, kVisVal = 16u
+};
+
+// evaluateCellScore for the mobile sensor, :656-701 with is_zx120 == false
+__device__ __forceinline__ double mobile_cell_score(const SweepDev& P, const plc_pose& s, const plc_cell& c,
+                                                    unsigned& outcome, RayStats& st) {
+    outcome = 0;
+    double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
+    double L = ray_length(dx, dy, dz);
+    if (!(L >= P.min_distance && L <= P.max_distance)) return 0.0;
+    outcome |= kRangeVal | kFovSet;
+    if (!in_fov(P, s.pitch, s.yaw, dx, dy, dz)) return 0.0;
+    outcome |= kFovVal | kVisSet;
+    bool vis = P.have_terrain ? ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st) : true;   // :727-728
+    if (!vis) return 0.0;
+    outcome |= kVisVal;
+    return ray_score(P, dx, dy, dz, L, c.nx, c.ny, c.nz);
+}
+
+// evaluateCellScore for the fixed sensor (is_zx120 == true), visibility per :716-752
+__device__ __forceinline__ double fixed_cell_score(const SweepDev& P, const plc_pose& s, const plc_cell& c,
+                                                   unsigned& outcome, RayStats& st) {
+    outcome = 0;
+    double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
+    double L = ray_length(dx, dy, dz);
+    if (!(L >= P.min_distance && L <= P.max_distance)) return 0.0;
+    outcome |= kRangeVal | kFovSet;
+    if (!in_fov(P, s.pitch, s.yaw, dx, dy, dz)) return 0.0;
+    outcome |= kFovVal | kVisSet;
+    bool vis;
+    if (P.fixed_mode == 1) {
+        // memo variant: observed cloud only
+        vis = P.have_observed && ball_any(P.observed, (float)c.x, (float)c.y, (float)c.z, P.thr_obs, nullptr);
+    } else if (!P.have_observed) {
+        vis = P.have_terrain ? ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st) : true;            // :719-723
+    } else if (ball_any(P.observed, (float)c.x, (float)c.y, (float)c.z, P.thr_obs, nullptr)) {
+        vis = true;                                                                              // :745-747
+    } else {
+        vis = P.have_terrain ? ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st) : true;            // :750-751
+    }
+    if (!vis) return 0.0;
+    outcome |= kVisVal;
+    return ray_score(P, dx, dy, dz, L, c.nx, c.ny, c.nz);
+}
+
+__device__ __forceinline__ plc_cell load_cell(const plc_cell* __restrict__ cells, size_t j) {
+    // 40-byte record (8-byte aligned): five 8-byte read-only loads
+    const unsigned long long* p = reinterpret_cast<const unsigned long long*>(cells + j);
+    unsigned long long w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2), w3 = __ldg(p + 3), w4 = __ldg(p + 4);
+    plc_cell c;
+    c.x = __longlong_as_double((long long)w0);
+    c.y = __longlong_as_double((long long)w1);
+    c.z = __longlong_as_double((long long)w2);
+    c.nx = __uint_as_float((unsigned)(w3 & 0xffffffffu));
+    c.ny = __uint_as_float((unsigned)(w3 >> 32));
+    c.nz = __uint_as_float((unsigned)(w4 & 0xffffffffu));
+    c.pad = 0;
+    return c;
+}
+
+// ---- K4: fixed sensor, one thread per cell -----------------------------------------------------
+__global__ void __launch_bounds__(kSweepThreads)
+k_fixed(SweepDev P, plc_pose fixed, const plc_cell* __restrict__ cells, unsigned n_cells,
+        double* __restrict__ fixed_scores, uint8_t* __restrict__ flags, double* __restrict__ block_totals,
+        SweepResult* __restrict__ res) {
+    unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    double score = 0.0;
+    RayStats st;
+    if (j < n_cells) {
+        plc_cell c = cells[j];
+        unsigned oc;
+        score = fixed_cell_score(P, fixed, c, oc, st);
+        fixed_scores[j] = score;
+        // flag writes with the reference's early-return pattern (:662-687)
+        unsigned f = flags[j];
+        f = (f & ~PLC_FLAG_RANGE_FIXED) | ((oc & kRangeVal) ? PLC_FLAG_RANGE_FIXED : 0);
+        if (oc & kFovSet) f = (f & ~PLC_FLAG_FOV_FIXED) | ((oc & kFovVal) ? PLC_FLAG_FOV_FIXED : 0);
+        if (oc & kVisSet) f = (f & ~PLC_FLAG_VIS_FIXED) | ((oc & kVisVal) ? PLC_FLAG_VIS_FIXED : 0);
+        flags[j] = (uint8_t)f;
+    }
+    // fixed-order block sum of positive scores (:384-386)
+    double v = score > 0 ? score : 0.0;
+    unsigned long long smp = st.samples;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v = __dadd_rn(v, __shfl_down_sync(0xffffffffu, v, o));
+        smp += __shfl_down_sync(0xffffffffu, smp, o);
+    }
+    __shared__ double wsum[kSweepThreads / 32];
+    __shared__ unsigned long long wsmp[kSweepThreads / 32];
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        wsum[warp] = v;
+        wsmp[warp] = smp;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        unsigned long long ts = 0;
+        for (int w = 0; w < kSweepThreads / 32; ++w) {
+            t = __dadd_rn(t, wsum[w]);
+            ts += wsmp[w];
+        }
+        block_totals[blockIdx.x] = t;
+        if (ts) atomicAdd(&res->fixed_samples, ts);
+    }
+}
+
+// ---- K2+K3: one thread per (candidate, cell) ray ----------------------------------------------
+// grid.x = n_local * tiles; block b handles candidate b / tiles, cells [tile*1024, tile*1024+1024).
+// A warp's 32 lanes hold 32 consecutive cells, so one ballot is one word of the visibility mask.
+__global__ void __launch_bounds__(kSweepThreads)
+k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned tiles,
+        const plc_cell* __restrict__ cells, unsigned n_cells, const double* __restrict__ fixed_scores,
+        double* __restrict__ partial_score, int* __restrict__ partial_cov, uint32_t* __restrict__ mask,
+        unsigned mask_words, SweepResult* __restrict__ res) {
+    unsigned local = blockIdx.x / tiles, tile = blockIdx.x - local * tiles;
+    plc_pose s = cands[cand_begin + local];
+    double total = 0.0;
+    int covered = 0;
+    unsigned gated = 0, nvis = 0;
+    RayStats st;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll 1
+    for (int r = 0; r < kRaysPerThread; ++r) {
+        unsigned j = tile * kTileCells + r * kSweepThreads + threadIdx.x;
+        bool vis = false;
+        if (j < n_cells) {
+            plc_cell c = load_cell(cells, j);
+            unsigned oc;
+            double mobile = mobile_cell_score(P, s, c, oc, st);
+            double combined = fmax(__ldg(&fixed_scores[j]), mobile);     // :639
+            if (combined > 0) {                                          // :641-644
+                ++covered;
+                total = __dadd_rn(total, combined);
+            }
+            gated += (oc & kFovVal) ? 1u : 0u;
+            vis = (oc & kVisVal) != 0;
+            nvis += vis ? 1u : 0u;
+        }
+        if (mask) {
+            unsigned word = __ballot_sync(0xffffffffu, vis);
+            unsigned w = (tile * kTileCells + r * kSweepThreads) / 32 + warp;
+            if (lane == 0 && w < mask_words) mask[(size_t)local * mask_words + w] = word;
+        }
+    }
+    // fixed-order reduction: lanes by shuffle tree, warps in index order
+    unsigned long long smp = st.samples, ex = st.exact;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        total = __dadd_rn(total, __shfl_down_sync(0xffffffffu, total, o));
+        covered += __shfl_down_sync(0xffffffffu, covered, o);
+        gated += __shfl_down_sync(0xffffffffu, gated, o);
+        nvis += __shfl_down_sync(0xffffffffu, nvis, o);
+        smp += __shfl_down_sync(0xffffffffu, smp, o);
+        ex += __shfl_down_sync(0xffffffffu, ex, o);
+    }
+    __shared__ double wtot[kSweepThreads / 32];
+    __shared__ int wcov[kSweepThreads / 32];
+    __shared__ unsigned long long wcnt[kSweepThreads / 32][4];
+    if (lane == 0) {
+        wtot[warp] = total;
+        wcov[warp] = covered;
+        wcnt[warp][0] = gated;
+        wcnt[warp][1] = nvis;
+        wcnt[warp][2] = smp;
+        wcnt[warp][3] = ex;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        int cv = 0;
+        unsigned long long c4[4] = {0, 0, 0, 0};
+        for (int w = 0; w < kSweepThreads / 32; ++w) {
+            t = __dadd_rn(t, wtot[w]);
+            cv += wcov[w];
+            for (int k = 0; k < 4; ++k) c4[k] += wcnt[w][k];
+        }
+        partial_score[blockIdx.x] = t;
+        partial_cov[blockIdx.x] = cv;
+        if (c4[0]) atomicAdd(&res->rays_gated_in, c4[0]);
+        if (c4[1]) atomicAdd(&res->rays_visible, c4[1]);
+        if (c4[2]) atomicAdd(&res->samples, c4[2]);
+        if (c4[3]) atomicAdd(&res->exact_tests, c4[3]);
+    }
+}
+
+// per candidate: tiles summed in tile order
+__global__ void __launch_bounds__(256)
+k_finalize(const double* __restrict__ partial_score, const int* __restrict__ partial_cov, unsigned n_local,
+           unsigned tiles, double* __restrict__ scores, int* __restrict__ covered) {
+    unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_local) return;
+    double t = 0.0;
+    int cv = 0;
+    for (unsigned k = 0; k < tiles; ++k) {
+        t = __dadd_rn(t, partial_score[(size_t)c * tiles + k]);
+        cv += partial_cov[(size_t)c * tiles + k];
+    }
+    scores[c] = t;
+    covered[c] = cv;
+}
+
+// single block: first maximum over the local candidates (:464-475), fixed-sensor total
+__global__ void __launch_bounds__(1024)
+k_argmax(const double* __restrict__ scores, const int* __restrict__ covered, unsigned n_local,
+         unsigned long long cand_begin, const double* __restrict__ fixed_block_totals, unsigned n_fixed_blocks,
+         SweepResult* __restrict__ res) {
+    double best = -INFINITY;
+    long long idx = -1;
+    for (unsigned c = threadIdx.x; c < n_local; c += blockDim.x) {
+        double v = scores[c];
+        if (v > best) {     // strict: within a thread indices ascend, so the first maximum is kept
+            best = v;
+            idx = c;
+        }
+    }
+    auto better = [](double a, long long ia, double b, long long ib) {
+        // is (b, ib) a better "first maximum" than (a, ia)?
+        if (ib < 0) return false;
+        if (ia < 0) return true;
+        return b > a || (b == a && ib < ia);
+    };
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        double ob = __shfl_down_sync(0xffffffffu, best, o);
+        long long oi = __shfl_down_sync(0xffffffffu, idx, o);
+        if (better(best, idx, ob, oi)) {
+            best = ob;
+            idx = oi;
+        }
+    }
+    __shared__ double sb[32];
+    __shared__ long long si[32];
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        sb[warp] = best;
+        si[warp] = idx;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 32; ++w)
+            if (better(best, idx, sb[w], si[w])) {
+                best = sb[w];
+                idx = si[w];
+            }
+        res->best_score = best;
+        res->best_index = idx >= 0 ? (long long)cand_begin + idx : -1;
+        res->best_covered = idx >= 0 ? covered[idx] : 0;
+        double ft = 0.0;
+        for (unsigned b = 0; b < n_fixed_blocks; ++b) ft = __dadd_rn(ft, fixed_block_totals[b]);
+        res->fixed_total = ft;
+    }
+}
+
+// The mobile-sensor flags the reference leaves in the cells after its candidate loop:
+// in_range from the last candidate, in_fov from the last candidate that was in range, visible from
+// the last candidate that passed both gates; untouched where no candidate got that far.
+__global__ void __launch_bounds__(kSweepThreads)
+k_flags(SweepDev P, const plc_pose* __restrict__ cands, unsigned n_cands, const plc_cell* __restrict__ cells,
+        unsigned n_cells, uint8_t* __restrict__ flags) {
+    unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_cells || n_cands == 0) return;
+    plc_cell c = cells[j];
+    unsigned f = flags[j];
+    bool range_done = false, fov_done = false;
+    for (long long i = (long long)n_cands - 1; i >= 0; --i) {
+        plc_pose s = cands[i];
+        double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
+        double L = ray_length(dx, dy, dz);
+        bool in_range = (L >= P.min_distance && L <= P.max_distance);
+        if (!range_done) {
+            f = (f & ~PLC_FLAG_RANGE_MOBILE) | (in_range ? PLC_FLAG_RANGE_MOBILE : 0);
+            range_done = true;
+        }
+        if (!in_range) continue;
+        bool fov = in_fov(P, s.pitch, s.yaw, dx, dy, dz);
+        if (!fov_done) {
+            f = (f & ~PLC_FLAG_FOV_MOBILE) | (fov ? PLC_FLAG_FOV_MOBILE : 0);
+            fov_done = true;
+        }
+        if (!fov) continue;
+        RayStats st;
+        bool vis = P.have_terrain ? ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st) : true;
+        f = (f & ~PLC_FLAG_VIS_MOBILE) | (vis ? PLC_FLAG_VIS_MOBILE : 0);
+        break;
+    }
+    flags[j] = (uint8_t)f;
+}
+
+__global__ void k_reset_result(SweepResult* res) {
+    res->best_score = -INFINITY;
+    res->best_index = -1;
+    res->best_covered = 0;
+    res->pad = 0;
+    res->fixed_total = 0.0;
+    res->rays_gated_in = res->rays_visible = res->samples = res->fixed_samples = res->exact_tests = 0;
+}
+
+bool params_ok(const plc_params* p) {
+    if (!p) return false;
+    const double v[] = {p->max_distance, p->min_distance, p->ray_step, p->ray_start, p->vis_radius,
+                        p->block_radius_scale, p->observed_radius_scale, p->fov_vertical, p->alpha, p->beta};
+    for (double d : v)
+        if (!std::isfinite(d)) return false;
+    if (!(p->ray_step > 0) || !(p->vis_radius > 0) || !(p->block_radius_scale > 0) || !(p->observed_radius_scale > 0))
+        return false;
+    // a ray may take at most this many samples; refuse parameterisations that would spin
+    if ((p->max_distance - p->ray_start) / p->ray_step > 1.0e6) return false;
+    return p->fixed_mode == 0 || p->fixed_mode == 1;
+}
+
+float ceil_to_float(double v) {
+    float f = static_cast<float>(v);
+    if (static_cast<double>(f) < v) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+    return f;
+}
+
+}  // namespace
+}  // namespace plc
+
+using namespace plc;
+
+extern "C" plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* cloud) {
+    if (!ctx || !cloud_view_ok(cloud)) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    PLC_TRY(voxel_set_cloud(ctx, ctx->terrain, cloud));
+    // build for the node's default block radius right away; a sweep with other parameters rebuilds
+    plc_params d;
+    plc_params_default(&d);
+    PLC_TRY(voxel_build(ctx, ctx->terrain, d.vis_radius * d.block_radius_scale));
+    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_vl_set_observed(plc_ctx* ctx, const plc_cloud_view* cloud) {
+    if (!ctx || !cloud_view_ok(cloud)) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    PLC_TRY(voxel_set_cloud(ctx, ctx->observed, cloud));
+    plc_params d;
+    plc_params_default(&d);
+    PLC_TRY(voxel_build(ctx, ctx->observed, d.vis_radius * d.observed_radius_scale));
+    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint64_t n_cells) {
+    if (!ctx || (n_cells && !cells) || n_cells > 0x7fffff00ull) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    ctx->n_cells = 0;
+    ctx->ran = false;
+    if (n_cells == 0) return PLC_OK;
+    PLC_CUDA_TRY(ctx, ctx->cells.reserve(n_cells * sizeof(plc_cell)));
+    PLC_CUDA_TRY(ctx, ctx->cell_flags.reserve(n_cells));
+    PLC_CUDA_TRY(ctx, ctx->fixed_scores.reserve(n_cells * sizeof(double)));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->cells.ptr, cells, n_cells * sizeof(plc_cell), cudaMemcpyHostToDevice, ctx->stream));
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ctx->cell_flags.ptr, 0, n_cells, ctx->stream));   // GridCell ctor: all false (:37-39)
+    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->n_cells = n_cells;
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
+                                               const plc_pose* cands, uint64_t n_cands, uint64_t cand_begin,
+                                               uint64_t cand_end) {
+    if (!ctx || !params_ok(prm) || !fixed || (n_cands && !cands)) return PLC_E_INVALID_ARG;
+    if (cand_begin > cand_end || cand_end > n_cands || n_cands > 0x7fffff00ull) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    ctx->have_job = false;
+    ctx->ran = false;
+    if (n_cands) {
+        PLC_CUDA_TRY(ctx, ctx->cands.reserve(n_cands * sizeof(plc_pose)));
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->cands.ptr, cands, n_cands * sizeof(plc_pose), cudaMemcpyHostToDevice, ctx->stream));
+        // the caller's array may go away as soon as we return
+        PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->prm = *prm;
+    ctx->fixed = *fixed;
+    ctx->n_cands = n_cands;
+    ctx->cand_begin = cand_begin;
+    ctx->cand_end = cand_end;
+    ctx->have_job = true;
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_flags) {
+    if (!ctx) return PLC_E_INVALID_ARG;
+    if (!ctx->have_job) return PLC_E_NO_CANDIDATES;
+    if (ctx->n_cells == 0) return PLC_E_NO_CELLS;                       // :455 excavation_grid_3d_.empty()
+    if (ctx->terrain.n_input == 0) return PLC_E_NO_TERRAIN;             // :455 !terrain_cloud_
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const plc_params& p = ctx->prm;
+    const double block_radius = p.vis_radius * p.block_radius_scale;    // :782
+    const double obs_radius = p.vis_radius * p.observed_radius_scale;   // :743
+    PLC_TRY(voxel_build(ctx, ctx->terrain, block_radius));
+    PLC_TRY(voxel_build(ctx, ctx->observed, obs_radius));
+
+    SweepDev P{};
+    P.terrain = ctx->terrain.geom;
+    P.observed = ctx->observed.geom;
+    P.have_terrain = ctx->terrain.has_points();     // all-NaN cloud: tree over zero points never blocks
+    P.have_observed = ctx->observed.has_points();   // :719 (!zx120_cloud_ || empty)
+    // blocked iff a point has d2 < (float)(r*r) and (double)d2 < vis_radius*0.5 (:782-790)
+    P.thr_block = fminf(static_cast<float>(block_radius * block_radius), ceil_to_float(p.vis_radius * 0.5));
+    P.thr_obs = static_cast<float>(obs_radius * obs_radius);
+    P.max_distance = p.max_distance;
+    P.min_distance = p.min_distance;
+    P.ray_step = p.ray_step;
+    P.ray_start = p.ray_start;
+    P.vis_radius = p.vis_radius;
+    P.half_fov_v = p.fov_vertical / 2.0;
+    P.half_fov_h = p.fov_horizontal >= 0.0 ? p.fov_horizontal / 2.0 : -1.0;
+    P.alpha = p.alpha;
+    P.beta = p.beta;
+    P.fixed_mode = p.fixed_mode;
+
+    const unsigned M = (unsigned)ctx->n_cells;
+    const unsigned n_local = (unsigned)(ctx->cand_end - ctx->cand_begin);
+    const unsigned tiles = (M + kTileCells - 1) / kTileCells;
+    const unsigned fixed_blocks = (M + kSweepThreads - 1) / kSweepThreads;
+    ctx->tiles = (int)tiles;
+    ctx->mask_words = (M + 31) / 32;
+    if ((uint64_t)n_local * tiles > 0x7fffffffull) return PLC_E_INVALID_ARG;
+
+    PLC_CUDA_TRY(ctx, ctx->scratch.reserve((size_t)fixed_blocks * sizeof(double) + 4096));
+    PLC_CUDA_TRY(ctx, ctx->partial_score.reserve((size_t)n_local * tiles * sizeof(double) + 8));
+    PLC_CUDA_TRY(ctx, ctx->partial_cov.reserve((size_t)n_local * tiles * sizeof(int) + 8));
+    PLC_CUDA_TRY(ctx, ctx->scores.reserve((size_t)n_local * sizeof(double) + 8));
+    PLC_CUDA_TRY(ctx, ctx->covered.reserve((size_t)n_local * sizeof(int) + 8));
+    if (want_mask) PLC_CUDA_TRY(ctx, ctx->mask.reserve((size_t)n_local * ctx->mask_words * 4 + 8));
+
+    cudaStream_t s = ctx->stream;
+    SweepResult* res = ctx->result.as<SweepResult>();
+    double* fixed_totals = ctx->scratch.as<double>();
+    k_reset_result<<<1, 1, 0, s>>>(res);
+    k_fixed<<<fixed_blocks, kSweepThreads, 0, s>>>(P, ctx->fixed, ctx->cells.as<plc_cell>(), M,
+                                                   ctx->fixed_scores.as<double>(), ctx->cell_flags.as<uint8_t>(),
+                                                   fixed_totals, res);
+    ctx->launches += 2;
+    if (n_local) {
+        k_sweep<<<n_local * tiles, kSweepThreads, 0, s>>>(
+            P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin, tiles, ctx->cells.as<plc_cell>(), M,
+            ctx->fixed_scores.as<double>(), ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
+            want_mask ? ctx->mask.as<uint32_t>() : nullptr, (unsigned)ctx->mask_words, res);
+        k_finalize<<<(n_local + 255) / 256, 256, 0, s>>>(ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
+                                                         n_local, tiles, ctx->scores.as<double>(), ctx->covered.as<int>());
+        ctx->launches += 2;
+    }
+    k_argmax<<<1, 1024, 0, s>>>(ctx->scores.as<double>(), ctx->covered.as<int>(), n_local, ctx->cand_begin,
+                                fixed_totals, fixed_blocks, res);
+    ctx->launches += 1;
+    if (want_flags) {
+        k_flags<<<fixed_blocks, kSweepThreads, 0, s>>>(P, ctx->cands.as<plc_pose>(), (unsigned)ctx->n_cands,
+                                                       ctx->cells.as<plc_cell>(), M, ctx->cell_flags.as<uint8_t>());
+        ctx->launches += 1;
+    }
+    PLC_CUDA_TRY(ctx, cudaGetLastError());
+    ctx->ran = true;
+    ctx->ran_mask = want_mask != 0;
+    ctx->ran_flags = want_flags != 0;
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out) {
+    if (!ctx || !out) return PLC_E_INVALID_ARG;
+    if (!ctx->ran) return PLC_E_NO_CANDIDATES;
+    if (out->mask && !ctx->ran_mask) return PLC_E_INVALID_ARG;
+    if (out->cell_flags && !ctx->ran_flags) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    const uint64_t n_local = ctx->cand_end - ctx->cand_begin, M = ctx->n_cells;
+    SweepResult* host = static_cast<SweepResult*>(ctx->pinned);
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(host, ctx->result.ptr, sizeof(SweepResult), cudaMemcpyDeviceToHost, s));
+    if (out->scores && n_local)
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->scores, ctx->scores.ptr, n_local * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (out->covered && n_local)
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->covered, ctx->covered.ptr, n_local * sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (out->mask && n_local)
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->mask, ctx->mask.ptr, n_local * ctx->mask_words * 4, cudaMemcpyDeviceToHost, s));
+    if (out->cell_flags)
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->cell_flags, ctx->cell_flags.ptr, M, cudaMemcpyDeviceToHost, s));
+    if (out->fixed_scores)
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->fixed_scores, ctx->fixed_scores.ptr, M * sizeof(double), cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    out->best_index = host->best_index;
+    out->best_score = host->best_score;
+    out->best_covered = host->best_covered;
+    out->n_cells = (int32_t)M;
+    out->fixed_total = host->fixed_total;
+    out->mask_words = ctx->mask_words;
+    out->counters.rays = n_local * M;
+    out->counters.rays_gated_in = host->rays_gated_in;
+    out->counters.rays_visible = host->rays_visible;
+    out->counters.samples = host->samples;
+    out->counters.fixed_samples = host->fixed_samples;
+    out->counters.exact_tests = host->exact_tests;
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_vl_sweep(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed, const plc_pose* cands,
+                                   uint64_t n_cands, uint64_t cand_begin, uint64_t cand_end, plc_sweep_out* out) {
+    if (!out) return PLC_E_INVALID_ARG;
+    PLC_TRY(plc_vl_upload_candidates(ctx, prm, fixed, cands, n_cands, cand_begin, cand_end));
+    PLC_TRY(plc_vl_run_async(ctx, out->mask != nullptr, out->cell_flags != nullptr));
+    return plc_vl_fetch(ctx, out);
+}
+
+extern "C" plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr) {
+    if (!ctx || !ptr) return PLC_E_INVALID_ARG;
+    *ptr = ctx->result.ptr;
+    return PLC_OK;
+}
+
+static void fill_info(const VoxelIndex& ix, plc_grid_info* o) {
+    memset(o, 0, sizeof(*o));
+    o->n_points = ix.n_raw;
+    if (ix.built_radius < 0) return;
+    o->n_voxels = ix.n_vox;
+    o->grid_bytes = ix.bytes();
+    o->dim[0] = ix.geom.dim_x;
+    o->dim[1] = ix.geom.dim_y;
+    o->dim[2] = ix.geom.dim_z;
+    o->origin[0] = ix.geom.ox;
+    o->origin[1] = ix.geom.oy;
+    o->origin[2] = ix.geom.oz;
+    o->voxel = ix.h;
+}
+
+extern "C" plc_status plc_vl_grid_info(const plc_ctx* ctx, plc_grid_info* terrain, plc_grid_info* observed) {
+    if (!ctx) return PLC_E_INVALID_ARG;
+    if (terrain) fill_info(ctx->terrain, terrain);
+    if (observed) fill_info(ctx->observed, observed);
+    return PLC_OK;
+}

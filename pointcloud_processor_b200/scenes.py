@@ -1,0 +1,244 @@
+"""Synthetic inputs for the virtual_lidar sweep, shaped like the reference's own data products
+(SURVEY §8 D2).  Everything is deterministic given the seed; the same arrays feed the CUDA path
+and the CPU oracle.
+
+  /excavated_terrain  ground height field on a jittered lattice with the pit carved out, plus the
+                      pit surface (bottom + slopes) laid out with the rules of
+                      excavated_surface_generator.cpp:487-584 (generateExcavatedSurface)
+  /excavation_area    target pit surface per excavated_surface_generator.cpp:350-455
+                      (generateExcavationArea), with analytic per-point normals
+  cells               reference lattice rule (virtual_lidar.cpp:236-340) via plc_host_generate_cells
+  candidates          reference lattice rule (virtual_lidar.cpp:550-625) via plc_host_generate_candidates,
+                      repeated for P_z sensor heights {1.1 + 0.4k}
+
+The reference's generator cannot run at these sizes (it rebuilds a KD-tree per point),
+so the ground height is analytic: z = 0.15 sin(0.4x) cos(0.3y) (+-1 cm noise on ground points).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _abi as A
+from .context import host_generate_candidates, host_generate_cells
+
+# excavated_surface_generator.cpp:28-47 defaults
+DEPTH = 1.0
+SLOPE_DEG = 75.0
+PIT_CENTER = (4.0, 1.0)          # offset_x, offset_y from zx120/base_link at the map origin
+FIXED_OFFSET = (0.4, 0.5, 3.5)   # virtual_lidar.cpp:103-105
+FIXED_PITCH = -np.pi / 6         # :106
+
+
+def ground_height(x, y):
+    return 0.15 * np.sin(0.4 * x) * np.cos(0.3 * y)
+
+
+def pit_boxes(shape: str):
+    """getExcavationBoxes (excavated_surface_generator.cpp:138-181): (min_x, max_x, min_y, max_y) per box."""
+    if shape == "L":
+        a1l, a1w, a2l, a2w = 2.0, 1.2, 2.0, 1.2
+        arm1 = (-a1w / 2, a1w / 2, -a1l / 2 - a1l / 2, -a1l / 2 + a1l / 2)
+        c2x, c2y = a2l / 2, -a1l + a2w / 2
+        arm2 = (c2x - a2l / 2, c2x + a2l / 2, c2y - a2w / 2, c2y + a2w / 2)
+        return [arm1, arm2]
+    if shape == "rect":
+        length, width = 1.8, 1.2
+        return [(-length / 2, length / 2, -width / 2, width / 2)]
+    raise ValueError(shape)
+
+
+def _inside_any(x, y, boxes):
+    m = np.zeros(np.broadcast(x, y).shape, bool)
+    for (x0, x1, y0, y1) in boxes:
+        m |= (x >= x0) & (x <= x1) & (y >= y0) & (y <= y1)
+    return m
+
+
+def _edge_lattice(boxes, d):
+    """Lattice of generateExcavationArea/generateExcavatedSurface: points inside any box, the outer-edge
+    subset (isOuterEdge with tolerance = point_density) and each edge point's outward direction."""
+    x0 = min(b[0] for b in boxes); x1 = max(b[1] for b in boxes)
+    y0 = min(b[2] for b in boxes); y1 = max(b[3] for b in boxes)
+    nx = int((x1 - x0) / d) + 1
+    ny = int((y1 - y0) / d) + 1
+    xs = x0 + np.arange(nx + 1) * d
+    ys = y0 + np.arange(ny + 1) * d
+    X, Y = np.meshgrid(xs, ys, indexing="ij")
+    X = X.ravel(); Y = Y.ravel()
+    inside = _inside_any(X, Y, boxes)
+    X = X[inside]; Y = Y[inside]
+    out_px = ~_inside_any(X + d, Y, boxes); out_mx = ~_inside_any(X - d, Y, boxes)
+    out_py = ~_inside_any(X, Y + d, boxes); out_my = ~_inside_any(X, Y - d, boxes)
+    edge = out_px | out_mx | out_py | out_my
+    dir_x = np.where(out_px, 1.0, np.where(out_mx, -1.0, 0.0))
+    dir_y = np.where(out_py, 1.0, np.where(out_my, -1.0, 0.0))
+    return X, Y, edge, dir_x, dir_y
+
+
+def excavation_area(shape: str, density: float = 0.05):
+    """/excavation_area cloud (yaw 0) and analytic unit normals (n_z >= 0) per point."""
+    boxes = pit_boxes(shape)
+    slope_offset = DEPTH / np.tan(np.deg2rad(SLOPE_DEG))
+    X, Y, edge, dx, dy = _edge_lattice(boxes, density)
+    cx, cy = PIT_CENTER
+    gx, gy = cx + X, cy + Y
+    h = ground_height(gx, gy)
+    pts = [np.stack([gx, gy, h - DEPTH], 1)]
+    nrm = [np.tile([0.0, 0.0, 1.0], (gx.size, 1))]
+    n_depth = int(DEPTH / density)
+    ex, ey, eh, edx, edy = X[edge], Y[edge], h[edge], dx[edge], dy[edge]
+    for k in range(1, n_depth):
+        off = slope_offset * (k / n_depth)
+        pts.append(np.stack([cx + ex + edx * off, cy + ey + edy * off, eh - DEPTH + k * density], 1))
+        # slope face rises outward: normal points inward and up
+        n = np.stack([-edx * DEPTH, -edy * DEPTH, np.full(ex.size, slope_offset)], 1)
+        n /= np.linalg.norm(n, axis=1, keepdims=True)
+        nrm.append(n)
+    return np.concatenate(pts).astype(np.float32), np.concatenate(nrm).astype(np.float32)
+
+
+def pit_surface(shape: str, density: float):
+    """generateExcavatedSurface: bottom lattice + slope lines from every outer-edge lattice point."""
+    boxes = pit_boxes(shape)
+    slope_offset = DEPTH / np.tan(np.deg2rad(SLOPE_DEG))
+    X, Y, edge, dx, dy = _edge_lattice(boxes, density)
+    cx, cy = PIT_CENTER
+    gx, gy = cx + X, cy + Y
+    pts = [np.stack([gx, gy, ground_height(gx, gy) - DEPTH], 1)]
+    n_slope = int(slope_offset / density) + 1
+    ex, ey, edx, edy = X[edge], Y[edge], dx[edge], dy[edge]
+    for k in range(n_slope + 1):
+        zr = k / n_slope
+        sx, sy = cx + ex + edx * slope_offset * zr, cy + ey + edy * slope_offset * zr
+        pts.append(np.stack([sx, sy, ground_height(sx, sy) - DEPTH * (1.0 - zr)], 1))
+    return np.concatenate(pts)
+
+
+def _pit_count(shape, density):
+    return pit_surface(shape, density).shape[0]
+
+
+def terrain(shape: str, n_points: int, seed: int, side: float = 30.0, pit_fraction: float = 0.10):
+    """/excavated_terrain with exactly n_points points (float32 xyz)."""
+    rng = np.random.default_rng(seed)
+    # pit density so that the pit surface is ~pit_fraction of the cloud
+    target = max(64, int(n_points * pit_fraction))
+    lo, hi = 0.002, 0.5
+    for _ in range(40):
+        mid = np.sqrt(lo * hi)
+        if _pit_count(shape, mid) > target:
+            lo = mid
+        else:
+            hi = mid
+    pit = pit_surface(shape, hi)
+    n_ground = n_points - pit.shape[0]
+    if n_ground < 0:
+        pit = pit[rng.permutation(pit.shape[0])[:n_points]]
+        n_ground = 0
+    boxes = pit_boxes(shape)
+    slope_offset = DEPTH / np.tan(np.deg2rad(SLOPE_DEG))
+    cx, cy = PIT_CENTER
+    area = side * side - sum((b[1] - b[0] + 2 * slope_offset) * (b[3] - b[2] + 2 * slope_offset) for b in boxes)
+    pitch = np.sqrt(area / max(n_ground, 1)) * 0.985     # a few percent spare, trimmed below
+    m = int(np.ceil(side / pitch))
+    ii, jj = np.meshgrid(np.arange(m), np.arange(m), indexing="ij")
+    gx = cx - side / 2 + (ii.ravel() + 0.5 + rng.uniform(-0.3, 0.3, ii.size)) * pitch
+    gy = cy - side / 2 + (jj.ravel() + 0.5 + rng.uniform(-0.3, 0.3, jj.size)) * pitch
+    # carve: drop ground inside the pit's top outline (boxes grown by the slope offset,
+    # isInsideExcavationArea at z_relative = 0, excavated_surface_generator.cpp:327-348)
+    keep = np.ones(gx.size, bool)
+    for (x0, x1, y0, y1) in boxes:
+        keep &= ~((gx - cx >= x0 - slope_offset) & (gx - cx <= x1 + slope_offset) &
+                  (gy - cy >= y0 - slope_offset) & (gy - cy <= y1 + slope_offset))
+    gx, gy = gx[keep], gy[keep]
+    if gx.size < n_ground:
+        raise RuntimeError(f"ground lattice too sparse: {gx.size} < {n_ground}")
+    sel = np.sort(rng.permutation(gx.size)[:n_ground])
+    gx, gy = gx[sel], gy[sel]
+    gz = ground_height(gx, gy) + rng.uniform(-0.01, 0.01, gx.size)
+    cloud = np.concatenate([np.stack([gx, gy, gz], 1), pit]).astype(np.float32)
+    assert cloud.shape[0] == n_points
+    return np.ascontiguousarray(cloud)
+
+
+@dataclass
+class Scene:
+    name: str
+    terrain: np.ndarray        # (N,3) float32
+    area: np.ndarray           # (A,3) float32
+    area_normals: np.ndarray   # (A,3) float32
+    cells: np.ndarray          # (M,) CELL_DTYPE
+    bounds: A.GridBounds
+    fixed: np.ndarray          # (1,) POSE_DTYPE
+    candidates: np.ndarray     # (C,) POSE_DTYPE
+    params: A.Params
+    meta: dict
+
+
+def fixed_pose() -> np.ndarray:
+    f = np.zeros(1, A.POSE_DTYPE)
+    f["x"], f["y"], f["z"] = FIXED_OFFSET          # zx120/base_link at the map origin
+    f["pitch"], f["yaw"] = FIXED_PITCH, 0.0
+    return f
+
+
+def make_cells(area, normals, m_target: int | None, res: float, layers: int | None):
+    if layers is None:
+        # smallest vertical_layers whose lattice yields at least m_target valid cells
+        lo, hi = 1, 8
+        while host_generate_cells(area, None, res, hi, 1.5)[0].size < m_target:
+            lo, hi = hi, hi * 2
+            if hi > 4096:
+                raise RuntimeError("cannot reach the requested cell count")
+        while lo < hi:
+            mid = (lo + hi) // 2
+            if host_generate_cells(area, None, res, mid, 1.5)[0].size >= m_target:
+                hi = mid
+            else:
+                lo = mid + 1
+        layers = hi
+    cells, bounds = host_generate_cells(area, normals, res, layers, 1.5)
+    if m_target is not None:
+        if cells.size < m_target:
+            raise RuntimeError(f"lattice res={res} layers={layers} gives {cells.size} < {m_target} cells")
+        cells = cells[:m_target].copy()    # truncate in reference order (D1)
+    return cells, bounds
+
+
+def make_candidates(terrain_xyz, bounds, fixed, px: int, pz: int, search_radius=3.0, base_height=1.1):
+    layers = [host_generate_candidates(terrain_xyz, bounds, fixed, px * px, search_radius, base_height + 0.4 * k)
+              for k in range(pz)]
+    return np.concatenate(layers) if layers else np.zeros(0, A.POSE_DTYPE)
+
+
+# BASELINE.json configs -> concrete sizes.  (res, layers) chosen so that the reference lattice
+# yields at least M valid cells; the list is then truncated to exactly M = V*H.
+CONFIGS = {
+    # name: shape, N, px, pz, M, seed, side, res, layers
+    "tiny": dict(shape="L", n=6_000, px=4, pz=1, m=None, seed=11, side=14.0, res=0.2, layers=4),
+    "small": dict(shape="rect", n=20_000, px=6, pz=1, m=None, seed=12, side=16.0, res=0.1, layers=6),
+    "ref_default": dict(shape="L", n=50_000, px=10, pz=1, m=None, seed=13, side=30.0, res=0.1, layers=10),
+    # layers=None: smallest vertical_layers giving >= m valid cells (then truncated to exactly m)
+    "cfg1": dict(shape="L", n=50_000, px=16, pz=1, m=16 * 900, seed=1, side=30.0, res=0.05, layers=None),
+    "cfg2": dict(shape="rect", n=200_000, px=32, pz=2, m=32 * 1800, seed=2, side=30.0, res=0.025, layers=None),
+    "cfg3": dict(shape="L", n=1_000_000, px=64, pz=4, m=32 * 1800, seed=3, side=30.0, res=0.03, layers=None),
+    "cfg5": dict(shape="L", n=4_000_000, px=128, pz=8, m=64 * 2048, seed=6, side=40.0, res=0.025, layers=None),
+}
+
+
+def build(name: str, **override) -> Scene:
+    cfg = dict(CONFIGS[name])
+    cfg.update(override)
+    terr = terrain(cfg["shape"], cfg["n"], cfg["seed"], cfg["side"])
+    area, normals = excavation_area(cfg["shape"], 0.05)
+    fixed = fixed_pose()
+    cells, bounds = make_cells(area, normals, cfg["m"], cfg["res"], cfg["layers"])
+    cands = make_candidates(terr, bounds, fixed, cfg["px"], cfg["pz"])
+    prm = A.default_params()
+    meta = dict(cfg)
+    meta.update(layers_used=int(round((bounds.max_z - bounds.min_z) / max(cells["z"][1] - cells["z"][0], 1e-12))) if cells.size > 1 and cells["x"][0] == cells["x"][1] else None,
+                n_cells=int(cells.size), n_candidates=int(cands.size), n_terrain=int(terr.shape[0]),
+                n_area=int(area.shape[0]))
+    return Scene(name, terr, area, normals, cells, bounds, fixed, cands, prm, meta)
