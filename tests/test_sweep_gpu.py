@@ -1,0 +1,182 @@
+"""GPU parity tests of the visibility sweep: the CUDA path (through the C ABI) against the CPU oracle
+on the same seeded inputs.
+
+Bars (BASELINE.json north_star): visibility masks identical except rays grazing a boundary (at most
+1e-4 of pairs, count reported) — in practice the arithmetic is bit-identical and the tests demand 0;
+candidate scores within 1e-12 relative (libm acos/sin round-off only); identical optimal pose;
+sample counters identical (they define the algorithmic bytes of the roofline)."""
+import numpy as np
+import pytest
+
+from oracle import binding as O
+from pointcloud_processor_b200 import _abi as A
+
+pytestmark = pytest.mark.gpu
+
+SCORE_RTOL = 1e-12          # tolerance stated by the spec for the double-precision score
+MASK_MISMATCH_BUDGET = 1e-4  # of (pose, cell) pairs; the tests below additionally require exactly 0
+
+
+def compare(got, ref, n_cells, want_flags=True):
+    pairs = ref["mask"].shape[0] * n_cells
+    mism = int(np.count_nonzero(np.unpackbits((got.mask ^ ref["mask"]).view(np.uint8))))
+    assert mism <= MASK_MISMATCH_BUDGET * pairs, f"{mism} of {pairs} visibility bits differ"
+    assert mism == 0, f"{mism} grazing-ray mismatches (allowed by the spec, but the arithmetic should be bit-exact)"
+    assert got.best_index == ref["best_index"]
+    assert got.best_covered == ref["best_covered"]
+    np.testing.assert_allclose(got.scores, ref["scores"], rtol=SCORE_RTOL, atol=1e-12)
+    assert np.array_equal(got.covered, ref["covered"])
+    np.testing.assert_allclose(got.fixed_scores, ref["fixed_scores"], rtol=SCORE_RTOL, atol=1e-15)
+    assert got.fixed_total == pytest.approx(ref["fixed_total"], rel=1e-12)
+    for k in ("rays", "rays_gated_in", "rays_visible", "samples", "fixed_samples"):
+        assert got.counters[k] == ref["counters"][k], k
+    if want_flags and ref["flags"] is not None:
+        assert np.array_equal(got.cell_flags, ref["flags"])
+
+
+def run_gpu(ctx, s, cands=None, params=None, observed=None, **kw):
+    ctx.set_terrain(s.terrain)
+    ctx.set_observed(observed if observed is not None else np.zeros((0, 3), np.float32))
+    ctx.set_cells(s.cells)
+    cands = s.candidates if cands is None else cands
+    return ctx.sweep(params or s.params, s.fixed, cands, mask=True, flags=True, fixed_scores=True, **kw)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "ref_default"])
+def test_parity_small_scenes(ctx, scene_cache, name):
+    s = scene_cache(name)
+    got = run_gpu(ctx, s)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, s.params, s.fixed, s.candidates)
+    compare(got, ref, s.cells.size)
+
+
+def test_parity_config1_full(ctx, scene_cache):
+    # BASELINE.json configs[0]: L-shape, ~50k points, 16x16x1 poses, 16x900 rays per pose
+    s = scene_cache("cfg1")
+    assert s.cells.size == 16 * 900 and s.terrain.shape[0] == 50_000
+    got = run_gpu(ctx, s)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, s.params, s.fixed, s.candidates)
+    compare(got, ref, s.cells.size)
+    assert 0.2 < got.counters["rays_visible"] / got.counters["rays"] < 0.9
+
+
+def test_parity_config2_candidate_subset(ctx, scene_cache):
+    # BASELINE.json configs[1] geometry (rect, 200k points, 57 600 rays per pose); the oracle takes
+    # seconds per pose, so a seeded subset of 48 poses is compared bit for bit
+    s = scene_cache("cfg2")
+    assert s.cells.size == 32 * 1800 and s.terrain.shape[0] == 200_000
+    sel = np.sort(np.random.default_rng(7).choice(s.candidates.size, 48, replace=False))
+    cands = s.candidates[sel]
+    got = run_gpu(ctx, s, cands=cands)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, s.params, s.fixed, cands, threads=8)
+    compare(got, ref, s.cells.size, want_flags=False)
+
+
+def test_observed_cloud_and_memo_variant(ctx, scene_cache):
+    s = scene_cache("small")
+    obs = np.stack([s.cells["x"], s.cells["y"], s.cells["z"]], 1).astype(np.float32)[::5] + np.float32(0.05)
+    ix, oix = O.Index(s.terrain, O.GRID), O.Index(obs, O.GRID)
+    got = run_gpu(ctx, s, observed=obs)
+    compare(got, O.sweep(ix, oix, s.cells, s.params, s.fixed, s.candidates), s.cells.size)
+    memo = A.memo_params()     # other radii (0.035 / 0.05), 0.2 m step, azimuth FOV, observed-only fixed sensor
+    got = run_gpu(ctx, s, observed=obs, params=memo)
+    compare(got, O.sweep(ix, oix, s.cells, memo, s.fixed, s.candidates), s.cells.size)
+    got = run_gpu(ctx, s, params=memo)                 # memo variant without an observed cloud
+    compare(got, O.sweep(ix, None, s.cells, memo, s.fixed, s.candidates), s.cells.size)
+    # back to the default radius: the index is rebuilt for it
+    got = run_gpu(ctx, s)
+    compare(got, O.sweep(ix, None, s.cells, s.params, s.fixed, s.candidates), s.cells.size)
+
+
+def test_pointcloud2_layouts_and_non_finite_points(ctx, scene_cache):
+    s = scene_cache("tiny")
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, s.params, s.fixed, s.candidates)
+    n = s.terrain.shape[0]
+    # XYZRGB-style record: point_step 32, x/y/z at 0/4/8; NaN points sprinkled in are dropped
+    rec = np.zeros((n + 50, 8), np.float32)
+    rec[:n, :3] = s.terrain
+    rec[n:, :3] = np.nan
+    rec[n + 10:, 0] = np.inf
+    rec = rec[np.random.default_rng(2).permutation(n + 50)]      # order is irrelevant
+    ctx.set_terrain(rec)
+    ctx.set_observed(np.zeros((0, 3), np.float32))
+    ctx.set_cells(s.cells)
+    got = ctx.sweep(s.params, s.fixed, s.candidates, mask=True, flags=True, fixed_scores=True)
+    compare(got, ref, s.cells.size)
+    assert ctx.grid_info()[0]["n_points"] == n
+    # velodyne-style unaligned record: point_step 22, fields at 2/6/10
+    raw = np.zeros((n, 22), np.uint8)
+    raw[:, 2:14] = s.terrain.view(np.uint8).reshape(n, 12)
+    ctx.set_terrain(raw.reshape(-1), point_step=22, off=(2, 6, 10))
+    got = ctx.sweep(s.params, s.fixed, s.candidates, mask=True, flags=True, fixed_scores=True)
+    compare(got, ref, s.cells.size)
+
+
+def test_sharded_sweep_equals_unsharded(ctx, scene_cache):
+    s = scene_cache("ref_default")
+    full = run_gpu(ctx, s)
+    C = s.candidates.size
+    for world in (2, 4, 8):
+        best = (-np.inf, -1)
+        scores = []
+        for r in range(world):
+            b, e = r * C // world, (r + 1) * C // world
+            part = ctx.sweep(s.params, s.fixed, s.candidates, b, e, mask=True)
+            assert np.array_equal(part.mask, full.mask[b:e])
+            scores.append(part.scores)
+            if part.best_score > best[0]:          # ranks ascend, so strict '>' keeps the lowest index
+                best = (part.best_score, part.best_index)
+        assert np.array_equal(np.concatenate(scores), full.scores)      # bit-identical, not just close
+        assert best == (full.best_score, full.best_index)
+
+
+def test_deterministic_across_runs(ctx, scene_cache):
+    s = scene_cache("ref_default")
+    a = run_gpu(ctx, s)
+    b = run_gpu(ctx, s)
+    assert np.array_equal(a.scores, b.scores) and np.array_equal(a.mask, b.mask)
+    assert a.fixed_total == b.fixed_total and a.counters == b.counters
+
+
+def test_flags_persist_across_sweeps(ctx, scene_cache):
+    s = scene_cache("tiny")
+    ix = O.Index(s.terrain, O.GRID)
+    far = s.candidates[-1:].copy()
+    far["x"] += 500.0
+    run_gpu(ctx, s)
+    got2 = ctx.sweep(s.params, s.fixed, far, flags=True)
+    flags = O.sweep(ix, None, s.cells, s.params, s.fixed, s.candidates)["flags"]
+    O.sweep(ix, None, s.cells, s.params, s.fixed, far, flags_inout=flags)
+    assert np.array_equal(got2.cell_flags, flags)
+    ctx.set_cells(s.cells)                       # a new grid resets the flags (GridCell ctor)
+    got3 = ctx.sweep(s.params, s.fixed, far, flags=True)
+    fresh = O.sweep(ix, None, s.cells, s.params, s.fixed, far)["flags"]
+    assert np.array_equal(got3.cell_flags, fresh)
+
+
+def test_edge_cases_and_error_codes(scene_cache):
+    from pointcloud_processor_b200 import Context
+    s = scene_cache("tiny")
+    with Context(0) as c:
+        with pytest.raises(A.PlcError) as e:
+            c.sweep(s.params, s.fixed, s.candidates)
+        assert e.value.status == A.PLC_E_NO_CELLS          # runOptimization guard (:455)
+        c.set_cells(s.cells)
+        with pytest.raises(A.PlcError) as e:
+            c.sweep(s.params, s.fixed, s.candidates)
+        assert e.value.status == A.PLC_E_NO_TERRAIN
+        c.set_terrain(s.terrain)
+        r = c.sweep(s.params, s.fixed, s.candidates[:0])   # no candidates survive: Q5
+        assert r.best_index == -1 and r.best_score == -np.inf
+        bad = A.default_params()
+        bad.ray_step = 0.0
+        with pytest.raises(A.PlcError) as e:
+            c.sweep(bad, s.fixed, s.candidates)
+        assert e.value.status == A.PLC_E_INVALID_ARG
+        with pytest.raises(A.PlcError):
+            c.sweep(s.params, s.fixed, s.candidates, 5, 3)
+        # an all-NaN terrain cloud is "a tree over zero points": nothing blocks
+        c.set_terrain(np.full((10, 3), np.nan, np.float32))
+        r = c.sweep(s.params, s.fixed, s.candidates)
+        assert r.counters["rays_visible"] == r.counters["rays_gated_in"] and r.counters["samples"] > 0
+        assert c.launch_count > 0
