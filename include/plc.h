@@ -172,6 +172,11 @@ plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out);
  * valid after plc_vl_run_async; the multi-GPU exchange all-gathers it. */
 plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr);
 
+/* Device time (ms, CUDA events on the context's stream) of the dominant kernel of the last
+ * plc_vl_run_async — the per-(pose, cell) traversal kernel k_sweep — for roofline accounting.
+ * Synchronises the stream.  0 if no candidates were evaluated. */
+plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms);
+
 /* Grid facts for roofline accounting: bytes of the occupancy structure the sweep reads. */
 typedef struct plc_grid_info {
     uint64_t n_points;        /* finite points indexed */

@@ -88,7 +88,7 @@ EXPORTS = [
     "plc_last_error", "plc_launch_count", "plc_abi_version", "plc_ctx_sync",
     "plc_vl_set_terrain", "plc_vl_set_observed", "plc_vl_set_cells", "plc_vl_sweep",
     "plc_vl_upload_candidates", "plc_vl_run_async", "plc_vl_fetch", "plc_vl_result_device_ptr",
-    "plc_vl_grid_info", "plc_filter", "plc_merge",
+    "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_filter", "plc_merge",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
 ]
 
@@ -138,6 +138,7 @@ def lib() -> C.CDLL:
     L.plc_vl_run_async.argtypes = [vp, C.c_int, C.c_int]
     L.plc_vl_fetch.argtypes = [vp, C.POINTER(SweepOut)]
     L.plc_vl_result_device_ptr.argtypes = [vp, C.POINTER(vp)]
+    L.plc_vl_last_sweep_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
     L.plc_vl_grid_info.argtypes = [vp, C.POINTER(GridInfo), C.POINTER(GridInfo)]
     L.plc_filter.argtypes = [vp, C.POINTER(CloudView), C.POINTER(CropBox), dbl, vp, u64,
                              C.POINTER(u64), C.POINTER(u64)]

@@ -148,6 +148,11 @@ class Context:
         self._check(self._L.plc_vl_result_device_ptr(self._h, C.byref(p)), "plc_vl_result_device_ptr")
         return int(p.value)
 
+    def last_sweep_kernel_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self._L.plc_vl_last_sweep_kernel_ms(self._h, C.byref(ms)), "plc_vl_last_sweep_kernel_ms")
+        return float(ms.value)
+
     def grid_info(self):
         t, o = A.GridInfo(), A.GridInfo()
         self._check(self._L.plc_vl_grid_info(self._h, C.byref(t), C.byref(o)), "plc_vl_grid_info")

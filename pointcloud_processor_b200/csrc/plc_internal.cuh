@@ -119,6 +119,8 @@ struct plc_ctx {
     plc::DevBuf result;          // SweepResult
     uint64_t mask_words = 0;
     int tiles = 0;
+    cudaEvent_t ev_sweep_begin = nullptr, ev_sweep_end = nullptr;   // around k_sweep
+    bool sweep_timed = false;
 
     // filter / merge scratch
     plc::DevBuf f_keys, f_vals, f_keys2, f_vals2, f_tmp, f_out, f_flags;

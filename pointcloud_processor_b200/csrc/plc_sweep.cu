@@ -528,11 +528,15 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
                                                    ctx->fixed_scores.as<double>(), ctx->cell_flags.as<uint8_t>(),
                                                    fixed_totals, res);
     ctx->launches += 2;
+    ctx->sweep_timed = false;
     if (n_local) {
+        cudaEventRecord(ctx->ev_sweep_begin, s);
         k_sweep<<<n_local * tiles, kSweepThreads, 0, s>>>(
             P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin, tiles, ctx->cells.as<plc_cell>(), M,
             ctx->fixed_scores.as<double>(), ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
             want_mask ? ctx->mask.as<uint32_t>() : nullptr, (unsigned)ctx->mask_words, res);
+        cudaEventRecord(ctx->ev_sweep_end, s);
+        ctx->sweep_timed = true;
         k_finalize<<<(n_local + 255) / 256, 256, 0, s>>>(ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
                                                          n_local, tiles, ctx->scores.as<double>(), ctx->covered.as<int>());
         ctx->launches += 2;
@@ -594,6 +598,16 @@ extern "C" plc_status plc_vl_sweep(plc_ctx* ctx, const plc_params* prm, const pl
     PLC_TRY(plc_vl_upload_candidates(ctx, prm, fixed, cands, n_cands, cand_begin, cand_end));
     PLC_TRY(plc_vl_run_async(ctx, out->mask != nullptr, out->cell_flags != nullptr));
     return plc_vl_fetch(ctx, out);
+}
+
+extern "C" plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms) {
+    if (!ctx || !ms) return PLC_E_INVALID_ARG;
+    *ms = 0.0f;
+    if (!ctx->sweep_timed) return PLC_OK;
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    PLC_CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_sweep_end));
+    PLC_CUDA_TRY(ctx, cudaEventElapsedTime(ms, ctx->ev_sweep_begin, ctx->ev_sweep_end));
+    return PLC_OK;
 }
 
 extern "C" plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr) {
