@@ -153,8 +153,12 @@ def run_ours(args) -> dict | None:
     C, M = int(scene.candidates.size), int(scene.cells.size)
     begin, end = exchange.shard_range(C, rank, world)
 
-    stream = torch.cuda.current_stream(dev)
-    ctx = Context(local_rank, stream=stream.cuda_stream)      # library launches on torch's current stream
+    # a non-default torch stream (handle != 0) made current: the library launches on it, NCCL orders
+    # against it, and torch.cuda.Event records see exactly the kernels that are timed
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
+    ctx = Context(local_rank, stream=stream.cuda_stream)
+    assert stream.cuda_stream != 0
     ctx.set_terrain(scene.terrain)
     ctx.set_cells(scene.cells)
     ctx.upload_candidates(scene.params, scene.fixed, scene.candidates, begin, end)

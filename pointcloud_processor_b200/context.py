@@ -119,7 +119,7 @@ class Context:
         cands = np.ascontiguousarray(cands, dtype=A.POSE_DTYPE)
         fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
         end = cands.size if end is None else end
-        out, arrays = self._alloc_out(end - begin, scores, mask, flags, fixed_scores)
+        out, arrays = self._alloc_out(max(end - begin, 0), scores, mask, flags, fixed_scores)
         st = self._L.plc_vl_sweep(self._h, C.byref(params), A.ptr(fixed), A.ptr(cands) if cands.size else None,
                                   cands.size, begin, end, C.byref(out))
         self._check(st, "plc_vl_sweep")

@@ -175,8 +175,9 @@ def test_edge_cases_and_error_codes(scene_cache):
         assert e.value.status == A.PLC_E_INVALID_ARG
         with pytest.raises(A.PlcError):
             c.sweep(s.params, s.fixed, s.candidates, 5, 3)
-        # an all-NaN terrain cloud is "a tree over zero points": nothing blocks
+        # an all-NaN terrain cloud indexes zero points: nothing blocks, no sample is searched (same as
+        # the oracle, which treats an index over zero points as "no terrain tree")
         c.set_terrain(np.full((10, 3), np.nan, np.float32))
         r = c.sweep(s.params, s.fixed, s.candidates)
-        assert r.counters["rays_visible"] == r.counters["rays_gated_in"] and r.counters["samples"] > 0
+        assert r.counters["rays_visible"] == r.counters["rays_gated_in"] and r.counters["samples"] == 0
         assert c.launch_count > 0
