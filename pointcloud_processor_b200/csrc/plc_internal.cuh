@@ -51,21 +51,21 @@ struct DevBuf {
 };
 
 // Geometry of a voxel index, passed to kernels by value.
-//   coarse voxel edge h (a power of two), fine voxel edge g = h/4, shared origin.
-//   mask32[2*v + ((fz>>1)&1)] bit ((fx&3) | (fy&3)<<2 | (fz&1)<<4): fine voxel may hold a sample that
-//   the radius test accepts (conservative dilation of the points by the query radius).
-//   vstart[v] .. vstart[v+1]: range of the coarse voxel's points in `pts` (x fastest, so voxels
-//   adjacent in x are adjacent in pts).
+//   coarse voxel edge h (a power of two >= 2*reach), mid voxel h/2, fine voxel g = h/4, shared origin.
+//   mask32[2*v + ((fz>>1)&1)] bit ((fx&3) | (fy&3)<<2 | (fz&1)<<4): the fine voxel may hold a sample
+//   that the radius test accepts (conservative dilation of the points by the query reach).
+//   cstart[m] .. cstart[m+1]: candidate list of mid voxel m in cpts — every point within reach of
+//   the mid voxel's box (x fastest).  A sample in mid voxel m can only be blocked by those points.
 struct VoxelGeom {
     float ox, oy, oz;        // origin (multiple of h, exactly representable)
     float inv_g;             // 1/g (power of two)
-    float reach;             // float radius + slack used to pick the coarse voxels to scan
+    float reach;             // real-number radius + slack used by the builder
     int dim_x, dim_y, dim_z; // coarse dims
-    int fdim_x, fdim_y, fdim_z;   // fine dims = 4*coarse
+    int mdim_x, mdim_y, mdim_z;   // mid dims = 2*coarse
+    float fdim_xf, fdim_yf, fdim_zf;   // fine dims = 4*coarse, as float for the bounds test
     const uint32_t* __restrict__ mask32;
-    const uint32_t* __restrict__ vstart;
-    const float4* __restrict__ pts;
-    uint32_t n_pts;
+    const uint32_t* __restrict__ cstart;
+    const float4* __restrict__ cpts;
 };
 
 struct VoxelIndex {
@@ -75,15 +75,16 @@ struct VoxelIndex {
     uint64_t n_input = 0;
     float bbox[6] = {0, 0, 0, 0, 0, 0};   // min xyz, max xyz of finite points
     // built index
-    double built_radius = -1.0;   // query radius (m) the mask was dilated for
+    double built_radius = -1.0;   // query radius (m) the structure was built for
     double h = 0.0;
-    DevBuf mask32, vstart, vfill, pts, scan_tmp;
+    DevBuf mask32, cstart, cfill, cpts, scan_tmp;
     VoxelGeom geom{};
-    uint64_t n_vox = 0;
+    uint64_t n_vox = 0;       // coarse voxels
+    uint64_t n_cand = 0;      // entries in cpts
     bool has_points() const { return n_raw > 0; }
-    uint64_t bytes() const { return n_vox * 8 + (n_vox + 1) * 4 + n_raw * 16; }
+    uint64_t bytes() const { return n_vox * 8 + (n_vox * 8 + 1) * 4 + n_cand * 16; }
     void release() {
-        raw.release(); mask32.release(); vstart.release(); vfill.release(); pts.release(); scan_tmp.release();
+        raw.release(); mask32.release(); cstart.release(); cfill.release(); cpts.release(); scan_tmp.release();
     }
 };
 

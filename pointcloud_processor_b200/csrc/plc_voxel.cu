@@ -2,16 +2,16 @@
 //
 // Replaces the KD-tree builds of terrainCallback / zx120PointsCallback
 // (/root/reference/src/virtual_lidar.cpp:180-207).  Instead of a tree, points are counting-sorted
-// into a dense uniform grid of coarse voxels (edge h = power of two >= 2*query reach, so a query
-// ball touches at most 2x2x2 voxels), and a 4x4x4-per-voxel bitmask of fine voxels records where
-// a sample could possibly be within the radius of a point (conservative dilation).  Most samples
-// of a ray are resolved by one bit test; only flagged samples run the exact float32 test.
+// into a dense uniform grid: a 4x4x4-per-coarse-voxel bitmask of fine voxels records where a sample
+// could possibly be within the radius of a point (conservative dilation), and every mid voxel
+// (2x2x2 fine voxels) owns the list of points within reach of its box.  Most samples of a ray are
+// resolved by one bit test; only flagged samples run the exact float32 test, over one short list.
 //
 // Kernels (all HBM-bound, N = points, V = coarse voxels):
 //   k_extract   raw PointCloud2 bytes -> float4, drops non-finite, bbox           N*(step) rd, N*16 wr
-//   k_count     per-voxel histogram                                                N*16 rd, N atomics
-//   k_scan_*    exclusive scan of the histogram (3 passes)                         ~3*V*4
-//   k_scatter   points into voxel order                                            N*16 rd, N*16 wr
+//   k_candidates<false>  per-mid-voxel candidate counts                            N*16 rd, <=27 atomics/pt
+//   k_scan_*    exclusive scan of the counts (3 passes)                            ~3*8V*4
+//   k_candidates<true>   points into their candidate lists                         N*16 rd, <=27*16 wr/pt
 //   k_dilate    fine-voxel mask bits within reach of each point                    N*16 rd, <=125 atomicOr/pt
 #include <algorithm>
 #include <cmath>
@@ -103,30 +103,36 @@ k_extract(const unsigned char* __restrict__ data, unsigned long long n, unsigned
     }
 }
 
-__device__ __forceinline__ size_t coarse_voxel_of(const VoxelGeom& g, float x, float y, float z) {
-    int ix = clamp_i((int)fine_coord_f(x, g.ox, g.inv_g) >> 2, 0, g.dim_x - 1);
-    int iy = clamp_i((int)fine_coord_f(y, g.oy, g.inv_g) >> 2, 0, g.dim_y - 1);
-    int iz = clamp_i((int)fine_coord_f(z, g.oz, g.inv_g) >> 2, 0, g.dim_z - 1);
-    return ((size_t)iz * g.dim_y + iy) * g.dim_x + ix;
-}
-
+// Candidate lists: a point belongs to the list of every mid voxel (edge 2g) whose box lies within
+// `reach` of it (double arithmetic, same slack as the mask).  FILL == false counts, FILL == true
+// writes the point into its slots.  Up to 3x3x3 mid voxels per point.
+template <bool FILL>
 __global__ void __launch_bounds__(256)
-k_count(VoxelGeom g, const float4* __restrict__ raw, unsigned n, uint32_t* __restrict__ vcount) {
+k_candidates(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double msz,
+             uint32_t* __restrict__ ccount, const uint32_t* __restrict__ cstart, float4* __restrict__ cpts) {
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float4 p = raw[i];
-    atomicAdd(&vcount[coarse_voxel_of(g, p.x, p.y, p.z)], 1u);
-}
-
-__global__ void __launch_bounds__(256)
-k_scatter(VoxelGeom g, const float4* __restrict__ raw, unsigned n, const uint32_t* __restrict__ vstart,
-          uint32_t* __restrict__ vfill, float4* __restrict__ pts) {
-    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float4 p = raw[i];
-    size_t v = coarse_voxel_of(g, p.x, p.y, p.z);
-    uint32_t slot = vstart[v] + atomicAdd(&vfill[v], 1u);
-    pts[slot] = p;
+    double px = (double)p.x - (double)g.ox, py = (double)p.y - (double)g.oy, pz = (double)p.z - (double)g.oz;
+    int x0 = max(0, (int)floor((px - reach) / msz)), x1 = min(g.mdim_x - 1, (int)floor((px + reach) / msz));
+    int y0 = max(0, (int)floor((py - reach) / msz)), y1 = min(g.mdim_y - 1, (int)floor((py + reach) / msz));
+    int z0 = max(0, (int)floor((pz - reach) / msz)), z1 = min(g.mdim_z - 1, (int)floor((pz + reach) / msz));
+    double r2 = reach * reach;
+    for (int z = z0; z <= z1; ++z) {
+        double dz = fmax(0.0, fmax(z * msz - pz, pz - (z + 1) * msz));
+        for (int y = y0; y <= y1; ++y) {
+            double dy = fmax(0.0, fmax(y * msz - py, py - (y + 1) * msz));
+            double dyz = dy * dy + dz * dz;
+            if (dyz > r2) continue;
+            size_t row = ((size_t)z * g.mdim_y + y) * g.mdim_x;
+            for (int x = x0; x <= x1; ++x) {
+                double dx = fmax(0.0, fmax(x * msz - px, px - (x + 1) * msz));
+                if (dx * dx + dyz > r2) continue;
+                uint32_t k = atomicAdd(&ccount[row + x], 1u);
+                if (FILL) cpts[cstart[row + x] + k] = p;
+            }
+        }
+    }
 }
 
 // Sets the bit of every fine voxel whose box lies within `reach` of the point (double arithmetic;
@@ -138,9 +144,9 @@ k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, 
     if (i >= n) return;
     float4 p = raw[i];
     double px = (double)p.x - (double)g.ox, py = (double)p.y - (double)g.oy, pz = (double)p.z - (double)g.oz;
-    int x0 = max(0, (int)floor((px - reach) / gsz)), x1 = min(g.fdim_x - 1, (int)floor((px + reach) / gsz));
-    int y0 = max(0, (int)floor((py - reach) / gsz)), y1 = min(g.fdim_y - 1, (int)floor((py + reach) / gsz));
-    int z0 = max(0, (int)floor((pz - reach) / gsz)), z1 = min(g.fdim_z - 1, (int)floor((pz + reach) / gsz));
+    int x0 = max(0, (int)floor((px - reach) / gsz)), x1 = min(g.dim_x * 4 - 1, (int)floor((px + reach) / gsz));
+    int y0 = max(0, (int)floor((py - reach) / gsz)), y1 = min(g.dim_y * 4 - 1, (int)floor((py + reach) / gsz));
+    int z0 = max(0, (int)floor((pz - reach) / gsz)), z1 = min(g.dim_z * 4 - 1, (int)floor((pz + reach) / gsz));
     double r2 = reach * reach;
     for (int z = z0; z <= z1; ++z) {
         double dz = fmax(0.0, fmax(z * gsz - pz, pz - (z + 1) * gsz));
@@ -225,18 +231,18 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius) {
             dim[a] = (long long)std::floor(((double)ix.bbox[3 + a] - org[a]) / h) + 2;
             cells *= (double)dim[a];
         }
-        bool fits = cells <= 1.0e9 && dim[0] * 4 < (1 << 23) && dim[1] * 4 < (1 << 23) && dim[2] * 4 < (1 << 23);
+        bool fits = cells <= 2.5e8 && dim[0] * 4 < (1 << 23) && dim[1] * 4 < (1 << 23) && dim[2] * 4 < (1 << 23);
         if (fits) break;
-        h *= 2.0;    // still >= 2*reach, so the 2x2x2 bound keeps holding
+        h *= 2.0;    // coarser voxels only make the lists longer, never incomplete
     }
     const size_t n_vox = (size_t)dim[0] * dim[1] * dim[2];
+    const size_t n_mid = n_vox * 8;
     const unsigned n = (unsigned)ix.n_raw;
 
     PLC_CUDA_TRY(ctx, ix.mask32.reserve(n_vox * 8));
-    PLC_CUDA_TRY(ctx, ix.vstart.reserve((n_vox + 1) * 4));
-    PLC_CUDA_TRY(ctx, ix.vfill.reserve(n_vox * 4));
-    PLC_CUDA_TRY(ctx, ix.pts.reserve((size_t)n * sizeof(float4)));
-    PLC_CUDA_TRY(ctx, ix.scan_tmp.reserve(scan_tmp_bytes(n_vox + 1)));
+    PLC_CUDA_TRY(ctx, ix.cstart.reserve((n_mid + 1) * 4));
+    PLC_CUDA_TRY(ctx, ix.cfill.reserve(n_mid * 4));
+    PLC_CUDA_TRY(ctx, ix.scan_tmp.reserve(scan_tmp_bytes(n_mid + 1)));
 
     VoxelGeom g{};
     g.ox = (float)org[0];
@@ -244,33 +250,45 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius) {
     g.oz = (float)org[2];
     g.inv_g = (float)(4.0 / h);
     g.reach = (float)reach;
-    if ((double)g.reach < reach) g.reach = std::nextafterf(g.reach, 1e30f);
     g.dim_x = (int)dim[0];
     g.dim_y = (int)dim[1];
     g.dim_z = (int)dim[2];
-    g.fdim_x = g.dim_x * 4;
-    g.fdim_y = g.dim_y * 4;
-    g.fdim_z = g.dim_z * 4;
+    g.mdim_x = g.dim_x * 2;
+    g.mdim_y = g.dim_y * 2;
+    g.mdim_z = g.dim_z * 2;
+    g.fdim_xf = (float)(g.dim_x * 4);
+    g.fdim_yf = (float)(g.dim_y * 4);
+    g.fdim_zf = (float)(g.dim_z * 4);
     g.mask32 = ix.mask32.as<uint32_t>();
-    g.vstart = ix.vstart.as<uint32_t>();
-    g.pts = ix.pts.as<float4>();
-    g.n_pts = n;
+    g.cstart = ix.cstart.as<uint32_t>();
+    g.cpts = nullptr;
 
     cudaStream_t s = ctx->stream;
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.mask32.ptr, 0, n_vox * 8, s));
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.vstart.ptr, 0, (n_vox + 1) * 4, s));
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.vfill.ptr, 0, n_vox * 4, s));
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cstart.ptr, 0, (n_mid + 1) * 4, s));
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
     unsigned pb = (n + 255) / 256;
-    k_count<<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, ix.vstart.as<uint32_t>());
-    scan_exclusive_u32(ix.vstart.as<uint32_t>(), n_vox + 1, ix.scan_tmp.as<uint32_t>(), s);
-    k_scatter<<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, ix.vstart.as<uint32_t>(), ix.vfill.as<uint32_t>(),
-                                 ix.pts.as<float4>());
+    k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.cstart.as<uint32_t>(),
+                                           nullptr, nullptr);
+    scan_exclusive_u32(ix.cstart.as<uint32_t>(), n_mid + 1, ix.scan_tmp.as<uint32_t>(), s);
     k_dilate<<<(n + 127) / 128, 128, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 4.0, ix.mask32.as<uint32_t>());
-    ctx->launches += 6;
+    ctx->launches += 5;
+    PLC_CUDA_TRY(ctx, cudaGetLastError());
+    // total number of list entries decides the size of the candidate array
+    uint32_t* total = static_cast<uint32_t*>(ctx->pinned);
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(total, ix.cstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    const size_t n_cand = *total;
+    PLC_CUDA_TRY(ctx, ix.cpts.reserve(std::max<size_t>(n_cand, 1) * sizeof(float4)));
+    g.cpts = ix.cpts.as<float4>();
+    k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.cfill.as<uint32_t>(),
+                                          ix.cstart.as<uint32_t>(), ix.cpts.as<float4>());
+    ctx->launches += 1;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ix.geom = g;
     ix.h = h;
     ix.n_vox = n_vox;
+    ix.n_cand = n_cand;
     ix.built_radius = radius;
     return PLC_OK;
 }

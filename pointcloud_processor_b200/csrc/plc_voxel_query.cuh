@@ -4,6 +4,11 @@
 // indexed point p satisfy  d2_f32(q,p) < thr  with  d2 = ((dx*dx)+(dy*dy))+(dz*dz)  evaluated in
 // float32 without FMA (FLANN L2_Simple<float>, strict compare as RadiusResultSet does).
 //
+// Two levels, both addressed from the fine-voxel coordinate of q (edge g, a power of two):
+//   mask   one bit per fine voxel: 0 = no point within reach of the voxel's box (certainly clear)
+//   cand   per mid voxel (2x2x2 fine voxels): the points within reach of its box, stored
+//          contiguously (a point appears in up to 27 lists) — the exact test scans just that list
+//
 // Every translation unit that includes this header is compiled with -fmad=false, so `a*b+c`
 // below is two roundings, as on the reference's x86-64 build.
 #pragma once
@@ -20,60 +25,42 @@ __device__ __forceinline__ float dist2_f32(float qx, float qy, float qz, float p
 }
 
 // Fine-voxel coordinate along one axis; monotone non-decreasing in v (float sub, float mul by a
-// power of two, floor), which is what makes range lookups complete.
+// power of two, floor).  The builder's dilation slack covers its rounding error.
 __device__ __forceinline__ float fine_coord_f(float v, float origin, float inv_g) {
     return floorf(__fmul_rn(__fsub_rn(v, origin), inv_g));
 }
 
-// 1 if the fine voxel holding q is flagged (a point may be within the query radius), 0 if q is
-// certainly clear.  Outside the grid nothing is within reach (the grid has a one-voxel margin).
-__device__ __forceinline__ bool mask_flagged(const VoxelGeom& g, float qx, float qy, float qz) {
+__device__ __forceinline__ int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// Exact existence test over the candidate list of the mid voxel (ix>>1, iy>>1, iz>>1).
+__device__ __forceinline__ bool cand_any(const VoxelGeom& g, int ix, int iy, int iz, float qx, float qy,
+                                         float qz, float thr) {
+    size_t m = ((size_t)(iz >> 1) * g.mdim_y + (iy >> 1)) * g.mdim_x + (ix >> 1);
+    uint32_t s = __ldg(&g.cstart[m]), e = __ldg(&g.cstart[m + 1]);
+    const float4* __restrict__ pts = g.cpts;
+    for (; s < e; ++s) {
+        float4 p = __ldg(&pts[s]);
+        if (dist2_f32(qx, qy, qz, p.x, p.y, p.z) < thr) return true;
+    }
+    return false;
+}
+
+// Mask first; the exact test only where the fine voxel is flagged.  Outside the grid nothing is
+// within reach (the grid has a one-coarse-voxel margin around every point).
+__device__ __forceinline__ bool ball_any(const VoxelGeom& g, float qx, float qy, float qz, float thr,
+                                         unsigned long long* exact_counter) {
     float fx = fine_coord_f(qx, g.ox, g.inv_g), fy = fine_coord_f(qy, g.oy, g.inv_g),
           fz = fine_coord_f(qz, g.oz, g.inv_g);
     // NaN fails every comparison => treated as outside
-    if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < (float)g.fdim_x && fy < (float)g.fdim_y &&
-          fz < (float)g.fdim_z))
+    if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < g.fdim_xf && fy < g.fdim_yf && fz < g.fdim_zf))
         return false;
     int ix = (int)fx, iy = (int)fy, iz = (int)fz;
     size_t v = ((size_t)(iz >> 2) * g.dim_y + (iy >> 2)) * g.dim_x + (ix >> 2);
     uint32_t w = __ldg(&g.mask32[2 * v + ((iz >> 1) & 1)]);
     int bit = (ix & 3) | ((iy & 3) << 2) | ((iz & 1) << 4);
-    return (w >> bit) & 1u;
-}
-
-__device__ __forceinline__ int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
-
-// Exact existence test over the (at most 2x2x2) coarse voxels the query ball can touch.
-__device__ __forceinline__ bool exact_any(const VoxelGeom& g, float qx, float qy, float qz, float thr) {
-    float r = g.reach;
-    // coarse index = fine index >> 2 (h = 4g, same origin, power-of-two scale => exact)
-    float lx = fine_coord_f(__fsub_rn(qx, r), g.ox, g.inv_g), hx = fine_coord_f(__fadd_rn(qx, r), g.ox, g.inv_g);
-    float ly = fine_coord_f(__fsub_rn(qy, r), g.oy, g.inv_g), hy = fine_coord_f(__fadd_rn(qy, r), g.oy, g.inv_g);
-    float lz = fine_coord_f(__fsub_rn(qz, r), g.oz, g.inv_g), hz = fine_coord_f(__fadd_rn(qz, r), g.oz, g.inv_g);
-    if (!(hx >= 0.0f && hy >= 0.0f && hz >= 0.0f && lx < (float)g.fdim_x && ly < (float)g.fdim_y &&
-          lz < (float)g.fdim_z))
-        return false;
-    int x0 = clamp_i((int)fmaxf(lx, 0.0f) >> 2, 0, g.dim_x - 1), x1 = clamp_i((int)fminf(hx, (float)(g.fdim_x - 1)) >> 2, 0, g.dim_x - 1);
-    int y0 = clamp_i((int)fmaxf(ly, 0.0f) >> 2, 0, g.dim_y - 1), y1 = clamp_i((int)fminf(hy, (float)(g.fdim_y - 1)) >> 2, 0, g.dim_y - 1);
-    int z0 = clamp_i((int)fmaxf(lz, 0.0f) >> 2, 0, g.dim_z - 1), z1 = clamp_i((int)fminf(hz, (float)(g.fdim_z - 1)) >> 2, 0, g.dim_z - 1);
-    for (int z = z0; z <= z1; ++z)
-        for (int y = y0; y <= y1; ++y) {
-            size_t row = ((size_t)z * g.dim_y + y) * g.dim_x;
-            uint32_t s = __ldg(&g.vstart[row + x0]), e = __ldg(&g.vstart[row + x1 + 1]);
-            for (; s < e; ++s) {
-                float4 p = __ldg(&g.pts[s]);
-                if (dist2_f32(qx, qy, qz, p.x, p.y, p.z) < thr) return true;
-            }
-        }
-    return false;
-}
-
-// mask first, exact test only where flagged
-__device__ __forceinline__ bool ball_any(const VoxelGeom& g, float qx, float qy, float qz, float thr,
-                                         unsigned long long* exact_counter) {
-    if (!mask_flagged(g, qx, qy, qz)) return false;
+    if (!((w >> bit) & 1u)) return false;
     if (exact_counter) ++*exact_counter;
-    return exact_any(g, qx, qy, qz, thr);
+    return cand_any(g, ix, iy, iz, qx, qy, qz, thr);
 }
 
 }  // namespace plc
