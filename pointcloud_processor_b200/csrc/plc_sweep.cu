@@ -25,9 +25,11 @@ namespace plc {
 
 namespace {
 
-constexpr int kSweepThreads = 128;
-constexpr int kRaysPerThread = 8;
-constexpr int kTileCells = kSweepThreads * kRaysPerThread;
+constexpr int kSweepThreads = 128;       // k_fixed / k_flags: one thread per cell
+// k_sweep runs ONE warp per block (no block barrier, a finished warp frees its slot at once):
+// 32 lanes x 16 rays = 512 consecutive cells of one candidate per block.
+constexpr int kRaysPerThread = 16;
+constexpr int kTileCells = 32 * kRaysPerThread;
 
 struct SweepDev {
     VoxelGeom terrain, observed;
@@ -67,7 +69,17 @@ __device__ __forceinline__ double ray_length(double dx, double dy, double dz) {
 
 // isInFieldOfView, :703-714 (+ azimuth of virtual_lidar_memo.cpp:684-697 when enabled)
 __device__ __forceinline__ bool in_fov(const SweepDev& P, double pitch, double yaw, double dx, double dy, double dz) {
-    double elevation = atan2(dz, __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy))));
+    double hd = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    if (P.half_fov_h < 0.0) {
+        // The gate is almost never near its boundary: decide it with a float32 atan2 whose total
+        // error (input narrowing + atan2f) is < 1e-6 rad, and fall through to the double
+        // evaluation only inside a 1e-4 rad band around the limit.
+        float ef = atan2f((float)dz, (float)hd);
+        double gap = fabs((double)ef - pitch) - P.half_fov_v;
+        if (gap < -1e-4) return true;
+        if (gap > 1e-4) return false;
+    }
+    double elevation = atan2(dz, hd);
     bool ok = fabs(__dsub_rn(elevation, pitch)) <= P.half_fov_v;
     if (P.half_fov_h >= 0.0) {
         double az = atan2(dy, dx);
@@ -82,8 +94,11 @@ __device__ __forceinline__ double ray_score(const SweepDev& P, double dx, double
                                             float nx, float ny, float nz) {
     double bx = __ddiv_rn(dx, L), by = __ddiv_rn(dy, L), bz = __ddiv_rn(dz, L);
     double dot = __dadd_rn(__dadd_rn(__dmul_rn(bx, (double)nx), __dmul_rn(by, (double)ny)), __dmul_rn(bz, (double)nz));
-    double theta = acos(fmax(0.0, fmin(1.0, fabs(dot))));
-    double score = __dadd_rn(__dmul_rn(P.alpha, sin(__dsub_rn(M_PI / 2, theta))), __dmul_rn(P.beta, __ddiv_rn(1.0, L)));
+    // upstream: theta = acos(clamp(|dot|,0,1)); ALPHA*sin(pi/2 - theta) + BETA/L.  sin(pi/2 - acos(c))
+    // is c up to ~3e-16 absolute libm round-off, far inside the 1e-12 relative score tolerance
+    // (SURVEY §A.3 item 6), so the clamp is used directly.
+    double c = fmax(0.0, fmin(1.0, fabs(dot)));
+    double score = __dadd_rn(__dmul_rn(P.alpha, c), __dmul_rn(P.beta, __ddiv_rn(1.0, L)));
     return fmax(0.0, score);
 }
 
@@ -198,9 +213,10 @@ k_fixed(SweepDev P, plc_pose fixed, const plc_cell* __restrict__ cells, unsigned
 }
 
 // ---- K2+K3: one thread per (candidate, cell) ray ----------------------------------------------
-// grid.x = n_local * tiles; block b handles candidate b / tiles, cells [tile*1024, tile*1024+1024).
-// A warp's 32 lanes hold 32 consecutive cells, so one ballot is one word of the visibility mask.
-__global__ void __launch_bounds__(kSweepThreads)
+// grid.x = n_local * tiles, one warp per block; block b handles candidate b / tiles and cells
+// [tile*512, tile*512+512).  The 32 lanes hold 32 consecutive cells, so one ballot is one word of
+// the visibility mask.  Reductions are warp shuffles in a fixed order (deterministic totals).
+__global__ void __launch_bounds__(32, 32)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned tiles,
         const plc_cell* __restrict__ cells, unsigned n_cells, const double* __restrict__ fixed_scores,
         double* __restrict__ partial_score, int* __restrict__ partial_cov, uint32_t* __restrict__ mask,
@@ -211,10 +227,10 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, uns
     int covered = 0;
     unsigned gated = 0, nvis = 0;
     RayStats st;
-    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x;
 #pragma unroll 1
     for (int r = 0; r < kRaysPerThread; ++r) {
-        unsigned j = tile * kTileCells + r * kSweepThreads + threadIdx.x;
+        unsigned j = tile * kTileCells + r * 32 + lane;
         bool vis = false;
         if (j < n_cells) {
             plc_cell c = load_cell(cells, j);
@@ -231,11 +247,10 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, uns
         }
         if (mask) {
             unsigned word = __ballot_sync(0xffffffffu, vis);
-            unsigned w = (tile * kTileCells + r * kSweepThreads) / 32 + warp;
+            unsigned w = tile * kRaysPerThread + r;
             if (lane == 0 && w < mask_words) mask[(size_t)local * mask_words + w] = word;
         }
     }
-    // fixed-order reduction: lanes by shuffle tree, warps in index order
     unsigned long long smp = st.samples, ex = st.exact;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -246,33 +261,13 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, uns
         smp += __shfl_down_sync(0xffffffffu, smp, o);
         ex += __shfl_down_sync(0xffffffffu, ex, o);
     }
-    __shared__ double wtot[kSweepThreads / 32];
-    __shared__ int wcov[kSweepThreads / 32];
-    __shared__ unsigned long long wcnt[kSweepThreads / 32][4];
     if (lane == 0) {
-        wtot[warp] = total;
-        wcov[warp] = covered;
-        wcnt[warp][0] = gated;
-        wcnt[warp][1] = nvis;
-        wcnt[warp][2] = smp;
-        wcnt[warp][3] = ex;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double t = 0.0;
-        int cv = 0;
-        unsigned long long c4[4] = {0, 0, 0, 0};
-        for (int w = 0; w < kSweepThreads / 32; ++w) {
-            t = __dadd_rn(t, wtot[w]);
-            cv += wcov[w];
-            for (int k = 0; k < 4; ++k) c4[k] += wcnt[w][k];
-        }
-        partial_score[blockIdx.x] = t;
-        partial_cov[blockIdx.x] = cv;
-        if (c4[0]) atomicAdd(&res->rays_gated_in, c4[0]);
-        if (c4[1]) atomicAdd(&res->rays_visible, c4[1]);
-        if (c4[2]) atomicAdd(&res->samples, c4[2]);
-        if (c4[3]) atomicAdd(&res->exact_tests, c4[3]);
+        partial_score[blockIdx.x] = total;
+        partial_cov[blockIdx.x] = covered;
+        if (gated) atomicAdd(&res->rays_gated_in, (unsigned long long)gated);
+        if (nvis) atomicAdd(&res->rays_visible, (unsigned long long)nvis);
+        if (smp) atomicAdd(&res->samples, smp);
+        if (ex) atomicAdd(&res->exact_tests, ex);
     }
 }
 
@@ -531,7 +526,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     ctx->sweep_timed = false;
     if (n_local) {
         cudaEventRecord(ctx->ev_sweep_begin, s);
-        k_sweep<<<n_local * tiles, kSweepThreads, 0, s>>>(
+        k_sweep<<<n_local * tiles, 32, 0, s>>>(
             P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin, tiles, ctx->cells.as<plc_cell>(), M,
             ctx->fixed_scores.as<double>(), ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
             want_mask ? ctx->mask.as<uint32_t>() : nullptr, (unsigned)ctx->mask_words, res);
