@@ -107,6 +107,22 @@ enum : unsigned {
     kRangeVal = 1u, kFovSet = 2u, kFovVal = 4u, kVisSet = 8u, kVisVal = 16u
 };
 
+// evaluateCellScore for the mobile sensor, :656-701 with is_zx120 == false
+__device__ __forceinline__ double mobile_cell_score(const SweepDev& P, const plc_pose& s, const plc_cell& c,
+                                                    unsigned& outcome, RayStats& st) {
+    outcome = 0;
+    double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
+    double L = ray_length(dx, dy, dz);
+    if (!(L >= P.min_distance && L <= P.max_distance)) return 0.0;
+    outcome |= kRangeVal | kFovSet;
+    if (!in_fov(P, s.pitch, s.yaw, dx, dy, dz)) return 0.0;
+    outcome |= kFovVal | kVisSet;
+    bool vis = P.have_terrain ? ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st) : true;   // :727-728
+    if (!vis) return 0.0;
+    outcome |= kVisVal;
+    return ray_score(P, dx, dy, dz, L, c.nx, c.ny, c.nz);
+}
+
 // evaluateCellScore for the fixed sensor (is_zx120 == true), visibility per :716-752
 __device__ __forceinline__ double fixed_cell_score(const SweepDev& P, const plc_pose& s, const plc_cell& c,
                                                    unsigned& outcome, RayStats& st) {
@@ -200,131 +216,33 @@ k_fixed(SweepDev P, plc_pose fixed, const plc_cell* __restrict__ cells, unsigned
 // grid.x = n_local * tiles, one warp per block; block b handles candidate b / tiles and cells
 // [tile*512, tile*512+512).  The 32 lanes hold 32 consecutive cells, so one ballot is one word of
 // the visibility mask.  Reductions are warp shuffles in a fixed order (deterministic totals).
-//
-// The march only tests the occupancy bit of each sample.  Flagged samples (a few percent) are not
-// resolved in place — that would idle the other lanes for the length of a point list — but pushed
-// into a per-warp queue in shared memory and resolved 32 at a time, one queued sample per lane.
-// A ray keeps marching speculatively until its blocked sample is resolved; the outcome is the
-// same because "visible" only asks whether ANY sample is blocked, and the evaluated-sample
-// counter uses the first blocked index, exactly what the sequential reference loop would count.
-constexpr int kQueueCap = 64;
-
 __global__ void __launch_bounds__(32, 32)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned tiles,
         const plc_cell* __restrict__ cells, unsigned n_cells, const double* __restrict__ fixed_scores,
         double* __restrict__ partial_score, int* __restrict__ partial_cov, uint32_t* __restrict__ mask,
         unsigned mask_words, SweepResult* __restrict__ res) {
-    __shared__ float4 q_pos[kQueueCap];       // sample position; w = (lane << 16 | sample index) bits
-    __shared__ uint32_t q_mid[kQueueCap];     // mid voxel whose candidate list decides the sample
-    __shared__ int first_blocked[32];         // per ray of the current round: lowest blocked sample index
-
     unsigned local = blockIdx.x / tiles, tile = blockIdx.x - local * tiles;
-    const plc_pose s = cands[cand_begin + local];
-    const int lane = threadIdx.x;
-    const unsigned lt_mask = (1u << lane) - 1u;
+    plc_pose s = cands[cand_begin + local];
     double total = 0.0;
     int covered = 0;
     unsigned gated = 0, nvis = 0;
-    unsigned long long samples = 0, exact = 0;
-
-    // resolves queue entries [0, min(qn,32)) one per lane, then moves the rest to the front
-    auto drain = [&](int& qn) {
-        int take = qn < 32 ? qn : 32;
-        if (lane < take) {
-            float4 e = q_pos[lane];
-            unsigned tag = __float_as_uint(e.w);
-            int ray = (int)(tag >> 16), k = (int)(tag & 0xffffu);
-            if (first_blocked[ray] > k) {      // not already blocked earlier on the ray
-                ++exact;
-                if (cand_any_m(P.terrain, q_mid[lane], e.x, e.y, e.z, P.thr_block)) atomicMin(&first_blocked[ray], k);
-            }
-        }
-        __syncwarp();
-        int rest = qn - take;
-        float4 mv = make_float4(0.f, 0.f, 0.f, 0.f);
-        uint32_t mm = 0;
-        if (lane < rest) {
-            mv = q_pos[32 + lane];
-            mm = q_mid[32 + lane];
-        }
-        __syncwarp();
-        if (lane < rest) {
-            q_pos[lane] = mv;
-            q_mid[lane] = mm;
-        }
-        __syncwarp();
-        qn = rest;
-    };
-
+    RayStats st;
+    const int lane = threadIdx.x;
 #pragma unroll 1
     for (int r = 0; r < kRaysPerThread; ++r) {
         unsigned j = tile * kTileCells + r * 32 + lane;
-        // ---- evaluateCellScore gates (:656-678)
-        plc_cell c;
-        double dx = 0, dy = 0, dz = 0, L = 1.0;
-        bool pass = false;
-        if (j < n_cells) {
-            c = load_cell(cells, j);
-            dx = __dsub_rn(c.x, s.x);
-            dy = __dsub_rn(c.y, s.y);
-            dz = __dsub_rn(c.z, s.z);
-            L = ray_length(dx, dy, dz);
-            pass = (L >= P.min_distance && L <= P.max_distance) && in_fov(P, s.pitch, s.yaw, dx, dy, dz);
-        }
-        gated += pass ? 1u : 0u;
-        // ---- checkVisibilityWithRaycasting (:754-800), occupancy bits only
-        first_blocked[lane] = 0x7fffffff;
-        __syncwarp();
-        bool marching = pass && P.have_terrain;
-        double ux = 0, uy = 0, uz = 0, t = P.ray_start, end = 0;
-        if (marching) {
-            ux = __ddiv_rn(dx, L);
-            uy = __ddiv_rn(dy, L);
-            uz = __ddiv_rn(dz, L);
-            end = __dsub_rn(L, P.vis_radius);
-            marching = t < end;
-        }
-        int k = 0, qn = 0;
-        while (__any_sync(0xffffffffu, marching)) {
-            bool flagged = false;
-            float qx = 0.f, qy = 0.f, qz = 0.f;
-            int ix = 0, iy = 0, iz = 0;
-            if (marching) {
-                qx = (float)__dadd_rn(s.x, __dmul_rn(ux, t));
-                qy = (float)__dadd_rn(s.y, __dmul_rn(uy, t));
-                qz = (float)__dadd_rn(s.z, __dmul_rn(uz, t));
-                flagged = mask_lookup(P.terrain, qx, qy, qz, ix, iy, iz);
-            }
-            unsigned fl = __ballot_sync(0xffffffffu, flagged);
-            if (fl) {
-                if (flagged) {
-                    int slot = qn + __popc(fl & lt_mask);
-                    q_pos[slot] = make_float4(qx, qy, qz, __uint_as_float(((unsigned)lane << 16) | (unsigned)k));
-                    q_mid[slot] = mid_voxel_of(P.terrain, ix, iy, iz);
-                }
-                qn += __popc(fl);
-                __syncwarp();
-                if (qn >= 32) drain(qn);
-            }
-            if (marching) {
-                ++k;
-                t = __dadd_rn(t, P.ray_step);
-                marching = (t < end) && (first_blocked[lane] == 0x7fffffff) && (k < 0xffff);
-            }
-        }
-        while (qn > 0) drain(qn);
-        // ---- score (:680-700) and per-candidate accumulation (:639-644)
         bool vis = false;
         if (j < n_cells) {
-            int fb = first_blocked[lane];
-            vis = pass && fb == 0x7fffffff;
-            if (pass && P.have_terrain) samples += vis ? (unsigned)k : (unsigned)(fb + 1);
-            double mobile = vis ? ray_score(P, dx, dy, dz, L, c.nx, c.ny, c.nz) : 0.0;
-            double combined = fmax(__ldg(&fixed_scores[j]), mobile);
-            if (combined > 0) {
+            plc_cell c = load_cell(cells, j);
+            unsigned oc;
+            double mobile = mobile_cell_score(P, s, c, oc, st);
+            double combined = fmax(__ldg(&fixed_scores[j]), mobile);     // :639
+            if (combined > 0) {                                          // :641-644
                 ++covered;
                 total = __dadd_rn(total, combined);
             }
+            gated += (oc & kFovVal) ? 1u : 0u;
+            vis = (oc & kVisVal) != 0;
             nvis += vis ? 1u : 0u;
         }
         if (mask) {
@@ -332,24 +250,24 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, uns
             unsigned w = tile * kRaysPerThread + r;
             if (lane == 0 && w < mask_words) mask[(size_t)local * mask_words + w] = word;
         }
-        __syncwarp();
     }
+    unsigned long long smp = st.samples, ex = st.exact;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         total = __dadd_rn(total, __shfl_down_sync(0xffffffffu, total, o));
         covered += __shfl_down_sync(0xffffffffu, covered, o);
         gated += __shfl_down_sync(0xffffffffu, gated, o);
         nvis += __shfl_down_sync(0xffffffffu, nvis, o);
-        samples += __shfl_down_sync(0xffffffffu, samples, o);
-        exact += __shfl_down_sync(0xffffffffu, exact, o);
+        smp += __shfl_down_sync(0xffffffffu, smp, o);
+        ex += __shfl_down_sync(0xffffffffu, ex, o);
     }
     if (lane == 0) {
         partial_score[blockIdx.x] = total;
         partial_cov[blockIdx.x] = covered;
         if (gated) atomicAdd(&res->rays_gated_in, (unsigned long long)gated);
         if (nvis) atomicAdd(&res->rays_visible, (unsigned long long)nvis);
-        if (samples) atomicAdd(&res->samples, samples);
-        if (exact) atomicAdd(&res->exact_tests, exact);
+        if (smp) atomicAdd(&res->samples, smp);
+        if (ex) atomicAdd(&res->exact_tests, ex);
     }
 }
 
@@ -473,9 +391,8 @@ bool params_ok(const plc_params* p) {
         if (!std::isfinite(d)) return false;
     if (!(p->ray_step > 0) || !(p->vis_radius > 0) || !(p->block_radius_scale > 0) || !(p->observed_radius_scale > 0))
         return false;
-    // a ray may take at most this many samples (the sweep queue packs the sample index in 16 bits);
-    // refuse parameterisations beyond that
-    if ((p->max_distance - p->ray_start) / p->ray_step > 6.0e4) return false;
+    // a ray may take at most this many samples; refuse parameterisations that would spin
+    if ((p->max_distance - p->ray_start) / p->ray_step > 1.0e6) return false;
     return p->fixed_mode == 0 || p->fixed_mode == 1;
 }
 

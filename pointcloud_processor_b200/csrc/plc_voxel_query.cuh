@@ -33,53 +33,32 @@ __device__ __forceinline__ float fine_coord_f(float v, float origin, float inv_g
 __device__ __forceinline__ int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
 // Exact existence test over the candidate list of the mid voxel (ix>>1, iy>>1, iz>>1).
-// The next point is fetched before the current one is tested (the loop is latency bound).
-__device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int iy, int iz) {
-    return (uint32_t)(((size_t)(iz >> 1) * g.mdim_y + (iy >> 1)) * g.mdim_x + (ix >> 1));   // < 2^31 by construction
-}
-
-__device__ __forceinline__ bool cand_any_m(const VoxelGeom& g, uint32_t m, float qx, float qy, float qz, float thr) {
-    uint32_t s = __ldg(&g.cstart[m]), e = __ldg(&g.cstart[m + 1]);
-    if (s >= e) return false;
-    const float4* __restrict__ pts = g.cpts;
-    float4 p = __ldg(&pts[s]);
-    for (;;) {
-        ++s;
-        float4 nxt = p;
-        if (s < e) nxt = __ldg(&pts[s]);
-        if (dist2_f32(qx, qy, qz, p.x, p.y, p.z) < thr) return true;
-        if (s >= e) return false;
-        p = nxt;
-    }
-}
-
 __device__ __forceinline__ bool cand_any(const VoxelGeom& g, int ix, int iy, int iz, float qx, float qy,
                                          float qz, float thr) {
-    return cand_any_m(g, mid_voxel_of(g, ix, iy, iz), qx, qy, qz, thr);
-}
-
-// Fine-voxel coordinates of q and the mask bit; false when q is outside the grid or unflagged.
-__device__ __forceinline__ bool mask_lookup(const VoxelGeom& g, float qx, float qy, float qz, int& ix, int& iy,
-                                            int& iz) {
-    float fx = fine_coord_f(qx, g.ox, g.inv_g), fy = fine_coord_f(qy, g.oy, g.inv_g),
-          fz = fine_coord_f(qz, g.oz, g.inv_g);
-    if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < g.fdim_xf && fy < g.fdim_yf && fz < g.fdim_zf))
-        return false;
-    ix = (int)fx;
-    iy = (int)fy;
-    iz = (int)fz;
-    size_t v = ((size_t)(iz >> 2) * g.dim_y + (iy >> 2)) * g.dim_x + (ix >> 2);
-    uint32_t w = __ldg(&g.mask32[2 * v + ((iz >> 1) & 1)]);
-    int bit = (ix & 3) | ((iy & 3) << 2) | ((iz & 1) << 4);
-    return (w >> bit) & 1u;
+    size_t m = ((size_t)(iz >> 1) * g.mdim_y + (iy >> 1)) * g.mdim_x + (ix >> 1);
+    uint32_t s = __ldg(&g.cstart[m]), e = __ldg(&g.cstart[m + 1]);
+    const float4* __restrict__ pts = g.cpts;
+    for (; s < e; ++s) {
+        float4 p = __ldg(&pts[s]);
+        if (dist2_f32(qx, qy, qz, p.x, p.y, p.z) < thr) return true;
+    }
+    return false;
 }
 
 // Mask first; the exact test only where the fine voxel is flagged.  Outside the grid nothing is
 // within reach (the grid has a one-coarse-voxel margin around every point).
 __device__ __forceinline__ bool ball_any(const VoxelGeom& g, float qx, float qy, float qz, float thr,
                                          unsigned long long* exact_counter) {
-    int ix, iy, iz;
-    if (!mask_lookup(g, qx, qy, qz, ix, iy, iz)) return false;
+    float fx = fine_coord_f(qx, g.ox, g.inv_g), fy = fine_coord_f(qy, g.oy, g.inv_g),
+          fz = fine_coord_f(qz, g.oz, g.inv_g);
+    // NaN fails every comparison => treated as outside
+    if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < g.fdim_xf && fy < g.fdim_yf && fz < g.fdim_zf))
+        return false;
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    size_t v = ((size_t)(iz >> 2) * g.dim_y + (iy >> 2)) * g.dim_x + (ix >> 2);
+    uint32_t w = __ldg(&g.mask32[2 * v + ((iz >> 1) & 1)]);
+    int bit = (ix & 3) | ((iy & 3) << 2) | ((iz & 1) << 4);
+    if (!((w >> bit) & 1u)) return false;
     if (exact_counter) ++*exact_counter;
     return cand_any(g, ix, iy, iz, qx, qy, qz, thr);
 }
