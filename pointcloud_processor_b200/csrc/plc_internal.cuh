@@ -51,21 +51,33 @@ struct DevBuf {
 };
 
 // Geometry of a voxel index, passed to kernels by value.
-//   coarse voxel edge h (a power of two >= 2*reach), mid voxel h/2, fine voxel g = h/4, shared origin.
-//   mask32[2*v + ((fz>>1)&1)] bit ((fx&3) | (fy&3)<<2 | (fz&1)<<4): the fine voxel may hold a sample
-//   that the radius test accepts (conservative dilation of the points by the query reach).
-//   cstart[m] .. cstart[m+1]: candidate list of mid voxel m in cpts — every point within reach of
-//   the mid voxel's box (x fastest).  A sample in mid voxel m can only be blocked by those points.
+//   coarse voxel edge h (a power of two >= 2*reach), mid voxel h/2, fine voxel g = h/8, shared origin.
+//   coarse[v]  0: no point within reach of any position in the coarse voxel (certainly clear);
+//              else 1 + index of the voxel's brick.
+//   bricks[32*b + (fz&7)*4 + ((fy&7)>>1)], 2 bits per fine voxel at bit 2*(((fy&1)<<3) | (fx&7)):
+//              bit 0  a sample in the fine voxel MAY be within the radius of a point
+//                     (conservative dilation of the points by `reach`)
+//              bit 1  every sample in the fine voxel IS within the radius of one and the same point
+//                     (conservative erosion by `inner`), so no exact test is needed
+//   gstart[m] .. gstart[m+1]: candidate list of mid voxel m (x fastest), in groups of four points
+//   stored as x4,y4,z4 (cgrp[3*group + 0..2]); it holds every point within reach of the mid voxel's
+//   box, so a sample in mid voxel m can only be blocked by those points.  Pad slots are +inf.
+constexpr int kFineShift = 3;            // fine voxels per coarse voxel edge = 8
+constexpr int kFixedBits = 16;           // fractional bits of the fixed-point fine coordinate of the march
+
 struct VoxelGeom {
     float ox, oy, oz;        // origin (multiple of h, exactly representable)
     float inv_g;             // 1/g (power of two)
     float reach;             // real-number radius + slack used by the builder
     int dim_x, dim_y, dim_z; // coarse dims
     int mdim_x, mdim_y, mdim_z;   // mid dims = 2*coarse
-    float fdim_xf, fdim_yf, fdim_zf;   // fine dims = 4*coarse, as float for the bounds test
-    const uint32_t* __restrict__ mask32;
-    const uint32_t* __restrict__ cstart;
-    const float4* __restrict__ cpts;
+    float fdim_xf, fdim_yf, fdim_zf;   // fine dims = 8*coarse, as float for the bounds test
+    float clip_lo[3], clip_hi[3];      // box outside which no position is within reach of a point
+    float clip_t;                      // slack (m along the ray) the clipped sample range may overshoot by
+    const uint32_t* __restrict__ coarse;
+    const uint32_t* __restrict__ bricks;
+    const uint32_t* __restrict__ gstart;
+    const float4* __restrict__ cgrp;
 };
 
 struct VoxelIndex {
@@ -76,15 +88,22 @@ struct VoxelIndex {
     float bbox[6] = {0, 0, 0, 0, 0, 0};   // min xyz, max xyz of finite points
     // built index
     double built_radius = -1.0;   // query radius (m) the structure was built for
+    float built_thr = 0.0f;       // float32 squared-distance threshold of the "certain" bit
+    double built_march_err = 0.0; // position error (fine voxels) of the fixed-point march covered by the slack
     double h = 0.0;
-    DevBuf mask32, cstart, cfill, cpts, scan_tmp;
+    DevBuf coarse, bricks, gstart, cfill, cgrp, scan_tmp;
     VoxelGeom geom{};
     uint64_t n_vox = 0;       // coarse voxels
-    uint64_t n_cand = 0;      // entries in cpts
+    uint64_t n_bricks = 0;    // coarse voxels with a brick
+    uint64_t n_groups = 0;    // 4-point groups in cgrp
     bool has_points() const { return n_raw > 0; }
-    uint64_t bytes() const { return n_vox * 8 + (n_vox * 8 + 1) * 4 + n_cand * 16; }
+    // compact size of the structure (points once + occupancy), the "G" term of the algorithmic bytes
+    uint64_t bytes() const { return n_raw * 16 + n_vox * 4 + n_bricks * 128; }
+    // what is actually resident (candidate lists replicate a point into every mid voxel in reach)
+    uint64_t resident_bytes() const { return n_vox * 4 + n_bricks * 128 + (n_vox * 8 + 1) * 4 + n_groups * 48; }
     void release() {
-        raw.release(); mask32.release(); cstart.release(); cfill.release(); cpts.release(); scan_tmp.release();
+        raw.release(); coarse.release(); bricks.release(); gstart.release(); cfill.release(); cgrp.release();
+        scan_tmp.release();
     }
 };
 
@@ -117,6 +136,10 @@ struct plc_ctx {
     bool ran = false, ran_mask = false, ran_flags = false;
     plc::DevBuf partial_score, partial_cov;   // per (candidate, tile)
     plc::DevBuf scores, covered, mask;
+    plc::DevBuf pose_aux;        // per local candidate: FOV gate constants (plc_sweep.cu PoseAux)
+    plc::DevBuf s_tab;           // double[n_tab]: sample parameters s_k of the upstream ray loop
+    int n_tab = 0;
+    double tab_start = 0, tab_step = 0, tab_max = 0;
     plc::DevBuf result;          // SweepResult
     uint64_t mask_words = 0;
     int tiles = 0;
@@ -154,7 +177,10 @@ struct SweepResult {
 };
 
 plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* cloud);
-plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius);
+// Builds (or keeps) the index for `radius`.  thr: float32 squared-distance threshold of the exact test
+// (normally (float)(radius*radius)); march_err: position error of the caller's fixed-point march in
+// fine-voxel units, folded into the conservative slack.
+plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err);
 
 inline bool cloud_view_ok(const plc_cloud_view* v) {
     if (!v) return false;

@@ -27,8 +27,8 @@ namespace {
 
 constexpr int kSweepThreads = 128;       // k_fixed / k_flags: one thread per cell
 // k_sweep runs ONE warp per block (no block barrier, a finished warp frees its slot at once):
-// 32 lanes x 16 rays = 512 consecutive cells of one candidate per block.
-constexpr int kRaysPerThread = 16;
+// 32 lanes x 8 rays = 256 consecutive cells of one candidate per block.
+constexpr int kRaysPerThread = 8;
 constexpr int kTileCells = 32 * kRaysPerThread;
 
 struct SweepDev {
@@ -39,6 +39,10 @@ struct SweepDev {
     double half_fov_v, half_fov_h;   // half_fov_h < 0: no azimuth test
     double alpha, beta;
     int fixed_mode;
+    // k_sweep: the upstream sample parameters s_k (s_0 = ray_start, s_{k+1} = s_k + ray_step in double)
+    const double* __restrict__ s_tab;
+    int n_tab;
+    double inv_step;
 };
 
 struct RayStats {
@@ -67,18 +71,9 @@ __device__ __forceinline__ double ray_length(double dx, double dy, double dz) {
     return __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
 }
 
-// isInFieldOfView, :703-714 (+ azimuth of virtual_lidar_memo.cpp:684-697 when enabled)
-__device__ __forceinline__ bool in_fov(const SweepDev& P, double pitch, double yaw, double dx, double dy, double dz) {
+// isInFieldOfView, :703-714 (+ azimuth of virtual_lidar_memo.cpp:684-697 when enabled), as written upstream
+__device__ __noinline__ bool in_fov_exact(const SweepDev& P, double pitch, double yaw, double dx, double dy, double dz) {
     double hd = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-    if (P.half_fov_h < 0.0) {
-        // The gate is almost never near its boundary: decide it with a float32 atan2 whose total
-        // error (input narrowing + atan2f) is < 1e-6 rad, and fall through to the double
-        // evaluation only inside a 1e-4 rad band around the limit.
-        float ef = atan2f((float)dz, (float)hd);
-        double gap = fabs((double)ef - pitch) - P.half_fov_v;
-        if (gap < -1e-4) return true;
-        if (gap > 1e-4) return false;
-    }
     double elevation = atan2(dz, hd);
     bool ok = fabs(__dsub_rn(elevation, pitch)) <= P.half_fov_v;
     if (P.half_fov_h >= 0.0) {
@@ -89,10 +84,22 @@ __device__ __forceinline__ bool in_fov(const SweepDev& P, double pitch, double y
     return ok;
 }
 
-// incidence + range score, :689-700
-__device__ __forceinline__ double ray_score(const SweepDev& P, double dx, double dy, double dz, double L,
-                                            float nx, float ny, float nz) {
-    double bx = __ddiv_rn(dx, L), by = __ddiv_rn(dy, L), bz = __ddiv_rn(dz, L);
+// Same gate for the once-per-sweep kernels (k_fixed, k_flags): a float32 atan2 whose total error
+// is < 1e-6 rad decides it outside a 1e-4 rad band around the limit.
+__device__ __forceinline__ bool in_fov(const SweepDev& P, double pitch, double yaw, double dx, double dy, double dz) {
+    if (P.half_fov_h < 0.0) {
+        double hd = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+        float ef = atan2f((float)dz, (float)hd);
+        double gap = fabs((double)ef - pitch) - P.half_fov_v;
+        if (gap < -1e-4) return true;
+        if (gap > 1e-4) return false;
+    }
+    return in_fov_exact(P, pitch, yaw, dx, dy, dz);
+}
+
+// incidence + range score, :689-700, from the unit beam direction b = d / L
+__device__ __forceinline__ double unit_score(const SweepDev& P, double bx, double by, double bz, double L,
+                                             float nx, float ny, float nz) {
     double dot = __dadd_rn(__dadd_rn(__dmul_rn(bx, (double)nx), __dmul_rn(by, (double)ny)), __dmul_rn(bz, (double)nz));
     // upstream: theta = acos(clamp(|dot|,0,1)); ALPHA*sin(pi/2 - theta) + BETA/L.  sin(pi/2 - acos(c))
     // is c up to ~3e-16 absolute libm round-off, far inside the 1e-12 relative score tolerance
@@ -102,26 +109,15 @@ __device__ __forceinline__ double ray_score(const SweepDev& P, double dx, double
     return fmax(0.0, score);
 }
 
+__device__ __forceinline__ double ray_score(const SweepDev& P, double dx, double dy, double dz, double L,
+                                            float nx, float ny, float nz) {
+    return unit_score(P, __ddiv_rn(dx, L), __ddiv_rn(dy, L), __ddiv_rn(dz, L), L, nx, ny, nz);
+}
+
 // Outcome bits of one evaluateCellScore call (which assignments the reference performed and their values)
 enum : unsigned {
     kRangeVal = 1u, kFovSet = 2u, kFovVal = 4u, kVisSet = 8u, kVisVal = 16u
 };
-
-// evaluateCellScore for the mobile sensor, :656-701 with is_zx120 == false
-__device__ __forceinline__ double mobile_cell_score(const SweepDev& P, const plc_pose& s, const plc_cell& c,
-                                                    unsigned& outcome, RayStats& st) {
-    outcome = 0;
-    double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
-    double L = ray_length(dx, dy, dz);
-    if (!(L >= P.min_distance && L <= P.max_distance)) return 0.0;
-    outcome |= kRangeVal | kFovSet;
-    if (!in_fov(P, s.pitch, s.yaw, dx, dy, dz)) return 0.0;
-    outcome |= kFovVal | kVisSet;
-    bool vis = P.have_terrain ? ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st) : true;   // :727-728
-    if (!vis) return 0.0;
-    outcome |= kVisVal;
-    return ray_score(P, dx, dy, dz, L, c.nx, c.ny, c.nz);
-}
 
 // evaluateCellScore for the fixed sensor (is_zx120 == true), visibility per :716-752
 __device__ __forceinline__ double fixed_cell_score(const SweepDev& P, const plc_pose& s, const plc_cell& c,
@@ -212,62 +208,297 @@ k_fixed(SweepDev P, plc_pose fixed, const plc_cell* __restrict__ cells, unsigned
     }
 }
 
+// ---- per-pose constants of the FOV gate -------------------------------------------------------
+// The elevation of a target lies in [-pi/2, pi/2], so |elevation - pitch| <= half_fov is the
+// interval test  e_lo <= elevation <= e_hi  with e_lo = max(-pi/2, pitch - half_fov) and
+// e_hi = min(pi/2, pitch + half_fov).  Both differences elevation - e_lo and e_hi - elevation stay
+// inside [-pi, pi], where the sign of the sine decides them:
+//   sin(elevation - e_lo) * L = dz*cos(e_lo) - hd*sin(e_lo),   sin(e_hi - elevation) * L = hd*sin(e_hi) - dz*cos(e_hi)
+// k_sweep evaluates these in float32 and only falls back to the reference's double atan2 inside a
+// band around zero that is far wider than the float error.
+struct PoseAux {
+    float c_lo, s_lo, c_hi, s_hi;
+    int fast;        // 0: always take the exact path for this pose
+    int pad[3];
+};
+
+__global__ void __launch_bounds__(128)
+k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned n_local,
+            PoseAux* __restrict__ aux) {
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_local) return;
+    double pitch = cands[cand_begin + i].pitch;
+    PoseAux a{};
+    double lo = pitch - P.half_fov_v, hi = pitch + P.half_fov_v;
+    a.fast = (P.half_fov_h < 0.0 && isfinite(pitch) && lo <= M_PI_2 && hi >= -M_PI_2) ? 1 : 0;
+    double e_lo = fmax(-M_PI_2, lo), e_hi = fmin(M_PI_2, hi);
+    a.c_lo = (float)cos(e_lo);
+    a.s_lo = (float)sin(e_lo);
+    a.c_hi = (float)cos(e_hi);
+    a.s_hi = (float)sin(e_hi);
+    aux[i] = a;
+}
+
 // ---- K2+K3: one thread per (candidate, cell) ray ----------------------------------------------
 // grid.x = n_local * tiles, one warp per block; block b handles candidate b / tiles and cells
-// [tile*512, tile*512+512).  The 32 lanes hold 32 consecutive cells, so one ballot is one word of
+// [tile*256, tile*256+256).  The 32 lanes hold 32 consecutive cells, so one ballot is one word of
 // the visibility mask.  Reductions are warp shuffles in a fixed order (deterministic totals).
-__global__ void __launch_bounds__(32, 32)
-k_sweep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned tiles,
-        const plc_cell* __restrict__ cells, unsigned n_cells, const double* __restrict__ fixed_scores,
-        double* __restrict__ partial_score, int* __restrict__ partial_cov, uint32_t* __restrict__ mask,
-        unsigned mask_words, SweepResult* __restrict__ res) {
+//
+// How a ray is marched (checkVisibilityWithRaycasting, :754-800):
+//   1. setup in double exactly as upstream: d, L, unit direction u = d / L, end = L - vis_radius; the number of
+//      samples n = #{k : s_k < end} comes from the table of the upstream accumulation s_0 = start, s_{k+1} = s_k + step.
+//   2. the sample range is clipped to the box that holds everything within reach of a terrain point
+//      (samples outside are clear by construction), conservatively, in float32.
+//   3. inside the clipped range the sample position is tracked in 16.16 fixed point in fine-voxel
+//      units (three integer adds per step).  Its error against the upstream double position is a
+//      few 1e-6 m and is covered by the slack of the occupancy structure (plc_voxel.cu), so
+//      "clear" and "certainly blocked" voxel states decide the sample without the exact position.
+//   4. a sample in an uncertain voxel needs the exact float32 test on the exact upstream position
+//      (double -> float32 narrowing, :774-777).  Doing that in place would idle the other 31 lanes
+//      for the length of a point list, so the sample is pushed into a per-warp queue in shared
+//      memory and the ray keeps marching; the queue is drained 32 samples at a time, one per lane.
+//      A ray's outcome (first blocked sample index, or none) is settled when the block's rays are
+//      finalised, after the last drain.
+// The visibility bit is the upstream one bit for bit; the evaluated-sample counter is the index
+// of the first blocked sample + 1, which is what the sequential upstream loop would have counted.
+constexpr int kQueueCap = 64;                    // ring buffer, power of two, >= 2 * 32
+constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not blocked (so far), low bits = n
+
+__global__ void __launch_bounds__(32, 24)
+k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin,
+        unsigned tiles, const plc_cell* __restrict__ cells, unsigned n_cells,
+        const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
+        int* __restrict__ partial_cov, uint32_t* __restrict__ mask, unsigned mask_words,
+        SweepResult* __restrict__ res) {
+    __shared__ float4 q_pos[kQueueCap];          // exact sample position; w = (ray slot << 16 | sample index) bits
+    __shared__ uint32_t q_mid[kQueueCap];        // mid voxel whose candidate list decides the sample
+    __shared__ int ray_state[kTileCells];        // first blocked sample index, or kOpen + n
+    __shared__ double ray_score_if_visible[kTileCells];
+
+    const unsigned FULL = 0xffffffffu;
     unsigned local = blockIdx.x / tiles, tile = blockIdx.x - local * tiles;
-    plc_pose s = cands[cand_begin + local];
-    double total = 0.0;
-    int covered = 0;
-    unsigned gated = 0, nvis = 0;
-    RayStats st;
+    const plc_pose s = cands[cand_begin + local];
+    const PoseAux A = aux[local];
+    const VoxelGeom& G = P.terrain;
     const int lane = threadIdx.x;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const float sxf = (float)s.x, syf = (float)s.y, szf = (float)s.z;
+    const double fscale = (double)G.inv_g * 65536.0;
+    unsigned gated = 0;
+    unsigned long long exact = 0;
+    int q_head = 0, q_n = 0;
+
+    // resolves up to 32 queued samples, one per lane
+    auto drain = [&]() {
+        int take = q_n < 32 ? q_n : 32;
+        if (lane < take) {
+            int at = (q_head + lane) & (kQueueCap - 1);
+            float4 e = q_pos[at];
+            unsigned tag = __float_as_uint(e.w);
+            int slot = (int)(tag >> 16), k = (int)(tag & 0xffffu);
+            if (ray_state[slot] > k) {               // not already blocked earlier on the ray
+                ++exact;
+                if (cand_any_m(G, q_mid[at], e.x, e.y, e.z, P.thr_block)) atomicMin(&ray_state[slot], k);
+            }
+        }
+        __syncwarp();
+        q_head = (q_head + take) & (kQueueCap - 1);
+        q_n -= take;
+    };
+
 #pragma unroll 1
     for (int r = 0; r < kRaysPerThread; ++r) {
-        unsigned j = tile * kTileCells + r * 32 + lane;
-        bool vis = false;
+        const int slot = r * 32 + lane;
+        unsigned j = tile * kTileCells + slot;
+        const bool valid = j < n_cells;
+        // ---- evaluateCellScore gates (:656-678)
+        plc_cell c = load_cell(cells, valid ? j : 0);
+        double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
+        double L = ray_length(dx, dy, dz);
+        bool pass = valid && (L >= P.min_distance && L <= P.max_distance);
+        if (pass) {
+            bool decided = false;
+            if (A.fast) {
+                float dzf = (float)dz, Lf = (float)L;
+                float hd = sqrtf(fmaxf(0.f, (float)__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy))));
+                float a = dzf * A.c_lo - hd * A.s_lo, b = hd * A.s_hi - dzf * A.c_hi;
+                float tol = 2e-5f * Lf;
+                if (a > tol && b > tol) decided = true;
+                else if (a < -tol || b < -tol) { decided = true; pass = false; }
+            }
+            if (!decided) pass = in_fov_exact(P, s.pitch, s.yaw, dx, dy, dz);
+        }
+        gated += pass ? 1u : 0u;
+
+        // ---- checkVisibilityWithRaycasting (:754-800)
+        double ux = 0, uy = 0, uz = 0;
+        int n = 0, k = 0, k_hi = 0, blocked_k = -1, pend_k = -1;
+        int fx = 0, fy = 0, fz = 0, dfx = 0, dfy = 0, dfz = 0;
+        if (pass) {
+            ux = __ddiv_rn(dx, L);
+            uy = __ddiv_rn(dy, L);
+            uz = __ddiv_rn(dz, L);
+        }
+        if (pass && P.have_terrain) {
+            double end = __dsub_rn(L, P.vis_radius);
+            // n = #{k : s_k < end}
+            if (end > P.ray_start) {
+                n = (int)(__dsub_rn(end, P.ray_start) * P.inv_step) + 1;
+                n = max(0, min(n, P.n_tab - 1));
+                while (n > 0 && !(__ldg(&P.s_tab[n - 1]) < end)) --n;
+                while (n < P.n_tab - 1 && __ldg(&P.s_tab[n]) < end) ++n;
+            }
+            // clip [0, n) against the reach box (float32, conservative by clip_t metres)
+            float uf[3] = {(float)ux, (float)uy, (float)uz};
+            float sf[3] = {sxf, syf, szf};
+            float t_in = 0.f, t_out = 3.0e38f;
+            bool miss = false;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                if (fabsf(uf[a]) > 1e-12f) {
+                    float inv = __fdividef(1.0f, uf[a]);
+                    float t0 = (G.clip_lo[a] - sf[a]) * inv, t1 = (G.clip_hi[a] - sf[a]) * inv;
+                    t_in = fmaxf(t_in, fminf(t0, t1));
+                    t_out = fminf(t_out, fmaxf(t0, t1));
+                } else if (sf[a] < G.clip_lo[a] || sf[a] > G.clip_hi[a]) {
+                    miss = true;
+                }
+            }
+            const float startf = (float)P.ray_start, inv_stepf = (float)P.inv_step;
+            float klo_f = ceilf((t_in - G.clip_t - startf) * inv_stepf);
+            float khi_f = floorf((t_out + G.clip_t - startf) * inv_stepf) + 1.0f;
+            k = (int)fminf(fmaxf(klo_f, 0.f), (float)n);
+            k_hi = miss ? k : (int)fminf(fmaxf(khi_f, 0.f), (float)n);
+            if (k < k_hi) {
+                // fixed-point fine-voxel coordinate of sample k and its per-step increment
+                double t0 = __ldg(&P.s_tab[k]);
+                fx = __double2int_rd(((s.x + ux * t0) - (double)G.ox) * fscale);
+                fy = __double2int_rd(((s.y + uy * t0) - (double)G.oy) * fscale);
+                fz = __double2int_rd(((s.z + uz * t0) - (double)G.oz) * fscale);
+                dfx = __double2int_rn(ux * P.ray_step * fscale);
+                dfy = __double2int_rn(uy * P.ray_step * fscale);
+                dfz = __double2int_rn(uz * P.ray_step * fscale);
+                // both ends of the clipped range must lie inside the grid (they do by construction;
+                // a ray that somehow does not is marched sample by sample with bounds-checked lookups)
+                const long long steps = k_hi - 1 - k;
+                const long long lx = fx + steps * dfx, ly = fy + steps * dfy, lz = fz + steps * dfz;
+                const long long mx = (long long)G.dim_x << (kFineShift + kFixedBits),
+                                my = (long long)G.dim_y << (kFineShift + kFixedBits),
+                                mz = (long long)G.dim_z << (kFineShift + kFixedBits);
+                if (fx < 0 || fy < 0 || fz < 0 || fx >= mx || fy >= my || fz >= mz || lx < 0 || ly < 0 || lz < 0 ||
+                    lx >= mx || ly >= my || lz >= mz) {
+                    RayStats st;
+                    bool clear = ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st);
+                    blocked_k = clear ? -1 : (int)st.samples - 1;
+                    exact += st.exact;
+                    k = k_hi = 0;
+                }
+            }
+        }
+        // the ray's state is published before any of its samples can be queued
+        ray_state[slot] = blocked_k >= 0 ? blocked_k : kOpen + n;
+        bool active = k < k_hi;
+        bool stalled = false;
+        for (;;) {
+            while (__any_sync(FULL, active)) {
+                if (active) {
+                    int ix = fx >> kFixedBits, iy = fy >> kFixedBits, iz = fz >> kFixedBits;
+                    unsigned st = voxel_state(G, ix, iy, iz);
+                    if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
+                        blocked_k = k;
+                        active = false;
+                    } else if (st == 1u && pend_k >= 0) { // a second uncertain sample: queue the first one first
+                        stalled = true;
+                        active = false;
+                    } else {
+                        if (st == 1u) pend_k = k;
+                        ++k;
+                        fx += dfx;
+                        fy += dfy;
+                        fz += dfz;
+                        active = k < k_hi;
+                    }
+                }
+            }
+            // queue the parked samples: exact upstream position, and the mid voxel the march saw
+            // (its list holds every point within reach of the voxel's box, and the exact position
+            // lies inside that box up to the slack)
+            bool need = pend_k >= 0;
+            unsigned nb = __ballot_sync(FULL, need);
+            if (nb == 0) break;
+            if (q_n + __popc(nb) > kQueueCap) drain();
+            if (need) {
+                double t = __ldg(&P.s_tab[pend_k]);
+                float qx = (float)__dadd_rn(s.x, __dmul_rn(ux, t));
+                float qy = (float)__dadd_rn(s.y, __dmul_rn(uy, t));
+                float qz = (float)__dadd_rn(s.z, __dmul_rn(uz, t));
+                int back = k - pend_k;
+                int px = fx - back * dfx, py = fy - back * dfy, pz = fz - back * dfz;
+                int at = (q_head + q_n + __popc(nb & lt_mask)) & (kQueueCap - 1);
+                q_pos[at] = make_float4(qx, qy, qz, __uint_as_float(((unsigned)slot << 16) | (unsigned)pend_k));
+                q_mid[at] = mid_voxel_of(G, px >> kFixedBits, py >> kFixedBits, pz >> kFixedBits);
+                pend_k = -1;
+                if (stalled) {
+                    stalled = false;
+                    active = true;                        // re-examines sample k, which parks it
+                }
+            }
+            q_n += __popc(nb);
+            __syncwarp();
+            if (!__any_sync(FULL, active)) break;
+        }
+        if (blocked_k >= 0) atomicMin(&ray_state[slot], blocked_k);
+        else if (pass) ray_score_if_visible[slot] = unit_score(P, ux, uy, uz, L, c.nx, c.ny, c.nz);
+        // incidence + range score (:689-700), used only if the ray turns out visible
+        if (!pass) ray_state[slot] = -1;                         // gated out: blocked "before the first sample"
+        __syncwarp();
+        if (q_n >= 32) drain();
+    }
+    while (q_n > 0) drain();
+
+    // ---- per-candidate accumulation (:639-644), rays in cell order
+    double total = 0.0;
+    int covered = 0;
+    unsigned nvis = 0;
+    unsigned long long samples = 0;
+#pragma unroll 1
+    for (int r = 0; r < kRaysPerThread; ++r) {
+        const int slot = r * 32 + lane;
+        unsigned j = tile * kTileCells + slot;
+        int st = ray_state[slot];
+        bool vis = st >= kOpen;
+        if (st >= 0 && P.have_terrain) samples += (unsigned)(vis ? st - kOpen : st + 1);
         if (j < n_cells) {
-            plc_cell c = load_cell(cells, j);
-            unsigned oc;
-            double mobile = mobile_cell_score(P, s, c, oc, st);
+            double mobile = vis ? ray_score_if_visible[slot] : 0.0;
             double combined = fmax(__ldg(&fixed_scores[j]), mobile);     // :639
             if (combined > 0) {                                          // :641-644
                 ++covered;
                 total = __dadd_rn(total, combined);
             }
-            gated += (oc & kFovVal) ? 1u : 0u;
-            vis = (oc & kVisVal) != 0;
             nvis += vis ? 1u : 0u;
         }
         if (mask) {
-            unsigned word = __ballot_sync(0xffffffffu, vis);
+            unsigned word = __ballot_sync(FULL, vis);
             unsigned w = tile * kRaysPerThread + r;
             if (lane == 0 && w < mask_words) mask[(size_t)local * mask_words + w] = word;
         }
     }
-    unsigned long long smp = st.samples, ex = st.exact;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        total = __dadd_rn(total, __shfl_down_sync(0xffffffffu, total, o));
-        covered += __shfl_down_sync(0xffffffffu, covered, o);
-        gated += __shfl_down_sync(0xffffffffu, gated, o);
-        nvis += __shfl_down_sync(0xffffffffu, nvis, o);
-        smp += __shfl_down_sync(0xffffffffu, smp, o);
-        ex += __shfl_down_sync(0xffffffffu, ex, o);
+        total = __dadd_rn(total, __shfl_down_sync(FULL, total, o));
+        covered += __shfl_down_sync(FULL, covered, o);
+        gated += __shfl_down_sync(FULL, gated, o);
+        nvis += __shfl_down_sync(FULL, nvis, o);
+        samples += __shfl_down_sync(FULL, samples, o);
+        exact += __shfl_down_sync(FULL, exact, o);
     }
     if (lane == 0) {
         partial_score[blockIdx.x] = total;
         partial_cov[blockIdx.x] = covered;
         if (gated) atomicAdd(&res->rays_gated_in, (unsigned long long)gated);
         if (nvis) atomicAdd(&res->rays_visible, (unsigned long long)nvis);
-        if (smp) atomicAdd(&res->samples, smp);
-        if (ex) atomicAdd(&res->exact_tests, ex);
+        if (samples) atomicAdd(&res->samples, samples);
+        if (exact) atomicAdd(&res->exact_tests, exact);
     }
 }
 
@@ -392,7 +623,7 @@ bool params_ok(const plc_params* p) {
     if (!(p->ray_step > 0) || !(p->vis_radius > 0) || !(p->block_radius_scale > 0) || !(p->observed_radius_scale > 0))
         return false;
     // a ray may take at most this many samples; refuse parameterisations that would spin
-    if ((p->max_distance - p->ray_start) / p->ray_step > 1.0e6) return false;
+    if ((p->max_distance - p->ray_start) / p->ray_step > 6.0e4) return false;
     return p->fixed_mode == 0 || p->fixed_mode == 1;
 }
 
@@ -400,6 +631,55 @@ float ceil_to_float(double v) {
     float f = static_cast<float>(v);
     if (static_cast<double>(f) < v) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
     return f;
+}
+
+// blocked iff a point has d2 < (float)(r*r) and (double)d2 < vis_radius*0.5 (:782-790)
+float block_threshold(const plc_params* p) {
+    const double r = p->vis_radius * p->block_radius_scale;             // :782
+    return fminf(static_cast<float>(r * r), ceil_to_float(p->vis_radius * 0.5));
+}
+float observed_threshold(const plc_params* p) {
+    const double r = p->vis_radius * p->observed_radius_scale;          // :743
+    return static_cast<float>(r * r);
+}
+
+// number of sample parameters a ray in range can reach, plus the first one at or beyond max_distance
+size_t sample_table_size(const plc_params* p) {
+    size_t n = 1;
+    for (double s = p->ray_start; s < p->max_distance; s += p->ray_step) ++n;    // same accumulation as :765-796
+    return n;
+}
+
+plc_status build_terrain_index(plc_ctx* ctx, const plc_params* p) {
+    // error of k_sweep's 16.16 fixed-point position in fine-voxel units: origin 1, each step 1/2
+    const double march_err = (2.0 + 0.5 * (double)sample_table_size(p)) / 65536.0;
+    return voxel_build(ctx, ctx->terrain, p->vis_radius * p->block_radius_scale, block_threshold(p), march_err);
+}
+plc_status build_observed_index(plc_ctx* ctx, const plc_params* p) {
+    return voxel_build(ctx, ctx->observed, p->vis_radius * p->observed_radius_scale, observed_threshold(p), 0.0);
+}
+
+// s_0 = ray_start, s_{k+1} = s_k + ray_step, accumulated in double exactly as the upstream loop does
+plc_status upload_sample_table(plc_ctx* ctx, const plc_params* p) {
+    if (ctx->n_tab > 0 && ctx->tab_start == p->ray_start && ctx->tab_step == p->ray_step &&
+        ctx->tab_max == p->max_distance)
+        return PLC_OK;
+    const size_t n = sample_table_size(p);
+    double* host = static_cast<double*>(ctx->pinned_reserve(n * sizeof(double)));
+    if (!host) return PLC_E_OOM;
+    double s = p->ray_start;
+    for (size_t k = 0; k < n; ++k) {
+        host[k] = s;
+        s += p->ray_step;
+    }
+    PLC_CUDA_TRY(ctx, ctx->s_tab.reserve(n * sizeof(double)));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_tab.ptr, host, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));    // the pinned block is reused by other calls
+    ctx->n_tab = (int)n;
+    ctx->tab_start = p->ray_start;
+    ctx->tab_step = p->ray_step;
+    ctx->tab_max = p->max_distance;
+    return PLC_OK;
 }
 
 }  // namespace
@@ -414,7 +694,7 @@ extern "C" plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* clo
     // build for the node's default block radius right away; a sweep with other parameters rebuilds
     plc_params d;
     plc_params_default(&d);
-    PLC_TRY(voxel_build(ctx, ctx->terrain, d.vis_radius * d.block_radius_scale));
+    PLC_TRY(build_terrain_index(ctx, &d));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PLC_OK;
 }
@@ -425,7 +705,7 @@ extern "C" plc_status plc_vl_set_observed(plc_ctx* ctx, const plc_cloud_view* cl
     PLC_TRY(voxel_set_cloud(ctx, ctx->observed, cloud));
     plc_params d;
     plc_params_default(&d);
-    PLC_TRY(voxel_build(ctx, ctx->observed, d.vis_radius * d.observed_radius_scale));
+    PLC_TRY(build_observed_index(ctx, &d));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PLC_OK;
 }
@@ -476,19 +756,20 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     if (ctx->terrain.n_input == 0) return PLC_E_NO_TERRAIN;             // :455 !terrain_cloud_
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const plc_params& p = ctx->prm;
-    const double block_radius = p.vis_radius * p.block_radius_scale;    // :782
-    const double obs_radius = p.vis_radius * p.observed_radius_scale;   // :743
-    PLC_TRY(voxel_build(ctx, ctx->terrain, block_radius));
-    PLC_TRY(voxel_build(ctx, ctx->observed, obs_radius));
+    PLC_TRY(build_terrain_index(ctx, &p));
+    PLC_TRY(build_observed_index(ctx, &p));
+    PLC_TRY(upload_sample_table(ctx, &p));
 
     SweepDev P{};
     P.terrain = ctx->terrain.geom;
     P.observed = ctx->observed.geom;
     P.have_terrain = ctx->terrain.has_points();     // all-NaN cloud: tree over zero points never blocks
     P.have_observed = ctx->observed.has_points();   // :719 (!zx120_cloud_ || empty)
-    // blocked iff a point has d2 < (float)(r*r) and (double)d2 < vis_radius*0.5 (:782-790)
-    P.thr_block = fminf(static_cast<float>(block_radius * block_radius), ceil_to_float(p.vis_radius * 0.5));
-    P.thr_obs = static_cast<float>(obs_radius * obs_radius);
+    P.thr_block = block_threshold(&p);
+    P.thr_obs = observed_threshold(&p);
+    P.s_tab = ctx->s_tab.as<double>();
+    P.n_tab = ctx->n_tab;
+    P.inv_step = 1.0 / p.ray_step;
     P.max_distance = p.max_distance;
     P.min_distance = p.min_distance;
     P.ray_step = p.ray_step;
@@ -514,6 +795,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     PLC_CUDA_TRY(ctx, ctx->scores.reserve((size_t)n_local * sizeof(double) + 8));
     PLC_CUDA_TRY(ctx, ctx->covered.reserve((size_t)n_local * sizeof(int) + 8));
     if (want_mask) PLC_CUDA_TRY(ctx, ctx->mask.reserve((size_t)n_local * ctx->mask_words * 4 + 8));
+    PLC_CUDA_TRY(ctx, ctx->pose_aux.reserve((size_t)n_local * sizeof(PoseAux) + 8));
 
     cudaStream_t s = ctx->stream;
     SweepResult* res = ctx->result.as<SweepResult>();
@@ -525,16 +807,25 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     ctx->launches += 2;
     ctx->sweep_timed = false;
     if (n_local) {
+        k_pose_prep<<<(n_local + 127) / 128, 128, 0, s>>>(P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin,
+                                                          n_local, ctx->pose_aux.as<PoseAux>());
+        // 24 one-warp blocks per SM x (4.25 KB + 1 KB reserved) of shared memory; the rest stays L1
+        static bool carveout_set = false;
+        if (!carveout_set) {
+            cudaFuncSetAttribute(k_sweep, cudaFuncAttributePreferredSharedMemoryCarveout, 60);
+            carveout_set = true;
+        }
         cudaEventRecord(ctx->ev_sweep_begin, s);
         k_sweep<<<n_local * tiles, 32, 0, s>>>(
-            P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin, tiles, ctx->cells.as<plc_cell>(), M,
+            P, ctx->cands.as<plc_pose>(), ctx->pose_aux.as<PoseAux>(), (unsigned)ctx->cand_begin, tiles,
+            ctx->cells.as<plc_cell>(), M,
             ctx->fixed_scores.as<double>(), ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
             want_mask ? ctx->mask.as<uint32_t>() : nullptr, (unsigned)ctx->mask_words, res);
         cudaEventRecord(ctx->ev_sweep_end, s);
         ctx->sweep_timed = true;
         k_finalize<<<(n_local + 255) / 256, 256, 0, s>>>(ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
                                                          n_local, tiles, ctx->scores.as<double>(), ctx->covered.as<int>());
-        ctx->launches += 2;
+        ctx->launches += 3;
     }
     k_argmax<<<1, 1024, 0, s>>>(ctx->scores.as<double>(), ctx->covered.as<int>(), n_local, ctx->cand_begin,
                                 fixed_totals, fixed_blocks, res);

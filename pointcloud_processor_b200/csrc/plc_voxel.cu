@@ -2,17 +2,19 @@
 //
 // Replaces the KD-tree builds of terrainCallback / zx120PointsCallback
 // (/root/reference/src/virtual_lidar.cpp:180-207).  Instead of a tree, points are counting-sorted
-// into a dense uniform grid: a 4x4x4-per-coarse-voxel bitmask of fine voxels records where a sample
-// could possibly be within the radius of a point (conservative dilation), and every mid voxel
-// (2x2x2 fine voxels) owns the list of points within reach of its box.  Most samples of a ray are
-// resolved by one bit test; only flagged samples run the exact float32 test, over one short list.
+// into a uniform grid: coarse voxels that can hold a blocked sample own a brick of 8x8x8 fine voxels
+// with two bits each — "a sample here may be within the radius of a point" (conservative dilation)
+// and "a sample here certainly is" (conservative erosion) — and every mid voxel (4x4x4 fine voxels)
+// owns the list of points within reach of its box.  Most samples of a ray are resolved by one or
+// two word loads; only samples in the thin uncertain shell run the exact float32 test, over one list.
 //
 // Kernels (all HBM-bound, N = points, V = coarse voxels):
 //   k_extract   raw PointCloud2 bytes -> float4, drops non-finite, bbox           N*(step) rd, N*16 wr
 //   k_candidates<false>  per-mid-voxel candidate counts                            N*16 rd, <=27 atomics/pt
 //   k_scan_*    exclusive scan of the counts (3 passes)                            ~3*8V*4
-//   k_candidates<true>   points into their candidate lists                         N*16 rd, <=27*16 wr/pt
-//   k_dilate    fine-voxel mask bits within reach of each point                    N*16 rd, <=125 atomicOr/pt
+//   k_candidates<true>   points into their candidate lists (SoA groups of 4)       N*16 rd, <=27*12 wr/pt
+//   k_mark_coarse / k_coarse_ids   coarse voxels that need a brick                  N*16 rd, 4V wr
+//   k_dilate    2-bit fine-voxel states within reach of each point                 N*16 rd, ~100 atomicOr/pt
 #include <algorithm>
 #include <cmath>
 
@@ -103,13 +105,16 @@ k_extract(const unsigned char* __restrict__ data, unsigned long long n, unsigned
     }
 }
 
-// Candidate lists: a point belongs to the list of every mid voxel (edge 2g) whose box lies within
-// `reach` of it (double arithmetic, same slack as the mask).  FILL == false counts, FILL == true
-// writes the point into its slots.  Up to 3x3x3 mid voxels per point.
+// Candidate lists: a point belongs to the list of every mid voxel (edge h/2) whose box lies within
+// `reach` of it (double arithmetic, same slack as the occupancy bits).  FILL == false counts,
+// FILL == true writes the point into its slot.  Up to 3x3x3 mid voxels per point.
+// A list is stored as groups of four points in SoA form — x4, y4, z4 as three float4 — so the exact
+// test handles four points per iteration from three independent 16-byte loads; unused slots of the
+// last group hold +inf (never within any radius).
 template <bool FILL>
 __global__ void __launch_bounds__(256)
 k_candidates(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double msz,
-             uint32_t* __restrict__ ccount, const uint32_t* __restrict__ cstart, float4* __restrict__ cpts) {
+             uint32_t* __restrict__ ccount, const uint32_t* __restrict__ gstart, float* __restrict__ cgrp) {
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float4 p = raw[i];
@@ -129,50 +134,105 @@ k_candidates(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double rea
                 double dx = fmax(0.0, fmax(x * msz - px, px - (x + 1) * msz));
                 if (dx * dx + dyz > r2) continue;
                 uint32_t k = atomicAdd(&ccount[row + x], 1u);
-                if (FILL) cpts[cstart[row + x] + k] = p;
+                if (FILL) {
+                    float* grp = cgrp + ((size_t)gstart[row + x] + (k >> 2)) * 12 + (k & 3);
+                    grp[0] = p.x;
+                    grp[4] = p.y;
+                    grp[8] = p.z;
+                }
             }
         }
     }
 }
 
-// Sets the bit of every fine voxel whose box lies within `reach` of the point (double arithmetic;
-// `reach` already contains the slack that covers float rounding in fine_coord_f).
-__global__ void __launch_bounds__(128)
-k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double gsz,
-         uint32_t* __restrict__ mask32) {
+// point counts -> group counts (in place), ahead of the exclusive scan that yields gstart
+__global__ void __launch_bounds__(256) k_counts_to_groups(uint32_t* __restrict__ c, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) c[i] = (c[i] + 3u) >> 2;
+}
+
+__global__ void __launch_bounds__(256) k_fill_f32(float* __restrict__ p, size_t n, float v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) p[i] = v;
+}
+
+// Marks every coarse voxel that the reach box of a point touches (at most 2x2x2: reach < h/2).
+__global__ void __launch_bounds__(256)
+k_mark_coarse(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double h,
+              uint32_t* __restrict__ flag) {
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float4 p = raw[i];
     double px = (double)p.x - (double)g.ox, py = (double)p.y - (double)g.oy, pz = (double)p.z - (double)g.oz;
-    int x0 = max(0, (int)floor((px - reach) / gsz)), x1 = min(g.dim_x * 4 - 1, (int)floor((px + reach) / gsz));
-    int y0 = max(0, (int)floor((py - reach) / gsz)), y1 = min(g.dim_y * 4 - 1, (int)floor((py + reach) / gsz));
-    int z0 = max(0, (int)floor((pz - reach) / gsz)), z1 = min(g.dim_z * 4 - 1, (int)floor((pz + reach) / gsz));
-    double r2 = reach * reach;
-    for (int z = z0; z <= z1; ++z) {
-        double dz = fmax(0.0, fmax(z * gsz - pz, pz - (z + 1) * gsz));
-        for (int y = y0; y <= y1; ++y) {
-            double dy = fmax(0.0, fmax(y * gsz - py, py - (y + 1) * gsz));
-            double dyz = dy * dy + dz * dz;
-            if (dyz > r2) continue;
-            // bits of this (y,z) row grouped per coarse voxel word
-            size_t row = ((size_t)(z >> 2) * g.dim_y + (y >> 2)) * g.dim_x;
-            int sub = ((z >> 1) & 1);
-            int bit_yz = ((y & 3) << 2) | ((z & 1) << 4);
-            uint32_t acc = 0;
-            int acc_v = -1;
-            for (int x = x0; x <= x1; ++x) {
-                double dx = fmax(0.0, fmax(x * gsz - px, px - (x + 1) * gsz));
-                if (dx * dx + dyz > r2) continue;
-                int v = x >> 2;
-                if (v != acc_v) {
-                    if (acc) atomicOr(&mask32[2 * (row + acc_v) + sub], acc);
-                    acc = 0;
-                    acc_v = v;
-                }
-                acc |= 1u << ((x & 3) | bit_yz);
+    int x0 = max(0, (int)floor((px - reach) / h)), x1 = min(g.dim_x - 1, (int)floor((px + reach) / h));
+    int y0 = max(0, (int)floor((py - reach) / h)), y1 = min(g.dim_y - 1, (int)floor((py + reach) / h));
+    int z0 = max(0, (int)floor((pz - reach) / h)), z1 = min(g.dim_z - 1, (int)floor((pz + reach) / h));
+    for (int z = z0; z <= z1; ++z)
+        for (int y = y0; y <= y1; ++y)
+            for (int x = x0; x <= x1; ++x) flag[((size_t)z * g.dim_y + y) * g.dim_x + x] = 1u;
+}
+
+// ids[v] = exclusive scan of the flags (ids[n_vox] = number of bricks): coarse[v] = flagged ? id + 1 : 0
+__global__ void __launch_bounds__(256)
+k_coarse_ids(const uint32_t* __restrict__ ids, size_t n_vox, uint32_t* __restrict__ coarse) {
+    size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n_vox) return;
+    uint32_t a = ids[v], b = ids[v + 1];
+    coarse[v] = b != a ? a + 1u : 0u;
+}
+
+// Two bits per fine voxel (double arithmetic; `reach` and `inner` already contain the slack that
+// covers float rounding in fine_coord_f / the fixed-point march):
+//   bit 0 where the voxel's box comes within `reach` of the point,
+//   bit 1 where the whole box lies within `inner` of the point (inner <= 0: never).
+// One thread per (point, fine z slice), so a warp shares the point and spreads over the slices.
+__global__ void __launch_bounds__(256)
+k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double inner, double gsz,
+         int slices, uint32_t* __restrict__ bricks) {
+    unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned i = (unsigned)(t / (unsigned)slices);
+    int sl = (int)(t - (unsigned long long)i * (unsigned)slices);
+    if (i >= n) return;
+    float4 p = raw[i];
+    double px = (double)p.x - (double)g.ox, py = (double)p.y - (double)g.oy, pz = (double)p.z - (double)g.oz;
+    const int fx_max = (g.dim_x << kFineShift) - 1, fy_max = (g.dim_y << kFineShift) - 1,
+              fz_max = (g.dim_z << kFineShift) - 1;
+    int z = max(0, (int)floor((pz - reach) / gsz)) + sl;
+    if (z > min(fz_max, (int)floor((pz + reach) / gsz))) return;
+    int x0 = max(0, (int)floor((px - reach) / gsz)), x1 = min(fx_max, (int)floor((px + reach) / gsz));
+    int y0 = max(0, (int)floor((py - reach) / gsz)), y1 = min(fy_max, (int)floor((py + reach) / gsz));
+    const double r2 = reach * reach, in2 = inner > 0.0 ? inner * inner : -1.0;
+    double dz_lo = z * gsz - pz, dz_hi = pz - (z + 1) * gsz;       // >0 when the box is above / below the point
+    double dz = fmax(0.0, fmax(dz_lo, dz_hi));
+    double fz = fmax(fabs(dz_lo), fabs(dz_hi));                     // farthest face along z
+    for (int y = y0; y <= y1; ++y) {
+        double dy_lo = y * gsz - py, dy_hi = py - (y + 1) * gsz;
+        double dy = fmax(0.0, fmax(dy_lo, dy_hi));
+        double dyz = dy * dy + dz * dz;
+        if (dyz > r2) continue;
+        double fy = fmax(fabs(dy_lo), fabs(dy_hi));
+        double fyz = fy * fy + fz * fz;
+        size_t row = ((size_t)(z >> kFineShift) * g.dim_y + (y >> kFineShift)) * g.dim_x;
+        int word = ((z & 7) << 2) | ((y & 7) >> 1);
+        int ybit = (y & 1) << 3;
+        uint32_t acc = 0;
+        int acc_v = -1;
+        for (int x = x0; x <= x1; ++x) {
+            double dx_lo = x * gsz - px, dx_hi = px - (x + 1) * gsz;
+            double dx = fmax(0.0, fmax(dx_lo, dx_hi));
+            if (dx * dx + dyz > r2) continue;
+            double fx = fmax(fabs(dx_lo), fabs(dx_hi));
+            uint32_t st = (fx * fx + fyz < in2) ? 3u : 1u;
+            int v = x >> kFineShift;
+            if (v != acc_v) {
+                if (acc) atomicOr(&bricks[(size_t)(g.coarse[row + acc_v] - 1u) * 32 + word], acc);
+                acc = 0;
+                acc_v = v;
             }
-            if (acc) atomicOr(&mask32[2 * (row + acc_v) + sub], acc);
+            acc |= st << (2 * (ybit | (x & 7)));
         }
+        if (acc) atomicOr(&bricks[(size_t)(g.coarse[row + acc_v] - 1u) * 32 + word], acc);
     }
 }
 
@@ -209,46 +269,57 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
     return PLC_OK;
 }
 
-plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius) {
+plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err) {
     if (!ix.has_points()) return PLC_OK;
-    if (ix.built_radius == radius) return PLC_OK;
-    if (!(radius > 0) || !std::isfinite(radius)) return PLC_E_INVALID_ARG;
+    if (ix.built_radius == radius && ix.built_thr == thr && march_err <= ix.built_march_err) return PLC_OK;
+    if (!(radius > 0) || !std::isfinite(radius) || !(thr >= 0) || !(march_err >= 0)) return PLC_E_INVALID_ARG;
 
-    // real-number reach that covers everything the float32 test can accept, plus float slack
+    // real-number reach that covers everything the float32 test can accept, plus the slack that
+    // absorbs float rounding of the voxel coordinate and the error of the fixed-point march
     const float r2f = static_cast<float>(radius * radius);
     double max_abs = 0.0;
     for (int a = 0; a < 6; ++a) max_abs = std::max(max_abs, (double)std::fabs(ix.bbox[a]));
-    const double slack = 1e-4 + max_abs * 4.8e-7;
-    const double reach = std::sqrt((double)r2f) * (1.0 + 1e-6) + slack;
-    double h = std::exp2(std::ceil(std::log2(2.0 * reach)));
-    if (h < 2.0 * reach) h *= 2.0;
-    double org[3];
+    const double slack0 = 1e-4 + max_abs * 4.8e-7;
+    const double r_out = std::sqrt((double)r2f) * (1.0 + 1e-6);
+    // h >= 2^-6 keeps the clip margins (h/16, h/32) far above float rounding at scene scale
+    double h = std::max(std::exp2(std::ceil(std::log2(2.0 * (r_out + slack0)))), 1.0 / 64.0);
+    double org[3], reach = 0.0, slack = 0.0;
     long long dim[3];
     for (;;) {
+        slack = slack0 + (h / 8.0) * march_err;
+        reach = r_out + slack;
+        if (h < 2.0 * reach) {
+            h *= 2.0;
+            continue;
+        }
         double cells = 1.0;
         for (int a = 0; a < 3; ++a) {
             org[a] = (std::floor((double)ix.bbox[a] / h) - 1.0) * h;
             dim[a] = (long long)std::floor(((double)ix.bbox[3 + a] - org[a]) / h) + 2;
             cells *= (double)dim[a];
         }
-        bool fits = cells <= 2.5e8 && dim[0] * 4 < (1 << 23) && dim[1] * 4 < (1 << 23) && dim[2] * 4 < (1 << 23);
+        // fine coordinates must fit the march's signed 16.16 fixed point with room to spare
+        bool fits = cells <= 2.5e8 && dim[0] <= 3600 && dim[1] <= 3600 && dim[2] <= 3600;
         if (fits) break;
         h *= 2.0;    // coarser voxels only make the lists longer, never incomplete
     }
+    // "certain" bit: the float32 test accepts every sample of the fine voxel against this point
+    const double inner = std::sqrt((double)std::min(thr, r2f)) * (1.0 - 1e-6) - slack;
     const size_t n_vox = (size_t)dim[0] * dim[1] * dim[2];
     const size_t n_mid = n_vox * 8;
     const unsigned n = (unsigned)ix.n_raw;
+    const double gsz = h / 8.0;
 
-    PLC_CUDA_TRY(ctx, ix.mask32.reserve(n_vox * 8));
-    PLC_CUDA_TRY(ctx, ix.cstart.reserve((n_mid + 1) * 4));
-    PLC_CUDA_TRY(ctx, ix.cfill.reserve(n_mid * 4));
+    PLC_CUDA_TRY(ctx, ix.coarse.reserve(n_vox * 4));
+    PLC_CUDA_TRY(ctx, ix.gstart.reserve((n_mid + 1) * 4));
+    PLC_CUDA_TRY(ctx, ix.cfill.reserve(std::max(n_mid, n_vox + 1) * 4));
     PLC_CUDA_TRY(ctx, ix.scan_tmp.reserve(scan_tmp_bytes(n_mid + 1)));
 
     VoxelGeom g{};
     g.ox = (float)org[0];
     g.oy = (float)org[1];
     g.oz = (float)org[2];
-    g.inv_g = (float)(4.0 / h);
+    g.inv_g = (float)(8.0 / h);
     g.reach = (float)reach;
     g.dim_x = (int)dim[0];
     g.dim_y = (int)dim[1];
@@ -256,40 +327,64 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius) {
     g.mdim_x = g.dim_x * 2;
     g.mdim_y = g.dim_y * 2;
     g.mdim_z = g.dim_z * 2;
-    g.fdim_xf = (float)(g.dim_x * 4);
-    g.fdim_yf = (float)(g.dim_y * 4);
-    g.fdim_zf = (float)(g.dim_z * 4);
-    g.mask32 = ix.mask32.as<uint32_t>();
-    g.cstart = ix.cstart.as<uint32_t>();
-    g.cpts = nullptr;
+    g.fdim_xf = (float)(g.dim_x * 8);
+    g.fdim_yf = (float)(g.dim_y * 8);
+    g.fdim_zf = (float)(g.dim_z * 8);
+    for (int a = 0; a < 3; ++a) {
+        g.clip_lo[a] = (float)((double)ix.bbox[a] - reach - h / 16.0);
+        g.clip_hi[a] = (float)((double)ix.bbox[3 + a] + reach + h / 16.0);
+    }
+    g.clip_t = (float)(h / 32.0);
+    g.coarse = ix.coarse.as<uint32_t>();
+    g.gstart = ix.gstart.as<uint32_t>();
+    g.bricks = nullptr;
+    g.cgrp = nullptr;
 
     cudaStream_t s = ctx->stream;
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.mask32.ptr, 0, n_vox * 8, s));
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cstart.ptr, 0, (n_mid + 1) * 4, s));
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
     unsigned pb = (n + 255) / 256;
-    k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.cstart.as<uint32_t>(),
+    // ---- occupancy: coarse flags -> brick ids -> 2-bit fine states
+    uint32_t* ids = ix.cfill.as<uint32_t>();      // scratch until the candidate fill pass needs it
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ids, 0, (n_vox + 1) * 4, s));
+    k_mark_coarse<<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h, ids);
+    scan_exclusive_u32(ids, n_vox + 1, ix.scan_tmp.as<uint32_t>(), s);
+    k_coarse_ids<<<(unsigned)((n_vox + 255) / 256), 256, 0, s>>>(ids, n_vox, ix.coarse.as<uint32_t>());
+    // ---- candidate lists: counts -> offsets
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.gstart.ptr, 0, (n_mid + 1) * 4, s));
+    k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.gstart.as<uint32_t>(),
                                            nullptr, nullptr);
-    scan_exclusive_u32(ix.cstart.as<uint32_t>(), n_mid + 1, ix.scan_tmp.as<uint32_t>(), s);
-    k_dilate<<<(n + 127) / 128, 128, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 4.0, ix.mask32.as<uint32_t>());
-    ctx->launches += 5;
+    ctx->launches += 6;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
-    // total number of list entries decides the size of the candidate array
-    uint32_t* total = static_cast<uint32_t*>(ctx->pinned);
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(total, ix.cstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
+    uint32_t* totals = static_cast<uint32_t*>(ctx->pinned);
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ids + n_vox, 4, cudaMemcpyDeviceToHost, s));
+    k_counts_to_groups<<<(unsigned)((n_mid + 255) / 256), 256, 0, s>>>(ix.gstart.as<uint32_t>(), n_mid);
+    scan_exclusive_u32(ix.gstart.as<uint32_t>(), n_mid + 1, ix.scan_tmp.as<uint32_t>(), s);
+    ctx->launches += 4;
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals + 1, ix.gstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
-    const size_t n_cand = *total;
-    PLC_CUDA_TRY(ctx, ix.cpts.reserve(std::max<size_t>(n_cand, 1) * sizeof(float4)));
-    g.cpts = ix.cpts.as<float4>();
+    const size_t n_bricks = totals[0], n_groups = totals[1];
+    PLC_CUDA_TRY(ctx, ix.bricks.reserve(std::max<size_t>(n_bricks, 1) * 128));
+    PLC_CUDA_TRY(ctx, ix.cgrp.reserve(std::max<size_t>(n_groups, 1) * 48));
+    g.bricks = ix.bricks.as<uint32_t>();
+    g.cgrp = ix.cgrp.as<float4>();
+    k_fill_f32<<<148 * 8, 256, 0, s>>>(ix.cgrp.as<float>(), n_groups * 12, INFINITY);
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, std::max<size_t>(n_bricks, 1) * 128, s));
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
+    const int slices = (int)std::floor(2.0 * reach / gsz) + 2;
+    const unsigned long long dthreads = (unsigned long long)n * (unsigned)slices;
+    k_dilate<<<(unsigned)((dthreads + 255) / 256), 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, inner, gsz, slices,
+                                                                ix.bricks.as<uint32_t>());
     k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.cfill.as<uint32_t>(),
-                                          ix.cstart.as<uint32_t>(), ix.cpts.as<float4>());
-    ctx->launches += 1;
+                                          ix.gstart.as<uint32_t>(), ix.cgrp.as<float>());
+    ctx->launches += 3;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ix.geom = g;
     ix.h = h;
     ix.n_vox = n_vox;
-    ix.n_cand = n_cand;
+    ix.n_bricks = n_bricks;
+    ix.n_groups = n_groups;
     ix.built_radius = radius;
+    ix.built_thr = thr;
+    ix.built_march_err = march_err;
     return PLC_OK;
 }
 

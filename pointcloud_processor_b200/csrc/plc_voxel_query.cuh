@@ -4,10 +4,12 @@
 // indexed point p satisfy  d2_f32(q,p) < thr  with  d2 = ((dx*dx)+(dy*dy))+(dz*dz)  evaluated in
 // float32 without FMA (FLANN L2_Simple<float>, strict compare as RadiusResultSet does).
 //
-// Two levels, both addressed from the fine-voxel coordinate of q (edge g, a power of two):
-//   mask   one bit per fine voxel: 0 = no point within reach of the voxel's box (certainly clear)
-//   cand   per mid voxel (2x2x2 fine voxels): the points within reach of its box, stored
-//          contiguously (a point appears in up to 27 lists) — the exact test scans just that list
+// Three levels, all addressed from the fine-voxel coordinate of q (edge g, a power of two):
+//   coarse  one word per coarse voxel (8x8x8 fine voxels): 0 = nothing within reach, else its brick
+//   brick   two bits per fine voxel: clear / uncertain / certainly blocked (plc_internal.cuh)
+//   cand    per mid voxel (4x4x4 fine voxels): the points within reach of its box, stored
+//           contiguously in SoA groups of four (a point appears in up to 27 lists) — the exact
+//           test scans just that list
 //
 // Every translation unit that includes this header is compiled with -fmad=false, so `a*b+c`
 // below is two roundings, as on the reference's x86-64 build.
@@ -32,21 +34,40 @@ __device__ __forceinline__ float fine_coord_f(float v, float origin, float inv_g
 
 __device__ __forceinline__ int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
-// Exact existence test over the candidate list of the mid voxel (ix>>1, iy>>1, iz>>1).
-__device__ __forceinline__ bool cand_any(const VoxelGeom& g, int ix, int iy, int iz, float qx, float qy,
-                                         float qz, float thr) {
-    size_t m = ((size_t)(iz >> 1) * g.mdim_y + (iy >> 1)) * g.mdim_x + (ix >> 1);
-    uint32_t s = __ldg(&g.cstart[m]), e = __ldg(&g.cstart[m + 1]);
-    const float4* __restrict__ pts = g.cpts;
-    for (; s < e; ++s) {
-        float4 p = __ldg(&pts[s]);
-        if (dist2_f32(qx, qy, qz, p.x, p.y, p.z) < thr) return true;
+// State of fine voxel (ix, iy, iz): 0 clear, 1 uncertain (run the exact test), 3 certainly blocked.
+__device__ __forceinline__ unsigned voxel_state(const VoxelGeom& g, int ix, int iy, int iz) {
+    size_t v = ((size_t)(iz >> kFineShift) * g.dim_y + (iy >> kFineShift)) * g.dim_x + (ix >> kFineShift);
+    uint32_t b = __ldg(&g.coarse[v]);
+    if (b == 0) return 0;
+    uint32_t w = __ldg(&g.bricks[(size_t)(b - 1u) * 32 + (((iz & 7) << 2) | ((iy & 7) >> 1))]);
+    return (w >> (2 * (((iy & 1) << 3) | (ix & 7)))) & 3u;
+}
+
+__device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int iy, int iz) {
+    return (uint32_t)(((size_t)(iz >> 2) * g.mdim_y + (iy >> 2)) * g.mdim_x + (ix >> 2));
+}
+
+// Exact existence test over the candidate list of mid voxel m, four points per iteration.
+__device__ __forceinline__ bool cand_any_m(const VoxelGeom& g, uint32_t m, float qx, float qy, float qz, float thr) {
+    uint32_t s = __ldg(&g.gstart[m]), e = __ldg(&g.gstart[m + 1]);
+    const float4* __restrict__ grp = g.cgrp + (size_t)s * 3;
+    for (; s < e; ++s, grp += 3) {
+        float4 X = __ldg(grp), Y = __ldg(grp + 1), Z = __ldg(grp + 2);
+        float d0 = dist2_f32(qx, qy, qz, X.x, Y.x, Z.x), d1 = dist2_f32(qx, qy, qz, X.y, Y.y, Z.y);
+        float d2 = dist2_f32(qx, qy, qz, X.z, Y.z, Z.z), d3 = dist2_f32(qx, qy, qz, X.w, Y.w, Z.w);
+        if (fminf(fminf(d0, d1), fminf(d2, d3)) < thr) return true;
     }
     return false;
 }
 
-// Mask first; the exact test only where the fine voxel is flagged.  Outside the grid nothing is
-// within reach (the grid has a one-coarse-voxel margin around every point).
+__device__ __forceinline__ bool cand_any(const VoxelGeom& g, int ix, int iy, int iz, float qx, float qy,
+                                         float qz, float thr) {
+    return cand_any_m(g, mid_voxel_of(g, ix, iy, iz), qx, qy, qz, thr);
+}
+
+// Occupancy first; the exact test only in the uncertain shell.  Outside the grid nothing is
+// within reach (the grid has a one-coarse-voxel margin around every point).  `thr` must be the
+// threshold the index was built for (the "certain" state is only valid for that one).
 __device__ __forceinline__ bool ball_any(const VoxelGeom& g, float qx, float qy, float qz, float thr,
                                          unsigned long long* exact_counter) {
     float fx = fine_coord_f(qx, g.ox, g.inv_g), fy = fine_coord_f(qy, g.oy, g.inv_g),
@@ -55,10 +76,9 @@ __device__ __forceinline__ bool ball_any(const VoxelGeom& g, float qx, float qy,
     if (!(fx >= 0.0f && fy >= 0.0f && fz >= 0.0f && fx < g.fdim_xf && fy < g.fdim_yf && fz < g.fdim_zf))
         return false;
     int ix = (int)fx, iy = (int)fy, iz = (int)fz;
-    size_t v = ((size_t)(iz >> 2) * g.dim_y + (iy >> 2)) * g.dim_x + (ix >> 2);
-    uint32_t w = __ldg(&g.mask32[2 * v + ((iz >> 1) & 1)]);
-    int bit = (ix & 3) | ((iy & 3) << 2) | ((iz & 1) << 4);
-    if (!((w >> bit) & 1u)) return false;
+    unsigned st = voxel_state(g, ix, iy, iz);
+    if (st == 0) return false;
+    if (st == 3) return true;
     if (exact_counter) ++*exact_counter;
     return cand_any(g, ix, iy, iz, qx, qy, qz, thr);
 }
