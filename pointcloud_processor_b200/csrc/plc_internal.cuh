@@ -52,8 +52,9 @@ struct DevBuf {
 
 // Geometry of a voxel index, passed to kernels by value.
 //   coarse voxel edge h (a power of two >= 2*reach), mid voxel h/2, fine voxel g = h/8, shared origin.
-//   coarse[v]  0: no point within reach of any position in the coarse voxel (certainly clear);
-//              else 1 + index of the voxel's brick.
+//   coarse[(z*dim_y + y)*wdim_x + (x>>5)] = {bits, base}: bit (x&31) clear = no point within reach of
+//              any position in the coarse voxel (certainly clear); set = the voxel owns brick
+//              base + popc(bits below it).  8 bytes per 32 coarse voxels, so this level lives in L1.
 //   bricks[32*b + (fz&7)*4 + ((fy&7)>>1)], 2 bits per fine voxel at bit 2*(((fy&1)<<3) | (fx&7)):
 //              bit 0  a sample in the fine voxel MAY be within the radius of a point
 //                     (conservative dilation of the points by `reach`)
@@ -70,11 +71,12 @@ struct VoxelGeom {
     float inv_g;             // 1/g (power of two)
     float reach;             // real-number radius + slack used by the builder
     int dim_x, dim_y, dim_z; // coarse dims
+    int wdim_x;              // ceil(dim_x / 32): words per coarse x row
     int mdim_x, mdim_y, mdim_z;   // mid dims = 2*coarse
     float fdim_xf, fdim_yf, fdim_zf;   // fine dims = 8*coarse, as float for the bounds test
     float clip_lo[3], clip_hi[3];      // box outside which no position is within reach of a point
     float clip_t;                      // slack (m along the ray) the clipped sample range may overshoot by
-    const uint32_t* __restrict__ coarse;
+    const uint2* __restrict__ coarse;
     const uint32_t* __restrict__ bricks;
     const uint32_t* __restrict__ gstart;
     const float4* __restrict__ cgrp;
@@ -94,13 +96,14 @@ struct VoxelIndex {
     DevBuf coarse, bricks, gstart, cfill, cgrp, scan_tmp;
     VoxelGeom geom{};
     uint64_t n_vox = 0;       // coarse voxels
+    uint64_t n_words = 0;     // coarse bitmap words
     uint64_t n_bricks = 0;    // coarse voxels with a brick
     uint64_t n_groups = 0;    // 4-point groups in cgrp
     bool has_points() const { return n_raw > 0; }
     // compact size of the structure (points once + occupancy), the "G" term of the algorithmic bytes
-    uint64_t bytes() const { return n_raw * 16 + n_vox * 4 + n_bricks * 128; }
+    uint64_t bytes() const { return n_raw * 16 + n_words * 8 + n_bricks * 128; }
     // what is actually resident (candidate lists replicate a point into every mid voxel in reach)
-    uint64_t resident_bytes() const { return n_vox * 4 + n_bricks * 128 + (n_vox * 8 + 1) * 4 + n_groups * 48; }
+    uint64_t resident_bytes() const { return n_words * 8 + n_bricks * 128 + (n_vox * 8 + 1) * 4 + n_groups * 48; }
     void release() {
         raw.release(); coarse.release(); bricks.release(); gstart.release(); cfill.release(); cgrp.release();
         scan_tmp.release();

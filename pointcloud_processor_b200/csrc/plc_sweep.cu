@@ -43,6 +43,7 @@ struct SweepDev {
     const double* __restrict__ s_tab;
     int n_tab;
     double inv_step;
+    float trust_limit;   // coordinates and ray lengths below this keep the float32 clip inside its margin (k_sweep)
 };
 
 struct RayStats {
@@ -282,7 +283,12 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     const VoxelGeom& G = P.terrain;
     const int lane = threadIdx.x;
     const unsigned lt_mask = (1u << lane) - 1u;
-    const float sxf = (float)s.x, syf = (float)s.y, szf = (float)s.z;
+    const float sf[3] = {(float)s.x, (float)s.y, (float)s.z};
+    bool s_in[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) s_in[a] = sf[a] >= G.clip_lo[a] && sf[a] <= G.clip_hi[a];
+    // float32 clipping is only trusted to keep the march inside the grid at ordinary scene scale
+    const bool trust_clip = fabsf(sf[0]) < P.trust_limit && fabsf(sf[1]) < P.trust_limit && fabsf(sf[2]) < P.trust_limit;
     const double fscale = (double)G.inv_g * 65536.0;
     unsigned gated = 0;
     unsigned long long exact = 0;
@@ -348,19 +354,21 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 while (n > 0 && !(__ldg(&P.s_tab[n - 1]) < end)) --n;
                 while (n < P.n_tab - 1 && __ldg(&P.s_tab[n]) < end) ++n;
             }
-            // clip [0, n) against the reach box (float32, conservative by clip_t metres)
+            // clip [0, n) against the reach box (float32, conservative by clip_t metres); an axis
+            // on which both the sensor and the target lie inside the box's slab cannot bind
             float uf[3] = {(float)ux, (float)uy, (float)uz};
-            float sf[3] = {sxf, syf, szf};
+            float cf[3] = {(float)c.x, (float)c.y, (float)c.z};
             float t_in = 0.f, t_out = 3.0e38f;
             bool miss = false;
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
+                if (s_in[a] && cf[a] >= G.clip_lo[a] && cf[a] <= G.clip_hi[a]) continue;
                 if (fabsf(uf[a]) > 1e-12f) {
                     float inv = __fdividef(1.0f, uf[a]);
                     float t0 = (G.clip_lo[a] - sf[a]) * inv, t1 = (G.clip_hi[a] - sf[a]) * inv;
                     t_in = fmaxf(t_in, fminf(t0, t1));
                     t_out = fminf(t_out, fmaxf(t0, t1));
-                } else if (sf[a] < G.clip_lo[a] || sf[a] > G.clip_hi[a]) {
+                } else if (!s_in[a]) {
                     miss = true;
                 }
             }
@@ -378,8 +386,10 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 dfx = __double2int_rn(ux * P.ray_step * fscale);
                 dfy = __double2int_rn(uy * P.ray_step * fscale);
                 dfz = __double2int_rn(uz * P.ray_step * fscale);
-                // both ends of the clipped range must lie inside the grid (they do by construction;
-                // a ray that somehow does not is marched sample by sample with bounds-checked lookups)
+                // Both ends of the clipped range lie inside the grid by construction as long as float32
+                // resolves clip_t at the scene's coordinates (trust_limit).  Beyond that the ends are checked,
+                // and a ray that leaves the grid is marched sample by sample with bounds-checked lookups.
+                if (!trust_clip) {
                 const long long steps = k_hi - 1 - k;
                 const long long lx = fx + steps * dfx, ly = fy + steps * dfy, lz = fz + steps * dfz;
                 const long long mx = (long long)G.dim_x << (kFineShift + kFixedBits),
@@ -392,6 +402,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     blocked_k = clear ? -1 : (int)st.samples - 1;
                     exact += st.exact;
                     k = k_hi = 0;
+                }
                 }
             }
         }
@@ -770,6 +781,13 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     P.s_tab = ctx->s_tab.as<double>();
     P.n_tab = ctx->n_tab;
     P.inv_step = 1.0 / p.ray_step;
+    {
+        double max_abs = p.max_distance;
+        for (int a = 0; a < 6; ++a) max_abs = std::max(max_abs, (double)std::fabs(ctx->terrain.bbox[a]));
+        // float32 error of a clipped ray parameter ~ 4 ulp of the largest coordinate: keep it under clip_t / 4
+        const double limit = (double)P.terrain.clip_t / 1.6e-6;
+        P.trust_limit = max_abs < limit ? (float)limit : 0.0f;
+    }
     P.max_distance = p.max_distance;
     P.min_distance = p.min_distance;
     P.ray_step = p.ray_step;

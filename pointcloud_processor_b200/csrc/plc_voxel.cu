@@ -13,7 +13,7 @@
 //   k_candidates<false>  per-mid-voxel candidate counts                            N*16 rd, <=27 atomics/pt
 //   k_scan_*    exclusive scan of the counts (3 passes)                            ~3*8V*4
 //   k_candidates<true>   points into their candidate lists (SoA groups of 4)       N*16 rd, <=27*12 wr/pt
-//   k_mark_coarse / k_coarse_ids   coarse voxels that need a brick                  N*16 rd, 4V wr
+//   k_mark_coarse / k_coarse_counts / k_coarse_pack   coarse voxels that need a brick: bitmap + brick base per 32
 //   k_dilate    2-bit fine-voxel states within reach of each point                 N*16 rd, ~100 atomicOr/pt
 #include <algorithm>
 #include <cmath>
@@ -157,10 +157,11 @@ __global__ void __launch_bounds__(256) k_fill_f32(float* __restrict__ p, size_t 
     for (; i < n; i += stride) p[i] = v;
 }
 
-// Marks every coarse voxel that the reach box of a point touches (at most 2x2x2: reach < h/2).
+// Marks every coarse voxel that the reach box of a point touches (at most 2x2x2: reach < h/2):
+// one bit per coarse voxel, 32 consecutive x per word.
 __global__ void __launch_bounds__(256)
 k_mark_coarse(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double h,
-              uint32_t* __restrict__ flag) {
+              uint32_t* __restrict__ bits) {
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float4 p = raw[i];
@@ -170,16 +171,23 @@ k_mark_coarse(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double re
     int z0 = max(0, (int)floor((pz - reach) / h)), z1 = min(g.dim_z - 1, (int)floor((pz + reach) / h));
     for (int z = z0; z <= z1; ++z)
         for (int y = y0; y <= y1; ++y)
-            for (int x = x0; x <= x1; ++x) flag[((size_t)z * g.dim_y + y) * g.dim_x + x] = 1u;
+            for (int x = x0; x <= x1; ++x)
+                atomicOr(&bits[((size_t)z * g.dim_y + y) * g.wdim_x + (x >> 5)], 1u << (x & 31));
 }
 
-// ids[v] = exclusive scan of the flags (ids[n_vox] = number of bricks): coarse[v] = flagged ? id + 1 : 0
 __global__ void __launch_bounds__(256)
-k_coarse_ids(const uint32_t* __restrict__ ids, size_t n_vox, uint32_t* __restrict__ coarse) {
-    size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= n_vox) return;
-    uint32_t a = ids[v], b = ids[v + 1];
-    coarse[v] = b != a ? a + 1u : 0u;
+k_coarse_counts(const uint32_t* __restrict__ bits, size_t n_words, uint32_t* __restrict__ counts) {
+    size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < n_words) counts[w] = __popc(bits[w]);
+    if (w == n_words) counts[w] = 0;
+}
+
+// coarse[w] = {occupancy bits of 32 coarse voxels, index of the first one's brick}
+__global__ void __launch_bounds__(256)
+k_coarse_pack(const uint32_t* __restrict__ bits, const uint32_t* __restrict__ base, size_t n_words,
+              uint2* __restrict__ coarse) {
+    size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < n_words) coarse[w] = make_uint2(bits[w], base[w]);
 }
 
 // Two bits per fine voxel (double arithmetic; `reach` and `inner` already contain the slack that
@@ -213,7 +221,6 @@ k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, 
         if (dyz > r2) continue;
         double fy = fmax(fabs(dy_lo), fabs(dy_hi));
         double fyz = fy * fy + fz * fz;
-        size_t row = ((size_t)(z >> kFineShift) * g.dim_y + (y >> kFineShift)) * g.dim_x;
         int word = ((z & 7) << 2) | ((y & 7) >> 1);
         int ybit = (y & 1) << 3;
         uint32_t acc = 0;
@@ -226,13 +233,13 @@ k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, 
             uint32_t st = (fx * fx + fyz < in2) ? 3u : 1u;
             int v = x >> kFineShift;
             if (v != acc_v) {
-                if (acc) atomicOr(&bricks[(size_t)(g.coarse[row + acc_v] - 1u) * 32 + word], acc);
+                if (acc) atomicOr(&bricks[(size_t)brick_of(g, acc_v, y >> kFineShift, z >> kFineShift) * 32 + word], acc);
                 acc = 0;
                 acc_v = v;
             }
             acc |= st << (2 * (ybit | (x & 7)));
         }
-        if (acc) atomicOr(&bricks[(size_t)(g.coarse[row + acc_v] - 1u) * 32 + word], acc);
+        if (acc) atomicOr(&bricks[(size_t)brick_of(g, acc_v, y >> kFineShift, z >> kFineShift) * 32 + word], acc);
     }
 }
 
@@ -310,9 +317,11 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     const unsigned n = (unsigned)ix.n_raw;
     const double gsz = h / 8.0;
 
-    PLC_CUDA_TRY(ctx, ix.coarse.reserve(n_vox * 4));
+    const size_t wdim_x = (size_t)(dim[0] + 31) / 32;
+    const size_t n_words = wdim_x * dim[1] * dim[2];
+    PLC_CUDA_TRY(ctx, ix.coarse.reserve(n_words * 8));
     PLC_CUDA_TRY(ctx, ix.gstart.reserve((n_mid + 1) * 4));
-    PLC_CUDA_TRY(ctx, ix.cfill.reserve(std::max(n_mid, n_vox + 1) * 4));
+    PLC_CUDA_TRY(ctx, ix.cfill.reserve(std::max(n_mid, 2 * n_words + 2) * 4));
     PLC_CUDA_TRY(ctx, ix.scan_tmp.reserve(scan_tmp_bytes(n_mid + 1)));
 
     VoxelGeom g{};
@@ -324,6 +333,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     g.dim_x = (int)dim[0];
     g.dim_y = (int)dim[1];
     g.dim_z = (int)dim[2];
+    g.wdim_x = (int)wdim_x;
     g.mdim_x = g.dim_x * 2;
     g.mdim_y = g.dim_y * 2;
     g.mdim_z = g.dim_z * 2;
@@ -335,7 +345,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
         g.clip_hi[a] = (float)((double)ix.bbox[3 + a] + reach + h / 16.0);
     }
     g.clip_t = (float)(h / 32.0);
-    g.coarse = ix.coarse.as<uint32_t>();
+    g.coarse = ix.coarse.as<uint2>();
     g.gstart = ix.gstart.as<uint32_t>();
     g.bricks = nullptr;
     g.cgrp = nullptr;
@@ -343,19 +353,21 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     cudaStream_t s = ctx->stream;
     unsigned pb = (n + 255) / 256;
     // ---- occupancy: coarse flags -> brick ids -> 2-bit fine states
-    uint32_t* ids = ix.cfill.as<uint32_t>();      // scratch until the candidate fill pass needs it
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ids, 0, (n_vox + 1) * 4, s));
-    k_mark_coarse<<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h, ids);
-    scan_exclusive_u32(ids, n_vox + 1, ix.scan_tmp.as<uint32_t>(), s);
-    k_coarse_ids<<<(unsigned)((n_vox + 255) / 256), 256, 0, s>>>(ids, n_vox, ix.coarse.as<uint32_t>());
+    uint32_t* cbits = ix.cfill.as<uint32_t>();    // scratch until the candidate fill pass needs it
+    uint32_t* ids = cbits + n_words;
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(cbits, 0, n_words * 4, s));
+    k_mark_coarse<<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h, cbits);
+    k_coarse_counts<<<(unsigned)((n_words + 256) / 256), 256, 0, s>>>(cbits, n_words, ids);
+    scan_exclusive_u32(ids, n_words + 1, ix.scan_tmp.as<uint32_t>(), s);
+    k_coarse_pack<<<(unsigned)((n_words + 255) / 256), 256, 0, s>>>(cbits, ids, n_words, ix.coarse.as<uint2>());
     // ---- candidate lists: counts -> offsets
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.gstart.ptr, 0, (n_mid + 1) * 4, s));
     k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.gstart.as<uint32_t>(),
                                            nullptr, nullptr);
-    ctx->launches += 6;
+    ctx->launches += 7;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     uint32_t* totals = static_cast<uint32_t*>(ctx->pinned);
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ids + n_vox, 4, cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ids + n_words, 4, cudaMemcpyDeviceToHost, s));
     k_counts_to_groups<<<(unsigned)((n_mid + 255) / 256), 256, 0, s>>>(ix.gstart.as<uint32_t>(), n_mid);
     scan_exclusive_u32(ix.gstart.as<uint32_t>(), n_mid + 1, ix.scan_tmp.as<uint32_t>(), s);
     ctx->launches += 4;
@@ -380,6 +392,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     ix.geom = g;
     ix.h = h;
     ix.n_vox = n_vox;
+    ix.n_words = n_words;
     ix.n_bricks = n_bricks;
     ix.n_groups = n_groups;
     ix.built_radius = radius;

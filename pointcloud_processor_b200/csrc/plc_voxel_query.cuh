@@ -5,7 +5,8 @@
 // float32 without FMA (FLANN L2_Simple<float>, strict compare as RadiusResultSet does).
 //
 // Three levels, all addressed from the fine-voxel coordinate of q (edge g, a power of two):
-//   coarse  one word per coarse voxel (8x8x8 fine voxels): 0 = nothing within reach, else its brick
+//   coarse  one bit per coarse voxel (8x8x8 fine voxels): clear = nothing within reach; set = it owns
+//           a brick, found by popcount from the word's base index
 //   brick   two bits per fine voxel: clear / uncertain / certainly blocked (plc_internal.cuh)
 //   cand    per mid voxel (4x4x4 fine voxels): the points within reach of its box, stored
 //           contiguously in SoA groups of four (a point appears in up to 27 lists) — the exact
@@ -34,12 +35,20 @@ __device__ __forceinline__ float fine_coord_f(float v, float origin, float inv_g
 
 __device__ __forceinline__ int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
+// Brick of coarse voxel (cx, cy, cz); the voxel must own one (its occupancy bit is set).
+__device__ __forceinline__ uint32_t brick_of(const VoxelGeom& g, int cx, int cy, int cz) {
+    uint2 e = __ldg(&g.coarse[(unsigned)((cz * g.dim_y + cy) * g.wdim_x + (cx >> 5))]);
+    return e.y + __popc(e.x & ((1u << (cx & 31)) - 1u));
+}
+
 // State of fine voxel (ix, iy, iz): 0 clear, 1 uncertain (run the exact test), 3 certainly blocked.
 __device__ __forceinline__ unsigned voxel_state(const VoxelGeom& g, int ix, int iy, int iz) {
-    size_t v = ((size_t)(iz >> kFineShift) * g.dim_y + (iy >> kFineShift)) * g.dim_x + (ix >> kFineShift);
-    uint32_t b = __ldg(&g.coarse[v]);
-    if (b == 0) return 0;
-    uint32_t w = __ldg(&g.bricks[(size_t)(b - 1u) * 32 + (((iz & 7) << 2) | ((iy & 7) >> 1))]);
+    int cx = ix >> kFineShift;
+    uint2 e = __ldg(&g.coarse[(unsigned)(((iz >> kFineShift) * g.dim_y + (iy >> kFineShift)) * g.wdim_x + (cx >> 5))]);
+    unsigned bit = 1u << (cx & 31);
+    if (!(e.x & bit)) return 0;
+    unsigned brick = e.y + __popc(e.x & (bit - 1u));
+    uint32_t w = __ldg(&g.bricks[(size_t)brick * 32 + (((iz & 7) << 2) | ((iy & 7) >> 1))]);
     return (w >> (2 * (((iy & 1) << 3) | (ix & 7)))) & 3u;
 }
 
