@@ -17,6 +17,7 @@
 // §8 D4).  The occupancy bricks and voxel ranges are L2-resident, so the kernel is issue/latency
 // bound; bench.py reports achieved algorithmic GB/s against the measured HBM peak.
 #include <cmath>
+#include <cstdlib>
 #include <limits>
 
 #include "plc_voxel_query.cuh"
@@ -265,7 +266,10 @@ k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin,
 constexpr int kQueueCap = 64;                    // ring buffer, power of two, >= 2 * 32
 constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not blocked (so far), low bits = n
 
-__global__ void __launch_bounds__(32, 24)
+#ifndef PLC_SWEEP_BLOCKS_PER_SM
+#define PLC_SWEEP_BLOCKS_PER_SM 32
+#endif
+__global__ void __launch_bounds__(32, PLC_SWEEP_BLOCKS_PER_SM)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin,
         unsigned tiles, const plc_cell* __restrict__ cells, unsigned n_cells,
         const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
@@ -827,10 +831,11 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     if (n_local) {
         k_pose_prep<<<(n_local + 127) / 128, 128, 0, s>>>(P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin,
                                                           n_local, ctx->pose_aux.as<PoseAux>());
-        // 24 one-warp blocks per SM x (4.25 KB + 1 KB reserved) of shared memory; the rest stays L1
+        // measured on cfg2/cfg3: a 50 % carve-out (L1 kept large) beats full occupancy of the 5.25 KB blocks
         static bool carveout_set = false;
         if (!carveout_set) {
-            cudaFuncSetAttribute(k_sweep, cudaFuncAttributePreferredSharedMemoryCarveout, 60);
+            const char* ev = getenv("PLC_DEV_CARVEOUT");
+            cudaFuncSetAttribute(k_sweep, cudaFuncAttributePreferredSharedMemoryCarveout, ev ? atoi(ev) : 50);
             carveout_set = true;
         }
         cudaEventRecord(ctx->ev_sweep_begin, s);
