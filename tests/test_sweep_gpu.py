@@ -181,3 +181,91 @@ def test_edge_cases_and_error_codes(scene_cache):
         r = c.sweep(s.params, s.fixed, s.candidates)
         assert r.counters["rays_visible"] == r.counters["rays_gated_in"] and r.counters["samples"] == 0
         assert c.launch_count > 0
+
+
+def _blob_scene(seed, offset=(0.0, 0.0, 0.0)):
+    """A lumpy cloud of wall/floor points with cells and poses in awkward places: poses inside the
+    terrain's bounding box, rays exactly along the axes, a vertical ray, rays that miss the box."""
+    rng = np.random.default_rng(seed)
+    floor = np.stack([rng.uniform(-4, 4, 6000), rng.uniform(-4, 4, 6000), rng.normal(0, 0.03, 6000)], 1)
+    wall = np.stack([rng.normal(1.5, 0.02, 3000), rng.uniform(-2, 2, 3000), rng.uniform(0, 1.5, 3000)], 1)
+    dust = rng.uniform([-4, -4, 0], [4, 4, 3], (400, 3))
+    off = np.asarray(offset, np.float64)
+    terrain = (np.concatenate([floor, wall, dust]) + off).astype(np.float32)
+    gx, gy, gz = np.meshgrid(np.linspace(-3, 3, 25), np.linspace(-3, 3, 25), np.linspace(0.1, 1.3, 4), indexing="ij")
+    cells = np.zeros(gx.size, A.CELL_DTYPE)
+    cells["x"], cells["y"], cells["z"] = gx.ravel() + off[0], gy.ravel() + off[1], gz.ravel() + off[2]
+    n = rng.normal(size=(gx.size, 3))
+    n /= np.linalg.norm(n, axis=1, keepdims=True)
+    n[:, 2] = np.abs(n[:, 2])
+    cells["nx"], cells["ny"], cells["nz"] = n.astype(np.float32).T
+    poses = np.zeros(14, A.POSE_DTYPE)
+    xyz = np.array([[-3, -3, 0.1], [0, 0, 2.5], [0, 0, 0.7], [-3.0, 0.5, 0.5], [0.25, -3.0, 0.9], [3.5, 3.5, 6.0],
+                    [0.0, 0.0, 9.0], [-9.0, 0.0, 0.5], [2.0, 0.0, 0.4], [0.5, 0.5, 1.3], [1.5, 0.0, 0.75],
+                    [-3.0, -3.0, 20.0], [0.0, 3.0, -0.5], [6.0, -6.0, 2.0]]) + off
+    poses["x"], poses["y"], poses["z"] = xyz.T
+    poses["pitch"] = [-0.3, -1.5, 0.0, 0.0, 0.2, -1.0, -np.pi / 2, 0.0, 0.5, -0.2, 0.0, -1.57, 0.9, -0.4]
+    fixed = np.zeros(1, A.POSE_DTYPE)
+    fixed["x"], fixed["y"], fixed["z"] = off + (0.4, 0.5, 3.5)
+    fixed["pitch"] = -np.pi / 6
+    return terrain, cells, poses, fixed
+
+
+@pytest.mark.parametrize("offset", [(0.0, 0.0, 0.0), (5000.0, -7000.0, 300.0)], ids=["origin", "far_from_origin"])
+def test_awkward_geometry(ctx, offset):
+    # origin: poses inside the occupancy box, axis-aligned and vertical rays, rays that miss the box;
+    # far_from_origin: the same 5-7 km away, where float32 can no longer guarantee the clipped march
+    # stays inside the grid and the kernel checks every ray's ends (or falls back per sample)
+    terrain, cells, poses, fixed = _blob_scene(3, offset)
+    prm = A.default_params()
+    ctx.set_terrain(terrain)
+    ctx.set_observed(np.zeros((0, 3), np.float32))
+    ctx.set_cells(cells)
+    got = ctx.sweep(prm, fixed, poses, mask=True, flags=True, fixed_scores=True)
+    ref = O.sweep(O.Index(terrain, O.GRID), None, cells, prm, fixed, poses)
+    compare(got, ref, cells.size)
+    assert 0 < got.counters["rays_visible"] < got.counters["rays_gated_in"] < got.counters["rays"]
+
+
+@pytest.mark.parametrize("step,vis,scale,maxd", [(0.05, 0.08, 0.7, 15.0), (0.3, 0.3, 0.7, 15.0), (0.11, 0.02, 1.0, 6.0),
+                                                 (1.7, 0.08, 0.7, 40.0)])
+def test_other_parameterisations(ctx, scene_cache, step, vis, scale, maxd):
+    # every constant of the ray test is a runtime parameter: fine and coarse steps, radii from 2 to 21 cm
+    # (each rebuilds the occupancy structure), ranges that cut the candidate set
+    s = scene_cache("small")
+    prm = A.default_params()
+    prm.ray_step, prm.vis_radius, prm.block_radius_scale, prm.max_distance = step, vis, scale, maxd
+    got = run_gpu(ctx, s, params=prm)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, prm, s.fixed, s.candidates)
+    compare(got, ref, s.cells.size)
+
+
+def test_parity_config3_candidate_subset(ctx, scene_cache):
+    # BASELINE.json configs[2] geometry: L-shape, 1M points, 57 600 rays per pose, poses from all four height layers
+    s = scene_cache("cfg3")
+    assert s.cells.size == 32 * 1800 and s.terrain.shape[0] == 1_000_000
+    sel = np.sort(np.random.default_rng(9).choice(s.candidates.size, 32, replace=False))
+    cands = s.candidates[sel]
+    got = run_gpu(ctx, s, cands=cands)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, s.params, s.fixed, cands, threads=8)
+    compare(got, ref, s.cells.size, want_flags=False)
+
+
+def test_full_size_properties_config2(ctx, scene_cache):
+    # size-independent properties on the full configs[1] sweep (1 930 poses x 57 600 rays):
+    # sharded == unsharded bit for bit, argmax is the first maximum of the returned scores, covered
+    # cells never drop below the fixed sensor's own count, and terrain point order is irrelevant
+    s = scene_cache("cfg2")
+    full = run_gpu(ctx, s)
+    C = s.candidates.size
+    assert full.best_index == int(np.argmax(full.scores)) and full.best_score == full.scores.max()
+    fixed_cov = int(np.count_nonzero(full.fixed_scores > 0))
+    assert np.all(full.covered >= fixed_cov) and np.all(full.scores >= full.fixed_total * (1 - 1e-12))
+    assert full.counters["rays_visible"] == int(np.unpackbits(full.mask.view(np.uint8)).sum())
+    parts = [ctx.sweep(s.params, s.fixed, s.candidates, r * C // 3, (r + 1) * C // 3) for r in range(3)]
+    assert np.array_equal(np.concatenate([p.scores for p in parts]), full.scores)
+    assert sum(p.counters["samples"] for p in parts) == full.counters["samples"]
+    perm = np.random.default_rng(1).permutation(s.terrain.shape[0])
+    ctx.set_terrain(s.terrain[perm])
+    again = ctx.sweep(s.params, s.fixed, s.candidates, mask=True)
+    assert np.array_equal(again.mask, full.mask) and np.array_equal(again.scores, full.scores)
