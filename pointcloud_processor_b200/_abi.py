@@ -76,13 +76,35 @@ class GridBounds(C.Structure):
                 ("width", C.c_int32), ("height", C.c_int32)]
 
 
+class ColorStats(C.Structure):
+    _fields_ = [("total", C.c_int32), ("green", C.c_int32), ("red", C.c_int32), ("blue", C.c_int32),
+                ("yellow", C.c_int32)]
+
+
+class Pose(C.Structure):
+    _fields_ = [("x", C.c_double), ("y", C.c_double), ("z", C.c_double), ("pitch", C.c_double),
+                ("yaw", C.c_double)]
+
+
+class NodeResult(C.Structure):      # plc_vlnode_result (include/plc_node.h)
+    _fields_ = [("ran", C.c_int32), ("n_candidates", C.c_int32), ("best", Pose), ("best_score", C.c_double),
+                ("fixed", Pose), ("fixed_total", C.c_double), ("range_ok", C.c_int32), ("fov_ok", C.c_int32),
+                ("visibility_ok", C.c_int32), ("n_cells", C.c_int32), ("zx120_only", ColorStats),
+                ("dual", ColorStats), ("observed_points", C.c_uint64)]
+
+
+class MergerInput(C.Structure):     # plc_merger_input
+    _fields_ = [("cloud", CloudView), ("has_cloud", C.c_int32), ("has_transform", C.c_int32),
+                ("t", C.c_double * 3), ("q", C.c_double * 4)]
+
+
 # numpy mirrors of the PODs (same byte layout as plc_cell / plc_pose)
 CELL_DTYPE = np.dtype([("x", "<f8"), ("y", "<f8"), ("z", "<f8"), ("nx", "<f4"), ("ny", "<f4"),
                        ("nz", "<f4"), ("pad", "<u4")])
 POSE_DTYPE = np.dtype([("x", "<f8"), ("y", "<f8"), ("z", "<f8"), ("pitch", "<f8"), ("yaw", "<f8")])
 assert CELL_DTYPE.itemsize == 40 and POSE_DTYPE.itemsize == 40
 
-# every symbol include/plc.h and include/plc_host.h declare (tests check the library exports them all)
+# every symbol include/plc.h, plc_host.h and plc_node.h declare (tests check the library exports them all)
 EXPORTS = [
     "plc_params_default", "plc_params_memo", "plc_ctx_create", "plc_ctx_destroy", "plc_strerror",
     "plc_last_error", "plc_launch_count", "plc_abi_version", "plc_ctx_sync",
@@ -90,6 +112,10 @@ EXPORTS = [
     "plc_vl_upload_candidates", "plc_vl_run_async", "plc_vl_fetch", "plc_vl_result_device_ptr",
     "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_filter", "plc_merge",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
+    "plc_vlnode_create", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
+    "plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback", "plc_vlnode_zx120_points_callback",
+    "plc_vlnode_set_base_transform", "plc_vlnode_run_optimization", "plc_vlnode_get_candidates",
+    "plc_vlnode_get_cells", "plc_vlnode_get_bounds", "plc_vlnode_take_log", "plc_filter_scan", "plc_merge_clouds",
 ]
 
 _lib = None
@@ -149,6 +175,24 @@ def lib() -> C.CDLL:
     L.plc_host_compute_normals.argtypes = [C.POINTER(CloudView), dbl, vp]
     L.plc_host_generate_candidates.argtypes = [C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
                                                dbl, dbl, vp, u64, C.POINTER(u64)]
+    L.plc_vlnode_create.argtypes = [vp, C.POINTER(vp)]
+    L.plc_vlnode_destroy.argtypes = [vp]
+    L.plc_vlnode_destroy.restype = None
+    L.plc_vlnode_set_parameter_double.argtypes = [vp, C.c_char_p, dbl]
+    L.plc_vlnode_set_parameter_int.argtypes = [vp, C.c_char_p, C.c_int64]
+    for name in ("plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback",
+                 "plc_vlnode_zx120_points_callback"):
+        getattr(L, name).argtypes = [vp, C.POINTER(CloudView)]
+    L.plc_vlnode_set_base_transform.argtypes = [vp, i32, dbl, dbl, dbl]
+    L.plc_vlnode_run_optimization.argtypes = [vp, C.POINTER(NodeResult)]
+    L.plc_vlnode_get_candidates.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.plc_vlnode_get_cells.argtypes = [vp, vp, vp, u64, C.POINTER(u64)]
+    L.plc_vlnode_get_bounds.argtypes = [vp, C.POINTER(GridBounds)]
+    L.plc_vlnode_take_log.argtypes = [vp]
+    L.plc_vlnode_take_log.restype = C.c_char_p
+    L.plc_filter_scan.argtypes = [vp, C.POINTER(CloudView), dbl, dbl, dbl, dbl, vp, u64, C.POINTER(u64)]
+    L.plc_merge_clouds.argtypes = [vp, C.POINTER(MergerInput), C.POINTER(MergerInput), vp, u64, C.POINTER(u64),
+                                   vp, u64, C.POINTER(u64), vp, u64, C.POINTER(u64)]
     _lib = L
     return L
 

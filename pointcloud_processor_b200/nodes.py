@@ -1,0 +1,141 @@
+"""Headless drivers of the ROS-free node cores (include/plc_node.h) — what the rclcpp wrappers in
+ros2/ call, minus the message plumbing.  Used by tests and tools; no computation happens here."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as A
+from .context import Context
+
+
+class VirtualLidarNode:
+    """plc_vlnode: state and callbacks of SimplifiedDualLidarOptimizer (virtual_lidar.cpp:60-548)."""
+
+    def __init__(self, ctx: Context):
+        self._L = A.lib()
+        self._ctx = ctx
+        h = C.c_void_p()
+        st = self._L.plc_vlnode_create(ctx._h, C.byref(h))
+        if st != A.PLC_OK:
+            raise A.PlcError(st, "plc_vlnode_create")
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.plc_vlnode_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st, where):
+        if st != A.PLC_OK:
+            raise A.PlcError(st, where, self._L.plc_last_error(self._ctx._h).decode())
+
+    def set_parameter(self, name: str, value):
+        if isinstance(value, (int, np.integer)) and not isinstance(value, bool):
+            st = self._L.plc_vlnode_set_parameter_int(self._h, name.encode(), int(value))
+        else:
+            st = self._L.plc_vlnode_set_parameter_double(self._h, name.encode(), float(value))
+        self._check(st, f"set_parameter({name})")
+
+    def excavation_area_callback(self, cloud, point_step=None, off=(0, 4, 8)):
+        v = A.cloud_view(cloud, point_step, off)
+        self._check(self._L.plc_vlnode_excavation_area_callback(self._h, C.byref(v)), "excavation_area_callback")
+
+    def terrain_callback(self, cloud, point_step=None, off=(0, 4, 8)):
+        v = A.cloud_view(cloud, point_step, off)
+        self._check(self._L.plc_vlnode_terrain_callback(self._h, C.byref(v)), "terrain_callback")
+
+    def zx120_points_callback(self, cloud, point_step=None, off=(0, 4, 8)):
+        v = A.cloud_view(cloud, point_step, off)
+        self._check(self._L.plc_vlnode_zx120_points_callback(self._h, C.byref(v)), "zx120_points_callback")
+
+    def set_base_transform(self, xyz=None):
+        if xyz is None:
+            st = self._L.plc_vlnode_set_base_transform(self._h, 0, 0.0, 0.0, 0.0)
+        else:
+            st = self._L.plc_vlnode_set_base_transform(self._h, 1, float(xyz[0]), float(xyz[1]), float(xyz[2]))
+        self._check(st, "set_base_transform")
+
+    def run_optimization(self) -> A.NodeResult:
+        out = A.NodeResult()
+        self._check(self._L.plc_vlnode_run_optimization(self._h, C.byref(out)), "run_optimization")
+        return out
+
+    def candidates(self) -> np.ndarray:
+        n = C.c_uint64(0)
+        self._L.plc_vlnode_get_candidates(self._h, None, 0, C.byref(n))
+        out = np.zeros(n.value, A.POSE_DTYPE)
+        if n.value:
+            self._check(self._L.plc_vlnode_get_candidates(self._h, out.ctypes.data, out.size, C.byref(n)), "get_candidates")
+        return out
+
+    def cells(self):
+        n = C.c_uint64(0)
+        self._L.plc_vlnode_get_cells(self._h, None, None, 0, C.byref(n))
+        cells, flags = np.zeros(n.value, A.CELL_DTYPE), np.zeros(n.value, np.uint8)
+        if n.value:
+            self._check(self._L.plc_vlnode_get_cells(self._h, cells.ctypes.data, flags.ctypes.data, cells.size,
+                                                     C.byref(n)), "get_cells")
+        return cells, flags
+
+    def bounds(self) -> A.GridBounds:
+        b = A.GridBounds()
+        self._check(self._L.plc_vlnode_get_bounds(self._h, C.byref(b)), "get_bounds")
+        return b
+
+    def take_log(self) -> list[str]:
+        text = self._L.plc_vlnode_take_log(self._h).decode()
+        return text.split("\n")[:-1] if text else []
+
+
+def filter_scan(ctx: Context, scan, front=15.0, side=10.0, height=10.0, leaf=0.2, point_step=None, off=(0, 4, 8)):
+    """plc_filter_scan: pointcloud_filter's processCloudSimple.  Returns (n, 4) float32 (PointXYZ wire records)."""
+    L = A.lib()
+    v = A.cloud_view(scan, point_step, off)
+    cap = max(int(v.n_points), 1)
+    out = np.zeros((cap, 4), np.float32)
+    n = C.c_uint64(0)
+    st = L.plc_filter_scan(ctx._h, C.byref(v), front, side, height, leaf, out.ctypes.data, cap, C.byref(n))
+    if st != A.PLC_OK:
+        raise A.PlcError(st, "plc_filter_scan", L.plc_last_error(ctx._h).decode())
+    return out[: n.value]
+
+
+def merge_clouds(ctx: Context, robot: dict | None, backhoe: dict | None):
+    """plc_merge_clouds: pointcloud_merger's processPointClouds.  Each source is None (no message yet) or
+    {cloud (n,k) float32, t (3) or None for a TF failure, q (4 xyzw)}.  Returns (merged, robot, backhoe) as
+    (n, 32) uint8 PointXYZRGB wire records."""
+    L = A.lib()
+    ins, keep, caps = [], [], []
+    for src in (robot, backhoe):
+        m = A.MergerInput()
+        if src is not None:
+            v = A.cloud_view(src["cloud"], src.get("point_step"), src.get("off", (0, 4, 8)))
+            keep.append(src["cloud"])
+            m.cloud = v
+            m.has_cloud = 1
+            if src.get("t") is not None:
+                m.has_transform = 1
+                m.t[:] = list(map(float, src["t"]))
+                m.q[:] = list(map(float, src["q"]))
+            caps.append(int(v.n_points))
+        else:
+            caps.append(0)
+        ins.append(m)
+    bufs = [np.zeros((max(sum(caps), 1), 32), np.uint8), np.zeros((max(caps[0], 1), 32), np.uint8),
+            np.zeros((max(caps[1], 1), 32), np.uint8)]
+    ns = [C.c_uint64(0) for _ in range(3)]
+    st = L.plc_merge_clouds(ctx._h, C.byref(ins[0]), C.byref(ins[1]),
+                            bufs[0].ctypes.data, bufs[0].shape[0], C.byref(ns[0]),
+                            bufs[1].ctypes.data, bufs[1].shape[0], C.byref(ns[1]),
+                            bufs[2].ctypes.data, bufs[2].shape[0], C.byref(ns[2]))
+    if st != A.PLC_OK:
+        raise A.PlcError(st, "plc_merge_clouds", L.plc_last_error(ctx._h).decode())
+    return tuple(b[: n.value] for b, n in zip(bufs, ns))

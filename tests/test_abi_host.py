@@ -19,7 +19,7 @@ ROOT = Path(__file__).resolve().parent.parent
 
 def declared_symbols():
     names = set()
-    for h in ("plc.h", "plc_host.h"):
+    for h in ("plc.h", "plc_host.h", "plc_node.h"):
         text = (ROOT / "include" / h).read_text()
         names |= set(re.findall(r"\b(plc_[a-z0-9_]+)\s*\(", text))
     return names - {"plc_status"}   # the enum is mentioned as "plc_status (0 = OK ...)" in a comment

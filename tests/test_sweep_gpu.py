@@ -17,13 +17,26 @@ SCORE_RTOL = 1e-12          # tolerance stated by the spec for the double-precis
 MASK_MISMATCH_BUDGET = 1e-4  # of (pose, cell) pairs; the tests below additionally require exactly 0
 
 
+def assert_same_optimum(best_index, ref):
+    """Identical optimal pose — up to exact ties.  The reference's candidate and cell lattices are
+    symmetric, so mirrored poses can have mathematically EQUAL totals; upstream, the winner among them
+    is then decided by the rounding noise of libm's acos/sin and of a 57 600-term sequential sum, which
+    no parallel evaluation reproduces.  A different index is accepted only if
+    the oracle itself scores that pose within 1e-12 relative of its best, i.e. it is co-optimal."""
+    if best_index == ref["best_index"]:
+        return
+    assert best_index >= 0 and ref["best_index"] >= 0
+    mine, best = ref["scores"][best_index], ref["best_score"]
+    assert abs(mine - best) <= SCORE_RTOL * abs(best), (best_index, ref["best_index"], mine, best)
+
+
 def compare(got, ref, n_cells, want_flags=True):
     pairs = ref["mask"].shape[0] * n_cells
     mism = int(np.count_nonzero(np.unpackbits((got.mask ^ ref["mask"]).view(np.uint8))))
     assert mism <= MASK_MISMATCH_BUDGET * pairs, f"{mism} of {pairs} visibility bits differ"
     assert mism == 0, f"{mism} grazing-ray mismatches (allowed by the spec, but the arithmetic should be bit-exact)"
-    assert got.best_index == ref["best_index"]
-    assert got.best_covered == ref["best_covered"]
+    assert_same_optimum(got.best_index, ref)
+    assert got.best_covered == ref["covered"][got.best_index] if got.best_index >= 0 else got.best_covered == 0
     np.testing.assert_allclose(got.scores, ref["scores"], rtol=SCORE_RTOL, atol=1e-12)
     assert np.array_equal(got.covered, ref["covered"])
     np.testing.assert_allclose(got.fixed_scores, ref["fixed_scores"], rtol=SCORE_RTOL, atol=1e-15)
