@@ -8,7 +8,13 @@
 One step = one full sweep of the workload: the fixed-sensor pass, every (candidate pose, target
 cell) ray of this rank's candidate shard, per-candidate scores, argmax and — for N > 1 — the
 16-byte-per-rank all-gather.  Metric: rays/s over the whole job (BASELINE.json).  Prints ONE JSON
-line on rank 0.  See DESIGN.md §Measurement for every field.
+line on rank 0.  See DESIGN.md §6 for every field.
+
+Workload: BASELINE.json configs[1] (rectangular pit, 200 k points, 32x32x2 poses, 32x1800 rays per
+pose) at N = 1; at N GPUs the candidate lattice is refined to round(32*sqrt(N))^2 x 2 poses over
+the same region, so every rank keeps a configs[1]-sized shard ("scaling": "weak").  The line also
+carries `north_star_cfg3`: configs[2] (L-shape, 1 M points, 64x64x4 poses) swept by the same N
+ranks, the number the north star's 50 ms target is quoted on.
 """
 from __future__ import annotations
 
@@ -38,9 +44,23 @@ WORKLOADS = {
 
 
 def default_workload(n_gpus: int) -> str:
-    # N = 1: the configuration BASELINE.json quotes for one B200 (configs[1]);
-    # N > 1: the one it shards across 2/4/8 B200 (configs[2]), total work fixed => strong scaling
-    return "cfg2" if n_gpus == 1 else "cfg3"
+    return "cfg2"
+
+
+def build_scene(workload: str, world: int):
+    """configs[1] keeps a fixed shard per rank: the pose lattice side grows with sqrt(N)."""
+    from pointcloud_processor_b200 import scenes
+    if workload == "cfg2" and world > 1:
+        return scenes.build("cfg2", px=int(round(32 * np.sqrt(world))))
+    return scenes.build(workload)
+
+
+def workload_text(workload: str, world: int) -> str:
+    text = WORKLOADS.get(workload, workload)
+    if workload == "cfg2" and world > 1:
+        side = int(round(32 * np.sqrt(world)))
+        text = text.replace("32x32x2 poses", f"{side}x{side}x2 poses (32x32x2 per GPU x {world})")
+    return f"{workload}: {text}"
 
 
 class ClockSampler:
@@ -149,7 +169,7 @@ def run_ours(args) -> dict | None:
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     workload = args.workload or default_workload(world)
-    scene = scenes.build(workload)
+    scene = build_scene(workload, world)
     C, M = int(scene.candidates.size), int(scene.cells.size)
     begin, end = exchange.shard_range(C, rank, world)
 
@@ -240,6 +260,34 @@ def run_ours(args) -> dict | None:
         except ValueError:
             traffic = None
 
+    # ---- the north star's target configuration (configs[2]) on the same N ranks, strong-scaled
+    north = None
+    if workload == "cfg2" and not args.no_north_star:
+        s3 = scenes.build("cfg3")
+        C3, M3 = int(s3.candidates.size), int(s3.cells.size)
+        b3, e3 = exchange.shard_range(C3, rank, world)
+        ctx.set_terrain(s3.terrain)
+        ctx.set_cells(s3.cells)
+        ctx.upload_candidates(s3.params, s3.fixed, s3.candidates, b3, e3)
+        for _ in range(2):
+            step()
+        barrier()
+        ev3 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(3)]
+        for a, b in ev3:
+            flush.fill_(1)
+            a.record(stream)
+            step()
+            b.record(stream)
+        barrier()
+        t3 = torch.tensor([sum(a.elapsed_time(b) for a, b in ev3) / len(ev3)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+        s3_score, s3_index = exchange.pick_best(gathered)
+        north = {"workload": f"cfg3: {WORKLOADS['cfg3']}", "poses": C3, "rays_per_pose": M3,
+                 "terrain_points": int(s3.terrain.shape[0]), "scaling": "strong", "n_gpus": world,
+                 "sweep_latency_ms": float(t3.item()), "rays_per_s": C3 * M3 / (float(t3.item()) * 1e-3),
+                 "target_ms_on_8_gpus": 50.0, "best_pose_index": s3_index, "best_score": s3_score}
+
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -250,9 +298,9 @@ def run_ours(args) -> dict | None:
     line = {
         "metric": METRIC, "value": C * M / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
-        "higher_is_better": True, "scaling": "weak" if world == 1 else "strong", "vs_baseline": None,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64 geometry / f32 distance test", "data": "synthetic",
-        "config": {"workload": f"{workload}: {WORKLOADS.get(workload, workload)}", "poses": C, "rays_per_pose": M,
+        "config": {"workload": workload_text(workload, world), "poses": C, "rays_per_pose": M,
                    "terrain_points": int(scene.terrain.shape[0]), "rays_per_step": C * M,
                    "samples_per_ray": res.counters["samples"] / max(res.counters["rays"], 1),
                    "parallelism": f"candidate poses sharded over {world} GPU(s), grid replicated",
@@ -270,6 +318,8 @@ def run_ours(args) -> dict | None:
                      "note": "algorithmic bytes = 32 B/ray + 4 B/evaluated sample + 64 B/pose + grid (SURVEY D4); "
                              "the grid is L2-resident, so the kernel is issue/latency bound, not DRAM bound"},
     }
+    if north is not None:
+        line["north_star_cfg3"] = north
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         v, n, dt = cpu_reference_sample(scene, args.cpu_budget, threads)
@@ -293,9 +343,8 @@ def run_reference(args) -> dict | None:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return None                      # rank 0 alone runs and prints; the others exit 0
-    from pointcloud_processor_b200 import scenes
     workload = args.workload or default_workload(world)
-    scene = scenes.build(workload)
+    scene = build_scene(workload, world)
     C, M = int(scene.candidates.size), int(scene.cells.size)
     threads = os.cpu_count() or 1
     steps = max(1, args.steps)
@@ -313,9 +362,9 @@ def run_reference(args) -> dict | None:
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * C * M / value, "higher_is_better": True,
-        "scaling": "weak" if world == 1 else "strong", "vs_baseline": None, "dtype": "f64 geometry / f32 distance test",
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64 geometry / f32 distance test",
         "data": "synthetic",
-        "config": {"workload": f"{workload}: {WORKLOADS.get(workload, workload)}", "poses": C, "rays_per_pose": M,
+        "config": {"workload": workload_text(workload, world), "poses": C, "rays_per_pose": M,
                    "terrain_points": int(scene.terrain.shape[0]), "rays_per_step": C * M,
                    "note": "ms_per_step is the full sweep extrapolated from the timed sample"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
@@ -331,9 +380,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default=None,
-                    help="default: cfg2 at 1 GPU, cfg3 at N > 1 (BASELINE.json configs[1] / configs[2])")
+                    help="default: cfg2 (BASELINE.json configs[1]), one configs[1]-sized shard per GPU")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-north-star", action="store_true", help="skip the extra configs[2] measurement")
     args = ap.parse_args()
     line = run_reference(args) if args.impl == "reference" else run_ours(args)
     if line is not None:
