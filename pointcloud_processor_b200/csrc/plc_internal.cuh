@@ -91,7 +91,8 @@ struct VoxelIndex {
     // built index
     double built_radius = -1.0;   // query radius (m) the structure was built for
     float built_thr = 0.0f;       // float32 squared-distance threshold of the "certain" bit
-    double built_march_err = 0.0; // position error (fine voxels) of the fixed-point march covered by the slack
+    double built_march_err = 0.0; // position error of the caller's march covered by the slack: in fine voxels ...
+    double built_march_err_m = 0.0;   // ... plus in metres
     double h = 0.0;
     DevBuf coarse, bricks, gstart, cfill, cgrp, scan_tmp;
     VoxelGeom geom{};
@@ -181,9 +182,9 @@ struct SweepResult {
 
 plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* cloud);
 // Builds (or keeps) the index for `radius`.  thr: float32 squared-distance threshold of the exact test
-// (normally (float)(radius*radius)); march_err: position error of the caller's fixed-point march in
+// (normally (float)(radius*radius)); march_err + march_err_m: position error of the caller's march, in
 // fine-voxel units, folded into the conservative slack.
-plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err);
+plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err, double march_err_m);
 
 inline bool cloud_view_ok(const plc_cloud_view* v) {
     if (!v) return false;

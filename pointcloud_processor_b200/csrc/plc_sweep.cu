@@ -28,8 +28,8 @@ namespace {
 
 constexpr int kSweepThreads = 128;       // k_fixed / k_flags: one thread per cell
 // k_sweep runs ONE warp per block (no block barrier, a finished warp frees its slot at once):
-// 32 lanes x 8 rays = 256 consecutive cells of one candidate per block.
-constexpr int kRaysPerThread = 8;
+// 32 lanes x 16 rays = 512 consecutive cells of one candidate per block.
+constexpr int kRaysPerThread = 16;
 constexpr int kTileCells = 32 * kRaysPerThread;
 
 struct SweepDev {
@@ -45,6 +45,9 @@ struct SweepDev {
     int n_tab;
     double inv_step;
     float trust_limit;   // coordinates and ray lengths below this keep the float32 clip inside its margin (k_sweep)
+    // float32 views of the gates for k_sweep's float-first path: min/max_distance rounded down and up,
+    // vis_radius + ray_start, ray_start, ray_step and its inverse, ray_step in 16.16 fine-voxel units
+    float min_lo, min_hi, max_lo, max_hi, vis_start_f, startf, stepf, inv_stepf, step_fine;
 };
 
 struct RayStats {
@@ -243,27 +246,35 @@ k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin,
 
 // ---- K2+K3: one thread per (candidate, cell) ray ----------------------------------------------
 // grid.x = n_local * tiles, one warp per block; block b handles candidate b / tiles and cells
-// [tile*256, tile*256+256).  The 32 lanes hold 32 consecutive cells, so one ballot is one word of
+// [tile*512, tile*512+512).  The 32 lanes hold 32 consecutive cells, so one ballot is one word of
 // the visibility mask.  Reductions are warp shuffles in a fixed order (deterministic totals).
 //
-// How a ray is marched (checkVisibilityWithRaycasting, :754-800):
-//   1. setup in double exactly as upstream: d, L, unit direction u = d / L, end = L - vis_radius; the number of
-//      samples n = #{k : s_k < end} comes from the table of the upstream accumulation s_0 = start, s_{k+1} = s_k + step.
-//   2. the sample range is clipped to the box that holds everything within reach of a terrain point
-//      (samples outside are clear by construction), conservatively, in float32.
-//   3. inside the clipped range the sample position is tracked in 16.16 fixed point in fine-voxel
-//      units (three integer adds per step).  Its error against the upstream double position is a
-//      few 1e-6 m and is covered by the slack of the occupancy structure (plc_voxel.cu), so
-//      "clear" and "certainly blocked" voxel states decide the sample without the exact position.
-//   4. a sample in an uncertain voxel needs the exact float32 test on the exact upstream position
-//      (double -> float32 narrowing, :774-777).  Doing that in place would idle the other 31 lanes
-//      for the length of a point list, so the sample is pushed into a per-warp queue in shared
-//      memory and the ray keeps marching; the queue is drained 32 samples at a time, one per lane.
-//      A ray's outcome (first blocked sample index, or none) is settled when the block's rays are
-//      finalised, after the last drain.
-// The visibility bit is the upstream one bit for bit; the evaluated-sample counter is the index
-// of the first blocked sample + 1, which is what the sequential upstream loop would have counted.
-constexpr int kQueueCap = 64;                    // ring buffer, power of two, >= 2 * 32
+// Float first, exact on demand.  Upstream does everything in double (d, L = sqrt, u = d / L, sample
+// positions) and narrows each sample position to float32 for the radius search (:754-800).  Only a
+// few of those double results can change an output bit, so the kernel computes a float32 version of
+// each with a rigorous error bound and redoes it exactly as upstream only where the bound does not
+// decide:
+//   range gate, sample count n   from Lf = |d|f (relative error < 1e-6): decided unless L is within
+//                                the bound of min/max_distance or of a sample parameter s_k + vis_radius;
+//                                otherwise the lane recomputes L = sqrt_rn(...) and counts from the
+//                                table of the upstream accumulation s_{k+1} = s_k + step (rare).
+//   FOV gate                     sign of sin(elevation - e_lo), sin(e_hi - elevation) (k_pose_prep),
+//                                upstream atan2 in double inside a 2e-5 L band.
+//   sample positions             float32 direction, range clipped to the box that holds everything
+//                                within reach of a terrain point, then 16.16 fixed point in fine-voxel
+//                                units (three integer adds per step).  The position error (a few 1e-5 m)
+//                                is part of the slack of the occupancy structure (plc_voxel.cu), so
+//                                "clear" and "certainly blocked" voxels decide a sample as they are.
+//   uncertain samples (~3 %)     (ray, k) is pushed to a per-warp ring in shared memory and the ray
+//                                keeps marching.  The ring is drained 32 entries at a time, one per
+//                                lane: the lane recomputes that ray in double exactly as upstream
+//                                (d, L, u, position of sample k narrowed to float32) and runs the
+//                                exact float32 test over one candidate list.
+//   score                        for rays that end up visible, in double from d and L (:689-700).
+// A ray's outcome — first blocked sample index, or none — lives in shared memory until the block's
+// rays are finalised in cell order.  The visibility bit is the upstream one bit for bit; the
+// evaluated-sample counter is the first blocked index + 1 (or n), what the sequential upstream loop counts.
+constexpr int kQueueCap = 128;                   // ring buffer of (ray slot << 16 | sample index), power of two
 constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not blocked (so far), low bits = n
 
 #ifndef PLC_SWEEP_BLOCKS_PER_SM
@@ -275,10 +286,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
         int* __restrict__ partial_cov, uint32_t* __restrict__ mask, unsigned mask_words,
         SweepResult* __restrict__ res) {
-    __shared__ float4 q_pos[kQueueCap];          // exact sample position; w = (ray slot << 16 | sample index) bits
-    __shared__ uint32_t q_mid[kQueueCap];        // mid voxel whose candidate list decides the sample
-    __shared__ int ray_state[kTileCells];        // first blocked sample index, or kOpen + n
-    __shared__ double ray_score_if_visible[kTileCells];
+    __shared__ uint32_t q_tag[kQueueCap];
+    __shared__ int ray_state[kTileCells];        // -1 gated out; first blocked sample index; or kOpen + n
 
     const unsigned FULL = 0xffffffffu;
     unsigned local = blockIdx.x / tiles, tile = blockIdx.x - local * tiles;
@@ -288,27 +297,41 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     const int lane = threadIdx.x;
     const unsigned lt_mask = (1u << lane) - 1u;
     const float sf[3] = {(float)s.x, (float)s.y, (float)s.z};
+    // sensor position relative to the grid origin, in fine voxels (exact subtraction, then narrowed)
+    const float sof[3] = {(float)(s.x - (double)G.ox) * G.inv_g, (float)(s.y - (double)G.oy) * G.inv_g,
+                          (float)(s.z - (double)G.oz) * G.inv_g};
     bool s_in[3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) s_in[a] = sf[a] >= G.clip_lo[a] && sf[a] <= G.clip_hi[a];
     // float32 clipping is only trusted to keep the march inside the grid at ordinary scene scale
     const bool trust_clip = fabsf(sf[0]) < P.trust_limit && fabsf(sf[1]) < P.trust_limit && fabsf(sf[2]) < P.trust_limit;
-    const double fscale = (double)G.inv_g * 65536.0;
     unsigned gated = 0;
     unsigned long long exact = 0;
     int q_head = 0, q_n = 0;
 
-    // resolves up to 32 queued samples, one per lane
+    // resolves up to 32 queued samples, one per lane, exactly as upstream evaluates them
     auto drain = [&]() {
+        __syncwarp();
         int take = q_n < 32 ? q_n : 32;
         if (lane < take) {
-            int at = (q_head + lane) & (kQueueCap - 1);
-            float4 e = q_pos[at];
-            unsigned tag = __float_as_uint(e.w);
-            int slot = (int)(tag >> 16), k = (int)(tag & 0xffffu);
-            if (ray_state[slot] > k) {               // not already blocked earlier on the ray
+            unsigned tag = q_tag[(q_head + lane) & (kQueueCap - 1)];
+            int eslot = (int)(tag >> 16), ek = (int)(tag & 0xffffu);
+            if (ray_state[eslot] > ek) {             // not already blocked earlier on the ray
                 ++exact;
-                if (cand_any_m(G, q_mid[at], e.x, e.y, e.z, P.thr_block)) atomicMin(&ray_state[slot], k);
+                const unsigned long long* cp = reinterpret_cast<const unsigned long long*>(cells + (tile * kTileCells + eslot));
+                double ex = __dsub_rn(__longlong_as_double((long long)__ldg(cp)), s.x);
+                double ey = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 1)), s.y);
+                double ez = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 2)), s.z);
+                double eL = ray_length(ex, ey, ez);
+                double t = __ldg(&P.s_tab[ek]);
+                float qx = (float)__dadd_rn(s.x, __dmul_rn(__ddiv_rn(ex, eL), t));      // :770-777
+                float qy = (float)__dadd_rn(s.y, __dmul_rn(__ddiv_rn(ey, eL), t));
+                float qz = (float)__dadd_rn(s.z, __dmul_rn(__ddiv_rn(ez, eL), t));
+                // candidate list of the sample's own mid voxel (clamped: the march kept it inside the grid)
+                int ix = clamp_i((int)fine_coord_f(qx, G.ox, G.inv_g), 0, (G.dim_x << kFineShift) - 1);
+                int iy = clamp_i((int)fine_coord_f(qy, G.oy, G.inv_g), 0, (G.dim_y << kFineShift) - 1);
+                int iz = clamp_i((int)fine_coord_f(qz, G.oz, G.inv_g), 0, (G.dim_z << kFineShift) - 1);
+                if (cand_any(G, ix, iy, iz, qx, qy, qz, P.thr_block)) atomicMin(&ray_state[eslot], ek);
             }
         }
         __syncwarp();
@@ -321,17 +344,49 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         const int slot = r * 32 + lane;
         unsigned j = tile * kTileCells + slot;
         const bool valid = j < n_cells;
-        // ---- evaluateCellScore gates (:656-678)
-        plc_cell c = load_cell(cells, valid ? j : 0);
-        double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
-        double L = ray_length(dx, dy, dz);
-        bool pass = valid && (L >= P.min_distance && L <= P.max_distance);
+        // ---- evaluateCellScore gates (:656-678): range
+        const unsigned long long* cp = reinterpret_cast<const unsigned long long*>(cells + (valid ? j : 0));
+        double dx = __dsub_rn(__longlong_as_double((long long)__ldg(cp)), s.x);
+        double dy = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 1)), s.y);
+        double dz = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 2)), s.z);
+        const float df[3] = {(float)dx, (float)dy, (float)dz};
+        const float hd2 = df[0] * df[0] + df[1] * df[1];
+        const float L2f = hd2 + df[2] * df[2];
+        const float rinv = rsqrtf(L2f);
+        const float Lf = L2f * rinv;
+        const float errL = 1e-6f * Lf + 1e-7f;           // |Lf - L| bound (float32 products, sums and rsqrt)
+        bool pass = false, redo = false;
+        int n = 0;
+        if (Lf - errL >= P.min_hi && Lf + errL <= P.max_lo) pass = true;
+        else if (!(Lf + errL < P.min_lo || Lf - errL > P.max_hi)) redo = true;      // NaN lands here too
+        if (pass && P.have_terrain) {
+            // n = #{k : s_k < L - vis_radius} = #{k >= 0 : k < kf}
+            float kf = (Lf - P.vis_start_f) * P.inv_stepf;
+            float tolk = (errL + 1e-6f) * P.inv_stepf + fabsf(kf) * 3e-7f + 1e-5f;
+            if (fabsf(kf - rintf(kf)) <= tolk) redo = true;
+            else n = kf > 0.f ? min((int)ceilf(kf), P.n_tab - 1) : 0;
+        }
+        if (redo) {                                       // as upstream, in double (rare)
+            double L = ray_length(dx, dy, dz);
+            pass = L >= P.min_distance && L <= P.max_distance;
+            n = 0;
+            if (pass && P.have_terrain) {
+                double end = __dsub_rn(L, P.vis_radius);
+                if (end > P.ray_start) {
+                    n = (int)(__dsub_rn(end, P.ray_start) * P.inv_step) + 1;
+                    n = max(0, min(n, P.n_tab - 1));
+                    while (n > 0 && !(__ldg(&P.s_tab[n - 1]) < end)) --n;
+                    while (n < P.n_tab - 1 && __ldg(&P.s_tab[n]) < end) ++n;
+                }
+            }
+        }
+        pass = pass && valid;
+        // ---- FOV (:671-678, :703-714)
         if (pass) {
             bool decided = false;
             if (A.fast) {
-                float dzf = (float)dz, Lf = (float)L;
-                float hd = sqrtf(fmaxf(0.f, (float)__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy))));
-                float a = dzf * A.c_lo - hd * A.s_lo, b = hd * A.s_hi - dzf * A.c_hi;
+                float hd = sqrtf(hd2);
+                float a = df[2] * A.c_lo - hd * A.s_lo, b = hd * A.s_hi - df[2] * A.c_hi;
                 float tol = 2e-5f * Lf;
                 if (a > tol && b > tol) decided = true;
                 else if (a < -tol || b < -tol) { decided = true; pass = false; }
@@ -339,34 +394,21 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             if (!decided) pass = in_fov_exact(P, s.pitch, s.yaw, dx, dy, dz);
         }
         gated += pass ? 1u : 0u;
+        ray_state[slot] = pass ? kOpen + n : -1;        // published before any of the ray's samples can be queued
 
-        // ---- checkVisibilityWithRaycasting (:754-800)
-        double ux = 0, uy = 0, uz = 0;
-        int n = 0, k = 0, k_hi = 0, blocked_k = -1, pend_k = -1;
+        // ---- checkVisibilityWithRaycasting (:754-800): clear / certain samples here, uncertain ones queued
+        int k = 0, k_hi = 0;
         int fx = 0, fy = 0, fz = 0, dfx = 0, dfy = 0, dfz = 0;
-        if (pass) {
-            ux = __ddiv_rn(dx, L);
-            uy = __ddiv_rn(dy, L);
-            uz = __ddiv_rn(dz, L);
-        }
-        if (pass && P.have_terrain) {
-            double end = __dsub_rn(L, P.vis_radius);
-            // n = #{k : s_k < end}
-            if (end > P.ray_start) {
-                n = (int)(__dsub_rn(end, P.ray_start) * P.inv_step) + 1;
-                n = max(0, min(n, P.n_tab - 1));
-                while (n > 0 && !(__ldg(&P.s_tab[n - 1]) < end)) --n;
-                while (n < P.n_tab - 1 && __ldg(&P.s_tab[n]) < end) ++n;
-            }
-            // clip [0, n) against the reach box (float32, conservative by clip_t metres); an axis
-            // on which both the sensor and the target lie inside the box's slab cannot bind
-            float uf[3] = {(float)ux, (float)uy, (float)uz};
-            float cf[3] = {(float)c.x, (float)c.y, (float)c.z};
+        if (pass && n > 0) {
+            const float uf[3] = {df[0] * rinv, df[1] * rinv, df[2] * rinv};
+            // clip [0, n) against the reach box (conservative by clip_t metres); an axis on which both
+            // the sensor and the target lie inside the box's slab cannot bind
             float t_in = 0.f, t_out = 3.0e38f;
             bool miss = false;
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
-                if (s_in[a] && cf[a] >= G.clip_lo[a] && cf[a] <= G.clip_hi[a]) continue;
+                const float ca = sf[a] + df[a];
+                if (s_in[a] && ca >= G.clip_lo[a] && ca <= G.clip_hi[a]) continue;
                 if (fabsf(uf[a]) > 1e-12f) {
                     float inv = __fdividef(1.0f, uf[a]);
                     float t0 = (G.clip_lo[a] - sf[a]) * inv, t1 = (G.clip_hi[a] - sf[a]) * inv;
@@ -376,57 +418,57 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     miss = true;
                 }
             }
-            const float startf = (float)P.ray_start, inv_stepf = (float)P.inv_step;
-            float klo_f = ceilf((t_in - G.clip_t - startf) * inv_stepf);
-            float khi_f = floorf((t_out + G.clip_t - startf) * inv_stepf) + 1.0f;
+            float klo_f = ceilf((t_in - G.clip_t - P.startf) * P.inv_stepf);
+            float khi_f = floorf((t_out + G.clip_t - P.startf) * P.inv_stepf) + 1.0f;
             k = (int)fminf(fmaxf(klo_f, 0.f), (float)n);
             k_hi = miss ? k : (int)fminf(fmaxf(khi_f, 0.f), (float)n);
             if (k < k_hi) {
                 // fixed-point fine-voxel coordinate of sample k and its per-step increment
-                double t0 = __ldg(&P.s_tab[k]);
-                fx = __double2int_rd(((s.x + ux * t0) - (double)G.ox) * fscale);
-                fy = __double2int_rd(((s.y + uy * t0) - (double)G.oy) * fscale);
-                fz = __double2int_rd(((s.z + uz * t0) - (double)G.oz) * fscale);
-                dfx = __double2int_rn(ux * P.ray_step * fscale);
-                dfy = __double2int_rn(uy * P.ray_step * fscale);
-                dfz = __double2int_rn(uz * P.ray_step * fscale);
+                const float t0 = fmaf((float)k, P.stepf, P.startf);
+                fx = __float2int_rd(fmaf(uf[0] * G.inv_g, t0, sof[0]) * 65536.f);
+                fy = __float2int_rd(fmaf(uf[1] * G.inv_g, t0, sof[1]) * 65536.f);
+                fz = __float2int_rd(fmaf(uf[2] * G.inv_g, t0, sof[2]) * 65536.f);
+                dfx = __float2int_rn(uf[0] * P.step_fine);
+                dfy = __float2int_rn(uf[1] * P.step_fine);
+                dfz = __float2int_rn(uf[2] * P.step_fine);
                 // Both ends of the clipped range lie inside the grid by construction as long as float32
                 // resolves clip_t at the scene's coordinates (trust_limit).  Beyond that the ends are checked,
                 // and a ray that leaves the grid is marched sample by sample with bounds-checked lookups.
                 if (!trust_clip) {
-                const long long steps = k_hi - 1 - k;
-                const long long lx = fx + steps * dfx, ly = fy + steps * dfy, lz = fz + steps * dfz;
-                const long long mx = (long long)G.dim_x << (kFineShift + kFixedBits),
-                                my = (long long)G.dim_y << (kFineShift + kFixedBits),
-                                mz = (long long)G.dim_z << (kFineShift + kFixedBits);
-                if (fx < 0 || fy < 0 || fz < 0 || fx >= mx || fy >= my || fz >= mz || lx < 0 || ly < 0 || lz < 0 ||
-                    lx >= mx || ly >= my || lz >= mz) {
-                    RayStats st;
-                    bool clear = ray_clear(P, s.x, s.y, s.z, dx, dy, dz, L, st);
-                    blocked_k = clear ? -1 : (int)st.samples - 1;
-                    exact += st.exact;
-                    k = k_hi = 0;
-                }
+                    const long long steps = k_hi - 1 - k;
+                    const long long lx = fx + steps * dfx, ly = fy + steps * dfy, lz = fz + steps * dfz;
+                    const long long mx = (long long)G.dim_x << (kFineShift + kFixedBits),
+                                    my = (long long)G.dim_y << (kFineShift + kFixedBits),
+                                    mz = (long long)G.dim_z << (kFineShift + kFixedBits);
+                    if (fx < 0 || fy < 0 || fz < 0 || fx >= mx || fy >= my || fz >= mz || lx < 0 || ly < 0 || lz < 0 ||
+                        lx >= mx || ly >= my || lz >= mz) {
+                        RayStats st;
+                        bool clear = ray_clear(P, s.x, s.y, s.z, dx, dy, dz, ray_length(dx, dy, dz), st);
+                        if (!clear) ray_state[slot] = (int)st.samples - 1;
+                        exact += st.exact;
+                        k = k_hi = 0;
+                    }
                 }
             }
         }
-        // the ray's state is published before any of its samples can be queued
-        ray_state[slot] = blocked_k >= 0 ? blocked_k : kOpen + n;
+        __syncwarp();
         bool active = k < k_hi;
-        bool stalled = false;
         for (;;) {
-            while (__any_sync(FULL, active)) {
+            while (q_n + 32 <= kQueueCap) {               // room for one more push from every lane
+                if (!__any_sync(FULL, active)) break;
+                unsigned st = 0;
+                if (active) st = voxel_state(G, fx >> kFixedBits, fy >> kFixedBits, fz >> kFixedBits);
+                unsigned ub = __ballot_sync(FULL, st == 1u);
+                if (ub) {
+                    if (st == 1u)
+                        q_tag[(q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)] = ((unsigned)slot << 16) | (unsigned)k;
+                    q_n += __popc(ub);
+                }
                 if (active) {
-                    int ix = fx >> kFixedBits, iy = fy >> kFixedBits, iz = fz >> kFixedBits;
-                    unsigned st = voxel_state(G, ix, iy, iz);
                     if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
-                        blocked_k = k;
-                        active = false;
-                    } else if (st == 1u && pend_k >= 0) { // a second uncertain sample: queue the first one first
-                        stalled = true;
+                        atomicMin(&ray_state[slot], k);
                         active = false;
                     } else {
-                        if (st == 1u) pend_k = k;
                         ++k;
                         fx += dfx;
                         fy += dfy;
@@ -435,43 +477,14 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     }
                 }
             }
-            // queue the parked samples: exact upstream position, and the mid voxel the march saw
-            // (its list holds every point within reach of the voxel's box, and the exact position
-            // lies inside that box up to the slack)
-            bool need = pend_k >= 0;
-            unsigned nb = __ballot_sync(FULL, need);
-            if (nb == 0) break;
-            if (q_n + __popc(nb) > kQueueCap) drain();
-            if (need) {
-                double t = __ldg(&P.s_tab[pend_k]);
-                float qx = (float)__dadd_rn(s.x, __dmul_rn(ux, t));
-                float qy = (float)__dadd_rn(s.y, __dmul_rn(uy, t));
-                float qz = (float)__dadd_rn(s.z, __dmul_rn(uz, t));
-                int back = k - pend_k;
-                int px = fx - back * dfx, py = fy - back * dfy, pz = fz - back * dfz;
-                int at = (q_head + q_n + __popc(nb & lt_mask)) & (kQueueCap - 1);
-                q_pos[at] = make_float4(qx, qy, qz, __uint_as_float(((unsigned)slot << 16) | (unsigned)pend_k));
-                q_mid[at] = mid_voxel_of(G, px >> kFixedBits, py >> kFixedBits, pz >> kFixedBits);
-                pend_k = -1;
-                if (stalled) {
-                    stalled = false;
-                    active = true;                        // re-examines sample k, which parks it
-                }
-            }
-            q_n += __popc(nb);
-            __syncwarp();
+            if (q_n >= 32) drain();
             if (!__any_sync(FULL, active)) break;
         }
-        if (blocked_k >= 0) atomicMin(&ray_state[slot], blocked_k);
-        else if (pass) ray_score_if_visible[slot] = unit_score(P, ux, uy, uz, L, c.nx, c.ny, c.nz);
-        // incidence + range score (:689-700), used only if the ray turns out visible
-        if (!pass) ray_state[slot] = -1;                         // gated out: blocked "before the first sample"
-        __syncwarp();
-        if (q_n >= 32) drain();
     }
     while (q_n > 0) drain();
+    __syncwarp();
 
-    // ---- per-candidate accumulation (:639-644), rays in cell order
+    // ---- score (:689-700) and per-candidate accumulation (:639-644), rays in cell order
     double total = 0.0;
     int covered = 0;
     unsigned nvis = 0;
@@ -484,7 +497,17 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         bool vis = st >= kOpen;
         if (st >= 0 && P.have_terrain) samples += (unsigned)(vis ? st - kOpen : st + 1);
         if (j < n_cells) {
-            double mobile = vis ? ray_score_if_visible[slot] : 0.0;
+            double mobile = 0.0;
+            if (vis) {
+                plc_cell c = load_cell(cells, j);
+                double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
+                double L = ray_length(dx, dy, dz);
+                // |b.n| with b = d / L: one division instead of upstream's three, same value to ~3 ulp
+                double dn = __dadd_rn(__dadd_rn(__dmul_rn(dx, (double)c.nx), __dmul_rn(dy, (double)c.ny)), __dmul_rn(dz, (double)c.nz));
+                double rl = __ddiv_rn(1.0, L);
+                double cc = fmax(0.0, fmin(1.0, fabs(dn) * rl));
+                mobile = fmax(0.0, __dadd_rn(__dmul_rn(P.alpha, cc), __dmul_rn(P.beta, rl)));
+            }
             double combined = fmax(__ldg(&fixed_scores[j]), mobile);     // :639
             if (combined > 0) {                                          // :641-644
                 ++covered;
@@ -666,12 +689,17 @@ size_t sample_table_size(const plc_params* p) {
 }
 
 plc_status build_terrain_index(plc_ctx* ctx, const plc_params* p) {
-    // error of k_sweep's 16.16 fixed-point position in fine-voxel units: origin 1, each step 1/2
+    // position error of k_sweep's march against the upstream double position:
+    //   16.16 fixed point, in fine voxels: origin 1, each step 1/2;
+    //   float32 direction (< 1e-6 relative) and sample parameter over a ray of at most max_distance, and the
+    //   float32 grid-relative origin and sum (the builder adds the grid-extent term itself), in metres
     const double march_err = (2.0 + 0.5 * (double)sample_table_size(p)) / 65536.0;
-    return voxel_build(ctx, ctx->terrain, p->vis_radius * p->block_radius_scale, block_threshold(p), march_err);
+    const double march_err_m = 3e-6 * p->max_distance + 2e-6;
+    return voxel_build(ctx, ctx->terrain, p->vis_radius * p->block_radius_scale, block_threshold(p), march_err,
+                       march_err_m);
 }
 plc_status build_observed_index(plc_ctx* ctx, const plc_params* p) {
-    return voxel_build(ctx, ctx->observed, p->vis_radius * p->observed_radius_scale, observed_threshold(p), 0.0);
+    return voxel_build(ctx, ctx->observed, p->vis_radius * p->observed_radius_scale, observed_threshold(p), 0.0, 0.0);
 }
 
 // s_0 = ray_start, s_{k+1} = s_k + ray_step, accumulated in double exactly as the upstream loop does
@@ -785,6 +813,15 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     P.s_tab = ctx->s_tab.as<double>();
     P.n_tab = ctx->n_tab;
     P.inv_step = 1.0 / p.ray_step;
+    P.min_hi = ceil_to_float(p.min_distance);
+    P.min_lo = -ceil_to_float(-p.min_distance);
+    P.max_hi = ceil_to_float(p.max_distance);
+    P.max_lo = -ceil_to_float(-p.max_distance);
+    P.vis_start_f = (float)(p.vis_radius + p.ray_start);
+    P.startf = (float)p.ray_start;
+    P.stepf = (float)p.ray_step;
+    P.inv_stepf = (float)(1.0 / p.ray_step);
+    P.step_fine = (float)(p.ray_step * (double)P.terrain.inv_g * 65536.0);
     {
         double max_abs = p.max_distance;
         for (int a = 0; a < 6; ++a) max_abs = std::max(max_abs, (double)std::fabs(ctx->terrain.bbox[a]));

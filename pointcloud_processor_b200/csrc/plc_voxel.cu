@@ -276,24 +276,30 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
     return PLC_OK;
 }
 
-plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err) {
+plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err, double march_err_m) {
     if (!ix.has_points()) return PLC_OK;
-    if (ix.built_radius == radius && ix.built_thr == thr && march_err <= ix.built_march_err) return PLC_OK;
-    if (!(radius > 0) || !std::isfinite(radius) || !(thr >= 0) || !(march_err >= 0)) return PLC_E_INVALID_ARG;
+    if (ix.built_radius == radius && ix.built_thr == thr && march_err <= ix.built_march_err &&
+        march_err_m <= ix.built_march_err_m)
+        return PLC_OK;
+    if (!(radius > 0) || !std::isfinite(radius) || !(thr >= 0) || !(march_err >= 0) || !(march_err_m >= 0))
+        return PLC_E_INVALID_ARG;
 
     // real-number reach that covers everything the float32 test can accept, plus the slack that
     // absorbs float rounding of the voxel coordinate and the error of the fixed-point march
     const float r2f = static_cast<float>(radius * radius);
     double max_abs = 0.0;
     for (int a = 0; a < 6; ++a) max_abs = std::max(max_abs, (double)std::fabs(ix.bbox[a]));
-    const double slack0 = 1e-4 + max_abs * 4.8e-7;
+    double extent = 0.0;
+    for (int a = 0; a < 3; ++a) extent = std::max(extent, (double)ix.bbox[3 + a] - (double)ix.bbox[a]);
+    // float32 rounding of a query coordinate (absolute) and of a grid-relative march position (extent)
+    const double slack0 = 1e-4 + max_abs * 4.8e-7 + (extent + 2.0) * 6e-7;
     const double r_out = std::sqrt((double)r2f) * (1.0 + 1e-6);
     // h >= 2^-6 keeps the clip margins (h/16, h/32) far above float rounding at scene scale
     double h = std::max(std::exp2(std::ceil(std::log2(2.0 * (r_out + slack0)))), 1.0 / 64.0);
     double org[3], reach = 0.0, slack = 0.0;
     long long dim[3];
     for (;;) {
-        slack = slack0 + (h / 8.0) * march_err;
+        slack = slack0 + (h / 8.0) * march_err + march_err_m;
         reach = r_out + slack;
         if (h < 2.0 * reach) {
             h *= 2.0;
@@ -398,6 +404,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     ix.built_radius = radius;
     ix.built_thr = thr;
     ix.built_march_err = march_err;
+    ix.built_march_err_m = march_err_m;
     return PLC_OK;
 }
 
