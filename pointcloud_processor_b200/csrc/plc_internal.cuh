@@ -52,9 +52,8 @@ struct DevBuf {
 
 // Geometry of a voxel index, passed to kernels by value.
 //   coarse voxel edge h (a power of two >= 2*reach), mid voxel h/2, fine voxel g = h/8, shared origin.
-//   coarse[(z*dim_y + y)*wdim_x + (x>>5)] = {bits, base}: bit (x&31) clear = no point within reach of
-//              any position in the coarse voxel (certainly clear); set = the voxel owns brick
-//              base + popc(bits below it).  8 bytes per 32 coarse voxels, so this level lives in L1.
+//   bricks are stored densely, brick b = (cz*dim_y + cy)*dim_x + cx: one 128-byte line per coarse voxel, so a
+//   sample's state is ONE load and the samples of neighbouring rays share lines.
 //   bricks[32*b + (fz&7)*4 + ((fy&7)>>1)], 2 bits per fine voxel at bit 2*(((fy&1)<<3) | (fx&7)):
 //              bit 0  a sample in the fine voxel MAY be within the radius of a point
 //                     (conservative dilation of the points by `reach`)
@@ -71,12 +70,10 @@ struct VoxelGeom {
     float inv_g;             // 1/g (power of two)
     float reach;             // real-number radius + slack used by the builder
     int dim_x, dim_y, dim_z; // coarse dims
-    int wdim_x;              // ceil(dim_x / 32): words per coarse x row
     int mdim_x, mdim_y, mdim_z;   // mid dims = 2*coarse
     float fdim_xf, fdim_yf, fdim_zf;   // fine dims = 8*coarse, as float for the bounds test
     float clip_lo[3], clip_hi[3];      // box outside which no position is within reach of a point
     float clip_t;                      // slack (m along the ray) the clipped sample range may overshoot by
-    const uint2* __restrict__ coarse;
     const uint32_t* __restrict__ bricks;
     const uint32_t* __restrict__ gstart;
     const float4* __restrict__ cgrp;
@@ -94,19 +91,17 @@ struct VoxelIndex {
     double built_march_err = 0.0; // position error of the caller's march covered by the slack: in fine voxels ...
     double built_march_err_m = 0.0;   // ... plus in metres
     double h = 0.0;
-    DevBuf coarse, bricks, gstart, cfill, cgrp, scan_tmp;
+    DevBuf bricks, gstart, cfill, cgrp, scan_tmp;
     VoxelGeom geom{};
     uint64_t n_vox = 0;       // coarse voxels
-    uint64_t n_words = 0;     // coarse bitmap words
-    uint64_t n_bricks = 0;    // coarse voxels with a brick
     uint64_t n_groups = 0;    // 4-point groups in cgrp
     bool has_points() const { return n_raw > 0; }
-    // compact size of the structure (points once + occupancy), the "G" term of the algorithmic bytes
-    uint64_t bytes() const { return n_raw * 16 + n_words * 8 + n_bricks * 128; }
+    // the "G" term of the algorithmic bytes: the indexed points, once (a lower bound of what the sweep must read)
+    uint64_t bytes() const { return n_raw * 16; }
     // what is actually resident (candidate lists replicate a point into every mid voxel in reach)
-    uint64_t resident_bytes() const { return n_words * 8 + n_bricks * 128 + (n_vox * 8 + 1) * 4 + n_groups * 48; }
+    uint64_t resident_bytes() const { return n_vox * 128 + (n_vox * 8 + 1) * 4 + n_groups * 48; }
     void release() {
-        raw.release(); coarse.release(); bricks.release(); gstart.release(); cfill.release(); cgrp.release();
+        raw.release(); bricks.release(); gstart.release(); cfill.release(); cgrp.release();
         scan_tmp.release();
     }
 };

@@ -352,7 +352,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         const float df[3] = {(float)dx, (float)dy, (float)dz};
         const float hd2 = df[0] * df[0] + df[1] * df[1];
         const float L2f = hd2 + df[2] * df[2];
-        const float rinv = rsqrtf(L2f);
+        const float rinv = __frsqrt_rn(L2f);          // L2f = 0 or overflow gives inf/NaN: every test below then fails over to `redo`
         const float Lf = L2f * rinv;
         const float errL = 1e-6f * Lf + 1e-7f;           // |Lf - L| bound (float32 products, sums and rsqrt)
         bool pass = false, redo = false;
@@ -385,7 +385,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         if (pass) {
             bool decided = false;
             if (A.fast) {
-                float hd = sqrtf(hd2);
+                float hd = hd2 * __frsqrt_rn(hd2);        // hd2 = 0 (vertical ray) gives NaN: not decided => exact path
                 float a = df[2] * A.c_lo - hd * A.s_lo, b = hd * A.s_hi - df[2] * A.c_hi;
                 float tol = 2e-5f * Lf;
                 if (a > tol && b > tol) decided = true;
@@ -501,10 +501,11 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             if (vis) {
                 plc_cell c = load_cell(cells, j);
                 double dx = __dsub_rn(c.x, s.x), dy = __dsub_rn(c.y, s.y), dz = __dsub_rn(c.z, s.z);
-                double L = ray_length(dx, dy, dz);
-                // |b.n| with b = d / L: one division instead of upstream's three, same value to ~3 ulp
+                // 1 / L by reciprocal square root and two Newton steps (~2 ulp); |b.n| with b = d / L taken as
+                // |d.n| / L: the score agrees with upstream's sqrt + three divisions to a few ulp (tolerance 1e-12)
+                double L2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+                double rl = rsqrt(L2);
                 double dn = __dadd_rn(__dadd_rn(__dmul_rn(dx, (double)c.nx), __dmul_rn(dy, (double)c.ny)), __dmul_rn(dz, (double)c.nz));
-                double rl = __ddiv_rn(1.0, L);
                 double cc = fmax(0.0, fmin(1.0, fabs(dn) * rl));
                 mobile = fmax(0.0, __dadd_rn(__dmul_rn(P.alpha, cc), __dmul_rn(P.beta, rl)));
             }

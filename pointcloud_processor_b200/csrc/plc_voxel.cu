@@ -2,8 +2,7 @@
 //
 // Replaces the KD-tree builds of terrainCallback / zx120PointsCallback
 // (/root/reference/src/virtual_lidar.cpp:180-207).  Instead of a tree, points are counting-sorted
-// into a uniform grid: coarse voxels that can hold a blocked sample own a brick of 8x8x8 fine voxels
-// with two bits each — "a sample here may be within the radius of a point" (conservative dilation)
+// into a uniform grid: every coarse voxel is a 128-byte brick of 8x8x8 fine voxels with two bits each — "a sample here may be within the radius of a point" (conservative dilation)
 // and "a sample here certainly is" (conservative erosion) — and every mid voxel (4x4x4 fine voxels)
 // owns the list of points within reach of its box.  Most samples of a ray are resolved by one or
 // two word loads; only samples in the thin uncertain shell run the exact float32 test, over one list.
@@ -13,7 +12,6 @@
 //   k_candidates<false>  per-mid-voxel candidate counts                            N*16 rd, <=27 atomics/pt
 //   k_scan_*    exclusive scan of the counts (3 passes)                            ~3*8V*4
 //   k_candidates<true>   points into their candidate lists (SoA groups of 4)       N*16 rd, <=27*12 wr/pt
-//   k_mark_coarse / k_coarse_counts / k_coarse_pack   coarse voxels that need a brick: bitmap + brick base per 32
 //   k_dilate    2-bit fine-voxel states within reach of each point                 N*16 rd, ~100 atomicOr/pt
 #include <algorithm>
 #include <cmath>
@@ -157,39 +155,6 @@ __global__ void __launch_bounds__(256) k_fill_f32(float* __restrict__ p, size_t 
     for (; i < n; i += stride) p[i] = v;
 }
 
-// Marks every coarse voxel that the reach box of a point touches (at most 2x2x2: reach < h/2):
-// one bit per coarse voxel, 32 consecutive x per word.
-__global__ void __launch_bounds__(256)
-k_mark_coarse(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double h,
-              uint32_t* __restrict__ bits) {
-    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float4 p = raw[i];
-    double px = (double)p.x - (double)g.ox, py = (double)p.y - (double)g.oy, pz = (double)p.z - (double)g.oz;
-    int x0 = max(0, (int)floor((px - reach) / h)), x1 = min(g.dim_x - 1, (int)floor((px + reach) / h));
-    int y0 = max(0, (int)floor((py - reach) / h)), y1 = min(g.dim_y - 1, (int)floor((py + reach) / h));
-    int z0 = max(0, (int)floor((pz - reach) / h)), z1 = min(g.dim_z - 1, (int)floor((pz + reach) / h));
-    for (int z = z0; z <= z1; ++z)
-        for (int y = y0; y <= y1; ++y)
-            for (int x = x0; x <= x1; ++x)
-                atomicOr(&bits[((size_t)z * g.dim_y + y) * g.wdim_x + (x >> 5)], 1u << (x & 31));
-}
-
-__global__ void __launch_bounds__(256)
-k_coarse_counts(const uint32_t* __restrict__ bits, size_t n_words, uint32_t* __restrict__ counts) {
-    size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (w < n_words) counts[w] = __popc(bits[w]);
-    if (w == n_words) counts[w] = 0;
-}
-
-// coarse[w] = {occupancy bits of 32 coarse voxels, index of the first one's brick}
-__global__ void __launch_bounds__(256)
-k_coarse_pack(const uint32_t* __restrict__ bits, const uint32_t* __restrict__ base, size_t n_words,
-              uint2* __restrict__ coarse) {
-    size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (w < n_words) coarse[w] = make_uint2(bits[w], base[w]);
-}
-
 // Two bits per fine voxel (double arithmetic; `reach` and `inner` already contain the slack that
 // covers float rounding in fine_coord_f / the fixed-point march):
 //   bit 0 where the voxel's box comes within `reach` of the point,
@@ -312,7 +277,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
             cells *= (double)dim[a];
         }
         // fine coordinates must fit the march's signed 16.16 fixed point with room to spare
-        bool fits = cells <= 2.5e8 && dim[0] <= 3600 && dim[1] <= 3600 && dim[2] <= 3600;
+        bool fits = cells <= 1.6e7 && dim[0] <= 3600 && dim[1] <= 3600 && dim[2] <= 3600;
         if (fits) break;
         h *= 2.0;    // coarser voxels only make the lists longer, never incomplete
     }
@@ -323,11 +288,8 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     const unsigned n = (unsigned)ix.n_raw;
     const double gsz = h / 8.0;
 
-    const size_t wdim_x = (size_t)(dim[0] + 31) / 32;
-    const size_t n_words = wdim_x * dim[1] * dim[2];
-    PLC_CUDA_TRY(ctx, ix.coarse.reserve(n_words * 8));
     PLC_CUDA_TRY(ctx, ix.gstart.reserve((n_mid + 1) * 4));
-    PLC_CUDA_TRY(ctx, ix.cfill.reserve(std::max(n_mid, 2 * n_words + 2) * 4));
+    PLC_CUDA_TRY(ctx, ix.cfill.reserve(n_mid * 4));
     PLC_CUDA_TRY(ctx, ix.scan_tmp.reserve(scan_tmp_bytes(n_mid + 1)));
 
     VoxelGeom g{};
@@ -339,7 +301,6 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     g.dim_x = (int)dim[0];
     g.dim_y = (int)dim[1];
     g.dim_z = (int)dim[2];
-    g.wdim_x = (int)wdim_x;
     g.mdim_x = g.dim_x * 2;
     g.mdim_y = g.dim_y * 2;
     g.mdim_z = g.dim_z * 2;
@@ -351,41 +312,31 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
         g.clip_hi[a] = (float)((double)ix.bbox[3 + a] + reach + h / 16.0);
     }
     g.clip_t = (float)(h / 32.0);
-    g.coarse = ix.coarse.as<uint2>();
     g.gstart = ix.gstart.as<uint32_t>();
     g.bricks = nullptr;
     g.cgrp = nullptr;
 
     cudaStream_t s = ctx->stream;
     unsigned pb = (n + 255) / 256;
-    // ---- occupancy: coarse flags -> brick ids -> 2-bit fine states
-    uint32_t* cbits = ix.cfill.as<uint32_t>();    // scratch until the candidate fill pass needs it
-    uint32_t* ids = cbits + n_words;
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(cbits, 0, n_words * 4, s));
-    k_mark_coarse<<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h, cbits);
-    k_coarse_counts<<<(unsigned)((n_words + 256) / 256), 256, 0, s>>>(cbits, n_words, ids);
-    scan_exclusive_u32(ids, n_words + 1, ix.scan_tmp.as<uint32_t>(), s);
-    k_coarse_pack<<<(unsigned)((n_words + 255) / 256), 256, 0, s>>>(cbits, ids, n_words, ix.coarse.as<uint2>());
     // ---- candidate lists: counts -> offsets
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.gstart.ptr, 0, (n_mid + 1) * 4, s));
     k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.gstart.as<uint32_t>(),
                                            nullptr, nullptr);
-    ctx->launches += 7;
+    ctx->launches += 1;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     uint32_t* totals = static_cast<uint32_t*>(ctx->pinned);
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ids + n_words, 4, cudaMemcpyDeviceToHost, s));
     k_counts_to_groups<<<(unsigned)((n_mid + 255) / 256), 256, 0, s>>>(ix.gstart.as<uint32_t>(), n_mid);
     scan_exclusive_u32(ix.gstart.as<uint32_t>(), n_mid + 1, ix.scan_tmp.as<uint32_t>(), s);
     ctx->launches += 4;
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals + 1, ix.gstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ix.gstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
-    const size_t n_bricks = totals[0], n_groups = totals[1];
-    PLC_CUDA_TRY(ctx, ix.bricks.reserve(std::max<size_t>(n_bricks, 1) * 128));
+    const size_t n_groups = totals[0];
+    PLC_CUDA_TRY(ctx, ix.bricks.reserve(n_vox * 128));
     PLC_CUDA_TRY(ctx, ix.cgrp.reserve(std::max<size_t>(n_groups, 1) * 48));
     g.bricks = ix.bricks.as<uint32_t>();
     g.cgrp = ix.cgrp.as<float4>();
     k_fill_f32<<<148 * 8, 256, 0, s>>>(ix.cgrp.as<float>(), n_groups * 12, INFINITY);
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, std::max<size_t>(n_bricks, 1) * 128, s));
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, n_vox * 128, s));
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
     const int slices = (int)std::floor(2.0 * reach / gsz) + 2;
     const unsigned long long dthreads = (unsigned long long)n * (unsigned)slices;
@@ -398,8 +349,6 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     ix.geom = g;
     ix.h = h;
     ix.n_vox = n_vox;
-    ix.n_words = n_words;
-    ix.n_bricks = n_bricks;
     ix.n_groups = n_groups;
     ix.built_radius = radius;
     ix.built_thr = thr;

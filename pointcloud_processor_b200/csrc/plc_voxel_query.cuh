@@ -4,10 +4,9 @@
 // indexed point p satisfy  d2_f32(q,p) < thr  with  d2 = ((dx*dx)+(dy*dy))+(dz*dz)  evaluated in
 // float32 without FMA (FLANN L2_Simple<float>, strict compare as RadiusResultSet does).
 //
-// Three levels, all addressed from the fine-voxel coordinate of q (edge g, a power of two):
-//   coarse  one bit per coarse voxel (8x8x8 fine voxels): clear = nothing within reach; set = it owns
-//           a brick, found by popcount from the word's base index
-//   brick   two bits per fine voxel: clear / uncertain / certainly blocked (plc_internal.cuh)
+// Two levels, both addressed from the fine-voxel coordinate of q (edge g, a power of two):
+//   brick   two bits per fine voxel, 8x8x8 fine voxels per 128-byte brick, bricks stored densely:
+//           clear / uncertain / certainly blocked (plc_internal.cuh)
 //   cand    per mid voxel (4x4x4 fine voxels): the points within reach of its box, stored
 //           contiguously in SoA groups of four (a point appears in up to 27 lists) — the exact
 //           test scans just that list
@@ -18,6 +17,20 @@
 #include "plc_internal.cuh"
 
 namespace plc {
+
+// Read-only loads that do not allocate in L1: candidate lists and cell records are touched once per
+// block, while the occupancy words they would evict are reused by neighbouring rays.
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ unsigned long long ldg_stream(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
 
 __device__ __forceinline__ float dist2_f32(float qx, float qy, float qz, float px, float py, float pz) {
     float ex = __fsub_rn(qx, px), ey = __fsub_rn(qy, py), ez = __fsub_rn(qz, pz);
@@ -35,19 +48,15 @@ __device__ __forceinline__ float fine_coord_f(float v, float origin, float inv_g
 
 __device__ __forceinline__ int clamp_i(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
-// Brick of coarse voxel (cx, cy, cz); the voxel must own one (its occupancy bit is set).
+// Brick of coarse voxel (cx, cy, cz): bricks are stored densely, x fastest.
 __device__ __forceinline__ uint32_t brick_of(const VoxelGeom& g, int cx, int cy, int cz) {
-    uint2 e = __ldg(&g.coarse[(unsigned)((cz * g.dim_y + cy) * g.wdim_x + (cx >> 5))]);
-    return e.y + __popc(e.x & ((1u << (cx & 31)) - 1u));
+    return (uint32_t)((cz * g.dim_y + cy) * g.dim_x + cx);
 }
 
 // State of fine voxel (ix, iy, iz): 0 clear, 1 uncertain (run the exact test), 3 certainly blocked.
+// One load: brick word ((iz&7)*4 + (iy&7)/2) of the voxel's coarse cell.
 __device__ __forceinline__ unsigned voxel_state(const VoxelGeom& g, int ix, int iy, int iz) {
-    int cx = ix >> kFineShift;
-    uint2 e = __ldg(&g.coarse[(unsigned)(((iz >> kFineShift) * g.dim_y + (iy >> kFineShift)) * g.wdim_x + (cx >> 5))]);
-    unsigned bit = 1u << (cx & 31);
-    if (!(e.x & bit)) return 0;
-    unsigned brick = e.y + __popc(e.x & (bit - 1u));
+    unsigned brick = brick_of(g, ix >> kFineShift, iy >> kFineShift, iz >> kFineShift);
     uint32_t w = __ldg(&g.bricks[(size_t)brick * 32 + (((iz & 7) << 2) | ((iy & 7) >> 1))]);
     return (w >> (2 * (((iy & 1) << 3) | (ix & 7)))) & 3u;
 }
@@ -61,7 +70,7 @@ __device__ __forceinline__ bool cand_any_m(const VoxelGeom& g, uint32_t m, float
     uint32_t s = __ldg(&g.gstart[m]), e = __ldg(&g.gstart[m + 1]);
     const float4* __restrict__ grp = g.cgrp + (size_t)s * 3;
     for (; s < e; ++s, grp += 3) {
-        float4 X = __ldg(grp), Y = __ldg(grp + 1), Z = __ldg(grp + 2);
+        float4 X = ldg_stream(grp), Y = ldg_stream(grp + 1), Z = ldg_stream(grp + 2);
         float d0 = dist2_f32(qx, qy, qz, X.x, Y.x, Z.x), d1 = dist2_f32(qx, qy, qz, X.y, Y.y, Z.y);
         float d2 = dist2_f32(qx, qy, qz, X.z, Y.z, Z.z), d3 = dist2_f32(qx, qy, qz, X.w, Y.w, Z.w);
         if (fminf(fminf(d0, d1), fminf(d2, d3)) < thr) return true;

@@ -8,12 +8,10 @@ def line_of(pat, after=0):
         if i + 1 > after and pat in l: return i + 1
     raise KeyError(pat)
 k0 = line_of("k_sweep(SweepDev P")
-marks = [("prologue", k0), ("drain lambda", line_of("auto drain")), ("load cell + gates", line_of("for (int r = 0; r < kRaysPerThread", k0)),
-         ("u = d/L", line_of("checkVisibilityWithRaycasting (:754", k0)), ("n samples", line_of("n = #{k", k0)),
-         ("clip", line_of("clip [0, n)", k0)), ("fixed-point init", line_of("fixed-point fine-voxel coordinate", k0)),
-         ("state publish", line_of("the ray's state is published", k0)), ("march loop", line_of("while (__any_sync(FULL, active))", k0)),
-         ("queue push", line_of("queue the parked samples", k0)), ("post march", line_of("if (blocked_k >= 0) atomicMin", k0)),
-         ("finalise", line_of("while (q_n > 0) drain", k0)), ("end", line_of("// per candidate: tiles summed"))]
+marks = [("prologue", k0), ("drain (exact recompute)", line_of("auto drain")), ("load + range/n", line_of("for (int r = 0; r < kRaysPerThread", k0)),
+         ("FOV", line_of("---- FOV", k0)), ("clip + init", line_of("checkVisibilityWithRaycasting (:754-800): clear", k0)),
+         ("march loop", line_of("bool active = k < k_hi;", k0)),
+         ("finalise + score", line_of("while (q_n > 0) drain", k0)), ("end", line_of("// per candidate: tiles summed"))]
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass,cuda"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hi = next(i for i, r in enumerate(rows) if "Instructions Executed" in r)
