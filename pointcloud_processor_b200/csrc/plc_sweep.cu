@@ -50,6 +50,13 @@ struct SweepDev {
     float min_lo, min_hi, max_lo, max_hi, vis_start_f, startf, stepf, inv_stepf, step_fine;
 };
 
+// MUFU.RSQ (2 ulp); denormal inputs flush to zero, which the callers treat like zero anyway
+__device__ __forceinline__ float rsqrt_fast(float v) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+    return r;
+}
+
 struct RayStats {
     unsigned samples = 0;
     unsigned long long exact = 0;
@@ -352,7 +359,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         const float df[3] = {(float)dx, (float)dy, (float)dz};
         const float hd2 = df[0] * df[0] + df[1] * df[1];
         const float L2f = hd2 + df[2] * df[2];
-        const float rinv = __frsqrt_rn(L2f);          // L2f = 0 or overflow gives inf/NaN: every test below then fails over to `redo`
+        const float rinv = rsqrt_fast(L2f);           // L2f = 0 or overflow gives inf/NaN: every test below then fails over to `redo`
         const float Lf = L2f * rinv;
         const float errL = 1e-6f * Lf + 1e-7f;           // |Lf - L| bound (float32 products, sums and rsqrt)
         bool pass = false, redo = false;
@@ -385,7 +392,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         if (pass) {
             bool decided = false;
             if (A.fast) {
-                float hd = hd2 * __frsqrt_rn(hd2);        // hd2 = 0 (vertical ray) gives NaN: not decided => exact path
+                float hd = hd2 * rsqrt_fast(hd2);         // hd2 = 0 (vertical ray) gives NaN: not decided => exact path
                 float a = df[2] * A.c_lo - hd * A.s_lo, b = hd * A.s_hi - df[2] * A.c_hi;
                 float tol = 2e-5f * Lf;
                 if (a > tol && b > tol) decided = true;
