@@ -287,21 +287,29 @@ constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not bloc
 #ifndef PLC_SWEEP_BLOCKS_PER_SM
 #define PLC_SWEEP_BLOCKS_PER_SM 32
 #endif
-__global__ void __launch_bounds__(32, PLC_SWEEP_BLOCKS_PER_SM)
+#ifndef PLC_SWEEP_WARPS
+#define PLC_SWEEP_WARPS 1
+#endif
+constexpr int kSweepWarps = PLC_SWEEP_WARPS;     // independent warps per block (no block-level synchronisation)
+__global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin,
-        unsigned tiles, const plc_cell* __restrict__ cells, unsigned n_cells,
+        unsigned tiles, unsigned n_work, const plc_cell* __restrict__ cells, unsigned n_cells,
         const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
         int* __restrict__ partial_cov, uint32_t* __restrict__ mask, unsigned mask_words,
         SweepResult* __restrict__ res) {
-    __shared__ uint32_t q_tag[kQueueCap];
-    __shared__ int ray_state[kTileCells];        // -1 gated out; first blocked sample index; or kOpen + n
+    __shared__ uint32_t q_tag_all[kSweepWarps][kQueueCap];
+    __shared__ int ray_state_all[kSweepWarps][kTileCells];   // -1 gated out; first blocked sample index; or kOpen + n
+    uint32_t* const q_tag = q_tag_all[threadIdx.x >> 5];
+    int* const ray_state = ray_state_all[threadIdx.x >> 5];
+    const unsigned wid = blockIdx.x * kSweepWarps + (threadIdx.x >> 5);      // this warp's (candidate, tile) index
+    if (wid >= n_work) return;
 
     const unsigned FULL = 0xffffffffu;
-    unsigned local = blockIdx.x / tiles, tile = blockIdx.x - local * tiles;
+    unsigned local = wid / tiles, tile = wid - local * tiles;
     const plc_pose s = cands[cand_begin + local];
     const PoseAux A = aux[local];
     const VoxelGeom& G = P.terrain;
-    const int lane = threadIdx.x;
+    const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     const float sf[3] = {(float)s.x, (float)s.y, (float)s.z};
     // sensor position relative to the grid origin, in fine voxels (exact subtraction, then narrowed)
@@ -539,8 +547,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         exact += __shfl_down_sync(FULL, exact, o);
     }
     if (lane == 0) {
-        partial_score[blockIdx.x] = total;
-        partial_cov[blockIdx.x] = covered;
+        partial_score[wid] = total;
+        partial_cov[wid] = covered;
         if (gated) atomicAdd(&res->rays_gated_in, (unsigned long long)gated);
         if (nvis) atomicAdd(&res->rays_visible, (unsigned long long)nvis);
         if (samples) atomicAdd(&res->samples, samples);
@@ -884,8 +892,8 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
             carveout_set = true;
         }
         cudaEventRecord(ctx->ev_sweep_begin, s);
-        k_sweep<<<n_local * tiles, 32, 0, s>>>(
-            P, ctx->cands.as<plc_pose>(), ctx->pose_aux.as<PoseAux>(), (unsigned)ctx->cand_begin, tiles,
+        k_sweep<<<(n_local * tiles + kSweepWarps - 1) / kSweepWarps, 32 * kSweepWarps, 0, s>>>(
+            P, ctx->cands.as<plc_pose>(), ctx->pose_aux.as<PoseAux>(), (unsigned)ctx->cand_begin, tiles, n_local * tiles,
             ctx->cells.as<plc_cell>(), M,
             ctx->fixed_scores.as<double>(), ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
             want_mask ? ctx->mask.as<uint32_t>() : nullptr, (unsigned)ctx->mask_words, res);
