@@ -48,6 +48,11 @@ struct SweepDev {
     // float32 views of the gates for k_sweep's float-first path: min/max_distance rounded down and up,
     // vis_radius + ray_start, ray_start, ray_step and its inverse, ray_step in 16.16 fine-voxel units
     float min_lo, min_hi, max_lo, max_hi, vis_start_f, startf, stepf, inv_stepf, step_fine;
+    // float32 cell positions relative to cell_ref (the centre of the cells' bounding box), one float4 per
+    // cell, and the radius of that box: k_sweep's float-first path reads these instead of the doubles
+    const float4* __restrict__ cells_f;
+    double cell_ref[3];
+    float cells_radius;
 };
 
 // MUFU.RSQ (2 ulp); denormal inputs flush to zero, which the callers treat like zero anyway
@@ -231,16 +236,36 @@ k_fixed(SweepDev P, plc_pose fixed, const plc_cell* __restrict__ cells, unsigned
 struct PoseAux {
     float c_lo, s_lo, c_hi, s_hi;
     int fast;        // 0: always take the exact path for this pose
-    int pad[3];
+    float eabs;      // bound on |d_float - d| for this pose's rays (metres), see k_sweep
+    float sr[3];     // sensor position relative to SweepDev::cell_ref
+    float sof[3];    // sensor position relative to the terrain grid origin, in fine voxels
+    float sf[3];     // sensor position
+    int pad;
 };
+static_assert(sizeof(PoseAux) == 64, "PoseAux is read as four 16-byte words");
 
 __global__ void __launch_bounds__(128)
 k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned n_local,
             PoseAux* __restrict__ aux) {
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_local) return;
-    double pitch = cands[cand_begin + i].pitch;
+    const plc_pose s = cands[cand_begin + i];
+    double pitch = s.pitch;
     PoseAux a{};
+    const VoxelGeom& G = P.terrain;
+    const double sd[3] = {s.x, s.y, s.z};
+    const float go[3] = {G.ox, G.oy, G.oz};
+    float rn = 0.f;
+    for (int k = 0; k < 3; ++k) {
+        a.sf[k] = (float)sd[k];
+        a.sr[k] = (float)(sd[k] - P.cell_ref[k]);
+        // exact subtraction, then narrowed
+        a.sof[k] = (float)(sd[k] - (double)go[k]) * G.inv_g;
+        rn += fabsf(a.sr[k]);
+    }
+    // d_float = fl(fl(c - ref) - fl(s - ref)): each narrowing is within 2^-24 of its operand, so the
+    // vector error is below 1.2e-7 (|c - ref| + |s - ref|); doubled, plus the absolute floor of before
+    a.eabs = 2.5e-7f * (P.cells_radius + rn) + 1e-7f;
     double lo = pitch - P.half_fov_v, hi = pitch + P.half_fov_v;
     a.fast = (P.half_fov_h < 0.0 && isfinite(pitch) && lo <= M_PI_2 && hi >= -M_PI_2) ? 1 : 0;
     double e_lo = fmax(-M_PI_2, lo), e_hi = fmin(M_PI_2, hi);
@@ -249,6 +274,15 @@ k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin,
     a.c_hi = (float)cos(e_hi);
     a.s_hi = (float)sin(e_hi);
     aux[i] = a;
+}
+
+// float32 copy of the cell positions relative to `ref` (exact subtraction in double, one narrowing)
+__global__ void __launch_bounds__(256)
+k_cells_f32(const plc_cell* __restrict__ cells, unsigned n, double rx, double ry, double rz, float4* __restrict__ out) {
+    unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    plc_cell c = load_cell(cells, j);
+    out[j] = make_float4((float)(c.x - rx), (float)(c.y - ry), (float)(c.z - rz), 0.f);
 }
 
 // ---- K2+K3: one thread per (candidate, cell) ray ----------------------------------------------
@@ -311,10 +345,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     const VoxelGeom& G = P.terrain;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
-    const float sf[3] = {(float)s.x, (float)s.y, (float)s.z};
-    // sensor position relative to the grid origin, in fine voxels (exact subtraction, then narrowed)
-    const float sof[3] = {(float)(s.x - (double)G.ox) * G.inv_g, (float)(s.y - (double)G.oy) * G.inv_g,
-                          (float)(s.z - (double)G.oz) * G.inv_g};
+    const float sf[3] = {A.sf[0], A.sf[1], A.sf[2]};
+    const float sof[3] = {A.sof[0], A.sof[1], A.sof[2]};
     bool s_in[3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) s_in[a] = sf[a] >= G.clip_lo[a] && sf[a] <= G.clip_hi[a];
@@ -323,6 +355,14 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     unsigned gated = 0;
     unsigned long long exact = 0;
     int q_head = 0, q_n = 0;
+
+    // d = cell - sensor exactly as upstream forms it (:660-664)
+    auto exact_d = [&](unsigned cell, double& dx, double& dy, double& dz) {
+        const unsigned long long* cp = reinterpret_cast<const unsigned long long*>(cells + cell);
+        dx = __dsub_rn(__longlong_as_double((long long)__ldg(cp)), s.x);
+        dy = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 1)), s.y);
+        dz = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 2)), s.z);
+    };
 
     // resolves up to 32 queued samples, one per lane, exactly as upstream evaluates them
     auto drain = [&]() {
@@ -333,10 +373,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             int eslot = (int)(tag >> 16), ek = (int)(tag & 0xffffu);
             if (ray_state[eslot] > ek) {             // not already blocked earlier on the ray
                 ++exact;
-                const unsigned long long* cp = reinterpret_cast<const unsigned long long*>(cells + (tile * kTileCells + eslot));
-                double ex = __dsub_rn(__longlong_as_double((long long)__ldg(cp)), s.x);
-                double ey = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 1)), s.y);
-                double ez = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 2)), s.z);
+                double ex, ey, ez;
+                exact_d(tile * kTileCells + eslot, ex, ey, ez);
                 double eL = ray_length(ex, ey, ez);
                 double t = __ldg(&P.s_tab[ek]);
                 float qx = (float)__dadd_rn(s.x, __dmul_rn(__ddiv_rn(ex, eL), t));      // :770-777
@@ -360,16 +398,14 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         unsigned j = tile * kTileCells + slot;
         const bool valid = j < n_cells;
         // ---- evaluateCellScore gates (:656-678): range
-        const unsigned long long* cp = reinterpret_cast<const unsigned long long*>(cells + (valid ? j : 0));
-        double dx = __dsub_rn(__longlong_as_double((long long)__ldg(cp)), s.x);
-        double dy = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 1)), s.y);
-        double dz = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 2)), s.z);
-        const float df[3] = {(float)dx, (float)dy, (float)dz};
+        const unsigned jc = valid ? j : 0;
+        const float4 cf = __ldg(&P.cells_f[jc]);
+        const float df[3] = {cf.x - A.sr[0], cf.y - A.sr[1], cf.z - A.sr[2]};
         const float hd2 = df[0] * df[0] + df[1] * df[1];
         const float L2f = hd2 + df[2] * df[2];
         const float rinv = rsqrt_fast(L2f);           // L2f = 0 or overflow gives inf/NaN: every test below then fails over to `redo`
         const float Lf = L2f * rinv;
-        const float errL = 1e-6f * Lf + 1e-7f;           // |Lf - L| bound (float32 products, sums and rsqrt)
+        const float errL = 1e-6f * Lf + A.eabs;          // |Lf - L| bound (float32 cell/sensor offsets, products, sums and rsqrt)
         bool pass = false, redo = false;
         int n = 0;
         if (Lf - errL >= P.min_hi && Lf + errL <= P.max_lo) pass = true;
@@ -382,6 +418,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             else n = kf > 0.f ? min((int)ceilf(kf), P.n_tab - 1) : 0;
         }
         if (redo) {                                       // as upstream, in double (rare)
+            double dx, dy, dz;
+            exact_d(jc, dx, dy, dz);
             double L = ray_length(dx, dy, dz);
             pass = L >= P.min_distance && L <= P.max_distance;
             n = 0;
@@ -402,11 +440,15 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             if (A.fast) {
                 float hd = hd2 * rsqrt_fast(hd2);         // hd2 = 0 (vertical ray) gives NaN: not decided => exact path
                 float a = df[2] * A.c_lo - hd * A.s_lo, b = hd * A.s_hi - df[2] * A.c_hi;
-                float tol = 2e-5f * Lf;
+                float tol = 2e-5f * Lf + 4.f * A.eabs;
                 if (a > tol && b > tol) decided = true;
                 else if (a < -tol || b < -tol) { decided = true; pass = false; }
             }
-            if (!decided) pass = in_fov_exact(P, s.pitch, s.yaw, dx, dy, dz);
+            if (!decided) {
+                double dx, dy, dz;
+                exact_d(jc, dx, dy, dz);
+                pass = in_fov_exact(P, s.pitch, s.yaw, dx, dy, dz);
+            }
         }
         gated += pass ? 1u : 0u;
         ray_state[slot] = pass ? kOpen + n : -1;        // published before any of the ray's samples can be queued
@@ -458,6 +500,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     if (fx < 0 || fy < 0 || fz < 0 || fx >= mx || fy >= my || fz >= mz || lx < 0 || ly < 0 || lz < 0 ||
                         lx >= mx || ly >= my || lz >= mz) {
                         RayStats st;
+                        double dx, dy, dz;
+                        exact_d(jc, dx, dy, dz);
                         bool clear = ray_clear(P, s.x, s.y, s.z, dx, dy, dz, ray_length(dx, dy, dz), st);
                         if (!clear) ray_state[slot] = (int)st.samples - 1;
                         exact += st.exact;
@@ -468,18 +512,12 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         }
         __syncwarp();
         bool active = k < k_hi;
-        for (;;) {
+        bool more = __any_sync(FULL, active);
+        while (more) {
             while (q_n + 32 <= kQueueCap) {               // room for one more push from every lane
-                if (!__any_sync(FULL, active)) break;
                 unsigned st = 0;
-                if (active) st = voxel_state(G, fx >> kFixedBits, fy >> kFixedBits, fz >> kFixedBits);
-                unsigned ub = __ballot_sync(FULL, st == 1u);
-                if (ub) {
-                    if (st == 1u)
-                        q_tag[(q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)] = ((unsigned)slot << 16) | (unsigned)k;
-                    q_n += __popc(ub);
-                }
                 if (active) {
+                    st = voxel_state(G, fx >> kFixedBits, fy >> kFixedBits, fz >> kFixedBits);
                     if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
                         atomicMin(&ray_state[slot], k);
                         active = false;
@@ -491,9 +529,16 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                         active = k < k_hi;
                     }
                 }
+                unsigned ub = __ballot_sync(FULL, st == 1u);     // lanes whose sample k - 1 was uncertain
+                if (ub) {
+                    if (st == 1u)
+                        q_tag[(q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)] = ((unsigned)slot << 16) | (unsigned)(k - 1);
+                    q_n += __popc(ub);
+                }
+                more = __any_sync(FULL, active);
+                if (!more) break;
             }
             if (q_n >= 32) drain();
-            if (!__any_sync(FULL, active)) break;
         }
     }
     while (q_n > 0) drain();
@@ -521,10 +566,14 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 double L2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
                 double rl = rsqrt(L2);
                 double dn = __dadd_rn(__dadd_rn(__dmul_rn(dx, (double)c.nx), __dmul_rn(dy, (double)c.ny)), __dmul_rn(dz, (double)c.nz));
-                double cc = fmax(0.0, fmin(1.0, fabs(dn) * rl));
-                mobile = fmax(0.0, __dadd_rn(__dmul_rn(P.alpha, cc), __dmul_rn(P.beta, rl)));
+                // clamp(|b.n|, 0, 1) and max(0, score) (:692-699); the operands are never NaN for a visible ray
+                double cc = __dmul_rn(fabs(dn), rl);
+                cc = cc < 1.0 ? cc : 1.0;
+                mobile = __dadd_rn(__dmul_rn(P.alpha, cc), __dmul_rn(P.beta, rl));
+                mobile = mobile > 0.0 ? mobile : 0.0;
             }
-            double combined = fmax(__ldg(&fixed_scores[j]), mobile);     // :639
+            const double fixed = __ldg(&fixed_scores[j]);
+            double combined = mobile > fixed ? mobile : fixed;           // :639
             if (combined > 0) {                                          // :641-644
                 ++covered;
                 total = __dadd_rn(total, combined);
@@ -710,7 +759,10 @@ plc_status build_terrain_index(plc_ctx* ctx, const plc_params* p) {
     //   float32 direction (< 1e-6 relative) and sample parameter over a ray of at most max_distance, and the
     //   float32 grid-relative origin and sum (the builder adds the grid-extent term itself), in metres
     const double march_err = (2.0 + 0.5 * (double)sample_table_size(p)) / 65536.0;
-    const double march_err_m = 3e-6 * p->max_distance + 2e-6;
+    // ... and k_sweep's float32 ray (PoseAux::eabs), for cells within 16 m of their centre at least so that
+    // a terrain set before the cells is not rebuilt for them
+    const double cells_radius = std::fmax(16.0, (double)ctx->cells_radius);
+    const double march_err_m = 3e-6 * p->max_distance + 2e-6 + 2.5e-7 * (2.0 * cells_radius + 2.0 * p->max_distance) + 1e-7;
     return voxel_build(ctx, ctx->terrain, p->vis_radius * p->block_radius_scale, block_threshold(p), march_err,
                        march_err_m);
 }
@@ -780,6 +832,29 @@ extern "C" plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint
     PLC_CUDA_TRY(ctx, ctx->fixed_scores.reserve(n_cells * sizeof(double)));
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->cells.ptr, cells, n_cells * sizeof(plc_cell), cudaMemcpyHostToDevice, ctx->stream));
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ctx->cell_flags.ptr, 0, n_cells, ctx->stream));   // GridCell ctor: all false (:37-39)
+    // reference point and radius of the float32 copy: centre and half diagonal of the finite cells' box
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (uint64_t j = 0; j < n_cells; ++j) {
+        const double v[3] = {cells[j].x, cells[j].y, cells[j].z};
+        if (!(std::isfinite(v[0]) && std::isfinite(v[1]) && std::isfinite(v[2]))) continue;
+        for (int a = 0; a < 3; ++a) {
+            lo[a] = v[a] < lo[a] ? v[a] : lo[a];
+            hi[a] = v[a] > hi[a] ? v[a] : hi[a];
+        }
+    }
+    double r2 = 0.0;
+    for (int a = 0; a < 3; ++a) {
+        const bool any = lo[a] <= hi[a];
+        ctx->cell_ref[a] = any ? 0.5 * (lo[a] + hi[a]) : 0.0;
+        const double half = any ? 0.5 * (hi[a] - lo[a]) : 0.0;
+        r2 += half * half;
+    }
+    ctx->cells_radius = ceil_to_float(std::sqrt(r2));
+    PLC_CUDA_TRY(ctx, ctx->cells_f.reserve(n_cells * sizeof(float4)));
+    k_cells_f32<<<(unsigned)((n_cells + 255) / 256), 256, 0, ctx->stream>>>(
+        ctx->cells.as<plc_cell>(), (unsigned)n_cells, ctx->cell_ref[0], ctx->cell_ref[1], ctx->cell_ref[2],
+        ctx->cells_f.as<float4>());
+    PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->n_cells = n_cells;
     return PLC_OK;
@@ -838,6 +913,9 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     P.stepf = (float)p.ray_step;
     P.inv_stepf = (float)(1.0 / p.ray_step);
     P.step_fine = (float)(p.ray_step * (double)P.terrain.inv_g * 65536.0);
+    P.cells_f = ctx->cells_f.as<float4>();
+    for (int a = 0; a < 3; ++a) P.cell_ref[a] = ctx->cell_ref[a];
+    P.cells_radius = ctx->cells_radius;
     {
         double max_abs = p.max_distance;
         for (int a = 0; a < 6; ++a) max_abs = std::max(max_abs, (double)std::fabs(ctx->terrain.bbox[a]));
