@@ -320,6 +320,8 @@ def run_ours(args) -> dict | None:
     }
     if north is not None:
         line["north_star_cfg3"] = north
+    if not args.no_feeders:
+        line["feeders"] = measure_feeders(ctx, scene, peak)
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         v, n, dt = cpu_reference_sample(scene, args.cpu_budget, threads)
@@ -332,6 +334,55 @@ def run_ours(args) -> dict | None:
     if world > 1:
         dist.destroy_process_group()
     return line
+
+
+def measure_feeders(ctx, scene, peak, reps: int = 5) -> dict:
+    """The secondary kernels of the path on config 4's inputs: crop + voxel downsample of two
+    1 M-point scans (K6+K7), the merge into the map frame (K8), and the occupancy build the sweep starts from
+    (K1).  Kernel time is the library's own CUDA-event time per call (copies excluded); wall time is the
+    C-ABI call with host buffers.  Algorithmic bytes per SURVEY D4."""
+    from pointcloud_processor_b200 import scenes
+    from pointcloud_processor_b200.nodes import filter_scan, merge_clouds
+    zt, zq = scenes.sensor_in_map(dict(xyz=(0.0, 0.0, 0.0), yaw=0.0), scenes.ZX120_VELODYNE)
+    rt, rq = scenes.sensor_in_map(scenes.ROBOT_BASE, scenes.ROBOT_VELODYNE)
+    scans = [scenes.lidar_scan(rt, rq, 1_000_000, 4, "rect"), scenes.lidar_scan(zt, zq, 1_000_000, 5, "rect")]
+
+    def best(fn, key):
+        ks, ws, out = [], [], None
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            out = fn()
+            ws.append((time.perf_counter() - t0) * 1e3)
+            ks.append(ctx.device_times()[key])
+        return out, float(np.median(ks)), float(np.median(ws))
+
+    def row(kernel_ms, wall_ms, alg_bytes, units, unit_name):
+        gbs = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+        return {"kernel_ms": kernel_ms, "wall_ms": wall_ms, f"{unit_name}_per_s": units / (kernel_ms * 1e-3) if kernel_ms > 0 else 0.0,
+                "algorithmic_bytes": int(alg_bytes), "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / peak}
+
+    out = {"config": "cfg4: two 1M-point 32-ring scans -> crop 15/10/10 -> voxel 0.2 -> merge; K1 on this workload's terrain"}
+    filtered = []
+    for name, scan in zip(("robot", "zx120"), scans):
+        f, k_ms, w_ms = best(lambda: filter_scan(ctx, scan), "filter_ms")
+        p = scan[:, :3].astype(np.float64)
+        m_crop = int(np.count_nonzero((p[:, 0] > 0) & (p[:, 0] < 15) & (np.abs(p[:, 1]) < 10) & (p[:, 2] > -1.5) & (p[:, 2] < 10)))
+        v = int(f.shape[0])
+        alg = scan.shape[0] * 12 + m_crop * 12 + m_crop * 12 + v * 12      # K6 + K7
+        r = row(k_ms, w_ms, alg, scan.shape[0], "points")
+        r.update(points_in=int(scan.shape[0]), cropped=m_crop, voxels=v)
+        out[f"filter_{name}"] = r
+        filtered.append(f)
+    (merged, _, _), k_ms, w_ms = best(lambda: merge_clouds(ctx, dict(cloud=filtered[0], t=rt, q=rq),
+                                                          dict(cloud=filtered[1], t=zt, q=zq)), "merge_ms")
+    v = int(merged.shape[0])
+    out["merge"] = row(k_ms, w_ms, v * 12 + v * 16 * 2, v, "points")
+    out["merge"]["points_in"] = v
+    _, k_ms, w_ms = best(lambda: ctx.set_terrain(scene.terrain), "set_terrain_ms")
+    n = int(scene.terrain.shape[0])
+    out["voxelise_terrain"] = row(k_ms, w_ms, n * (12 + 16), n, "points")
+    out["voxelise_terrain"]["points_in"] = n
+    return out
 
 
 def run_reference(args) -> dict | None:
@@ -384,6 +435,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-north-star", action="store_true", help="skip the extra configs[2] measurement")
+    ap.add_argument("--no-feeders", action="store_true", help="skip the crop/voxel/merge/voxelise measurements (config 4)")
     args = ap.parse_args()
     line = run_reference(args) if args.impl == "reference" else run_ours(args)
     if line is not None:

@@ -178,6 +178,19 @@ plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr);
 plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms);
 
 /* Grid facts for roofline accounting: bytes of the occupancy structure the sweep reads. */
+/* Device time (ms, CUDA events on the context's stream) spent in the kernels of the most recent call of each
+ * kind; host<->device copies and host-side waits are excluded.  0 until that call has run.  For benchmarks and
+ * profiles: the reference has no counterpart. */
+typedef struct plc_device_times {
+    float set_terrain_ms;   /* plc_vl_set_terrain: extraction + occupancy/candidate-list build (K1) */
+    float set_observed_ms;  /* plc_vl_set_observed */
+    float filter_ms;        /* plc_filter: crop (K6) + voxel downsample (K7) */
+    float merge_ms;         /* plc_merge: transform + colour + concatenate (K8) */
+    float sweep_kernel_ms;  /* k_sweep of the last plc_vl_sweep / plc_vl_run_async */
+    float reserved[3];
+} plc_device_times;
+plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out);
+
 typedef struct plc_grid_info {
     uint64_t n_points;        /* finite points indexed */
     uint64_t n_voxels;        /* coarse voxels */

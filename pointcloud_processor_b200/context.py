@@ -153,6 +153,12 @@ class Context:
         self._check(self._L.plc_vl_last_sweep_kernel_ms(self._h, C.byref(ms)), "plc_vl_last_sweep_kernel_ms")
         return float(ms.value)
 
+    def device_times(self) -> dict:
+        """Kernel time (ms) of the last call of each kind, host<->device copies excluded."""
+        t = A.DeviceTimes()
+        self._check(self._L.plc_last_device_times(self._h, C.byref(t)), "plc_last_device_times")
+        return {k: float(getattr(t, k)) for k, _ in A.DeviceTimes._fields_ if k != "reserved"}
+
     def grid_info(self):
         t, o = A.GridInfo(), A.GridInfo()
         self._check(self._L.plc_vl_grid_info(self._h, C.byref(t), C.byref(o)), "plc_vl_grid_info")

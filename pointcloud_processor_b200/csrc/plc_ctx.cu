@@ -91,6 +91,7 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
                            &c->m_out};
     for (plc::DevBuf* b : bufs) b->release();
     if (c->pinned) cudaFreeHost(c->pinned);
+    c->timer.destroy();
     if (c->ev_sweep_begin) cudaEventDestroy(c->ev_sweep_begin);
     if (c->ev_sweep_end) cudaEventDestroy(c->ev_sweep_end);
     if (c->own_stream) cudaStreamDestroy(c->stream);

@@ -187,6 +187,9 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     FilterState* st = ctx->scratch.as<FilterState>();
     const unsigned blocks1 = (n + 1 + 255) / 256;
 
+    ctx->timer.reset();
+    ctx->times.filter_ms = 0.f;
+    ctx->timer.begin(s);
     k_filter_state_init<<<1, 1, 0, s>>>(st);
     k_crop_flag<<<blocks1, 256, 0, s>>>(ctx->upload.as<unsigned char>(), n, in->point_step, in->off_x, in->off_y,
                                         in->off_z, aligned, cb, flag);
@@ -194,6 +197,7 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     k_crop_compact<<<(n + 255) / 256, 256, 0, s>>>(ctx->upload.as<unsigned char>(), n, in->point_step, in->off_x,
                                                    in->off_y, in->off_z, aligned, flag, cropped, st);
     ctx->launches += 6;
+    ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
 
     struct HostState { FilterState st; uint32_t total; };
@@ -202,6 +206,7 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(&host->total, flag + n, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     const unsigned m = host->total;
+    ctx->times.filter_ms = ctx->timer.total_ms();
     if (n_cropped) *n_cropped = m;
     if (m == 0) return PLC_OK;                      // downsampleCloud returns the empty input (:125-127, Q7)
 
@@ -246,6 +251,7 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     PLC_CUDA_TRY(ctx, ctx->f_vals2.reserve((size_t)m * 4 + sort_table_entries(m) * 4));
     uint32_t* table = ctx->f_vals2.as<uint32_t>() + m;
     const unsigned mb = (m + 255) / 256;
+    ctx->timer.begin(s);
     k_voxel_keys<<<mb, 256, 0, s>>>(cropped, m, vd, ctx->f_keys.as<uint32_t>(), ctx->f_vals.as<uint32_t>());
     ctx->launches += 1;
     int where = radix_sort_pairs(ctx->f_keys.as<uint32_t>(), ctx->f_vals.as<uint32_t>(), ctx->f_keys2.as<uint32_t>(),
@@ -256,8 +262,10 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     scan_exclusive_u32(flag, (size_t)m + 1, scan_tmp, s);
     k_centroid<<<mb, 256, 0, s>>>(skeys, svals, m, flag, cropped, centroids);
     ctx->launches += 5;
+    ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(&host->total, flag + m, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    ctx->times.filter_ms = ctx->timer.total_ms();
     return copy_out(centroids, host->total);
 }

@@ -106,6 +106,44 @@ struct VoxelIndex {
     }
 };
 
+// Device time of one C-ABI call's kernels: event pairs on the launching stream around each stretch of kernels
+// (host<->device copies and host synchronisation points stay outside), summed once the call has synchronised.
+struct DevTimer {
+    static constexpr int kPairs = 8;
+    cudaEvent_t a[kPairs] = {}, b[kPairs] = {};
+    int n = 0;
+    bool open = false;
+    void reset() { n = 0; open = false; }
+    void begin(cudaStream_t s) {
+        if (n >= kPairs || open) return;
+        if (!a[n] && (cudaEventCreate(&a[n]) != cudaSuccess || cudaEventCreate(&b[n]) != cudaSuccess)) return;
+        cudaEventRecord(a[n], s);
+        open = true;
+    }
+    void end(cudaStream_t s) {
+        if (!open) return;
+        cudaEventRecord(b[n], s);
+        open = false;
+        ++n;
+    }
+    // the stream must have been synchronised after the last end()
+    float total_ms() const {
+        float t = 0.f;
+        for (int i = 0; i < n; ++i) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, a[i], b[i]) == cudaSuccess) t += ms;
+        }
+        return t;
+    }
+    void destroy() {
+        for (int i = 0; i < kPairs; ++i) {
+            if (a[i]) cudaEventDestroy(a[i]);
+            if (b[i]) cudaEventDestroy(b[i]);
+            a[i] = b[i] = nullptr;
+        }
+    }
+};
+
 }  // namespace plc
 
 struct plc_ctx {
@@ -147,6 +185,8 @@ struct plc_ctx {
     int tiles = 0;
     cudaEvent_t ev_sweep_begin = nullptr, ev_sweep_end = nullptr;   // around k_sweep
     bool sweep_timed = false;
+    plc::DevTimer timer;         // kernels of the call in progress
+    plc_device_times times{};    // last completed call of each kind (plc_last_device_times)
 
     // filter / merge scratch
     plc::DevBuf f_keys, f_vals, f_keys2, f_vals2, f_tmp, f_out, f_flags;

@@ -92,6 +92,8 @@ extern "C" plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_s
     uint4* merged = ctx->m_out.as<uint4>();
     uint4* each = merged + total * 2;
     uint64_t at = 0;
+    ctx->timer.reset();
+    ctx->times.merge_ms = 0.f;
     for (int i = 0; i < n_src; ++i) {
         const plc_merge_src& src = srcs[i];
         if (!src.present || src.cloud.n_points == 0) continue;
@@ -102,11 +104,13 @@ extern "C" plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_s
         const bool aligned = ((src.cloud.point_step | src.cloud.off_x | src.cloud.off_y | src.cloud.off_z) & 3u) == 0;
         const unsigned rgba = 0xff000000u | ((unsigned)src.r << 16) | ((unsigned)src.g << 8) | (unsigned)src.b;
         const bool want_own = out_each && out_each[i];
+        ctx->timer.begin(s);
         k_transform_colour<<<(n + 255) / 256, 256, 0, s>>>(ctx->upload.as<unsigned char>(), n, src.cloud.point_step,
                                                            src.cloud.off_x, src.cloud.off_y, src.cloud.off_z, aligned,
                                                            make_affine(src.t, src.q), rgba, merged + at * 2,
                                                            want_own ? each + at * 2 : nullptr);
         ctx->launches += 1;
+        ctx->timer.end(s);
         if (want_own)
             PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_each[i], each + at * 2, (size_t)n * 32, cudaMemcpyDeviceToHost, s));
         if (n_each) n_each[i] = n;
@@ -115,6 +119,7 @@ extern "C" plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_s
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_merged, merged, total * 32, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    ctx->times.merge_ms = ctx->timer.total_ms();
     *n_out = total;
     return PLC_OK;
 }

@@ -801,23 +801,27 @@ using namespace plc;
 extern "C" plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* cloud) {
     if (!ctx || !cloud_view_ok(cloud)) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    ctx->timer.reset();
     PLC_TRY(voxel_set_cloud(ctx, ctx->terrain, cloud));
     // build for the node's default block radius right away; a sweep with other parameters rebuilds
     plc_params d;
     plc_params_default(&d);
     PLC_TRY(build_terrain_index(ctx, &d));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->times.set_terrain_ms = ctx->timer.total_ms();
     return PLC_OK;
 }
 
 extern "C" plc_status plc_vl_set_observed(plc_ctx* ctx, const plc_cloud_view* cloud) {
     if (!ctx || !cloud_view_ok(cloud)) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    ctx->timer.reset();
     PLC_TRY(voxel_set_cloud(ctx, ctx->observed, cloud));
     plc_params d;
     plc_params_default(&d);
     PLC_TRY(build_observed_index(ctx, &d));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->times.set_observed_ms = ctx->timer.total_ms();
     return PLC_OK;
 }
 
@@ -1047,6 +1051,15 @@ extern "C" plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms) {
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     PLC_CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_sweep_end));
     PLC_CUDA_TRY(ctx, cudaEventElapsedTime(ms, ctx->ev_sweep_begin, ctx->ev_sweep_end));
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out) {
+    if (!ctx || !out) return PLC_E_INVALID_ARG;
+    float ms = 0.f;
+    PLC_TRY(plc_vl_last_sweep_kernel_ms(ctx, &ms));
+    ctx->times.sweep_kernel_ms = ms;
+    *out = ctx->times;
     return PLC_OK;
 }
 

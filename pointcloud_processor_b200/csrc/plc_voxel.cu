@@ -225,6 +225,7 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
     PLC_CUDA_TRY(ctx, ctx->scratch.reserve(4096));
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, cloud->data, bytes, cudaMemcpyHostToDevice, ctx->stream));
     ExtractState* st = ctx->scratch.as<ExtractState>();
+    ctx->timer.begin(ctx->stream);
     k_extract_init<<<1, 1, 0, ctx->stream>>>(st);
     bool aligned = ((cloud->point_step | cloud->off_x | cloud->off_y | cloud->off_z) & 3u) == 0;
     unsigned blocks = (unsigned)((cloud->n_points + 255) / 256);
@@ -232,6 +233,7 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
                                                cloud->off_x, cloud->off_y, cloud->off_z, aligned,
                                                ix.raw.as<float4>(), st);
     ctx->launches += 2;
+    ctx->timer.end(ctx->stream);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ExtractState* host = static_cast<ExtractState*>(ctx->pinned);
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(host, st, sizeof(ExtractState), cudaMemcpyDeviceToHost, ctx->stream));
@@ -319,6 +321,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     cudaStream_t s = ctx->stream;
     unsigned pb = (n + 255) / 256;
     // ---- candidate lists: counts -> offsets
+    ctx->timer.begin(s);
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.gstart.ptr, 0, (n_mid + 1) * 4, s));
     k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.gstart.as<uint32_t>(),
                                            nullptr, nullptr);
@@ -328,6 +331,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     k_counts_to_groups<<<(unsigned)((n_mid + 255) / 256), 256, 0, s>>>(ix.gstart.as<uint32_t>(), n_mid);
     scan_exclusive_u32(ix.gstart.as<uint32_t>(), n_mid + 1, ix.scan_tmp.as<uint32_t>(), s);
     ctx->launches += 4;
+    ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ix.gstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     const size_t n_groups = totals[0];
@@ -335,6 +339,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     PLC_CUDA_TRY(ctx, ix.cgrp.reserve(std::max<size_t>(n_groups, 1) * 48));
     g.bricks = ix.bricks.as<uint32_t>();
     g.cgrp = ix.cgrp.as<float4>();
+    ctx->timer.begin(s);
     k_fill_f32<<<148 * 8, 256, 0, s>>>(ix.cgrp.as<float>(), n_groups * 12, INFINITY);
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, n_vox * 128, s));
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
@@ -345,6 +350,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.cfill.as<uint32_t>(),
                                           ix.gstart.as<uint32_t>(), ix.cgrp.as<float>());
     ctx->launches += 3;
+    ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ix.geom = g;
     ix.h = h;

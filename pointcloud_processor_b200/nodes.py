@@ -139,3 +139,30 @@ def merge_clouds(ctx: Context, robot: dict | None, backhoe: dict | None):
     if st != A.PLC_OK:
         raise A.PlcError(st, "plc_merge_clouds", L.plc_last_error(ctx._h).decode())
     return tuple(b[: n.value] for b, n in zip(bufs, ns))
+
+
+def run_pipeline(ctx: Context, inp, leaf: float = 0.2, **sweep_kw):
+    """BASELINE config 4: the launch file's dataflow for one scan pair:
+    pointcloud_filter (both scans) -> pointcloud_merger -> virtual_lidar, where the zx120 filter output is
+    also the fixed sensor's observed cloud (virtual_lidar.cpp:81-85; sensor frame, as upstream).
+    Returns a dict with every intermediate product and the kernel time of each stage."""
+    sc = inp.scene
+    out = {}
+    times = {}
+    out["robot_filtered"] = filter_scan(ctx, inp.robot_scan, leaf=leaf)
+    times["filter_robot_ms"] = ctx.device_times()["filter_ms"]
+    out["zx120_filtered"] = filter_scan(ctx, inp.zx120_scan, leaf=leaf)
+    times["filter_zx120_ms"] = ctx.device_times()["filter_ms"]
+    merged, rc, bc = merge_clouds(ctx, dict(cloud=out["robot_filtered"], t=inp.robot_tf[0], q=inp.robot_tf[1]),
+                                  dict(cloud=out["zx120_filtered"], t=inp.zx120_tf[0], q=inp.zx120_tf[1]))
+    times["merge_ms"] = ctx.device_times()["merge_ms"]
+    out.update(merged=merged, robot_coloured=rc, backhoe_coloured=bc)
+    ctx.set_terrain(sc.terrain)
+    times["set_terrain_ms"] = ctx.device_times()["set_terrain_ms"]
+    ctx.set_cells(sc.cells)
+    ctx.set_observed(out["zx120_filtered"], point_step=16)
+    times["set_observed_ms"] = ctx.device_times()["set_observed_ms"]
+    out["sweep"] = ctx.sweep(sc.params, sc.fixed, sc.candidates, **sweep_kw)
+    times["sweep_kernel_ms"] = ctx.device_times()["sweep_kernel_ms"]
+    out["device_ms"] = times
+    return out

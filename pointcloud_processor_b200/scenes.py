@@ -242,3 +242,104 @@ def build(name: str, **override) -> Scene:
                 n_cells=int(cells.size), n_candidates=int(cands.size), n_terrain=int(terr.shape[0]),
                 n_area=int(area.shape[0]))
     return Scene(name, terr, area, normals, cells, bounds, fixed, cands, prm, meta)
+
+
+# ---- config 4: two LiDAR scans -> pointcloud_filter -> pointcloud_merger -> virtual_lidar ------------------
+# Static transforms base_link -> velodyne_link, "x y z yaw pitch roll" (launch/tf_zx120.launch.xml:4,
+# launch/tf_four_wheel_robot.launch.xml:4), and the map poses of the two bases: zx120/base_link is pinned to
+# the map origin (pointcloud_merger.cpp:218-228); the robot stands beside the pit, facing it.
+ZX120_VELODYNE = dict(xyz=(0.55, 0.4, 3.5), yaw=0.0, pitch=0.4363)
+ROBOT_VELODYNE = dict(xyz=(0.25, 0.0, 2.0), yaw=0.0, pitch=0.1245)
+ROBOT_BASE = dict(xyz=(9.0, -3.0, 0.0), yaw=2.6)
+
+
+def _quat_yp(yaw: float, pitch: float) -> np.ndarray:
+    """Quaternion (x, y, z, w) of Rz(yaw) * Ry(pitch), the composition static_transform_publisher applies."""
+    cy, sy, cp, sp = np.cos(yaw / 2), np.sin(yaw / 2), np.cos(pitch / 2), np.sin(pitch / 2)
+    return np.array([-sy * sp, cy * sp, sy * cp, cy * cp])
+
+
+def _rot(q: np.ndarray) -> np.ndarray:
+    x, y, z, w = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+def sensor_in_map(base: dict, mount: dict):
+    """lookupTransform("map", "<name>/velodyne_link") (pointcloud_merger.cpp:362-366): translation, quaternion."""
+    qb = _quat_yp(base.get("yaw", 0.0), 0.0)
+    qm = _quat_yp(mount["yaw"], mount["pitch"])
+    t = np.asarray(base["xyz"], float) + _rot(qb) @ np.asarray(mount["xyz"], float)
+    x1, y1, z1, w1 = qb
+    x2, y2, z2, w2 = qm
+    q = np.array([w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2, w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2,
+                  w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2, w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2])
+    return t, q
+
+
+def lidar_scan(t: np.ndarray, q: np.ndarray, n_points: int, seed: int, shape: str = "rect", rings: int = 32,
+               sigma: float = 0.02, max_range: float = 100.0) -> np.ndarray:
+    """One revolution of a 32-ring spinning LiDAR at map pose (t, q) over the analytic ground with the pit's
+    bottom sunk by DEPTH, returned in the sensor's own frame as pcl::PointXYZ records ((n, 4) float32, 1.0f in
+    the pad) in firing order (azimuth-major, ring-minor).  Range noise N(0, sigma).  Rays that hit nothing
+    within max_range give no point (as a velodyne driver does), so azimuth steps are added until n_points
+    returns exist and the list is cut to exactly n_points."""
+    rng = np.random.default_rng(seed)
+    R = _rot(q)
+    elev = np.deg2rad(np.linspace(-25.0, 15.0, rings))
+    boxes = pit_boxes(shape)
+    cx, cy = PIT_CENTER
+
+    def surface(x, y):
+        h = ground_height(x, y)
+        return np.where(_inside_any(x - cx, y - cy, boxes), h - DEPTH, h)
+
+    out = np.zeros((0, 4), np.float32)
+    n_az = max(16, int(np.ceil(n_points / rings * 1.15)))
+    for _ in range(6):
+        az = (np.arange(n_az) + 0.5) * (2 * np.pi / n_az)
+        A2, E2 = np.meshgrid(az, elev, indexing="ij")
+        d_s = np.stack([np.cos(E2) * np.cos(A2), np.cos(E2) * np.sin(A2), np.sin(E2)], -1).reshape(-1, 3)
+        d_m = d_s @ R.T
+        down = d_m[:, 2] < -1e-3
+        rng_hit = np.full(d_m.shape[0], np.inf)
+        # fixed-point iteration on the height field (gentle slopes: converges in a few rounds)
+        tt = np.where(down, (t[2] - 0.0) / np.maximum(-d_m[:, 2], 1e-3), np.inf)
+        for _it in range(6):
+            ok = np.isfinite(tt)
+            x = t[0] + d_m[:, 0] * np.where(ok, tt, 0.0)
+            y = t[1] + d_m[:, 1] * np.where(ok, tt, 0.0)
+            tt = np.where(ok, (t[2] - surface(x, y)) / np.maximum(-d_m[:, 2], 1e-3), np.inf)
+        rng_hit = np.where(down & (tt > 0.3) & (tt < max_range), tt, np.inf)
+        hit = np.isfinite(rng_hit)
+        r = rng_hit[hit] + rng.normal(0.0, sigma, int(hit.sum()))
+        pts = d_s[hit] * r[:, None]
+        if pts.shape[0] >= n_points:
+            out = np.ones((n_points, 4), np.float32)
+            out[:, :3] = pts[:n_points].astype(np.float32)
+            return out
+        n_az = int(n_az * max(1.2, 1.1 * n_points / max(pts.shape[0], 1)))
+    raise RuntimeError("lidar_scan: could not reach the requested number of returns")
+
+
+@dataclass
+class PipelineInputs:
+    robot_scan: np.ndarray      # (n, 4) float32 PointXYZ, sensor frame   /four_wheel_robot/velodyne_points
+    zx120_scan: np.ndarray      #                                          /zx120/velodyne_points
+    robot_tf: tuple             # (t, q) of map -> four_wheel_robot/velodyne_link
+    zx120_tf: tuple             # (t, q) of map -> zx120/velodyne_link
+    scene: Scene                # the sweep the pipeline feeds (terrain, cells, candidates)
+
+
+def pipeline_inputs(n_scan: int = 1_000_000, sweep: str = "cfg2", seeds=(4, 5)) -> PipelineInputs:
+    """BASELINE config 4: two synthetic n_scan-point 32-ring scans (seeds 4 and 5) that go through
+    crop + voxel downsample, are merged into the map frame, and feed a `sweep`-sized visibility sweep whose
+    fixed sensor sees the zx120 filter output as its observed cloud (virtual_lidar.cpp:81-85)."""
+    sc = build(sweep)
+    shape = CONFIGS[sweep]["shape"]
+    zt, zq = sensor_in_map(dict(xyz=(0.0, 0.0, 0.0), yaw=0.0), ZX120_VELODYNE)
+    rt, rq = sensor_in_map(ROBOT_BASE, ROBOT_VELODYNE)
+    return PipelineInputs(robot_scan=lidar_scan(rt, rq, n_scan, seeds[0], shape),
+                          zx120_scan=lidar_scan(zt, zq, n_scan, seeds[1], shape),
+                          robot_tf=(rt, rq), zx120_tf=(zt, zq), scene=sc)
