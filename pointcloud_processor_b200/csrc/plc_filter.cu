@@ -78,26 +78,33 @@ k_crop_compact(const unsigned char* __restrict__ data, unsigned n, unsigned step
             out[pos[i]] = make_float4(x, y, z, 1.0f);   // pcl::PointXYZ keeps 1.0f in data[3]
         }
     }
+    // block-wide min/max of the order-preserving keys, then one set of atomics per block
+    __shared__ int red[6][8];
+    const unsigned FULL = 0xffffffffu;
+    const int lo_id = 0x7fffffff, hi_id = (int)0x80000000;
     int k[6];
-    k[0] = keep ? order_key(x) : 0x7fffffff;
-    k[1] = keep ? order_key(y) : 0x7fffffff;
-    k[2] = keep ? order_key(z) : 0x7fffffff;
-    k[3] = keep ? order_key(x) : (int)0x80000000;
-    k[4] = keep ? order_key(y) : (int)0x80000000;
-    k[5] = keep ? order_key(z) : (int)0x80000000;
+    k[0] = __reduce_min_sync(FULL, keep ? order_key(x) : lo_id);
+    k[1] = __reduce_min_sync(FULL, keep ? order_key(y) : lo_id);
+    k[2] = __reduce_min_sync(FULL, keep ? order_key(z) : lo_id);
+    k[3] = __reduce_max_sync(FULL, keep ? order_key(x) : hi_id);
+    k[4] = __reduce_max_sync(FULL, keep ? order_key(y) : hi_id);
+    k[5] = __reduce_max_sync(FULL, keep ? order_key(z) : hi_id);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane < 6) {
+        int mine = k[0];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            k[a] = min(k[a], __shfl_xor_sync(0xffffffffu, k[a], o));
-            k[3 + a] = max(k[3 + a], __shfl_xor_sync(0xffffffffu, k[3 + a], o));
-        }
-    const bool any_kept = __any_sync(0xffffffffu, keep);
-    if ((threadIdx.x & 31) == 0 && any_kept) {
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            atomicMin(&st->bbox_key[a], k[a]);
-            atomicMax(&st->bbox_key[3 + a], k[3 + a]);
+        for (int a = 1; a < 6; ++a) mine = lane == a ? k[a] : mine;
+        red[lane][warp] = mine;
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        const int a = threadIdx.x;
+        int v = red[a][0];
+        for (int w = 1; w < 8; ++w) v = a < 3 ? min(v, red[a][w]) : max(v, red[a][w]);
+        if (a < 3) {
+            if (v != lo_id) atomicMin(&st->bbox_key[a], v);
+        } else {
+            if (v != hi_id) atomicMax(&st->bbox_key[a], v);
         }
     }
 }
@@ -128,24 +135,46 @@ k_heads(const uint32_t* __restrict__ keys, unsigned n, uint32_t* __restrict__ he
     head[i] = (i < n && (i == 0 || keys[i] != keys[i - 1])) ? 1u : 0u;
 }
 
-// one thread per voxel segment: float32 running sum in sorted order, divided by (float)count
+// position of every segment head, in output order (slot = exclusive scan of the head flags)
 __global__ void __launch_bounds__(256)
-k_centroid(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals, unsigned n,
-           const uint32_t* __restrict__ slot, const float4* __restrict__ pts, float4* __restrict__ out) {
+k_segment_starts(const uint32_t* __restrict__ slot, unsigned n, uint32_t* __restrict__ seg_start) {
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    if (slot[i + 1] == slot[i]) return;   // not a segment head
-    uint32_t key = keys[i];
-    float sx = 0.f, sy = 0.f, sz = 0.f;
-    unsigned j = i;
-    for (; j < n && keys[j] == key; ++j) {
-        float4 p = pts[vals[j]];
-        sx = __fadd_rn(sx, p.x);
-        sy = __fadd_rn(sy, p.y);
-        sz = __fadd_rn(sz, p.z);
+    if (i > n) return;
+    if (i == n) {
+        seg_start[slot[n]] = n;       // end sentinel
+        return;
     }
-    float cnt = (float)(j - i);
-    out[slot[i]] = make_float4(__fdiv_rn(sx, cnt), __fdiv_rn(sy, cnt), __fdiv_rn(sz, cnt), 1.0f);
+    if (slot[i + 1] != slot[i]) seg_start[slot[i]] = i;
+}
+
+// One warp per voxel.  PCL accumulates a voxel's points one after another in float32 (sorted order, which
+// the oracle fixes to ascending point index), so the adds are serial by definition; the warp gathers 32
+// points at a time in parallel and replays them in order through shuffles, every lane holding the same sums.
+__global__ void __launch_bounds__(256)
+k_centroid(const uint32_t* __restrict__ vals, const uint32_t* __restrict__ seg_start, unsigned n_seg,
+           const float4* __restrict__ pts, float4* __restrict__ out) {
+    const unsigned w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n_seg) return;
+    const int lane = threadIdx.x & 31;
+    const unsigned FULL = 0xffffffffu;
+    const unsigned begin = seg_start[w], end = seg_start[w + 1];
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+    float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (begin + lane < end) nxt = pts[vals[begin + lane]];
+    for (unsigned base = begin; base < end; base += 32) {
+        const float4 cur = nxt;
+        if (base + 32 + lane < end) nxt = pts[vals[base + 32 + lane]];     // in flight while this batch is summed
+        const int cnt = (int)min(32u, end - base);
+        for (int i = 0; i < cnt; ++i) {
+            sx = __fadd_rn(sx, __shfl_sync(FULL, cur.x, i));
+            sy = __fadd_rn(sy, __shfl_sync(FULL, cur.y, i));
+            sz = __fadd_rn(sz, __shfl_sync(FULL, cur.z, i));
+        }
+    }
+    if (lane == 0) {
+        const float cnt = (float)(end - begin);
+        out[w] = make_float4(__fdiv_rn(sx, cnt), __fdiv_rn(sy, cnt), __fdiv_rn(sz, cnt), 1.0f);
+    }
 }
 
 float key_to_float(int k) {
@@ -245,9 +274,9 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     int key_bits = 1;
     while (key_bits < 32 && (1ull << key_bits) < n_keys) ++key_bits;
 
-    PLC_CUDA_TRY(ctx, ctx->f_keys.reserve((size_t)m * 4));
+    PLC_CUDA_TRY(ctx, ctx->f_keys.reserve(((size_t)m + 1) * 4));
     PLC_CUDA_TRY(ctx, ctx->f_vals.reserve((size_t)m * 4));
-    PLC_CUDA_TRY(ctx, ctx->f_keys2.reserve((size_t)m * 4));
+    PLC_CUDA_TRY(ctx, ctx->f_keys2.reserve(((size_t)m + 1) * 4));
     PLC_CUDA_TRY(ctx, ctx->f_vals2.reserve((size_t)m * 4 + sort_table_entries(m) * 4));
     uint32_t* table = ctx->f_vals2.as<uint32_t>() + m;
     const unsigned mb = (m + 255) / 256;
@@ -260,12 +289,19 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     const uint32_t* svals = where ? ctx->f_vals2.as<uint32_t>() : ctx->f_vals.as<uint32_t>();
     k_heads<<<(m + 1 + 255) / 256, 256, 0, s>>>(skeys, m, flag);
     scan_exclusive_u32(flag, (size_t)m + 1, scan_tmp, s);
-    k_centroid<<<mb, 256, 0, s>>>(skeys, svals, m, flag, cropped, centroids);
-    ctx->launches += 5;
+    // the unsorted key buffer is free again: it holds the segment starts (at most m + 1 entries)
+    uint32_t* seg_start = where ? ctx->f_keys.as<uint32_t>() : ctx->f_keys2.as<uint32_t>();
+    k_segment_starts<<<(m + 1 + 255) / 256, 256, 0, s>>>(flag, m, seg_start);
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(&host->total, flag + m, 4, cudaMemcpyDeviceToHost, s));
+    ctx->timer.end(s);
+    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    const unsigned n_seg = host->total;
+    ctx->timer.begin(s);
+    k_centroid<<<(n_seg * 32 + 255) / 256, 256, 0, s>>>(svals, seg_start, n_seg, cropped, centroids);
+    ctx->launches += 6;
     ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(&host->total, flag + m, 4, cudaMemcpyDeviceToHost, s));
-    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    plc_status rc = copy_out(centroids, n_seg);           // synchronises the stream
     ctx->times.filter_ms = ctx->timer.total_ms();
-    return copy_out(centroids, host->total);
+    return rc;
 }
