@@ -1,0 +1,104 @@
+"""Fills BASELINE.md's results table: every BASELINE.json config on this rank's GPU, next to the oracle
+(CPU) on the same inputs.  Run on the GPU box; prints one JSON object per config.
+
+    python tools/results_table.py [cfg1 cfg2 cfg3 cfg4 cfg5] [--cpu-budget 10]
+
+Parity columns: cfg1 is compared in full (every mask bit, every score); the larger configs on a seeded
+subset of poses (all rays each), because the single-threaded reference path would take hours.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import binding as O  # noqa: E402  (checker + CPU baseline, never on the product path)
+from pointcloud_processor_b200 import Context, scenes  # noqa: E402
+from pointcloud_processor_b200.nodes import run_pipeline  # noqa: E402
+
+
+def gpu_sweep(ctx, sc, reps=3):
+    ctx.set_terrain(sc.terrain)
+    ctx.set_cells(sc.cells)
+    ctx.set_observed(np.zeros((0, 3), np.float32))
+    ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)
+    wall, kern = [], []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        r = ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)
+        wall.append((time.perf_counter() - t0) * 1e3)
+        kern.append(ctx.last_sweep_kernel_ms())
+    return r, float(np.median(wall)), float(np.median(kern))
+
+
+def cpu_rate(sc, ix, poses, threads, faithful=True):
+    t0 = time.perf_counter()
+    ref = O.sweep(ix, None, sc.cells, sc.params, sc.fixed, sc.candidates[poses], threads=threads, want_mask=True,
+                  faithful=faithful)
+    dt = time.perf_counter() - t0
+    return ref, poses.size * sc.cells.size / dt, dt
+
+
+def sweep_row(ctx, name, budget):
+    sc = scenes.build(name)
+    C, M, N = int(sc.candidates.size), int(sc.cells.size), int(sc.terrain.shape[0])
+    r, wall_ms, kern_ms = gpu_sweep(ctx, sc)
+    row = dict(config=name, poses=C, rays_per_pose=M, terrain_points=N, sweep_ms=wall_ms, k_sweep_ms=kern_ms,
+               rays_per_s=C * M / (wall_ms * 1e-3), samples=r.counters["samples"], best_index=int(r.best_index),
+               best_score=float(r.best_score))
+    alg = 32 * r.counters["rays"] + 4 * r.counters["samples"] + 64 * C + 16 * N
+    row["algorithmic_GBps"] = alg / (kern_ms * 1e-3) / 1e9
+    # parity + CPU baseline on a seeded pose subset sized to the budget (cfg1: everything)
+    threads = os.cpu_count() or 1
+    kd = O.Index(sc.terrain, O.KDTREE)
+    rng = np.random.default_rng(99)
+    probe = np.sort(rng.permutation(C)[: min(C, 4)])
+    _, rate1, _ = cpu_rate(sc, kd, probe, 1)
+    n1 = C if name == "cfg1" and C * M / rate1 < 4 * budget else int(max(2, min(C, rate1 * budget / M)))
+    sub1 = np.sort(rng.permutation(C)[:n1])
+    _, row["cpu_1t_rays_per_s"], dt1 = cpu_rate(sc, kd, sub1, 1)
+    row["cpu_1t_sample"] = f"{n1} of {C} poses, {dt1:.1f} s"
+    nmt = C if name == "cfg1" else int(max(threads, min(C, row["cpu_1t_rays_per_s"] * threads * 0.6 * budget / M)))
+    subm = np.sort(rng.permutation(C)[:nmt])
+    ref, row["cpu_mt_rays_per_s"], dtm = cpu_rate(sc, kd, subm, threads)
+    row["cpu_mt_sample"] = f"{nmt} of {C} poses, {dtm:.1f} s, {threads} threads"
+    got = ctx.sweep(sc.params, sc.fixed, sc.candidates[subm], mask=True)
+    row["pairs_compared"] = int(subm.size * M)
+    row["mask_mismatches"] = int(np.count_nonzero(np.unpackbits((got.mask ^ ref["mask"]).view(np.uint8))))
+    row["score_max_rel_err"] = float(np.max(np.abs(got.scores - ref["scores"]) / np.maximum(1.0, np.abs(ref["scores"]))))
+    row["argmax_equal_on_subset"] = bool(got.best_index == ref["best_index"])
+    row["samples_equal_on_subset"] = bool(got.counters["samples"] == ref["counters"]["samples"])
+    return row
+
+
+def pipeline_row(ctx):
+    inp = scenes.pipeline_inputs(n_scan=1_000_000, sweep="cfg2")
+    run_pipeline(ctx, inp, scores=False)
+    t0 = time.perf_counter()
+    got = run_pipeline(ctx, inp, scores=False)
+    wall = (time.perf_counter() - t0) * 1e3
+    sc = inp.scene
+    r = got["sweep"]
+    return dict(config="cfg4", scan_points=[int(inp.robot_scan.shape[0]), int(inp.zx120_scan.shape[0])],
+                filtered=[int(got["robot_filtered"].shape[0]), int(got["zx120_filtered"].shape[0])],
+                merged=int(got["merged"].shape[0]), poses=int(sc.candidates.size), rays_per_pose=int(sc.cells.size),
+                pipeline_wall_ms=wall, device_ms=got["device_ms"], best_index=int(r.best_index),
+                rays_per_s=sc.candidates.size * sc.cells.size / (got["device_ms"]["sweep_kernel_ms"] * 1e-3))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("configs", nargs="*", default=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
+    ap.add_argument("--cpu-budget", type=float, default=8.0, help="seconds per CPU timing")
+    a = ap.parse_args()
+    with Context(0) as ctx:
+        for name in a.configs:
+            row = pipeline_row(ctx) if name == "cfg4" else sweep_row(ctx, name, a.cpu_budget)
+            print(json.dumps(row), flush=True)
+
+
+if __name__ == "__main__":
+    main()
