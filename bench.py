@@ -64,53 +64,92 @@ def workload_text(workload: str, world: int) -> str:
 
 
 class ClockSampler:
-    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    """Samples SM clocks and throttle reasons through NVML (every few ms, in a thread) while the timed
+    region runs; falls back to an `nvidia-smi -lms` child process if NVML cannot be loaded."""
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
     def __init__(self, gpu_index: int):
-        self.rows = []
+        self.sm, self.mx, self.reasons = [], [], set()
         self.proc = None
+        self.thread = None
+        self.stop = threading.Event()
         self.gpu = gpu_index
+        self.nvml = None
 
     def __enter__(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            self.nvml = pynvml
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
+            return self
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
                  "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread = threading.Thread(target=self._read_smi, daemon=True)
             self.thread.start()
         except OSError:
             self.proc = None
         return self
 
-    def _read(self):
+    def _sample_nvml(self):
+        n = self.nvml
+        self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        self.mx.append(float(n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        get = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        mask = int(get(self.handle))
+        for name, bit in self.BITS.items():
+            if mask & bit:
+                self.reasons.add(name)
+
+    def _poll_nvml(self):
+        while not self.stop.is_set():
+            try:
+                self._sample_nvml()
+            except Exception:
+                return
+            self.stop.wait(0.004)
+
+    def _read_smi(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            r = [c.strip() for c in line.split(",")]
+            try:
+                self.sm.append(float(r[0]))
+                self.mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(self.NAMES, r[3:7]):
+                if v.lower().startswith("active"):
+                    self.reasons.add(name)
 
     def __exit__(self, *exc):
-        if self.proc:
+        if self.nvml:
+            try:
+                self._sample_nvml()          # at least one sample while the last step's kernels are still recent
+            except Exception:
+                pass
+            self.stop.set()
+            self.thread.join(timeout=2)
+        elif self.proc:
             time.sleep(0.15)
             self.proc.terminate()
             self.thread.join(timeout=2)
 
     def summary(self) -> dict:
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx.append(float(r[1]))
-            except (ValueError, IndexError):
-                continue
-            for name, v in zip(names, r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        if not sm:
+        if not self.sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm)}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(max(self.mx)),
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def measured_peaks() -> tuple[float, str]:
@@ -437,7 +476,17 @@ def main():
     ap.add_argument("--no-north-star", action="store_true", help="skip the extra configs[2] measurement")
     ap.add_argument("--no-feeders", action="store_true", help="skip the crop/voxel/merge/voxelise measurements (config 4)")
     args = ap.parse_args()
-    line = run_reference(args) if args.impl == "reference" else run_ours(args)
+    # stdout carries exactly one JSON line: anything libraries write to fd 1 meanwhile (NCCL prints its version
+    # banner there) is sent to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        line = run_reference(args) if args.impl == "reference" else run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     if line is not None:
         print(json.dumps(line), flush=True)
 
