@@ -62,6 +62,20 @@ __device__ __forceinline__ float rsqrt_fast(float v) {
     return r;
 }
 
+// Shared-memory accesses by 32-bit shared-window address (one cvta at kernel entry instead of a generic
+// address computation at every access)
+__device__ __forceinline__ void sts_u32(unsigned addr, unsigned v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned lds_u32(unsigned addr) {
+    unsigned v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void reds_min_s32(unsigned addr, int v) {
+    asm volatile("red.shared.min.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
 struct RayStats {
     unsigned samples = 0;
     unsigned long long exact = 0;
@@ -321,21 +335,26 @@ constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not bloc
 #ifndef PLC_SWEEP_BLOCKS_PER_SM
 #define PLC_SWEEP_BLOCKS_PER_SM 32
 #endif
-#ifndef PLC_SWEEP_WARPS
-#define PLC_SWEEP_WARPS 1
-#endif
-constexpr int kSweepWarps = PLC_SWEEP_WARPS;     // independent warps per block (no block-level synchronisation)
+constexpr int kSweepWarps = 1;                  // one warp per block: no block-level synchronisation anywhere
 __global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin,
         unsigned tiles, unsigned n_work, const plc_cell* __restrict__ cells, unsigned n_cells,
         const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
         int* __restrict__ partial_cov, uint32_t* __restrict__ mask, unsigned mask_words,
         SweepResult* __restrict__ res) {
-    __shared__ uint32_t q_tag_all[kSweepWarps][kQueueCap];
-    __shared__ int ray_state_all[kSweepWarps][kTileCells];   // -1 gated out; first blocked sample index; or kOpen + n
-    uint32_t* const q_tag = q_tag_all[threadIdx.x >> 5];
-    int* const ray_state = ray_state_all[threadIdx.x >> 5];
-    const unsigned wid = blockIdx.x * kSweepWarps + (threadIdx.x >> 5);      // this warp's (candidate, tile) index
+    // Shared memory is declared and addressed in PTX: the symbol's shared-window address is a link-time constant,
+    // whereas a C++ __shared__ array is reached through a generic pointer whose conversion the compiler redoes
+    // (three uniform instructions) at every access.
+    //   plc_ray_state  int[kTileCells]    -1 gated out; first blocked sample index; or kOpen + n
+    //   plc_q_tag      uint32[kQueueCap]  ring of (ray slot << 16 | sample index)
+    static_assert(kTileCells == 512 && kQueueCap == 128, "sizes are spelled out in the PTX declaration below");
+    unsigned q_tag, ray_state;
+    asm volatile(".shared .align 16 .b8 plc_ray_state[2048];\n\t"
+                 ".shared .align 16 .b8 plc_q_tag[512];\n\t"
+                 "mov.u32 %0, plc_ray_state;\n\t"
+                 "mov.u32 %1, plc_q_tag;"
+                 : "=r"(ray_state), "=r"(q_tag));
+    const unsigned wid = blockIdx.x;         // this warp's (candidate, tile) index
     if (wid >= n_work) return;
 
     const unsigned FULL = 0xffffffffu;
@@ -369,9 +388,9 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         __syncwarp();
         int take = q_n < 32 ? q_n : 32;
         if (lane < take) {
-            unsigned tag = q_tag[(q_head + lane) & (kQueueCap - 1)];
+            unsigned tag = lds_u32(q_tag + 4u * ((q_head + lane) & (kQueueCap - 1)));
             int eslot = (int)(tag >> 16), ek = (int)(tag & 0xffffu);
-            if (ray_state[eslot] > ek) {             // not already blocked earlier on the ray
+            if ((int)lds_u32(ray_state + 4u * eslot) > ek) {             // not already blocked earlier on the ray
                 ++exact;
                 double ex, ey, ez;
                 exact_d(tile * kTileCells + eslot, ex, ey, ez);
@@ -384,7 +403,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 int ix = clamp_i((int)fine_coord_f(qx, G.ox, G.inv_g), 0, (G.dim_x << kFineShift) - 1);
                 int iy = clamp_i((int)fine_coord_f(qy, G.oy, G.inv_g), 0, (G.dim_y << kFineShift) - 1);
                 int iz = clamp_i((int)fine_coord_f(qz, G.oz, G.inv_g), 0, (G.dim_z << kFineShift) - 1);
-                if (cand_any(G, ix, iy, iz, qx, qy, qz, P.thr_block)) atomicMin(&ray_state[eslot], ek);
+                if (cand_any(G, ix, iy, iz, qx, qy, qz, P.thr_block)) reds_min_s32(ray_state + 4u * eslot, ek);
             }
         }
         __syncwarp();
@@ -451,7 +470,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             }
         }
         gated += pass ? 1u : 0u;
-        ray_state[slot] = pass ? kOpen + n : -1;        // published before any of the ray's samples can be queued
+        sts_u32(ray_state + 4u * slot, (unsigned)(pass ? kOpen + n : -1));        // published before any of the ray's samples can be queued
 
         // ---- checkVisibilityWithRaycasting (:754-800): clear / certain samples here, uncertain ones queued
         int k = 0, k_hi = 0;
@@ -503,7 +522,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                         double dx, dy, dz;
                         exact_d(jc, dx, dy, dz);
                         bool clear = ray_clear(P, s.x, s.y, s.z, dx, dy, dz, ray_length(dx, dy, dz), st);
-                        if (!clear) ray_state[slot] = (int)st.samples - 1;
+                        if (!clear) sts_u32(ray_state + 4u * slot, st.samples - 1u);
                         exact += st.exact;
                         k = k_hi = 0;
                     }
@@ -511,31 +530,30 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             }
         }
         __syncwarp();
-        bool active = k < k_hi;
-        bool more = __any_sync(FULL, active);
+        // a lane is marching while k < k_hi; a blocked ray jumps to k = k_hi
+        const unsigned tag_base = ((unsigned)slot << 16) - 1u;
+        bool more = __any_sync(FULL, k < k_hi);
         while (more) {
             while (q_n + 32 <= kQueueCap) {               // room for one more push from every lane
                 unsigned st = 0;
-                if (active) {
-                    st = voxel_state(G, fx >> kFixedBits, fy >> kFixedBits, fz >> kFixedBits);
+                if (k < k_hi) {
+                    st = voxel_state_fixed(G, fx, fy, fz);
                     if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
-                        atomicMin(&ray_state[slot], k);
-                        active = false;
+                        reds_min_s32(ray_state + 4u * slot, k);
+                        k = k_hi;
                     } else {
                         ++k;
                         fx += dfx;
                         fy += dfy;
                         fz += dfz;
-                        active = k < k_hi;
                     }
                 }
-                unsigned ub = __ballot_sync(FULL, st == 1u);     // lanes whose sample k - 1 was uncertain
+                const unsigned ub = __ballot_sync(FULL, st == 1u);     // lanes whose sample k - 1 was uncertain
                 if (ub) {
-                    if (st == 1u)
-                        q_tag[(q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)] = ((unsigned)slot << 16) | (unsigned)(k - 1);
+                    if (st == 1u) sts_u32(q_tag + 4u * ((q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)), tag_base + (unsigned)k);
                     q_n += __popc(ub);
                 }
-                more = __any_sync(FULL, active);
+                more = __any_sync(FULL, k < k_hi);
                 if (!more) break;
             }
             if (q_n >= 32) drain();
@@ -553,7 +571,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     for (int r = 0; r < kRaysPerThread; ++r) {
         const int slot = r * 32 + lane;
         unsigned j = tile * kTileCells + slot;
-        int st = ray_state[slot];
+        int st = (int)lds_u32(ray_state + 4u * slot);
         bool vis = st >= kOpen;
         if (st >= 0 && P.have_terrain) samples += (unsigned)(vis ? st - kOpen : st + 1);
         if (j < n_cells) {

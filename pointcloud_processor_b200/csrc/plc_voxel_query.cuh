@@ -61,6 +61,16 @@ __device__ __forceinline__ unsigned voxel_state(const VoxelGeom& g, int ix, int 
     return (w >> (2 * (((iy & 1) << 3) | (ix & 7)))) & 3u;
 }
 
+// The same for a position in 16.16 fixed-point fine-voxel units (k_sweep's march).  A brick is 8 z-slabs of
+// 16 bytes, each 8 y-rows of 2 bytes, each 8 x-fields of 2 bits, so the row is one aligned 16-bit load at a
+// byte offset made of bit fields of the coordinates.
+__device__ __forceinline__ unsigned voxel_state_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
+    const unsigned brick = brick_of(g, fx >> (16 + kFineShift), fy >> (16 + kFineShift), fz >> (16 + kFineShift));
+    const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
+    const unsigned short row = __ldg(reinterpret_cast<const unsigned short*>(reinterpret_cast<const char*>(g.bricks) + off));
+    return ((unsigned)row >> (((unsigned)fx >> 15) & 0xeu)) & 3u;
+}
+
 __device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int iy, int iz) {
     return (uint32_t)(((size_t)(iz >> 2) * g.mdim_y + (iy >> 2)) * g.mdim_x + (ix >> 2));
 }
