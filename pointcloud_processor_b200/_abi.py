@@ -14,7 +14,7 @@ from pathlib import Path
 import numpy as np
 
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "lib" / "libplc.so"
+LIB_PATH = Path(os.environ["PLC_DEV_LIB"]) if os.environ.get("PLC_DEV_LIB") else _HERE / "lib" / "libplc.so"   # PLC_DEV_LIB: kernel experiments only
 
 PLC_OK = 0
 PLC_E_INVALID_ARG = -1

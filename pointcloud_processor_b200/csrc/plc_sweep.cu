@@ -290,11 +290,17 @@ k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin,
     aux[i] = a;
 }
 
-// float32 copy of the cell positions relative to `ref` (exact subtraction in double, one narrowing)
+// float32 copy of the cell positions relative to `ref` (exact subtraction in double, one narrowing), padded to
+// whole k_sweep tiles with positions 1e15 m away: the range gate rejects those without a bounds test per ray
 __global__ void __launch_bounds__(256)
-k_cells_f32(const plc_cell* __restrict__ cells, unsigned n, double rx, double ry, double rz, float4* __restrict__ out) {
+k_cells_f32(const plc_cell* __restrict__ cells, unsigned n, unsigned n_padded, double rx, double ry, double rz,
+            float4* __restrict__ out) {
     unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+    if (j >= n_padded) return;
+    if (j >= n) {
+        out[j] = make_float4(1e15f, 1e15f, 1e15f, 0.f);
+        return;
+    }
     plc_cell c = load_cell(cells, j);
     out[j] = make_float4((float)(c.x - rx), (float)(c.y - ry), (float)(c.z - rz), 0.f);
 }
@@ -415,10 +421,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     for (int r = 0; r < kRaysPerThread; ++r) {
         const int slot = r * 32 + lane;
         unsigned j = tile * kTileCells + slot;
-        const bool valid = j < n_cells;
         // ---- evaluateCellScore gates (:656-678): range
-        const unsigned jc = valid ? j : 0;
-        const float4 cf = __ldg(&P.cells_f[jc]);
+        const float4 cf = __ldg(&P.cells_f[j]);          // padded to whole tiles: no bounds test
         const float df[3] = {cf.x - A.sr[0], cf.y - A.sr[1], cf.z - A.sr[2]};
         const float hd2 = df[0] * df[0] + df[1] * df[1];
         const float L2f = hd2 + df[2] * df[2];
@@ -436,9 +440,10 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             if (fabsf(kf - rintf(kf)) <= tolk) redo = true;
             else n = kf > 0.f ? min((int)ceilf(kf), P.n_tab - 1) : 0;
         }
+        if (redo && j >= n_cells) redo = false;          // padding can only get here if the error bound is not finite
         if (redo) {                                       // as upstream, in double (rare)
             double dx, dy, dz;
-            exact_d(jc, dx, dy, dz);
+            exact_d(j, dx, dy, dz);
             double L = ray_length(dx, dy, dz);
             pass = L >= P.min_distance && L <= P.max_distance;
             n = 0;
@@ -452,7 +457,6 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 }
             }
         }
-        pass = pass && valid;
         // ---- FOV (:671-678, :703-714)
         if (pass) {
             bool decided = false;
@@ -465,7 +469,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             }
             if (!decided) {
                 double dx, dy, dz;
-                exact_d(jc, dx, dy, dz);
+                exact_d(j, dx, dy, dz);
                 pass = in_fov_exact(P, s.pitch, s.yaw, dx, dy, dz);
             }
         }
@@ -520,7 +524,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                         lx >= mx || ly >= my || lz >= mz) {
                         RayStats st;
                         double dx, dy, dz;
-                        exact_d(jc, dx, dy, dz);
+                        exact_d(j, dx, dy, dz);
                         bool clear = ray_clear(P, s.x, s.y, s.z, dx, dy, dz, ray_length(dx, dy, dz), st);
                         if (!clear) sts_u32(ray_state + 4u * slot, st.samples - 1u);
                         exact += st.exact;
@@ -533,11 +537,18 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         // a lane is marching while k < k_hi; a blocked ray jumps to k = k_hi
         const unsigned tag_base = ((unsigned)slot << 16) - 1u;
         bool more = __any_sync(FULL, k < k_hi);
+        // software pipeline of depth one: the occupancy row of the next sample is requested before the current
+        // one is examined, so each marching lane keeps a load in flight through the whole step
+        unsigned row = 0;
+        if (k < k_hi) row = brick_row_fixed(G, fx, fy, fz);
         while (more) {
             while (q_n + 32 <= kQueueCap) {               // room for one more push from every lane
                 unsigned st = 0;
                 if (k < k_hi) {
-                    st = voxel_state_fixed(G, fx, fy, fz);
+                    unsigned row_next = 0;
+                    if (k + 1 < k_hi) row_next = brick_row_fixed(G, fx + dfx, fy + dfy, fz + dfz);
+                    st = row_state(row, fx);
+                    row = row_next;
                     if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
                         reds_min_s32(ray_state + 4u * slot, k);
                         k = k_hi;
@@ -872,10 +883,11 @@ extern "C" plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint
         r2 += half * half;
     }
     ctx->cells_radius = ceil_to_float(std::sqrt(r2));
-    PLC_CUDA_TRY(ctx, ctx->cells_f.reserve(n_cells * sizeof(float4)));
-    k_cells_f32<<<(unsigned)((n_cells + 255) / 256), 256, 0, ctx->stream>>>(
-        ctx->cells.as<plc_cell>(), (unsigned)n_cells, ctx->cell_ref[0], ctx->cell_ref[1], ctx->cell_ref[2],
-        ctx->cells_f.as<float4>());
+    const uint64_t n_padded = (n_cells + kTileCells - 1) / kTileCells * kTileCells;
+    PLC_CUDA_TRY(ctx, ctx->cells_f.reserve(n_padded * sizeof(float4)));
+    k_cells_f32<<<(unsigned)((n_padded + 255) / 256), 256, 0, ctx->stream>>>(
+        ctx->cells.as<plc_cell>(), (unsigned)n_cells, (unsigned)n_padded, ctx->cell_ref[0], ctx->cell_ref[1],
+        ctx->cell_ref[2], ctx->cells_f.as<float4>());
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->n_cells = n_cells;

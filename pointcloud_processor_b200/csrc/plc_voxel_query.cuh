@@ -32,6 +32,13 @@ __device__ __forceinline__ unsigned long long ldg_stream(const unsigned long lon
     return v;
 }
 
+// One 16-bit occupancy row (an L1::evict_last hint made no measurable difference).
+__device__ __forceinline__ unsigned ldg_brick_row(const char* p) {
+    unsigned short v;
+    asm("ld.global.nc.u16 %0, [%1];" : "=h"(v) : "l"(p));
+    return v;
+}
+
 __device__ __forceinline__ float dist2_f32(float qx, float qy, float qz, float px, float py, float pz) {
     float ex = __fsub_rn(qx, px), ey = __fsub_rn(qy, py), ez = __fsub_rn(qz, pz);
     float acc = __fmul_rn(ex, ex);
@@ -67,9 +74,16 @@ __device__ __forceinline__ unsigned voxel_state(const VoxelGeom& g, int ix, int 
 __device__ __forceinline__ unsigned voxel_state_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
     const unsigned brick = brick_of(g, fx >> (16 + kFineShift), fy >> (16 + kFineShift), fz >> (16 + kFineShift));
     const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
-    const unsigned short row = __ldg(reinterpret_cast<const unsigned short*>(reinterpret_cast<const char*>(g.bricks) + off));
-    return ((unsigned)row >> (((unsigned)fx >> 15) & 0xeu)) & 3u;
+    return ((unsigned)ldg_brick_row(reinterpret_cast<const char*>(g.bricks) + off) >> (((unsigned)fx >> 15) & 0xeu)) & 3u;
 }
+
+// Split form for software pipelining: the row of the voxel holding (fx, fy, fz), and the state from a row.
+__device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
+    const unsigned brick = brick_of(g, fx >> (16 + kFineShift), fy >> (16 + kFineShift), fz >> (16 + kFineShift));
+    const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
+    return ldg_brick_row(reinterpret_cast<const char*>(g.bricks) + off);
+}
+__device__ __forceinline__ unsigned row_state(unsigned row, int fx) { return (row >> (((unsigned)fx >> 15) & 0xeu)) & 3u; }
 
 __device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int iy, int iz) {
     return (uint32_t)(((size_t)(iz >> 2) * g.mdim_y + (iy >> 2)) * g.mdim_x + (ix >> 2));
