@@ -85,7 +85,7 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->terrain.release();
     c->observed.release();
-    plc::DevBuf* bufs[] = {&c->upload, &c->scratch, &c->cells, &c->cells_f, &c->cell_flags, &c->fixed_scores, &c->cands,
+    plc::DevBuf* bufs[] = {&c->upload, &c->scratch, &c->cells, &c->cells_f, &c->tile_boxes, &c->cell_flags, &c->fixed_scores, &c->cands,
                            &c->partial_score, &c->partial_cov, &c->scores, &c->covered, &c->mask, &c->result, &c->pose_aux, &c->s_tab,
                            &c->f_keys, &c->f_vals, &c->f_keys2, &c->f_vals2, &c->f_tmp, &c->f_out, &c->f_flags,
                            &c->m_out};

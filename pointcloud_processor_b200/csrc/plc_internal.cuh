@@ -164,6 +164,7 @@ struct plc_ctx {
     plc::DevBuf cells;           // plc_cell[n_cells]
     uint64_t n_cells = 0;
     plc::DevBuf cells_f;         // float4[n_cells]: position relative to cell_ref, narrowed (k_sweep's float-first path)
+    plc::DevBuf tile_boxes;      // per k_sweep tile: bounding box of its cells (plc_sweep.cu TileBox)
     double cell_ref[3] = {0, 0, 0};
     float cells_radius = 0.f;    // half diagonal of the cells' bounding box (inf if a finite box does not exist)
     plc::DevBuf cell_flags;      // uint8[n_cells], persists across sweeps (Q3)

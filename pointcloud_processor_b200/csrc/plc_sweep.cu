@@ -51,6 +51,7 @@ struct SweepDev {
     // float32 cell positions relative to cell_ref (the centre of the cells' bounding box), one float4 per
     // cell, and the radius of that box: k_sweep's float-first path reads these instead of the doubles
     const float4* __restrict__ cells_f;
+    const void* __restrict__ tile_boxes;   // TileBox[tiles]
     double cell_ref[3];
     float cells_radius;
 };
@@ -305,6 +306,66 @@ k_cells_f32(const plc_cell* __restrict__ cells, unsigned n, unsigned n_padded, d
     out[j] = make_float4((float)(c.x - rx), (float)(c.y - ry), (float)(c.z - rz), 0.f);
 }
 
+// Bounding box of each k_sweep tile's cells, in the frame of the float32 copy.  k_sweep uses it to decide
+// once per (pose, tile) that no ray of the tile can fail the range and FOV gates, or be clipped on an axis.
+struct TileBox {
+    float lo[3], hi[3];
+    int full;        // 0: the tile has padding or a non-finite cell, which only the per-ray range gate rejects
+    int pad;
+};
+static_assert(sizeof(TileBox) == 32, "TileBox is read as two 16-byte words");
+
+__global__ void __launch_bounds__(256)
+k_tile_boxes(const float4* __restrict__ cells_f, unsigned n, TileBox* __restrict__ boxes) {
+    __shared__ float red[6][8];
+    const unsigned tile = blockIdx.x;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    bool finite = true;
+    for (unsigned i = threadIdx.x; i < (unsigned)kTileCells; i += blockDim.x) {
+        const unsigned j = tile * kTileCells + i;
+        if (j >= n) break;
+        const float4 c = cells_f[j];
+        const float v[3] = {c.x, c.y, c.z};
+        finite = finite && isfinite(c.x) && isfinite(c.y) && isfinite(c.z);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            lo[a] = fminf(lo[a], v[a]);
+            hi[a] = fmaxf(hi[a], v[a]);
+        }
+    }
+    const int all_finite = __syncthreads_and(finite ? 1 : 0);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0)
+        for (int a = 0; a < 3; ++a) {
+            red[a][warp] = lo[a];
+            red[3 + a][warp] = hi[a];
+        }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        TileBox b{};
+        for (int a = 0; a < 3; ++a) {
+            float l = red[a][0], h = red[3 + a][0];
+            for (int w = 1; w < 8; ++w) {
+                l = fminf(l, red[a][w]);
+                h = fmaxf(h, red[3 + a][w]);
+            }
+            b.lo[a] = l;
+            b.hi[a] = h;
+        }
+        // the per-tile shortcut is only taken for whole tiles of finite cells: padding and non-finite cells are
+        // rejected by the per-ray gate
+        b.full = ((tile + 1) * (unsigned)kTileCells <= n && all_finite) ? 1 : 0;
+        boxes[tile] = b;
+    }
+}
+
 // ---- K2+K3: one thread per (candidate, cell) ray ----------------------------------------------
 // grid.x = n_local * tiles, one warp per block; block b handles candidate b / tiles and cells
 // [tile*512, tile*512+512).  The 32 lanes hold 32 consecutive cells, so one ballot is one word of
@@ -377,6 +438,36 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     for (int a = 0; a < 3; ++a) s_in[a] = sf[a] >= G.clip_lo[a] && sf[a] <= G.clip_hi[a];
     // float32 clipping is only trusted to keep the march inside the grid at ordinary scene scale
     const bool trust_clip = fabsf(sf[0]) < P.trust_limit && fabsf(sf[1]) < P.trust_limit && fabsf(sf[2]) < P.trust_limit;
+    // ---- once per (pose, tile): can any ray of the tile fail a gate or be clipped on an axis?
+    bool skip_gates = false, skip_axis[3] = {false, false, false};
+    {
+        const float4* tbp = reinterpret_cast<const float4*>(static_cast<const TileBox*>(P.tile_boxes) + tile);
+        const float4 t0 = __ldg(tbp), t1 = __ldg(tbp + 1);      // lo.xyz hi.x | hi.yz full pad
+        const float lo_d[3] = {t0.x - A.sr[0], t0.y - A.sr[1], t0.z - A.sr[2]};
+        const float hi_d[3] = {t0.w - A.sr[0], t1.x - A.sr[1], t1.y - A.sr[2]};
+        float near2 = 0.f, far2 = 0.f, hnear2 = 0.f, hfar2 = 0.f;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float nr = lo_d[a] > 0.f ? lo_d[a] : (hi_d[a] < 0.f ? hi_d[a] : 0.f);
+            const float fr = fmaxf(fabsf(lo_d[a]), fabsf(hi_d[a]));
+            near2 += nr * nr;
+            far2 += fr * fr;
+            if (a == 1) {
+                hnear2 = near2;
+                hfar2 = far2;
+            }
+            skip_axis[a] = s_in[a] && sf[a] + lo_d[a] >= G.clip_lo[a] && sf[a] + hi_d[a] <= G.clip_hi[a];
+        }
+        const float dmin = sqrtf(near2), dmax = sqrtf(far2), h0 = sqrtf(hnear2), h1 = sqrtf(hfar2);
+        const float m = 1e-5f * dmax + 8.f * A.eabs + 1e-6f;         // float32 error of everything above, generously
+        const bool in_range = __float_as_int(t1.z) != 0 && dmin - m >= P.min_hi && dmax + m <= P.max_lo;
+        // elevation gate over the box: a = dz c_lo - hd s_lo grows with dz, b = hd s_hi - dz c_hi falls with dz
+        // (c_lo, c_hi >= 0), and both are linear in hd: their minima are at box corners in (dz, hd)
+        const float tol = 2.f * (2e-5f * dmax + 4.f * A.eabs) + m;
+        const float a_min = lo_d[2] * A.c_lo - (A.s_lo > 0.f ? h1 : h0) * A.s_lo;
+        const float b_min = (A.s_hi > 0.f ? h0 : h1) * A.s_hi - hi_d[2] * A.c_hi;
+        skip_gates = in_range && A.fast != 0 && a_min > tol && b_min > tol;
+    }
     unsigned gated = 0;
     unsigned long long exact = 0;
     int q_head = 0, q_n = 0;
@@ -431,7 +522,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         const float errL = 1e-6f * Lf + A.eabs;          // |Lf - L| bound (float32 cell/sensor offsets, products, sums and rsqrt)
         bool pass = false, redo = false;
         int n = 0;
-        if (Lf - errL >= P.min_hi && Lf + errL <= P.max_lo) pass = true;
+        if (skip_gates) pass = true;                     // the whole tile is in range and inside the FOV
+        else if (Lf - errL >= P.min_hi && Lf + errL <= P.max_lo) pass = true;
         else if (!(Lf + errL < P.min_lo || Lf - errL > P.max_hi)) redo = true;      // NaN lands here too
         if (pass && P.have_terrain) {
             // n = #{k : s_k < L - vis_radius} = #{k >= 0 : k < kf}
@@ -458,7 +550,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             }
         }
         // ---- FOV (:671-678, :703-714)
-        if (pass) {
+        if (pass && !skip_gates) {
             bool decided = false;
             if (A.fast) {
                 float hd = hd2 * rsqrt_fast(hd2);         // hd2 = 0 (vertical ray) gives NaN: not decided => exact path
@@ -488,9 +580,11 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
                 const float ca = sf[a] + df[a];
+                if (skip_axis[a]) continue;
                 if (s_in[a] && ca >= G.clip_lo[a] && ca <= G.clip_hi[a]) continue;
                 if (fabsf(uf[a]) > 1e-12f) {
-                    float inv = __fdividef(1.0f, uf[a]);
+                    float inv;
+                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(uf[a]));     // |uf| > 1e-12: no denormals
                     float t0 = (G.clip_lo[a] - sf[a]) * inv, t1 = (G.clip_hi[a] - sf[a]) * inv;
                     t_in = fmaxf(t_in, fminf(t0, t1));
                     t_out = fminf(t_out, fmaxf(t0, t1));
@@ -888,6 +982,10 @@ extern "C" plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint
     k_cells_f32<<<(unsigned)((n_padded + 255) / 256), 256, 0, ctx->stream>>>(
         ctx->cells.as<plc_cell>(), (unsigned)n_cells, (unsigned)n_padded, ctx->cell_ref[0], ctx->cell_ref[1],
         ctx->cell_ref[2], ctx->cells_f.as<float4>());
+    PLC_CUDA_TRY(ctx, ctx->tile_boxes.reserve(n_padded / kTileCells * sizeof(TileBox)));
+    k_tile_boxes<<<(unsigned)(n_padded / kTileCells), 256, 0, ctx->stream>>>(ctx->cells_f.as<float4>(), (unsigned)n_cells,
+                                                                             ctx->tile_boxes.as<TileBox>());
+    ctx->launches += 2;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->n_cells = n_cells;
@@ -948,6 +1046,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     P.inv_stepf = (float)(1.0 / p.ray_step);
     P.step_fine = (float)(p.ray_step * (double)P.terrain.inv_g * 65536.0);
     P.cells_f = ctx->cells_f.as<float4>();
+    P.tile_boxes = ctx->tile_boxes.ptr;
     for (int a = 0; a < 3; ++a) P.cell_ref[a] = ctx->cell_ref[a];
     P.cells_radius = ctx->cells_radius;
     {
