@@ -282,3 +282,22 @@ def test_full_size_properties_config2(ctx, scene_cache):
     ctx.set_terrain(s.terrain[perm])
     again = ctx.sweep(s.params, s.fixed, s.candidates, mask=True)
     assert np.array_equal(again.mask, full.mask) and np.array_equal(again.scores, full.scores)
+
+
+@pytest.mark.parametrize("fov_v, maxd, mind", [(0.35, 15.0, 0.5), (0.8, 5.5, 0.5), (3.0, 9.0, 6.0), (0.2, 7.0, 3.0)])
+def test_gates_cut_through_tiles(ctx, scene_cache, fov_v, maxd, mind):
+    # k_sweep decides the range and FOV gates once per (pose, 512-cell tile) when the tile's bounding box allows it
+    # and per ray otherwise: narrow FOVs, short ranges and a large minimum distance, with random pitches, make
+    # the gate boundaries cut through tiles in every way (all in, all out, straddling)
+    s = scene_cache("ref_default")
+    assert s.cells.size > 4 * 512
+    prm = A.default_params()
+    prm.fov_vertical, prm.max_distance, prm.min_distance = fov_v, maxd, mind
+    rng = np.random.default_rng(int(fov_v * 100) + int(maxd * 10))
+    cands = s.candidates.copy()
+    cands["pitch"] = rng.uniform(-1.4, 0.3, cands.size)
+    cands["z"] += rng.uniform(-0.5, 2.5, cands.size)
+    got = run_gpu(ctx, s, params=prm, cands=cands)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, prm, s.fixed, cands)
+    assert 0 < ref["counters"]["rays_gated_in"] < cands.size * s.cells.size
+    compare(got, ref, s.cells.size)
