@@ -248,6 +248,24 @@ k_fixed(SweepDev P, plc_pose fixed, const plc_cell* __restrict__ cells, unsigned
 //   sin(elevation - e_lo) * L = dz*cos(e_lo) - hd*sin(e_lo),   sin(e_hi - elevation) * L = hd*sin(e_hi) - dz*cos(e_hi)
 // k_sweep evaluates these in float32 and only falls back to the reference's double atan2 inside a
 // band around zero that is far wider than the float error.
+// Range gate and sample count exactly as upstream forms them (:662-669, :765-769), for the rays whose
+// float32 estimate does not decide: -1 if out of range, else #{k : s_k < L - vis_radius}.
+__device__ __forceinline__ int exact_range_gate(const SweepDev& P, double dx, double dy, double dz) {
+    const double L = ray_length(dx, dy, dz);
+    if (!(L >= P.min_distance && L <= P.max_distance)) return -1;
+    int n = 0;
+    if (P.have_terrain) {
+        const double end = __dsub_rn(L, P.vis_radius);
+        if (end > P.ray_start) {
+            n = (int)(__dsub_rn(end, P.ray_start) * P.inv_step) + 1;
+            n = max(0, min(n, P.n_tab - 1));
+            while (n > 0 && !(__ldg(&P.s_tab[n - 1]) < end)) --n;
+            while (n < P.n_tab - 1 && __ldg(&P.s_tab[n]) < end) ++n;
+        }
+    }
+    return n;
+}
+
 struct PoseAux {
     float c_lo, s_lo, c_hi, s_hi;
     int fast;        // 0: always take the exact path for this pose
@@ -520,63 +538,50 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         const float rinv = rsqrt_fast(L2f);           // L2f = 0 or overflow gives inf/NaN: every test below then fails over to `redo`
         const float Lf = L2f * rinv;
         const float errL = 1e-6f * Lf + A.eabs;          // |Lf - L| bound (float32 cell/sensor offsets, products, sums and rsqrt)
-        bool pass = false, redo = false;
-        int n = 0;
-        if (skip_gates) pass = true;                     // the whole tile is in range and inside the FOV
-        else if (Lf - errL >= P.min_hi && Lf + errL <= P.max_lo) pass = true;
-        else if (!(Lf + errL < P.min_lo || Lf - errL > P.max_hi)) redo = true;      // NaN lands here too
-        if (pass && P.have_terrain) {
+        // n >= 0: the ray passes the gates and upstream would evaluate n samples; n < 0: gated out
+        int n = -1;
+        bool redo = false;
+        if (skip_gates || (Lf - errL >= P.min_hi && Lf + errL <= P.max_lo)) {
             // n = #{k : s_k < L - vis_radius} = #{k >= 0 : k < kf}
-            float kf = (Lf - P.vis_start_f) * P.inv_stepf;
-            float tolk = (errL + 1e-6f) * P.inv_stepf + fabsf(kf) * 3e-7f + 1e-5f;
-            if (fabsf(kf - rintf(kf)) <= tolk) redo = true;
-            else n = kf > 0.f ? min((int)ceilf(kf), P.n_tab - 1) : 0;
+            const float kf = (Lf - P.vis_start_f) * P.inv_stepf;
+            const float tolk = (errL + 1e-6f) * P.inv_stepf + fabsf(kf) * 3e-7f + 1e-5f;
+            n = P.have_terrain ? min(max((int)ceilf(kf), 0), P.n_tab - 1) : 0;
+            redo = P.have_terrain && !(fabsf(kf - rintf(kf)) > tolk);       // too close to an integer (or NaN)
+        } else {
+            redo = !(Lf + errL < P.min_lo || Lf - errL > P.max_hi) && j < n_cells;   // NaN lands here too; padding never
         }
-        if (redo && j >= n_cells) redo = false;          // padding can only get here if the error bound is not finite
         if (redo) {                                       // as upstream, in double (rare)
             double dx, dy, dz;
             exact_d(j, dx, dy, dz);
-            double L = ray_length(dx, dy, dz);
-            pass = L >= P.min_distance && L <= P.max_distance;
-            n = 0;
-            if (pass && P.have_terrain) {
-                double end = __dsub_rn(L, P.vis_radius);
-                if (end > P.ray_start) {
-                    n = (int)(__dsub_rn(end, P.ray_start) * P.inv_step) + 1;
-                    n = max(0, min(n, P.n_tab - 1));
-                    while (n > 0 && !(__ldg(&P.s_tab[n - 1]) < end)) --n;
-                    while (n < P.n_tab - 1 && __ldg(&P.s_tab[n]) < end) ++n;
-                }
-            }
+            n = exact_range_gate(P, dx, dy, dz);
         }
         // ---- FOV (:671-678, :703-714)
-        if (pass && !skip_gates) {
+        if (n >= 0 && !skip_gates) {
             bool decided = false;
             if (A.fast) {
                 float hd = hd2 * rsqrt_fast(hd2);         // hd2 = 0 (vertical ray) gives NaN: not decided => exact path
                 float a = df[2] * A.c_lo - hd * A.s_lo, b = hd * A.s_hi - df[2] * A.c_hi;
                 float tol = 2e-5f * Lf + 4.f * A.eabs;
                 if (a > tol && b > tol) decided = true;
-                else if (a < -tol || b < -tol) { decided = true; pass = false; }
+                else if (a < -tol || b < -tol) { decided = true; n = -1; }
             }
             if (!decided) {
                 double dx, dy, dz;
                 exact_d(j, dx, dy, dz);
-                pass = in_fov_exact(P, s.pitch, s.yaw, dx, dy, dz);
+                if (!in_fov_exact(P, s.pitch, s.yaw, dx, dy, dz)) n = -1;
             }
         }
-        gated += pass ? 1u : 0u;
-        sts_u32(ray_state + 4u * slot, (unsigned)(pass ? kOpen + n : -1));        // published before any of the ray's samples can be queued
+        gated += n >= 0 ? 1u : 0u;
+        sts_u32(ray_state + 4u * slot, (unsigned)(n >= 0 ? kOpen + n : -1));      // published before any of the ray's samples can be queued
 
         // ---- checkVisibilityWithRaycasting (:754-800): clear / certain samples here, uncertain ones queued
         int k = 0, k_hi = 0;
         int fx = 0, fy = 0, fz = 0, dfx = 0, dfy = 0, dfz = 0;
-        if (pass && n > 0) {
+        if (n > 0) {
             const float uf[3] = {df[0] * rinv, df[1] * rinv, df[2] * rinv};
             // clip [0, n) against the reach box (conservative by clip_t metres); an axis on which both
             // the sensor and the target lie inside the box's slab cannot bind
             float t_in = 0.f, t_out = 3.0e38f;
-            bool miss = false;
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
                 const float ca = sf[a] + df[a];
@@ -589,13 +594,13 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     t_in = fmaxf(t_in, fminf(t0, t1));
                     t_out = fminf(t_out, fmaxf(t0, t1));
                 } else if (!s_in[a]) {
-                    miss = true;
+                    t_out = -3.0e38f;                     // parallel to the slab and outside it: misses the box
                 }
             }
             float klo_f = ceilf((t_in - G.clip_t - P.startf) * P.inv_stepf);
             float khi_f = floorf((t_out + G.clip_t - P.startf) * P.inv_stepf) + 1.0f;
             k = (int)fminf(fmaxf(klo_f, 0.f), (float)n);
-            k_hi = miss ? k : (int)fminf(fmaxf(khi_f, 0.f), (float)n);
+            k_hi = (int)fminf(fmaxf(khi_f, 0.f), (float)n);
             if (k < k_hi) {
                 // fixed-point fine-voxel coordinate of sample k and its per-step increment
                 const float t0 = fmaf((float)k, P.stepf, P.startf);
