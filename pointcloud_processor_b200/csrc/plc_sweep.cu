@@ -644,18 +644,17 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             while (q_n + 32 <= kQueueCap) {               // room for one more push from every lane
                 unsigned st = 0;
                 if (k < k_hi) {
-                    unsigned row_next = 0;
-                    if (k + 1 < k_hi) row_next = brick_row_fixed(G, fx + dfx, fy + dfy, fz + dfz);
-                    st = row_state(row, fx);
-                    row = row_next;
+                    st = (row >> row_shift(fx)) & 3u;
+                    fx += dfx;                            // position of sample k + 1 (unused if the ray ends here)
+                    fy += dfy;
+                    fz += dfz;
+                    row = 0;
+                    if (k + 1 < k_hi) row = brick_row_fixed(G, fx, fy, fz);      // in flight through the rest of the step
                     if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
                         reds_min_s32(ray_state + 4u * slot, k);
                         k = k_hi;
                     } else {
                         ++k;
-                        fx += dfx;
-                        fy += dfy;
-                        fz += dfz;
                     }
                 }
                 const unsigned ub = __ballot_sync(FULL, st == 1u);     // lanes whose sample k - 1 was uncertain
@@ -685,6 +684,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         bool vis = st >= kOpen;
         if (st >= 0 && P.have_terrain) samples += (unsigned)(vis ? st - kOpen : st + 1);
         if (j < n_cells) {
+            const double fixed = __ldg(&fixed_scores[j]);                // requested before the score arithmetic
             double mobile = 0.0;
             if (vis) {
                 plc_cell c = load_cell(cells, j);
@@ -700,7 +700,6 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 mobile = __dadd_rn(__dmul_rn(P.alpha, cc), __dmul_rn(P.beta, rl));
                 mobile = mobile > 0.0 ? mobile : 0.0;
             }
-            const double fixed = __ldg(&fixed_scores[j]);
             double combined = mobile > fixed ? mobile : fixed;           // :639
             if (combined > 0) {                                          // :641-644
                 ++covered;

@@ -83,7 +83,7 @@ __device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, 
     const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
     return ldg_brick_row(reinterpret_cast<const char*>(g.bricks) + off);
 }
-__device__ __forceinline__ unsigned row_state(unsigned row, int fx) { return (row >> (((unsigned)fx >> 15) & 0xeu)) & 3u; }
+__device__ __forceinline__ unsigned row_shift(int fx) { return ((unsigned)fx >> 15) & 0xeu; }
 
 __device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int iy, int iz) {
     return (uint32_t)(((size_t)(iz >> 2) * g.mdim_y + (iy >> 2)) * g.mdim_x + (ix >> 2));
