@@ -29,7 +29,10 @@ namespace {
 constexpr int kSweepThreads = 128;       // k_fixed / k_flags: one thread per cell
 // k_sweep runs ONE warp per block (no block barrier, a finished warp frees its slot at once):
 // 32 lanes x 16 rays = 512 consecutive cells of one candidate per block.
-constexpr int kRaysPerThread = 16;
+#ifndef PLC_RAYS_PER_THREAD
+#define PLC_RAYS_PER_THREAD 16
+#endif
+constexpr int kRaysPerThread = PLC_RAYS_PER_THREAD;
 constexpr int kTileCells = 32 * kRaysPerThread;
 
 struct SweepDev {
@@ -432,9 +435,19 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     // (three uniform instructions) at every access.
     //   plc_ray_state  int[kTileCells]    -1 gated out; first blocked sample index; or kOpen + n
     //   plc_q_tag      uint32[kQueueCap]  ring of (ray slot << 16 | sample index)
-    static_assert(kTileCells == 512 && kQueueCap == 128, "sizes are spelled out in the PTX declaration below");
+    static_assert(kQueueCap == 128, "sizes are spelled out in the PTX declaration below");
+#if PLC_RAYS_PER_THREAD == 8
+#define PLC_RAY_STATE_BYTES "1024"
+#elif PLC_RAYS_PER_THREAD == 16
+#define PLC_RAY_STATE_BYTES "2048"
+#elif PLC_RAYS_PER_THREAD == 32
+#define PLC_RAY_STATE_BYTES "4096"
+#else
+#error "PLC_RAYS_PER_THREAD must be 8, 16 or 32"
+#endif
+    static_assert(kTileCells * 4 == PLC_RAYS_PER_THREAD * 128, "ray state bytes");
     unsigned q_tag, ray_state;
-    asm volatile(".shared .align 16 .b8 plc_ray_state[2048];\n\t"
+    asm volatile(".shared .align 16 .b8 plc_ray_state[" PLC_RAY_STATE_BYTES "];\n\t"
                  ".shared .align 16 .b8 plc_q_tag[512];\n\t"
                  "mov.u32 %0, plc_ray_state;\n\t"
                  "mov.u32 %1, plc_q_tag;"
@@ -1186,6 +1199,14 @@ extern "C" plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms) {
     PLC_CUDA_TRY(ctx, cudaEventElapsedTime(ms, ctx->ev_sweep_begin, ctx->ev_sweep_end));
     return PLC_OK;
 }
+
+#ifdef PLC_BOUNDS_CHECK
+extern "C" unsigned long long plc_dev_oob_count() {
+    unsigned long long v = ~0ull;
+    cudaMemcpyFromSymbol(&v, plc_oob_count, sizeof(v));
+    return v;
+}
+#endif
 
 extern "C" plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out) {
     if (!ctx || !out) return PLC_E_INVALID_ARG;

@@ -32,6 +32,18 @@ __device__ __forceinline__ unsigned long long ldg_stream(const unsigned long lon
     return v;
 }
 
+#ifdef PLC_BOUNDS_CHECK
+// Debug build only (tools/sanitize.py): out-of-range structure accesses are counted and skipped.
+__device__ unsigned long long plc_oob_count = 0;
+#define PLC_CHECK_OOB(cond, fallback)              \
+    if (cond) {                                     \
+        atomicAdd(&plc_oob_count, 1ull);            \
+        return fallback;                            \
+    }
+#else
+#define PLC_CHECK_OOB(cond, fallback)
+#endif
+
 // One 16-bit occupancy row (an L1::evict_last hint made no measurable difference).
 __device__ __forceinline__ unsigned ldg_brick_row(const char* p) {
     unsigned short v;
@@ -79,6 +91,8 @@ __device__ __forceinline__ unsigned voxel_state_fixed(const VoxelGeom& g, int fx
 
 // Split form for software pipelining: the row of the voxel holding (fx, fy, fz), and the state from a row.
 __device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
+    PLC_CHECK_OOB((unsigned)(fx >> 16) >= (unsigned)(g.dim_x << kFineShift) || (unsigned)(fy >> 16) >= (unsigned)(g.dim_y << kFineShift) ||
+                  (unsigned)(fz >> 16) >= (unsigned)(g.dim_z << kFineShift), 0u)
     const unsigned brick = brick_of(g, fx >> (16 + kFineShift), fy >> (16 + kFineShift), fz >> (16 + kFineShift));
     const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
     return ldg_brick_row(reinterpret_cast<const char*>(g.bricks) + off);
@@ -91,6 +105,7 @@ __device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int
 
 // Exact existence test over the candidate list of mid voxel m, four points per iteration.
 __device__ __forceinline__ bool cand_any_m(const VoxelGeom& g, uint32_t m, float qx, float qy, float qz, float thr) {
+    PLC_CHECK_OOB(m >= (uint32_t)g.mdim_x * (uint32_t)g.mdim_y * (uint32_t)g.mdim_z, false)
     uint32_t s = __ldg(&g.gstart[m]), e = __ldg(&g.gstart[m + 1]);
     const float4* __restrict__ grp = g.cgrp + (size_t)s * 3;
     for (; s < e; ++s, grp += 3) {
