@@ -511,12 +511,16 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         dz = __dsub_rn(__longlong_as_double((long long)__ldg(cp + 2)), s.z);
     };
 
-    // resolves up to 32 queued samples, one per lane, exactly as upstream evaluates them
+    // Resolves up to 32 queued samples exactly as upstream evaluates them.  Each lane recomputes one sample's
+    // position; the candidate groups of all 32 lists are then dealt out evenly over the lanes (list lengths vary
+    // several-fold), each lane testing groups that may belong to another lane's sample.
     auto drain = [&]() {
         __syncwarp();
         int take = q_n < 32 ? q_n : 32;
+        unsigned tag = 0, g0 = 0, gn = 0;          // this lane's sample: tag, first candidate group, group count
+        float qx = 0.f, qy = 0.f, qz = 0.f;
         if (lane < take) {
-            unsigned tag = lds_u32(q_tag + 4u * ((q_head + lane) & (kQueueCap - 1)));
+            tag = lds_u32(q_tag + 4u * ((q_head + lane) & (kQueueCap - 1)));
             int eslot = (int)(tag >> 16), ek = (int)(tag & 0xffffu);
             if ((int)lds_u32(ray_state + 4u * eslot) > ek) {             // not already blocked earlier on the ray
                 ++exact;
@@ -524,14 +528,45 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 exact_d(tile * kTileCells + eslot, ex, ey, ez);
                 double eL = ray_length(ex, ey, ez);
                 double t = __ldg(&P.s_tab[ek]);
-                float qx = (float)__dadd_rn(s.x, __dmul_rn(__ddiv_rn(ex, eL), t));      // :770-777
-                float qy = (float)__dadd_rn(s.y, __dmul_rn(__ddiv_rn(ey, eL), t));
-                float qz = (float)__dadd_rn(s.z, __dmul_rn(__ddiv_rn(ez, eL), t));
+                qx = (float)__dadd_rn(s.x, __dmul_rn(__ddiv_rn(ex, eL), t));      // :770-777
+                qy = (float)__dadd_rn(s.y, __dmul_rn(__ddiv_rn(ey, eL), t));
+                qz = (float)__dadd_rn(s.z, __dmul_rn(__ddiv_rn(ez, eL), t));
                 // candidate list of the sample's own mid voxel (clamped: the march kept it inside the grid)
                 int ix = clamp_i((int)fine_coord_f(qx, G.ox, G.inv_g), 0, (G.dim_x << kFineShift) - 1);
                 int iy = clamp_i((int)fine_coord_f(qy, G.oy, G.inv_g), 0, (G.dim_y << kFineShift) - 1);
                 int iz = clamp_i((int)fine_coord_f(qz, G.oz, G.inv_g), 0, (G.dim_z << kFineShift) - 1);
-                if (cand_any(G, ix, iy, iz, qx, qy, qz, P.thr_block)) reds_min_s32(ray_state + 4u * eslot, ek);
+                const uint32_t m = mid_voxel_of(G, ix, iy, iz);
+                g0 = __ldg(&G.gstart[m]);
+                gn = __ldg(&G.gstart[m + 1]) - g0;
+            }
+        }
+        // exclusive prefix of the group counts: flat group index i belongs to the last lane o with pre[o] <= i
+        unsigned pre = gn;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned v = __shfl_up_sync(FULL, pre, o);
+            if (lane >= o) pre += v;
+        }
+        const unsigned total = __shfl_sync(FULL, pre, 31);
+        pre -= gn;
+        for (unsigned base = 0; base < total; base += 32) {
+            const unsigned i = base + lane;
+            unsigned o = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+                const unsigned c = o + step;                              // c <= 31
+                if (__shfl_sync(FULL, pre, c) <= i) o = c;
+            }
+            const unsigned o_pre = __shfl_sync(FULL, pre, o), o_g0 = __shfl_sync(FULL, g0, o);
+            const unsigned o_tag = __shfl_sync(FULL, tag, o);
+            const float ox = __shfl_sync(FULL, qx, o), oy = __shfl_sync(FULL, qy, o), oz = __shfl_sync(FULL, qz, o);
+            if (i < total) {
+                const float4* grp = G.cgrp + (size_t)(o_g0 + (i - o_pre)) * 3;
+                const float4 X = ldg_stream(grp), Y = ldg_stream(grp + 1), Z = ldg_stream(grp + 2);
+                const float d0 = dist2_f32(ox, oy, oz, X.x, Y.x, Z.x), d1 = dist2_f32(ox, oy, oz, X.y, Y.y, Z.y);
+                const float d2 = dist2_f32(ox, oy, oz, X.z, Y.z, Z.z), d3 = dist2_f32(ox, oy, oz, X.w, Y.w, Z.w);
+                if (fminf(fminf(d0, d1), fminf(d2, d3)) < P.thr_block)
+                    reds_min_s32(ray_state + 4u * (o_tag >> 16), (int)(o_tag & 0xffffu));
             }
         }
         __syncwarp();
