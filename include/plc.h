@@ -178,6 +178,29 @@ plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr);
 plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms);
 
 /* Grid facts for roofline accounting: bytes of the occupancy structure the sweep reads. */
+/* ---------------------------------------------------------------- several GPUs, one process -- */
+
+/* The reference node is one process (virtual_lidar.cpp:965-969).  A group owns one context per listed CUDA
+ * device and runs the sweep over all of them: terrain, observed cloud and cells replicated, candidate poses
+ * sharded in contiguous blocks [floor(g C / G), floor((g+1) C / G)), one NCCL all-gather of 16 bytes per device
+ * ({f64 best_score, i64 best_global_index}), first maximum = lowest global index.  NCCL is
+ * loaded at run time (libnccl.so.2) and only for groups of more than one device; failure is PLC_E_NCCL.
+ * Same threading contract as a context: calls on one group must not overlap. */
+typedef struct plc_group plc_group;
+plc_status plc_group_create(const int* devices, int n_devices, plc_group** out);
+void plc_group_destroy(plc_group* group);
+int plc_group_size(const plc_group* group);
+/* Context of the i-th device, for the per-context queries (plc_vl_grid_info, plc_last_device_times, ...). */
+plc_ctx* plc_group_ctx(plc_group* group, int i);
+const char* plc_group_last_error(const plc_group* group);
+/* plc_vl_set_* on every device (one host thread each). */
+plc_status plc_group_set_terrain(plc_group* group, const plc_cloud_view* cloud);
+plc_status plc_group_set_observed(plc_group* group, const plc_cloud_view* cloud);
+plc_status plc_group_set_cells(plc_group* group, const plc_cell* cells, uint64_t n_cells);
+/* plc_vl_sweep over the whole candidate list; the optional arrays of `out` are indexed by GLOBAL candidate. */
+plc_status plc_group_sweep(plc_group* group, const plc_params* prm, const plc_pose* fixed,
+                           const plc_pose* cands, uint64_t n_cands, plc_sweep_out* out);
+
 /* Device time (ms, CUDA events on the context's stream) spent in the kernels of the most recent call of each
  * kind; host<->device copies and host-side waits are excluded.  0 until that call has run.  For benchmarks and
  * profiles: the reference has no counterpart. */

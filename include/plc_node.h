@@ -48,6 +48,8 @@ typedef struct plc_vlnode_result {
 
 /* The node's constructor (:62-97) minus rclcpp: parameters at their declared defaults. */
 plc_status plc_vlnode_create(plc_ctx* ctx, plc_vlnode** out);
+/* The same node over a multi-GPU group (plc.h, plc_group_*): every sweep is sharded over the group's devices. */
+plc_status plc_vlnode_create_on_group(plc_group* group, plc_vlnode** out);
 void plc_vlnode_destroy(plc_vlnode* node);
 
 /* declare_parameter/get_parameter surface (:66-71): grid_resolution, sensor_height, search_radius,

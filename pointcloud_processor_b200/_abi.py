@@ -117,10 +117,12 @@ EXPORTS = [
     "plc_vl_upload_candidates", "plc_vl_run_async", "plc_vl_fetch", "plc_vl_result_device_ptr",
     "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times", "plc_filter", "plc_merge",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
-    "plc_vlnode_create", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
+    "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
     "plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback", "plc_vlnode_zx120_points_callback",
     "plc_vlnode_set_base_transform", "plc_vlnode_run_optimization", "plc_vlnode_get_candidates",
     "plc_vlnode_get_cells", "plc_vlnode_get_bounds", "plc_vlnode_take_log", "plc_filter_scan", "plc_merge_clouds",
+    "plc_group_create", "plc_group_destroy", "plc_group_size", "plc_group_ctx", "plc_group_last_error",
+    "plc_group_set_terrain", "plc_group_set_observed", "plc_group_set_cells", "plc_group_sweep",
 ]
 
 _lib = None
@@ -182,6 +184,7 @@ def lib() -> C.CDLL:
     L.plc_host_generate_candidates.argtypes = [C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
                                                dbl, dbl, vp, u64, C.POINTER(u64)]
     L.plc_vlnode_create.argtypes = [vp, C.POINTER(vp)]
+    L.plc_vlnode_create_on_group.argtypes = [vp, C.POINTER(vp)]
     L.plc_vlnode_destroy.argtypes = [vp]
     L.plc_vlnode_destroy.restype = None
     L.plc_vlnode_set_parameter_double.argtypes = [vp, C.c_char_p, dbl]
@@ -199,6 +202,18 @@ def lib() -> C.CDLL:
     L.plc_filter_scan.argtypes = [vp, C.POINTER(CloudView), dbl, dbl, dbl, dbl, vp, u64, C.POINTER(u64)]
     L.plc_merge_clouds.argtypes = [vp, C.POINTER(MergerInput), C.POINTER(MergerInput), vp, u64, C.POINTER(u64),
                                    vp, u64, C.POINTER(u64), vp, u64, C.POINTER(u64)]
+    L.plc_group_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+    L.plc_group_destroy.argtypes = [vp]
+    L.plc_group_destroy.restype = None
+    L.plc_group_size.argtypes = [vp]
+    L.plc_group_ctx.argtypes = [vp, C.c_int]
+    L.plc_group_ctx.restype = vp
+    L.plc_group_last_error.argtypes = [vp]
+    L.plc_group_last_error.restype = C.c_char_p
+    L.plc_group_set_terrain.argtypes = [vp, C.POINTER(CloudView)]
+    L.plc_group_set_observed.argtypes = [vp, C.POINTER(CloudView)]
+    L.plc_group_set_cells.argtypes = [vp, vp, u64]
+    L.plc_group_sweep.argtypes = [vp, C.POINTER(Params), vp, vp, u64, C.POINTER(SweepOut)]
     _lib = L
     return L
 

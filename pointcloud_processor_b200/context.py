@@ -252,3 +252,63 @@ def host_generate_candidates(terrain: np.ndarray, bounds: A.GridBounds, fixed: n
     if st != A.PLC_OK:
         raise A.PlcError(st, "plc_host_generate_candidates")
     return out[: n.value].copy()
+
+
+class Group:
+    """plc_group_*: the sweep on several GPUs from one process (terrain and cells replicated, candidate poses
+    sharded, one NCCL all-gather of 16 bytes per device).  Results are indexed by global candidate."""
+
+    def __init__(self, devices):
+        self._L = A.lib()
+        devs = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        st = self._L.plc_group_create(devs, len(devices), C.byref(h))
+        if st != A.PLC_OK:
+            raise A.PlcError(st, "plc_group_create", "")
+        self._h = h
+        self.devices = list(devices)
+        self.n_cells = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.plc_group_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st, where):
+        if st != A.PLC_OK:
+            raise A.PlcError(st, where, self._L.plc_group_last_error(self._h).decode())
+
+    def set_terrain(self, cloud, point_step=None, off=(0, 4, 8)):
+        v = A.cloud_view(cloud, point_step, off)
+        self._check(self._L.plc_group_set_terrain(self._h, C.byref(v)), "plc_group_set_terrain")
+
+    def set_observed(self, cloud, point_step=None, off=(0, 4, 8)):
+        v = A.cloud_view(cloud, point_step, off)
+        self._check(self._L.plc_group_set_observed(self._h, C.byref(v)), "plc_group_set_observed")
+
+    def set_cells(self, cells):
+        cells = np.ascontiguousarray(cells, dtype=A.CELL_DTYPE)
+        self._check(self._L.plc_group_set_cells(self._h, A.ptr(cells) if cells.size else None, cells.size),
+                    "plc_group_set_cells")
+        self.n_cells = int(cells.size)
+
+    def sweep(self, params, fixed, cands, *, scores=True, mask=False, flags=False, fixed_scores=False) -> SweepResult:
+        cands = np.ascontiguousarray(cands, dtype=A.POSE_DTYPE)
+        fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
+        out, arrays = Context._alloc_out(self, cands.size, scores, mask, flags, fixed_scores)
+        st = self._L.plc_group_sweep(self._h, C.byref(params), A.ptr(fixed), A.ptr(cands) if cands.size else None,
+                                     cands.size, C.byref(out))
+        self._check(st, "plc_group_sweep")
+        return Context._result(self, out, arrays)

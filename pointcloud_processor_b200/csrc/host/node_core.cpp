@@ -52,6 +52,10 @@ double percent(int part, int total) { return total > 0 ? static_cast<double>(par
 
 struct plc_vlnode {
     plc_ctx* ctx = nullptr;
+    plc_group* group = nullptr;      // set instead of ctx when the node drives several GPUs
+    plc_status set_terrain(const plc_cloud_view* c) { return group ? plc_group_set_terrain(group, c) : plc_vl_set_terrain(ctx, c); }
+    plc_status set_observed(const plc_cloud_view* c) { return group ? plc_group_set_observed(group, c) : plc_vl_set_observed(ctx, c); }
+    plc_status set_cells(const plc_cell* c, uint64_t m) { return group ? plc_group_set_cells(group, c, m) : plc_vl_set_cells(ctx, c, m); }
     // declared parameters (:66-71) and the copies updateParameters() refreshes (:155-162)
     double p_grid_resolution = 0.1, p_sensor_height = 1.1, p_search_radius = 3.0, p_max_distance = 15.0;
     int64_t p_num_candidates = 100, p_vertical_layers = 10;
@@ -93,23 +97,33 @@ struct plc_vlnode {
     }
 };
 
-extern "C" plc_status plc_vlnode_create(plc_ctx* ctx, plc_vlnode** out) {
-    if (!ctx || !out) return PLC_E_INVALID_ARG;
+static plc_status vlnode_create(plc_ctx* ctx, plc_group* group, plc_vlnode** out) {
     plc_vlnode* n = new (std::nothrow) plc_vlnode();
     if (!n) return PLC_E_OOM;
     n->ctx = ctx;
+    n->group = group;
     n->update_parameters();     // constructor, :73
-    // a freshly constructed node has no clouds and no grid: drop whatever the context held before
+    // a freshly constructed node has no clouds and no grid: drop whatever the context(s) held before
     plc_cloud_view none{};
-    plc_status st = plc_vl_set_terrain(ctx, &none);
-    if (st == PLC_OK) st = plc_vl_set_observed(ctx, &none);
-    if (st == PLC_OK) st = plc_vl_set_cells(ctx, nullptr, 0);
+    plc_status st = n->set_terrain(&none);
+    if (st == PLC_OK) st = n->set_observed(&none);
+    if (st == PLC_OK) st = n->set_cells(nullptr, 0);
     if (st != PLC_OK) {
         delete n;
         return st;
     }
     *out = n;
     return PLC_OK;
+}
+
+extern "C" plc_status plc_vlnode_create(plc_ctx* ctx, plc_vlnode** out) {
+    if (!ctx || !out) return PLC_E_INVALID_ARG;
+    return vlnode_create(ctx, nullptr, out);
+}
+
+extern "C" plc_status plc_vlnode_create_on_group(plc_group* group, plc_vlnode** out) {
+    if (!group || !out) return PLC_E_INVALID_ARG;
+    return vlnode_create(nullptr, group, out);
 }
 
 extern "C" void plc_vlnode_destroy(plc_vlnode* node) { delete node; }
@@ -156,7 +170,7 @@ extern "C" plc_status plc_vlnode_excavation_area_callback(plc_vlnode* n, const p
     n->bounds = b;
     n->info("Generated 3D grid: %d valid cells across %d vertical layers", static_cast<int>(n->cells.size()),
             n->vertical_layers);              // :284-285
-    return plc_vl_set_cells(n->ctx, n->cells.data(), n->cells.size());
+    return n->set_cells(n->cells.data(), n->cells.size());
 }
 
 // terrainCallback (:180-192): the cloud pointer is replaced even when empty, the index only when not.
@@ -164,7 +178,7 @@ extern "C" plc_status plc_vlnode_terrain_callback(plc_vlnode* n, const plc_cloud
     if (!n || !view_ok(cloud)) return PLC_E_INVALID_ARG;
     n->terrain.store(*cloud);
     if (cloud->n_points == 0) return PLC_OK;
-    plc_status st = plc_vl_set_terrain(n->ctx, cloud);
+    plc_status st = n->set_terrain(cloud);
     if (st == PLC_OK) n->terrain_indexed = true;
     return st;
 }
@@ -175,7 +189,7 @@ extern "C" plc_status plc_vlnode_zx120_points_callback(plc_vlnode* n, const plc_
     n->observed_points = cloud->n_points;
     // an empty message empties zx120_cloud_, and checkVisibility then takes the ray path (:719) whatever
     // tree is left over: clearing the observed index has the same effect
-    plc_status st = plc_vl_set_observed(n->ctx, cloud);
+    plc_status st = n->set_observed(cloud);
     if (st == PLC_OK && cloud->n_points) n->info("ZX120 point cloud updated: %zu points", static_cast<size_t>(cloud->n_points));   // :204
     return st;
 }
@@ -256,7 +270,8 @@ extern "C" plc_status plc_vlnode_run_optimization(plc_vlnode* n, plc_vlnode_resu
     so.scores = n_cands ? n->scores.data() : nullptr;
     so.cell_flags = n->flags.data();
     so.fixed_scores = fixed_scores.data();
-    st = plc_vl_sweep(n->ctx, &prm, &fixed, cands.data(), n_cands, 0, n_cands, &so);
+    st = n->group ? plc_group_sweep(n->group, &prm, &fixed, cands.data(), n_cands, &so)
+                  : plc_vl_sweep(n->ctx, &prm, &fixed, cands.data(), n_cands, 0, n_cands, &so);
     if (st != PLC_OK) return st;
 
     // ---- evaluateZX120Only statistics (:360-452)

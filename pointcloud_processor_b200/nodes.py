@@ -13,11 +13,14 @@ from .context import Context
 class VirtualLidarNode:
     """plc_vlnode: state and callbacks of SimplifiedDualLidarOptimizer (virtual_lidar.cpp:60-548)."""
 
-    def __init__(self, ctx: Context):
+    def __init__(self, ctx):
+        """ctx: a Context (one GPU) or a context.Group (several GPUs, sweeps sharded over them)."""
         self._L = A.lib()
         self._ctx = ctx
+        self._on_group = not isinstance(ctx, Context)
         h = C.c_void_p()
-        st = self._L.plc_vlnode_create(ctx._h, C.byref(h))
+        create = self._L.plc_vlnode_create_on_group if self._on_group else self._L.plc_vlnode_create
+        st = create(ctx._h, C.byref(h))
         if st != A.PLC_OK:
             raise A.PlcError(st, "plc_vlnode_create")
         self._h = h
@@ -35,7 +38,8 @@ class VirtualLidarNode:
 
     def _check(self, st, where):
         if st != A.PLC_OK:
-            raise A.PlcError(st, where, self._L.plc_last_error(self._ctx._h).decode())
+            err = self._L.plc_group_last_error if self._on_group else self._L.plc_last_error
+            raise A.PlcError(st, where, err(self._ctx._h).decode())
 
     def set_parameter(self, name: str, value):
         if isinstance(value, (int, np.integer)) and not isinstance(value, bool):

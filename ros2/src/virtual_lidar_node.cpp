@@ -64,12 +64,26 @@ public:
         for (const char* name : kDoubleParams) declare_parameter(name, default_of(name));
         declare_parameter("num_candidates", 100);
         declare_parameter("vertical_layers", 10);
-        declare_parameter("cuda_device", 0);     // the one addition: which GPU this node runs on
+        // the two additions: which GPU this node runs on, or how many GPUs (0..n-1) its sweeps are sharded over
+        declare_parameter("cuda_device", 0);
+        declare_parameter("cuda_devices", 1);
 
         const int device = static_cast<int>(get_parameter("cuda_device").as_int());
-        if (plc_ctx_create(device, nullptr, &ctx_) != PLC_OK || plc_vlnode_create(ctx_, &core_) != PLC_OK) {
-            RCLCPP_FATAL(get_logger(), "no usable CUDA device %d: this node has no CPU fallback", device);
-            throw std::runtime_error("plc_ctx_create failed");
+        const int n_devices = static_cast<int>(get_parameter("cuda_devices").as_int());
+        plc_status st;
+        if (n_devices > 1) {
+            std::vector<int> devs(n_devices);
+            for (int i = 0; i < n_devices; ++i) devs[i] = i;
+            st = plc_group_create(devs.data(), n_devices, &group_);
+            if (st == PLC_OK) st = plc_vlnode_create_on_group(group_, &core_);
+            if (st == PLC_OK) ctx_ = plc_group_ctx(group_, 0);      // for error text and the per-context queries
+        } else {
+            st = plc_ctx_create(device, nullptr, &ctx_);
+            if (st == PLC_OK) st = plc_vlnode_create(ctx_, &core_);
+        }
+        if (st != PLC_OK) {
+            RCLCPP_FATAL(get_logger(), "no usable CUDA device(s) (%s): this node has no CPU fallback", plc_strerror(st));
+            throw std::runtime_error("plc context creation failed");
         }
         push_parameters();
 
@@ -99,7 +113,8 @@ public:
 
     ~VirtualLidarGpuNode() override {
         plc_vlnode_destroy(core_);
-        plc_ctx_destroy(ctx_);
+        if (group_) plc_group_destroy(group_);      // owns its contexts
+        else plc_ctx_destroy(ctx_);
     }
 
 private:
@@ -192,6 +207,7 @@ private:
     }
 
     plc_ctx* ctx_ = nullptr;
+    plc_group* group_ = nullptr;
     plc_vlnode* core_ = nullptr;
     std::shared_ptr<tf2_ros::Buffer> tf_buffer_;
     std::shared_ptr<tf2_ros::TransformListener> tf_listener_;
