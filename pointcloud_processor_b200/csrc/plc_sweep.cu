@@ -51,6 +51,7 @@ struct SweepDev {
     // float32 views of the gates for k_sweep's float-first path: min/max_distance rounded down and up,
     // vis_radius + ray_start, ray_start, ray_step and its inverse, ray_step in 16.16 fine-voxel units
     float min_lo, min_hi, max_lo, max_hi, vis_start_f, startf, stepf, inv_stepf, step_fine;
+    float inv_g16;       // 65536 / g: metres -> 16.16 fixed-point fine-voxel units
     // float32 cell positions relative to cell_ref (the centre of the cells' bounding box), one float4 per
     // cell, and the radius of that box: k_sweep's float-first path reads these instead of the doubles
     const float4* __restrict__ cells_f;
@@ -274,7 +275,7 @@ struct PoseAux {
     int fast;        // 0: always take the exact path for this pose
     float eabs;      // bound on |d_float - d| for this pose's rays (metres), see k_sweep
     float sr[3];     // sensor position relative to SweepDev::cell_ref
-    float sof[3];    // sensor position relative to the terrain grid origin, in fine voxels
+    float sof[3];    // sensor position relative to the terrain grid origin, in 2^-16 fine voxels
     float sf[3];     // sensor position
     int pad;
 };
@@ -296,7 +297,7 @@ k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin,
         a.sf[k] = (float)sd[k];
         a.sr[k] = (float)(sd[k] - P.cell_ref[k]);
         // exact subtraction, then narrowed
-        a.sof[k] = (float)(sd[k] - (double)go[k]) * G.inv_g;
+        a.sof[k] = (float)(sd[k] - (double)go[k]) * G.inv_g * 65536.0f;      // 16.16 fixed-point units
         rn += fabsf(a.sr[k]);
     }
     // d_float = fl(fl(c - ref) - fl(s - ref)): each narrowing is within 2^-24 of its operand, so the
@@ -645,16 +646,17 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     t_out = -3.0e38f;                     // parallel to the slab and outside it: misses the box
                 }
             }
-            float klo_f = ceilf((t_in - G.clip_t - P.startf) * P.inv_stepf);
-            float khi_f = floorf((t_out + G.clip_t - P.startf) * P.inv_stepf) + 1.0f;
-            k = (int)fminf(fmaxf(klo_f, 0.f), (float)n);
-            k_hi = (int)fminf(fmaxf(khi_f, 0.f), (float)n);
+            // float -> int conversions saturate (and give 0 for NaN), so the clamps can be done on integers
+            k = min(max(__float2int_ru((t_in - G.clip_t - P.startf) * P.inv_stepf), 0), n);
+            k_hi = min(max(__float2int_rd((t_out + G.clip_t - P.startf) * P.inv_stepf), -1), n - 1) + 1;
             if (k < k_hi) {
-                // fixed-point fine-voxel coordinate of sample k and its per-step increment
+                // fixed-point fine-voxel coordinate of sample k and its per-step increment; the 2^16 scale is
+                // folded into the (power-of-two) voxel pitch and the pose offset, which changes no rounding
                 const float t0 = fmaf((float)k, P.stepf, P.startf);
-                fx = __float2int_rd(fmaf(uf[0] * G.inv_g, t0, sof[0]) * 65536.f);
-                fy = __float2int_rd(fmaf(uf[1] * G.inv_g, t0, sof[1]) * 65536.f);
-                fz = __float2int_rd(fmaf(uf[2] * G.inv_g, t0, sof[2]) * 65536.f);
+                const float ug[3] = {uf[0] * P.inv_g16, uf[1] * P.inv_g16, uf[2] * P.inv_g16};
+                fx = __float2int_rd(fmaf(ug[0], t0, sof[0]));
+                fy = __float2int_rd(fmaf(ug[1], t0, sof[1]));
+                fz = __float2int_rd(fmaf(ug[2], t0, sof[2]));
                 dfx = __float2int_rn(uf[0] * P.step_fine);
                 dfy = __float2int_rn(uf[1] * P.step_fine);
                 dfz = __float2int_rn(uf[2] * P.step_fine);
@@ -1097,6 +1099,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     P.stepf = (float)p.ray_step;
     P.inv_stepf = (float)(1.0 / p.ray_step);
     P.step_fine = (float)(p.ray_step * (double)P.terrain.inv_g * 65536.0);
+    P.inv_g16 = P.terrain.inv_g * 65536.0f;
     P.cells_f = ctx->cells_f.as<float4>();
     P.tile_boxes = ctx->tile_boxes.ptr;
     for (int a = 0; a < 3; ++a) P.cell_ref[a] = ctx->cell_ref[a];
