@@ -301,3 +301,29 @@ def test_gates_cut_through_tiles(ctx, scene_cache, fov_v, maxd, mind):
     ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, prm, s.fixed, cands)
     assert 0 < ref["counters"]["rays_gated_in"] < cands.size * s.cells.size
     compare(got, ref, s.cells.size)
+
+
+def test_random_scenes_against_oracle(ctx):
+    # a slice of tools/fuzz_sweep.py: random clouds, cells (non-finite entries, partial tiles), poses and parameters
+    import importlib.util
+    import pathlib
+    spec = importlib.util.spec_from_file_location("fuzz_sweep", pathlib.Path(__file__).resolve().parent.parent / "tools" / "fuzz_sweep.py")
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    gated = 0
+    for it in range(60):
+        terrain, observed, cells, poses, fixed, prm = fz.scene(np.random.default_rng(7 * 100003 + it))
+        ctx.set_terrain(terrain)
+        ctx.set_observed(observed if observed is not None else np.zeros((0, 3), np.float32))
+        ctx.set_cells(cells)
+        got = ctx.sweep(prm, fixed, poses, mask=True, flags=True, fixed_scores=True)
+        ref = O.sweep(O.Index(terrain, O.GRID), O.Index(observed, O.GRID) if observed is not None else None, cells, prm,
+                      fixed, poses)
+        assert np.array_equal(got.mask, ref["mask"]), it
+        assert np.array_equal(got.covered, ref["covered"]), it
+        assert np.array_equal(got.cell_flags, ref["flags"]), it
+        np.testing.assert_allclose(got.scores, ref["scores"], rtol=SCORE_RTOL, atol=1e-12)
+        for k in ("rays_gated_in", "rays_visible", "samples", "fixed_samples"):
+            assert got.counters[k] == ref["counters"][k], (it, k)
+        gated += ref["counters"]["rays_gated_in"]
+    assert gated > 100_000
