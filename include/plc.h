@@ -166,6 +166,17 @@ plc_status plc_vl_sweep(plc_ctx* ctx, const plc_params* prm, const plc_pose* fix
 plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
                                     const plc_pose* cands, uint64_t n_cands,
                                     uint64_t cand_begin, uint64_t cand_end);
+/* The same with a strided share of the list: this context evaluates candidates first, first + stride,
+ * first + 2 stride, ... (< n_cands).  Dealing the list out round-robin (first = rank, stride = ranks) balances
+ * the devices better than contiguous blocks, because neighbouring poses cost about the same.  The optional
+ * arrays of plc_sweep_out are indexed by LOCAL candidate i (global index first + i * stride); best_index is
+ * global as always. */
+plc_status plc_vl_upload_candidates_strided(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
+                                            const plc_pose* cands, uint64_t n_cands,
+                                            uint64_t first, uint64_t stride);
+plc_status plc_vl_sweep_strided(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
+                                const plc_pose* cands, uint64_t n_cands,
+                                uint64_t first, uint64_t stride, plc_sweep_out* out);
 plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_flags);
 plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out);
 /* Device address of this context's {double best_score; int64 best_global_index} pair (16 bytes),
@@ -182,7 +193,7 @@ plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms);
 
 /* The reference node is one process (virtual_lidar.cpp:965-969).  A group owns one context per listed CUDA
  * device and runs the sweep over all of them: terrain, observed cloud and cells replicated, candidate poses
- * sharded in contiguous blocks [floor(g C / G), floor((g+1) C / G)), one NCCL all-gather of 16 bytes per device
+ * dealt out round-robin (device g of G evaluates g, g + G, ...), one NCCL all-gather of 16 bytes per device
  * ({f64 best_score, i64 best_global_index}), first maximum = lowest global index.  NCCL is
  * loaded at run time (libnccl.so.2) and only for groups of more than one device; failure is PLC_E_NCCL.
  * Same threading contract as a context: calls on one group must not overlap. */

@@ -115,7 +115,8 @@ EXPORTS = [
     "plc_last_error", "plc_launch_count", "plc_abi_version", "plc_ctx_sync",
     "plc_vl_set_terrain", "plc_vl_set_observed", "plc_vl_set_cells", "plc_vl_sweep",
     "plc_vl_upload_candidates", "plc_vl_run_async", "plc_vl_fetch", "plc_vl_result_device_ptr",
-    "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times", "plc_filter", "plc_merge",
+    "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times",
+    "plc_vl_upload_candidates_strided", "plc_vl_sweep_strided", "plc_filter", "plc_merge",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
     "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
     "plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback", "plc_vlnode_zx120_points_callback",
@@ -173,6 +174,8 @@ def lib() -> C.CDLL:
     L.plc_vl_result_device_ptr.argtypes = [vp, C.POINTER(vp)]
     L.plc_vl_last_sweep_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
     L.plc_last_device_times.argtypes = [vp, C.POINTER(DeviceTimes)]
+    L.plc_vl_upload_candidates_strided.argtypes = [vp, C.POINTER(Params), vp, vp, u64, u64, u64]
+    L.plc_vl_sweep_strided.argtypes = [vp, C.POINTER(Params), vp, vp, u64, u64, u64, C.POINTER(SweepOut)]
     L.plc_vl_grid_info.argtypes = [vp, C.POINTER(GridInfo), C.POINTER(GridInfo)]
     L.plc_filter.argtypes = [vp, C.POINTER(CloudView), C.POINTER(CropBox), dbl, vp, u64,
                              C.POINTER(u64), C.POINTER(u64)]

@@ -135,6 +135,26 @@ class Context:
                                               A.ptr(cands) if cands.size else None, cands.size, begin, end)
         self._check(st, "plc_vl_upload_candidates")
 
+    def upload_candidates_strided(self, params: A.Params, fixed: np.ndarray, cands: np.ndarray, first: int, stride: int):
+        """This context evaluates candidates first, first + stride, ... (round-robin share of the list)."""
+        cands = np.ascontiguousarray(cands, dtype=A.POSE_DTYPE)
+        fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
+        self._n_local = len(range(first, cands.size, stride))
+        st = self._L.plc_vl_upload_candidates_strided(self._h, C.byref(params), A.ptr(fixed),
+                                                      A.ptr(cands) if cands.size else None, cands.size, first, stride)
+        self._check(st, "plc_vl_upload_candidates_strided")
+
+    def sweep_strided(self, params: A.Params, fixed: np.ndarray, cands: np.ndarray, first: int, stride: int, *,
+                      scores=True, mask=False, flags=False, fixed_scores=False) -> SweepResult:
+        """plc_vl_sweep_strided: arrays are indexed by local candidate i (global index first + i * stride)."""
+        cands = np.ascontiguousarray(cands, dtype=A.POSE_DTYPE)
+        fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
+        out, arrays = self._alloc_out(len(range(first, cands.size, stride)), scores, mask, flags, fixed_scores)
+        st = self._L.plc_vl_sweep_strided(self._h, C.byref(params), A.ptr(fixed), A.ptr(cands) if cands.size else None,
+                                          cands.size, first, stride, C.byref(out))
+        self._check(st, "plc_vl_sweep_strided")
+        return self._result(out, arrays)
+
     def run_async(self, want_mask: bool = False, want_flags: bool = False):
         self._check(self._L.plc_vl_run_async(self._h, int(want_mask), int(want_flags)), "plc_vl_run_async")
 

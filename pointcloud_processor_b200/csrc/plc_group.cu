@@ -2,11 +2,12 @@
 //
 // The reference's virtual_lidar is a single rclcpp process (virtual_lidar.cpp:965-969), so a drop-in that
 // wants the whole box drives every device itself: one plc_ctx per GPU, the terrain index, cells and the
-// hoisted fixed-sensor pass replicated, candidate poses sharded in contiguous blocks
-// [floor(g C / G), floor((g+1) C / G)).  The only exchange is 16 bytes per device,
+// hoisted fixed-sensor pass replicated, candidate poses dealt out round-robin (device g of G evaluates candidates
+// g, g + G, g + 2G, ...: neighbouring poses cost about the same, contiguous blocks of the lattice do not).  The only exchange is 16 bytes per device,
 // {f64 best_score, i64 best_global_index}, all-gathered over NCCL (NVLink) straight from each context's
 // device result block; every device then holds all pairs and the first maximum is picked with the
-// reference's strict-> rule (lowest global index among equals, :464-475).
+// reference's strict-> rule (lowest global index among equals, :464-475; each pair carries its global index, so
+// the rule does not depend on how the list was dealt out).
 //
 // NCCL is bound at run time (dlopen of libnccl.so.2): a process that already loaded an NCCL — PyTorch's
 // bundled one in bench.py — gets that copy instead of a second one with clashing symbols.  A group of one
@@ -184,11 +185,9 @@ extern "C" plc_status plc_group_sweep(plc_group* g, const plc_params* prm, const
         g->last_error = "device " + std::to_string(g->dev[i]) + ": " + plc_last_error(g->ctx[i]);
         return st;
     };
-    std::vector<uint64_t> begin(n + 1);
-    for (int i = 0; i <= n; ++i) begin[i] = n_cands * (uint64_t)i / (uint64_t)n;
     // upload + launch on every device without waiting for any of them
     for (int i = 0; i < n; ++i) {
-        plc_status st = plc_vl_upload_candidates(g->ctx[i], prm, fixed, cands, n_cands, begin[i], begin[i + 1]);
+        plc_status st = plc_vl_upload_candidates_strided(g->ctx[i], prm, fixed, cands, n_cands, (uint64_t)i, (uint64_t)n);
         if (st != PLC_OK) return fail(i, st);
         // the stale-flag bytes depend on the whole candidate list, which every context holds: device 0 makes them
         st = plc_vl_run_async(g->ctx[i], out->mask != nullptr, i == 0 && out->cell_flags != nullptr);
@@ -211,20 +210,19 @@ extern "C" plc_status plc_group_sweep(plc_group* g, const plc_params* prm, const
         rc = g->nccl.GroupEnd();
         if (rc != 0) return nccl_fail(g, "ncclGroupEnd", rc);
     }
-    // results: arrays land at their shard's offset in the caller's buffers
+    // results: each shard's arrays are interleaved straight into the caller's global arrays
     plc_sweep_out total = *out;
     total.counters = plc_counters{};
     std::vector<Pair> pairs(n);
     for (int i = 0; i < n; ++i) {
         plc_sweep_out part{};
-        const uint64_t off = begin[i];
         const uint64_t words = (g->ctx[i]->n_cells + 31) / 32;
-        part.scores = out->scores ? out->scores + off : nullptr;
-        part.covered = out->covered ? out->covered + off : nullptr;
-        part.mask = out->mask ? out->mask + off * words : nullptr;
+        part.scores = out->scores ? out->scores + i : nullptr;
+        part.covered = out->covered ? out->covered + i : nullptr;
+        part.mask = out->mask ? out->mask + (uint64_t)i * words : nullptr;
         part.cell_flags = i == 0 ? out->cell_flags : nullptr;
         part.fixed_scores = i == 0 ? out->fixed_scores : nullptr;
-        plc_status st = plc_vl_fetch(g->ctx[i], &part);
+        plc_status st = plc::fetch_strided(g->ctx[i], &part, (uint64_t)n);
         if (st != PLC_OK) return fail(i, st);
         pairs[i] = Pair{part.best_score, (long long)part.best_index};
         total.counters.rays += part.counters.rays;
@@ -247,11 +245,13 @@ extern "C" plc_status plc_group_sweep(plc_group* g, const plc_params* prm, const
             return PLC_E_CUDA;
         }
     }
-    // first maximum in candidate order: shards are contiguous and ascending, so the lowest device wins ties
+    // first maximum in candidate order: strictly greater score, or an equal score at a lower global index
     int best = -1;
     for (int i = 0; i < n; ++i) {
         if (pairs[i].index < 0) continue;
-        if (best < 0 || pairs[i].score > pairs[best].score) best = i;
+        if (best < 0 || pairs[i].score > pairs[best].score ||
+            (pairs[i].score == pairs[best].score && pairs[i].index < pairs[best].index))
+            best = i;
     }
     total.best_index = best >= 0 ? pairs[best].index : -1;
     total.best_score = best >= 0 ? pairs[best].score : -INFINITY;

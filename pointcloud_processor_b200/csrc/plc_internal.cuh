@@ -170,7 +170,8 @@ struct plc_ctx {
     plc::DevBuf cell_flags;      // uint8[n_cells], persists across sweeps (Q3)
     plc::DevBuf fixed_scores;    // double[n_cells]
     plc::DevBuf cands;           // plc_pose[n_cands] (full list)
-    uint64_t n_cands = 0, cand_begin = 0, cand_end = 0;
+    uint64_t n_cands = 0;
+    uint64_t cand_begin = 0, cand_stride = 1, n_local = 0;   // this context evaluates cands[cand_begin + i*cand_stride], i < n_local
     plc_params prm{};
     plc_pose fixed{};
     bool have_job = false;
@@ -220,6 +221,7 @@ struct SweepResult {
 };
 
 plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* cloud);
+plc_status fetch_strided(plc_ctx* ctx, plc_sweep_out* out, uint64_t dst_stride);
 // Builds (or keeps) the index for `radius`.  thr: float32 squared-distance threshold of the exact test
 // (normally (float)(radius*radius)); march_err + march_err_m: position error of the caller's march, in
 // fine-voxel units, folded into the conservative slack.

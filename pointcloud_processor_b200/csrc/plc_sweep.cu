@@ -282,11 +282,11 @@ struct PoseAux {
 static_assert(sizeof(PoseAux) == 64, "PoseAux is read as four 16-byte words");
 
 __global__ void __launch_bounds__(128)
-k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned n_local,
+k_pose_prep(SweepDev P, const plc_pose* __restrict__ cands, unsigned cand_begin, unsigned cand_stride, unsigned n_local,
             PoseAux* __restrict__ aux) {
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_local) return;
-    const plc_pose s = cands[cand_begin + i];
+    const plc_pose s = cands[cand_begin + i * cand_stride];
     double pitch = s.pitch;
     PoseAux a{};
     const VoxelGeom& G = P.terrain;
@@ -426,7 +426,7 @@ constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not bloc
 #endif
 constexpr int kSweepWarps = 1;                  // one warp per block: no block-level synchronisation anywhere
 __global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM)
-k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin,
+k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin, unsigned cand_stride,
         unsigned tiles, unsigned n_work, const plc_cell* __restrict__ cells, unsigned n_cells,
         const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
         int* __restrict__ partial_cov, uint32_t* __restrict__ mask, unsigned mask_words,
@@ -458,7 +458,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
 
     const unsigned FULL = 0xffffffffu;
     unsigned local = wid / tiles, tile = wid - local * tiles;
-    const plc_pose s = cands[cand_begin + local];
+    const plc_pose s = cands[cand_begin + local * cand_stride];
     const PoseAux A = aux[local];
     const VoxelGeom& G = P.terrain;
     const int lane = threadIdx.x & 31;
@@ -801,7 +801,8 @@ k_finalize(const double* __restrict__ partial_score, const int* __restrict__ par
 // single block: first maximum over the local candidates (:464-475), fixed-sensor total
 __global__ void __launch_bounds__(1024)
 k_argmax(const double* __restrict__ scores, const int* __restrict__ covered, unsigned n_local,
-         unsigned long long cand_begin, const double* __restrict__ fixed_block_totals, unsigned n_fixed_blocks,
+         unsigned long long cand_begin, unsigned long long cand_stride, const double* __restrict__ fixed_block_totals,
+         unsigned n_fixed_blocks,
          SweepResult* __restrict__ res) {
     double best = -INFINITY;
     long long idx = -1;
@@ -842,7 +843,7 @@ k_argmax(const double* __restrict__ scores, const int* __restrict__ covered, uns
                 idx = si[w];
             }
         res->best_score = best;
-        res->best_index = idx >= 0 ? (long long)cand_begin + idx : -1;
+        res->best_index = idx >= 0 ? (long long)(cand_begin + (unsigned long long)idx * cand_stride) : -1;
         res->best_covered = idx >= 0 ? covered[idx] : 0;
         double ft = 0.0;
         for (unsigned b = 0; b < n_fixed_blocks; ++b) ft = __dadd_rn(ft, fixed_block_totals[b]);
@@ -1046,11 +1047,9 @@ extern "C" plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint
     return PLC_OK;
 }
 
-extern "C" plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
-                                               const plc_pose* cands, uint64_t n_cands, uint64_t cand_begin,
-                                               uint64_t cand_end) {
-    if (!ctx || !params_ok(prm) || !fixed || (n_cands && !cands)) return PLC_E_INVALID_ARG;
-    if (cand_begin > cand_end || cand_end > n_cands || n_cands > 0x7fffff00ull) return PLC_E_INVALID_ARG;
+namespace {
+plc_status upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed, const plc_pose* cands,
+                             uint64_t n_cands, uint64_t first, uint64_t stride, uint64_t n_local) {
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     ctx->have_job = false;
     ctx->ran = false;
@@ -1063,10 +1062,29 @@ extern "C" plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* p
     ctx->prm = *prm;
     ctx->fixed = *fixed;
     ctx->n_cands = n_cands;
-    ctx->cand_begin = cand_begin;
-    ctx->cand_end = cand_end;
+    ctx->cand_begin = first;
+    ctx->cand_stride = stride;
+    ctx->n_local = n_local;
     ctx->have_job = true;
     return PLC_OK;
+}
+}  // namespace
+
+extern "C" plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
+                                               const plc_pose* cands, uint64_t n_cands, uint64_t cand_begin,
+                                               uint64_t cand_end) {
+    if (!ctx || !params_ok(prm) || !fixed || (n_cands && !cands)) return PLC_E_INVALID_ARG;
+    if (cand_begin > cand_end || cand_end > n_cands || n_cands > 0x7fffff00ull) return PLC_E_INVALID_ARG;
+    return upload_candidates(ctx, prm, fixed, cands, n_cands, cand_begin, 1, cand_end - cand_begin);
+}
+
+extern "C" plc_status plc_vl_upload_candidates_strided(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
+                                                       const plc_pose* cands, uint64_t n_cands, uint64_t first,
+                                                       uint64_t stride) {
+    if (!ctx || !params_ok(prm) || !fixed || (n_cands && !cands)) return PLC_E_INVALID_ARG;
+    if (stride == 0 || stride > 0xffff || n_cands > 0x7fffff00ull) return PLC_E_INVALID_ARG;
+    const uint64_t n_local = first < n_cands ? (n_cands - first + stride - 1) / stride : 0;
+    return upload_candidates(ctx, prm, fixed, cands, n_cands, first, stride, n_local);
 }
 
 extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_flags) {
@@ -1123,7 +1141,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     P.fixed_mode = p.fixed_mode;
 
     const unsigned M = (unsigned)ctx->n_cells;
-    const unsigned n_local = (unsigned)(ctx->cand_end - ctx->cand_begin);
+    const unsigned n_local = (unsigned)ctx->n_local;
     const unsigned tiles = (M + kTileCells - 1) / kTileCells;
     const unsigned fixed_blocks = (M + kSweepThreads - 1) / kSweepThreads;
     ctx->tiles = (int)tiles;
@@ -1149,7 +1167,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     ctx->sweep_timed = false;
     if (n_local) {
         k_pose_prep<<<(n_local + 127) / 128, 128, 0, s>>>(P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin,
-                                                          n_local, ctx->pose_aux.as<PoseAux>());
+                                                          (unsigned)ctx->cand_stride, n_local, ctx->pose_aux.as<PoseAux>());
         // measured on cfg2/cfg3: a 50 % carve-out (L1 kept large) beats full occupancy of the 5.25 KB blocks
         static bool carveout_set = false;
         if (!carveout_set) {
@@ -1159,7 +1177,8 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
         }
         cudaEventRecord(ctx->ev_sweep_begin, s);
         k_sweep<<<(n_local * tiles + kSweepWarps - 1) / kSweepWarps, 32 * kSweepWarps, 0, s>>>(
-            P, ctx->cands.as<plc_pose>(), ctx->pose_aux.as<PoseAux>(), (unsigned)ctx->cand_begin, tiles, n_local * tiles,
+            P, ctx->cands.as<plc_pose>(), ctx->pose_aux.as<PoseAux>(), (unsigned)ctx->cand_begin, (unsigned)ctx->cand_stride,
+            tiles, n_local * tiles,
             ctx->cells.as<plc_cell>(), M,
             ctx->fixed_scores.as<double>(), ctx->partial_score.as<double>(), ctx->partial_cov.as<int>(),
             want_mask ? ctx->mask.as<uint32_t>() : nullptr, (unsigned)ctx->mask_words, res);
@@ -1170,7 +1189,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
         ctx->launches += 3;
     }
     k_argmax<<<1, 1024, 0, s>>>(ctx->scores.as<double>(), ctx->covered.as<int>(), n_local, ctx->cand_begin,
-                                fixed_totals, fixed_blocks, res);
+                                ctx->cand_stride, fixed_totals, fixed_blocks, res);
     ctx->launches += 1;
     if (want_flags) {
         k_flags<<<fixed_blocks, kSweepThreads, 0, s>>>(P, ctx->cands.as<plc_pose>(), (unsigned)ctx->n_cands,
@@ -1184,22 +1203,26 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     return PLC_OK;
 }
 
-extern "C" plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out) {
-    if (!ctx || !out) return PLC_E_INVALID_ARG;
+namespace plc {
+// plc_vl_fetch with the per-candidate arrays written every `dst_stride` elements (rows for the mask): what a
+// multi-device group uses to interleave strided shards straight into the caller's global arrays.
+plc_status fetch_strided(plc_ctx* ctx, plc_sweep_out* out, uint64_t dst_stride) {
+    if (!ctx || !out || dst_stride == 0) return PLC_E_INVALID_ARG;
     if (!ctx->ran) return PLC_E_NO_CANDIDATES;
     if (out->mask && !ctx->ran_mask) return PLC_E_INVALID_ARG;
     if (out->cell_flags && !ctx->ran_flags) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
-    const uint64_t n_local = ctx->cand_end - ctx->cand_begin, M = ctx->n_cells;
+    const uint64_t n_local = ctx->n_local, M = ctx->n_cells;
     SweepResult* host = static_cast<SweepResult*>(ctx->pinned);
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(host, ctx->result.ptr, sizeof(SweepResult), cudaMemcpyDeviceToHost, s));
-    if (out->scores && n_local)
-        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->scores, ctx->scores.ptr, n_local * sizeof(double), cudaMemcpyDeviceToHost, s));
-    if (out->covered && n_local)
-        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->covered, ctx->covered.ptr, n_local * sizeof(int), cudaMemcpyDeviceToHost, s));
-    if (out->mask && n_local)
-        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->mask, ctx->mask.ptr, n_local * ctx->mask_words * 4, cudaMemcpyDeviceToHost, s));
+    auto copy_rows = [&](void* dst, const void* src, size_t row_bytes) -> cudaError_t {
+        if (dst_stride == 1) return cudaMemcpyAsync(dst, src, n_local * row_bytes, cudaMemcpyDeviceToHost, s);
+        return cudaMemcpy2DAsync(dst, dst_stride * row_bytes, src, row_bytes, row_bytes, n_local, cudaMemcpyDeviceToHost, s);
+    };
+    if (out->scores && n_local) PLC_CUDA_TRY(ctx, copy_rows(out->scores, ctx->scores.ptr, sizeof(double)));
+    if (out->covered && n_local) PLC_CUDA_TRY(ctx, copy_rows(out->covered, ctx->covered.ptr, sizeof(int)));
+    if (out->mask && n_local) PLC_CUDA_TRY(ctx, copy_rows(out->mask, ctx->mask.ptr, ctx->mask_words * 4));
     if (out->cell_flags)
         PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out->cell_flags, ctx->cell_flags.ptr, M, cudaMemcpyDeviceToHost, s));
     if (out->fixed_scores)
@@ -1219,11 +1242,22 @@ extern "C" plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out) {
     out->counters.exact_tests = host->exact_tests;
     return PLC_OK;
 }
+}  // namespace plc
+
+extern "C" plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out) { return plc::fetch_strided(ctx, out, 1); }
 
 extern "C" plc_status plc_vl_sweep(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed, const plc_pose* cands,
                                    uint64_t n_cands, uint64_t cand_begin, uint64_t cand_end, plc_sweep_out* out) {
     if (!out) return PLC_E_INVALID_ARG;
     PLC_TRY(plc_vl_upload_candidates(ctx, prm, fixed, cands, n_cands, cand_begin, cand_end));
+    PLC_TRY(plc_vl_run_async(ctx, out->mask != nullptr, out->cell_flags != nullptr));
+    return plc_vl_fetch(ctx, out);
+}
+
+extern "C" plc_status plc_vl_sweep_strided(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed, const plc_pose* cands,
+                                           uint64_t n_cands, uint64_t first, uint64_t stride, plc_sweep_out* out) {
+    if (!out) return PLC_E_INVALID_ARG;
+    PLC_TRY(plc_vl_upload_candidates_strided(ctx, prm, fixed, cands, n_cands, first, stride));
     PLC_TRY(plc_vl_run_async(ctx, out->mask != nullptr, out->cell_flags != nullptr));
     return plc_vl_fetch(ctx, out);
 }

@@ -1,5 +1,5 @@
-"""Multi-GPU step of the sweep: candidates are sharded in contiguous blocks, the
-terrain grid and cells are replicated, and the only exchange is one all-gather of 16 bytes per rank
+"""Multi-GPU step of the sweep: candidates are sharded (contiguous blocks, or round-robin
+with plc_vl_upload_candidates_strided, which balances the ranks better), the terrain grid and cells are replicated, and the only exchange is one all-gather of 16 bytes per rank
 — {float64 best_score, int64 best_global_index} — followed by the same deterministic argmax on
 every rank (highest score, lowest global index on ties: the reference's first-maximum rule,
 virtual_lidar.cpp:464-475).  `torch.distributed` is the plumbing (NCCL over NVLink on the GPU box,

@@ -278,6 +278,16 @@ def test_full_size_properties_config2(ctx, scene_cache):
     parts = [ctx.sweep(s.params, s.fixed, s.candidates, r * C // 3, (r + 1) * C // 3) for r in range(3)]
     assert np.array_equal(np.concatenate([p.scores for p in parts]), full.scores)
     assert sum(p.counters["samples"] for p in parts) == full.counters["samples"]
+    # round-robin shares (what bench.py and plc_group use): interleaved back, bit for bit the unsharded result
+    shares = [ctx.sweep_strided(s.params, s.fixed, s.candidates, r, 3, mask=True) for r in range(3)]
+    inter = np.empty(C)
+    imask = np.empty_like(full.mask)
+    for r, p in enumerate(shares):
+        inter[r::3] = p.scores
+        imask[r::3] = p.mask
+        assert p.best_index % 3 == r and p.best_score == full.scores[p.best_index] == full.scores[r::3].max()
+    assert np.array_equal(inter, full.scores) and np.array_equal(imask, full.mask)
+    assert sum(p.counters["samples"] for p in shares) == full.counters["samples"]
     perm = np.random.default_rng(1).permutation(s.terrain.shape[0])
     ctx.set_terrain(s.terrain[perm])
     again = ctx.sweep(s.params, s.fixed, s.candidates, mask=True)
