@@ -10,7 +10,7 @@ def line_of(pat, after=0):
 k0 = line_of("k_sweep(SweepDev P")
 marks = [("prologue", k0), ("drain (exact recompute)", line_of("auto drain")), ("load + range/n", line_of("for (int r = 0; r < kRaysPerThread", k0)),
          ("FOV", line_of("---- FOV", k0)), ("clip + init", line_of("checkVisibilityWithRaycasting (:754-800): clear", k0)),
-         ("march loop", line_of("bool active = k < k_hi;", k0)),
+         ("march loop", line_of("const unsigned tag_base", k0)),
          ("finalise + score", line_of("while (q_n > 0) drain", k0)), ("end", line_of("// per candidate: tiles summed"))]
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass,cuda"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
