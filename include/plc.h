@@ -188,6 +188,36 @@ plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr);
  * Synchronises the stream.  0 if no candidates were evaluated. */
 plc_status plc_vl_last_sweep_kernel_ms(plc_ctx* ctx, float* ms);
 
+/* ---------------------------------------------------------------- virtual_lidar setup -- */
+
+/* grid_min_x_ ... excavation_max_z_, grid_width_, grid_height_ (virtual_lidar.cpp:144-146) */
+typedef struct plc_grid_bounds {
+    double min_x, max_x, min_y, max_y, min_z, max_z;
+    int32_t width, height;
+} plc_grid_bounds;
+
+/* Replaces computeTerrainNormals (virtual_lidar.cpp:209-234; pcl::NormalEstimation, radius search 1.5 m):
+ * one PCA normal per /excavation_area point, flipped to n_z >= 0; NaN where a point has fewer than three
+ * neighbours or is not finite.  normals_out: 3 floats per input point, in input order. */
+plc_status plc_vl_compute_normals(plc_ctx* ctx, const plc_cloud_view* area, double radius, float* normals_out);
+
+/* Replaces generateExcavationGrid3D + isPointNearExcavation + computeCellSurfaceNormal
+ * (virtual_lidar.cpp:236-340): the lattice over the area cloud's bounds (margin = resolution), the lattice
+ * points within 1.5 resolution of an area point kept in lattice order (y index, x index, layer), each with the
+ * normalised sum of the normals of the area points within normal_search_radius.
+ * normals: one float triple per area point (NaN allowed), or NULL => every cell keeps (0,0,1).
+ * *n_out receives the number of kept cells even when it exceeds capacity (then PLC_E_CAPACITY). */
+plc_status plc_vl_generate_cells(plc_ctx* ctx, const plc_cloud_view* area, const float* normals,
+                                 double grid_resolution, int32_t vertical_layers, double normal_search_radius,
+                                 plc_cell* out, uint64_t capacity, uint64_t* n_out, plc_grid_bounds* bounds);
+
+/* Replaces generateCandidatePositions + getGroundHeight (virtual_lidar.cpp:550-625): the pose lattice around
+ * the grid bounds, each kept pose standing sensor_height above the highest terrain point within 1 m.
+ * terrain == NULL: the cloud last given to plc_vl_set_terrain, which is already on the device. */
+plc_status plc_vl_generate_candidates(plc_ctx* ctx, const plc_cloud_view* terrain, const plc_grid_bounds* bounds,
+                                      const plc_pose* fixed, int32_t num_candidates, double search_radius,
+                                      double sensor_height, plc_pose* out, uint64_t capacity, uint64_t* n_out);
+
 /* Grid facts for roofline accounting: bytes of the occupancy structure the sweep reads. */
 /* ---------------------------------------------------------------- several GPUs, one process -- */
 
@@ -221,7 +251,9 @@ typedef struct plc_device_times {
     float filter_ms;        /* plc_filter: crop (K6) + voxel downsample (K7) */
     float merge_ms;         /* plc_merge: transform + colour + concatenate (K8) */
     float sweep_kernel_ms;  /* k_sweep of the last plc_vl_sweep / plc_vl_run_async */
-    float reserved[3];
+    float normals_ms;       /* plc_vl_compute_normals */
+    float cells_ms;         /* plc_vl_generate_cells */
+    float candidates_ms;    /* plc_vl_generate_candidates */
 } plc_device_times;
 plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out);
 

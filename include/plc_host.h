@@ -6,6 +6,9 @@
  *   plc_host_compute_normals      computeTerrainNormals (virtual_lidar.cpp:209-234)
  *   plc_host_generate_candidates  generateCandidatePositions + getGroundHeight (virtual_lidar.cpp:550-625)
  * Same conventions as plc.h (status codes, caller-owned buffers, capacity checks).
+ * The node runs the device versions of the same three steps (plc_vl_generate_cells, plc_vl_compute_normals,
+ * plc_vl_generate_candidates in plc.h); these host versions remain for callers without a context (scene
+ * generation in tests and tools) and as a second implementation the device versions are checked against.
  */
 #ifndef PLC_HOST_H_
 #define PLC_HOST_H_
@@ -16,11 +19,7 @@
 extern "C" {
 #endif
 
-/* grid_min_x_ ... excavation_max_z_, grid_width_, grid_height_ (virtual_lidar.cpp:144-146) */
-typedef struct plc_grid_bounds {
-    double min_x, max_x, min_y, max_y, min_z, max_z;
-    int32_t width, height;
-} plc_grid_bounds;
+/* plc_grid_bounds is declared in plc.h (the device versions plc_vl_generate_* share it). */
 
 /* normals: one float triple per area point (NaN allowed) or NULL => every cell keeps (0,0,1).
  * *n_out receives the number of valid cells even when it exceeds capacity (then PLC_E_CAPACITY). */

@@ -57,7 +57,8 @@ class SweepOut(C.Structure):
 
 class DeviceTimes(C.Structure):
     _fields_ = [("set_terrain_ms", C.c_float), ("set_observed_ms", C.c_float), ("filter_ms", C.c_float),
-                ("merge_ms", C.c_float), ("sweep_kernel_ms", C.c_float), ("reserved", C.c_float * 3)]
+                ("merge_ms", C.c_float), ("sweep_kernel_ms", C.c_float), ("normals_ms", C.c_float),
+                ("cells_ms", C.c_float), ("candidates_ms", C.c_float)]
 
 
 class GridInfo(C.Structure):
@@ -117,6 +118,7 @@ EXPORTS = [
     "plc_vl_upload_candidates", "plc_vl_run_async", "plc_vl_fetch", "plc_vl_result_device_ptr",
     "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times",
     "plc_vl_upload_candidates_strided", "plc_vl_sweep_strided", "plc_filter", "plc_merge",
+    "plc_vl_compute_normals", "plc_vl_generate_cells", "plc_vl_generate_candidates",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
     "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
     "plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback", "plc_vlnode_zx120_points_callback",
@@ -184,6 +186,11 @@ def lib() -> C.CDLL:
     L.plc_host_generate_cells.argtypes = [C.POINTER(CloudView), vp, dbl, i32, dbl, vp, u64,
                                           C.POINTER(u64), C.POINTER(GridBounds)]
     L.plc_host_compute_normals.argtypes = [C.POINTER(CloudView), dbl, vp]
+    L.plc_vl_generate_cells.argtypes = [vp, C.POINTER(CloudView), vp, dbl, i32, dbl, vp, u64,
+                                        C.POINTER(u64), C.POINTER(GridBounds)]
+    L.plc_vl_compute_normals.argtypes = [vp, C.POINTER(CloudView), dbl, vp]
+    L.plc_vl_generate_candidates.argtypes = [vp, C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
+                                             dbl, dbl, vp, u64, C.POINTER(u64)]
     L.plc_host_generate_candidates.argtypes = [C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
                                                dbl, dbl, vp, u64, C.POINTER(u64)]
     L.plc_vlnode_create.argtypes = [vp, C.POINTER(vp)]

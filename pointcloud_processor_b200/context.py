@@ -227,6 +227,48 @@ class Context:
         return merged[: n_out.value], [e[: n_each[i]] for i, e in enumerate(each)]
 
 
+    # ---- node setup on the device: same results as the host_* functions below
+    def compute_normals(self, area: np.ndarray, radius: float = 1.5, point_step: int | None = None, off=(0, 4, 8)) -> np.ndarray:
+        v = A.cloud_view(area, point_step, off)
+        out = np.zeros((int(v.n_points), 3), np.float32)
+        self._check(self._L.plc_vl_compute_normals(self._h, C.byref(v), radius, out.ctypes.data), "plc_vl_compute_normals")
+        return out
+
+    def generate_cells(self, area: np.ndarray, normals: np.ndarray | None, grid_resolution: float,
+                       vertical_layers: int, normal_search_radius: float = 1.5, point_step: int | None = None,
+                       off=(0, 4, 8)):
+        v = A.cloud_view(area, point_step, off)
+        if normals is not None:
+            normals = np.ascontiguousarray(normals, np.float32)
+        b = A.GridBounds()
+        n = C.c_uint64(0)
+        st = self._L.plc_vl_generate_cells(self._h, C.byref(v), A.ptr(normals), grid_resolution, vertical_layers,
+                                           normal_search_radius, None, 0, C.byref(n), C.byref(b))
+        if st not in (A.PLC_OK, A.PLC_E_CAPACITY):
+            self._check(st, "plc_vl_generate_cells")
+        cells = np.zeros(n.value, A.CELL_DTYPE)
+        if n.value:
+            st = self._L.plc_vl_generate_cells(self._h, C.byref(v), A.ptr(normals), grid_resolution, vertical_layers,
+                                               normal_search_radius, cells.ctypes.data, cells.size, C.byref(n), C.byref(b))
+            self._check(st, "plc_vl_generate_cells")
+        return cells, b
+
+    def generate_candidates(self, terrain: np.ndarray | None, bounds: A.GridBounds, fixed: np.ndarray,
+                            num_candidates: int, search_radius: float, sensor_height: float,
+                            point_step: int | None = None, off=(0, 4, 8)) -> np.ndarray:
+        """terrain=None: the cloud last given to set_terrain (already on the device)."""
+        v = A.cloud_view(terrain, point_step, off) if terrain is not None else None
+        fixed = np.ascontiguousarray(fixed, dtype=A.POSE_DTYPE).reshape(1)
+        side = int(np.ceil(np.sqrt(max(num_candidates, 1))))
+        out = np.zeros(side * side, A.POSE_DTYPE)
+        n = C.c_uint64(0)
+        st = self._L.plc_vl_generate_candidates(self._h, C.byref(v) if v is not None else None, C.byref(bounds),
+                                                fixed.ctypes.data, num_candidates, search_radius, sensor_height,
+                                                out.ctypes.data, out.size, C.byref(n))
+        self._check(st, "plc_vl_generate_candidates")
+        return out[: n.value].copy()
+
+
 # ---- host-side setup (include/plc_host.h) -------------------------------------------------------
 def host_generate_cells(area: np.ndarray, normals: np.ndarray | None, grid_resolution: float,
                         vertical_layers: int, normal_search_radius: float = 1.5):

@@ -53,6 +53,7 @@ double percent(int part, int total) { return total > 0 ? static_cast<double>(par
 struct plc_vlnode {
     plc_ctx* ctx = nullptr;
     plc_group* group = nullptr;      // set instead of ctx when the node drives several GPUs
+    plc_ctx* setup_ctx() { return group ? plc_group_ctx(group, 0) : ctx; }
     plc_status set_terrain(const plc_cloud_view* c) { return group ? plc_group_set_terrain(group, c) : plc_vl_set_terrain(ctx, c); }
     plc_status set_observed(const plc_cloud_view* c) { return group ? plc_group_set_observed(group, c) : plc_vl_set_observed(ctx, c); }
     plc_status set_cells(const plc_cell* c, uint64_t m) { return group ? plc_group_set_cells(group, c, m) : plc_vl_set_cells(ctx, c, m); }
@@ -152,17 +153,18 @@ extern "C" plc_status plc_vlnode_excavation_area_callback(plc_vlnode* n, const p
     if (!n || !view_ok(cloud)) return PLC_E_INVALID_ARG;
     if (cloud->n_points == 0) return PLC_OK;
     std::vector<float> normals(static_cast<size_t>(cloud->n_points) * 3);
-    plc_status st = plc_host_compute_normals(cloud, kNormalSearchRadius, normals.data());          // :173
+    plc_ctx* dev = n->setup_ctx();            // both steps run on the device (plc_setup.cu)
+    plc_status st = plc_vl_compute_normals(dev, cloud, kNormalSearchRadius, normals.data());       // :173
     if (st != PLC_OK) return st;
     uint64_t count = 0;
     plc_grid_bounds b{};
-    st = plc_host_generate_cells(cloud, normals.data(), n->grid_resolution, n->vertical_layers,    // :174
-                                 kNormalSearchRadius, nullptr, 0, &count, &b);
+    st = plc_vl_generate_cells(dev, cloud, normals.data(), n->grid_resolution, n->vertical_layers, // :174
+                               kNormalSearchRadius, nullptr, 0, &count, &b);
     if (st != PLC_OK && st != PLC_E_CAPACITY) return st;
     std::vector<plc_cell> cells(count);
     if (count) {
-        st = plc_host_generate_cells(cloud, normals.data(), n->grid_resolution, n->vertical_layers,
-                                     kNormalSearchRadius, cells.data(), count, &count, &b);
+        st = plc_vl_generate_cells(dev, cloud, normals.data(), n->grid_resolution, n->vertical_layers,
+                                   kNormalSearchRadius, cells.data(), count, &count, &b);
         if (st != PLC_OK) return st;
     }
     n->cells.swap(cells);                     // excavation_grid_3d_.clear() + refill (:239, :278)
@@ -238,7 +240,7 @@ void log_colour_block(plc_vlnode* n, const plc_color_stats& s) {
 }  // namespace
 
 // runOptimization (:454-548).  The fixed-sensor pass, the candidate loop and the argmax are one
-// plc_vl_sweep; the candidate lattice is generated on the host from the stored terrain cloud.
+// plc_vl_sweep; the candidate lattice is generated on the device as well.
 extern "C" plc_status plc_vlnode_run_optimization(plc_vlnode* n, plc_vlnode_result* out) {
     if (!n || !out) return PLC_E_INVALID_ARG;
     memset(out, 0, sizeof(*out));
@@ -255,9 +257,12 @@ extern "C" plc_status plc_vlnode_run_optimization(plc_vlnode* n, plc_vlnode_resu
     const int side = static_cast<int>(std::ceil(std::sqrt(static_cast<double>(n->num_candidates))));
     std::vector<plc_pose> cands(static_cast<size_t>(side) * side);
     uint64_t n_cands = 0;
-    plc_status st = plc_host_generate_candidates(&n->terrain.view, &n->bounds, &fixed, n->num_candidates,
-                                                 n->search_radius, n->sensor_height, cands.data(), cands.size(),
-                                                 &n_cands);
+    // on the device, against the terrain plc_vl_set_terrain left there; an empty cloud that arrived after it
+    // replaced terrain_cloud_ but not the tree (:180-192), so getGroundHeight answers 0 everywhere (:601)
+    const plc_cloud_view* ground = n->terrain.view.n_points ? nullptr : &n->terrain.view;
+    plc_status st = plc_vl_generate_candidates(n->setup_ctx(), ground, &n->bounds, &fixed, n->num_candidates,
+                                               n->search_radius, n->sensor_height, cands.data(), cands.size(),
+                                               &n_cands);
     if (st != PLC_OK) return st;
     cands.resize(n_cands);
 

@@ -88,7 +88,8 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
     plc::DevBuf* bufs[] = {&c->upload, &c->scratch, &c->cells, &c->cells_f, &c->tile_boxes, &c->cell_flags, &c->fixed_scores, &c->cands,
                            &c->partial_score, &c->partial_cov, &c->scores, &c->covered, &c->mask, &c->result, &c->pose_aux, &c->s_tab,
                            &c->f_keys, &c->f_vals, &c->f_keys2, &c->f_vals2, &c->f_tmp, &c->f_out, &c->f_flags,
-                           &c->m_out};
+                           &c->m_out, &c->su_pts, &c->su_sorted, &c->su_keys, &c->su_start, &c->su_table, &c->su_tmp,
+                           &c->su_flags, &c->su_out, &c->su_normals, &c->su_state};
     for (plc::DevBuf* b : bufs) b->release();
     if (c->pinned) cudaFreeHost(c->pinned);
     c->timer.destroy();

@@ -194,6 +194,10 @@ struct plc_ctx {
     plc::DevBuf f_keys, f_vals, f_keys2, f_vals2, f_tmp, f_out, f_flags;
     plc::DevBuf m_out;
 
+    // node setup on the device (plc_setup.cu): loaded points, bucket order, keys/values of the sort, bucket
+    // starts, sort table, scan scratch, flags + slots, packed outputs, per-point normals, bounds block
+    plc::DevBuf su_pts, su_sorted, su_keys, su_start, su_table, su_tmp, su_flags, su_out, su_normals, su_state;
+
     void set_error(const char* what, const char* why) {
         last_error = std::string(what) + ": " + why;
     }

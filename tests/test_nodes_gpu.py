@@ -71,8 +71,10 @@ def test_virtual_lidar_node_cycle(ctx, shape, n_pts, num_candidates):
     tix = O.Index(terrain, O.GRID)
     ocands = O.generate_candidates(tix, ob, fixed, num_candidates, 3.0, 1.1)
     assert cands.size == ocands.size == res.n_candidates
-    for k in ("x", "y", "z", "pitch", "yaw"):
+    for k in ("x", "y", "z"):
         assert np.array_equal(cands[k], ocands[k]), k
+    for k in ("pitch", "yaw"):                       # device atan2 (2 ulp) against libm's
+        assert np.allclose(cands[k], ocands[k], rtol=0, atol=4e-15), k
 
     # sweep: the oracle on the node's own cells and candidates
     ref = O.sweep(tix, None, cells, A.default_params(), fixed, cands)
