@@ -430,6 +430,43 @@ def measure_feeders(ctx, scene, peak, reps: int = 5) -> dict:
     n = int(scene.terrain.shape[0])
     out["voxelise_terrain"] = row(k_ms, w_ms, n * (12 + 16), n, "points")
     out["voxelise_terrain"]["points_in"] = n
+    out["setup"] = measure_setup(ctx, scene, peak, best)
+    return out
+
+
+def measure_setup(ctx, scene, peak, best) -> dict:
+    """The steps that produce the sweep's inputs on this workload: PCA normals of the
+    /excavation_area cloud, the evaluation-cell lattice with cell normals, the pose lattice with ground heights.
+    kernel_ms = the library's CUDA-event time of the call's kernels, wall_ms = the C-ABI call with host buffers,
+    host_ms = the same step by the multi-threaded host implementation (plc_host_*) on this box's cores.
+    Algorithmic bytes: 16 B per point a query has to look at (the points inside its ball)."""
+    from pointcloud_processor_b200 import context as ctxmod
+    m = scene.meta
+    area = scene.area
+    res, px = float(m["res"]), int(m["px"])
+    layers = int(m.get("layers_used") or m.get("layers") or 10)
+
+    def host(fn, reps=2):
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        return float(min(ts))
+
+    out = {"config": f"{m['shape']} area cloud of {area.shape[0]} points, lattice res {res} x {layers} layers, "
+                     f"{px}x{px} pose lattice over {scene.terrain.shape[0]} terrain points"}
+    normals, k_ms, w_ms = best(lambda: ctx.compute_normals(area, 1.5), "normals_ms")
+    out["pca_normals"] = {"kernel_ms": k_ms, "wall_ms": w_ms, "points": int(area.shape[0]),
+                          "host_ms": host(lambda: ctxmod.host_compute_normals(area, 1.5))}
+    (cells, _), k_ms, w_ms = best(lambda: ctx.generate_cells(area, normals, res, layers, 1.5), "cells_ms")
+    out["cell_lattice"] = {"kernel_ms": k_ms, "wall_ms": w_ms, "cells": int(cells.size),
+                           "host_ms": host(lambda: ctxmod.host_generate_cells(area, normals, res, layers, 1.5))}
+    ctx.set_terrain(scene.terrain)
+    cands, k_ms, w_ms = best(lambda: ctx.generate_candidates(None, scene.bounds, scene.fixed, px * px, 3.0, 1.1), "candidates_ms")
+    out["pose_lattice"] = {"kernel_ms": k_ms, "wall_ms": w_ms, "poses": int(cands.size),
+                           "host_ms": host(lambda: ctxmod.host_generate_candidates(scene.terrain, scene.bounds, scene.fixed,
+                                                                                   px * px, 3.0, 1.1))}
     return out
 
 

@@ -254,6 +254,8 @@ typedef struct plc_device_times {
     float normals_ms;       /* plc_vl_compute_normals */
     float cells_ms;         /* plc_vl_generate_cells */
     float candidates_ms;    /* plc_vl_generate_candidates */
+    float drivable_ms;      /* plc_drivable_area */
+    float reserved[3];
 } plc_device_times;
 plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out);
 
@@ -298,6 +300,40 @@ typedef struct plc_merge_src {
 plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_src,
                      void* out_merged, uint64_t capacity, uint64_t* n_out,
                      void* const* out_each, uint64_t* n_each);
+
+/* ---------------------------------------------------------------- calc_drivable_area -- */
+
+/* Parameters of the node (calc_drivable_area.cpp:21-26). */
+typedef struct plc_drivable_params {
+    double grid_resolution;       /* 1.0   */
+    double map_width, map_height; /* 100.0 */
+    double max_gradient;          /* 0.3   */
+    double start_clear_radius;    /* 3.0   */
+    int32_t min_points_per_cell;  /* 10    */
+    int32_t reserved;
+} plc_drivable_params;
+void plc_drivable_params_default(plc_drivable_params* p);
+
+/* nav_msgs/OccupancyGrid info of the result (:167-176). */
+typedef struct plc_drivable_info {
+    int32_t width, height;        /* (int)(map_width / resolution), (int)(map_height / resolution)  (:36-37) */
+    double origin_x, origin_y;    /* robot position minus half the map (:137-138) */
+    double resolution;
+    uint64_t n_cells;             /* width * height */
+    int32_t published;            /* 0: empty scan, the reference returns without publishing (:108-112) */
+    int32_t reserved;
+} plc_drivable_info;
+
+/* Replaces robotCloudCallback's data path (calc_drivable_area.cpp:87-232): the scan is transformed into the map
+ * frame (t, q = map <- scan frame as tf2::doTransform applies it in float32; both NULL: the scan is in the map
+ * frame already), its z values are binned into the robot-centred grid, and each cell becomes 0 (free: within
+ * start_clear_radius of the start position, or gradient (max z - min z) / resolution <= max_gradient),
+ * 100 (gradient above the limit) or -1 (fewer than min_points_per_cell points).
+ * out_grid: row-major int8[height * width] (OccupancyGrid.data). */
+plc_status plc_drivable_area(plc_ctx* ctx, const plc_cloud_view* scan, const double* t, const double* q,
+                             double robot_x, double robot_y, double start_x, double start_y,
+                             const plc_drivable_params* prm, int8_t* out_grid, uint64_t capacity,
+                             plc_drivable_info* info);
 
 #ifdef __cplusplus
 }

@@ -69,6 +69,9 @@ def lib() -> C.CDLL:
     L.orc_voxel_grid.argtypes = [vp, u64, dbl, vp, vp, vp, vp]
     L.orc_transform.argtypes = [vp, u64, vp, vp, vp]
     L.orc_transform.restype = None
+    L.orc_drivable_area.restype = i64
+    L.orc_drivable_area.argtypes = [vp, u64, vp, vp, dbl, dbl, dbl, dbl, dbl, dbl, dbl, dbl, C.c_int, dbl, vp,
+                                    C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     _lib = L
     return L
 
@@ -195,3 +198,22 @@ def transform(xyz, t, q):
     out = np.zeros_like(xyz)
     L.orc_transform(xyz.ctypes.data, xyz.shape[0], t.ctypes.data, q.ctypes.data, out.ctypes.data)
     return out
+
+
+def drivable_area(xyz, t, q, robot_xy, start_xy, *, grid_resolution=1.0, map_width=100.0, map_height=100.0,
+                  max_gradient=0.3, min_points_per_cell=10, start_clear_radius=3.0):
+    """calc_drivable_area.cpp:87-232.  Returns the (height, width) int8 grid, or None for an empty scan."""
+    L = lib()
+    xyz = np.ascontiguousarray(xyz[:, :3], np.float32)
+    tp = None if t is None else np.ascontiguousarray(t, np.float64)
+    qp = None if q is None else np.ascontiguousarray(q, np.float64)
+    w, h = C.c_int32(0), C.c_int32(0)
+    gw, gh = int(map_width / grid_resolution), int(map_height / grid_resolution)
+    out = np.zeros(max(gw * gh, 1), np.int8)
+    n = L.orc_drivable_area(xyz.ctypes.data, xyz.shape[0], A.ptr(tp), A.ptr(qp), robot_xy[0], robot_xy[1],
+                            start_xy[0], start_xy[1], grid_resolution, map_width, map_height, max_gradient,
+                            min_points_per_cell, start_clear_radius, out.ctypes.data, C.byref(w), C.byref(h))
+    assert (w.value, h.value) == (gw, gh)
+    if n < 0:
+        return None
+    return out[: gw * gh].reshape(gh, gw).copy()

@@ -110,6 +110,13 @@ int64_t orc_voxel_grid(const float* xyz, uint64_t n, double leaf, float* out_xyz
 /* tf2::doTransform float affine (§A.3 item 14): t (3 doubles) and quaternion x,y,z,w narrowed to float. */
 void orc_transform(const float* xyz, uint64_t n, const double* t, const double* q, float* out_xyz);
 
+/* calc_drivable_area.cpp:36-37, 87-232: the occupancy grid (row-major int8, width x height).  t, q: map <- scan
+ * frame (NULL: none).  Returns width*height, or -1 for an empty scan (nothing is published, :108-112). */
+int64_t orc_drivable_area(const float* xyz, uint64_t n, const double* t, const double* q, double robot_x,
+                          double robot_y, double start_x, double start_y, double grid_resolution, double map_width,
+                          double map_height, double max_gradient, int min_points_per_cell, double start_clear_radius,
+                          int8_t* out, int32_t* width_out, int32_t* height_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,7 +58,8 @@ class SweepOut(C.Structure):
 class DeviceTimes(C.Structure):
     _fields_ = [("set_terrain_ms", C.c_float), ("set_observed_ms", C.c_float), ("filter_ms", C.c_float),
                 ("merge_ms", C.c_float), ("sweep_kernel_ms", C.c_float), ("normals_ms", C.c_float),
-                ("cells_ms", C.c_float), ("candidates_ms", C.c_float)]
+                ("cells_ms", C.c_float), ("candidates_ms", C.c_float), ("drivable_ms", C.c_float),
+                ("reserved", C.c_float * 3)]
 
 
 class GridInfo(C.Structure):
@@ -104,6 +105,17 @@ class MergerInput(C.Structure):     # plc_merger_input
                 ("t", C.c_double * 3), ("q", C.c_double * 4)]
 
 
+class DrivableParams(C.Structure):  # plc_drivable_params
+    _fields_ = [("grid_resolution", C.c_double), ("map_width", C.c_double), ("map_height", C.c_double),
+                ("max_gradient", C.c_double), ("start_clear_radius", C.c_double),
+                ("min_points_per_cell", C.c_int32), ("reserved", C.c_int32)]
+
+
+class DrivableInfo(C.Structure):    # plc_drivable_info
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("origin_x", C.c_double), ("origin_y", C.c_double),
+                ("resolution", C.c_double), ("n_cells", C.c_uint64), ("published", C.c_int32), ("reserved", C.c_int32)]
+
+
 # numpy mirrors of the PODs (same byte layout as plc_cell / plc_pose)
 CELL_DTYPE = np.dtype([("x", "<f8"), ("y", "<f8"), ("z", "<f8"), ("nx", "<f4"), ("ny", "<f4"),
                        ("nz", "<f4"), ("pad", "<u4")])
@@ -119,6 +131,7 @@ EXPORTS = [
     "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times",
     "plc_vl_upload_candidates_strided", "plc_vl_sweep_strided", "plc_filter", "plc_merge",
     "plc_vl_compute_normals", "plc_vl_generate_cells", "plc_vl_generate_candidates",
+    "plc_drivable_params_default", "plc_drivable_area",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
     "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
     "plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback", "plc_vlnode_zx120_points_callback",
@@ -189,6 +202,10 @@ def lib() -> C.CDLL:
     L.plc_vl_generate_cells.argtypes = [vp, C.POINTER(CloudView), vp, dbl, i32, dbl, vp, u64,
                                         C.POINTER(u64), C.POINTER(GridBounds)]
     L.plc_vl_compute_normals.argtypes = [vp, C.POINTER(CloudView), dbl, vp]
+    L.plc_drivable_params_default.argtypes = [C.POINTER(DrivableParams)]
+    L.plc_drivable_params_default.restype = None
+    L.plc_drivable_area.argtypes = [vp, C.POINTER(CloudView), vp, vp, dbl, dbl, dbl, dbl, C.POINTER(DrivableParams),
+                                    vp, u64, C.POINTER(DrivableInfo)]
     L.plc_vl_generate_candidates.argtypes = [vp, C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
                                              dbl, dbl, vp, u64, C.POINTER(u64)]
     L.plc_host_generate_candidates.argtypes = [C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,

@@ -227,6 +227,26 @@ class Context:
         return merged[: n_out.value], [e[: n_each[i]] for i, e in enumerate(each)]
 
 
+    def drivable_area(self, scan: np.ndarray, t, q, robot_xy, start_xy, params: A.DrivableParams | None = None,
+                      point_step: int | None = None, off=(0, 4, 8)):
+        """calc_drivable_area's occupancy grid (plc_drivable_area).  Returns ((height, width) int8 grid or None for an
+        empty scan, info)."""
+        v = A.cloud_view(scan, point_step, off)
+        if params is None:
+            params = A.DrivableParams()
+            self._L.plc_drivable_params_default(C.byref(params))
+        tp = None if t is None else np.ascontiguousarray(t, np.float64)
+        qp = None if q is None else np.ascontiguousarray(q, np.float64)
+        info = A.DrivableInfo()
+        w, h = int(params.map_width / params.grid_resolution), int(params.map_height / params.grid_resolution)
+        grid = np.zeros(max(w * h, 1), np.int8)
+        st = self._L.plc_drivable_area(self._h, C.byref(v), A.ptr(tp), A.ptr(qp), robot_xy[0], robot_xy[1], start_xy[0],
+                                       start_xy[1], C.byref(params), grid.ctypes.data, grid.size, C.byref(info))
+        self._check(st, "plc_drivable_area")
+        if not info.published:
+            return None, info
+        return grid[: info.n_cells].reshape(info.height, info.width), info
+
     # ---- node setup on the device (SURVEY §8 N1): same results as the host_* functions below
     def compute_normals(self, area: np.ndarray, radius: float = 1.5, point_step: int | None = None, off=(0, 4, 8)) -> np.ndarray:
         v = A.cloud_view(area, point_step, off)
