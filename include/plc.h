@@ -255,7 +255,8 @@ typedef struct plc_device_times {
     float cells_ms;         /* plc_vl_generate_cells */
     float candidates_ms;    /* plc_vl_generate_candidates */
     float drivable_ms;      /* plc_drivable_area */
-    float reserved[3];
+    float excavate_ms;      /* plc_excavate */
+    float reserved[2];
 } plc_device_times;
 plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out);
 
@@ -300,6 +301,48 @@ typedef struct plc_merge_src {
 plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_src,
                      void* out_merged, uint64_t capacity, uint64_t* n_out,
                      void* const* out_each, uint64_t* n_each);
+
+/* ---------------------------------------------------------------- excavated_surface_generator -- */
+
+/* Parameters of the node (excavated_surface_generator.cpp:28-47); the _L and _square variants are the same
+ * algorithm with l_shape_enabled fixed. */
+typedef struct plc_excavation_params {
+    double depth;                  /* excavation.depth = 1.0 */
+    double slope_angle_deg;        /* excavation.slope_angle = 75.0 */
+    double offset_x, offset_y;     /* excavation.offset_x = 4.0, offset_y = 1.0 (zx120/base_link frame) */
+    double point_density;          /* excavation.point_density = 0.05 */
+    double terrain_search_radius;  /* excavation.terrain_search_radius = 0.5 */
+    double arm1_length, arm1_width, arm2_length, arm2_width;   /* 2.0, 1.2, 2.0, 1.2 */
+    double width, length;          /* rectangle mode: 1.2, 1.8 */
+    int32_t l_shape_enabled;       /* excavation.l_shape_enabled = true */
+    int32_t reserved;
+} plc_excavation_params;
+void plc_excavation_params_default(plc_excavation_params* p);
+
+typedef struct plc_excavation_info {
+    double center[3];              /* excavation centre in the map frame; z = terrain height there (:289-297) */
+    double yaw;                    /* yaw of zx120/base_link in the map frame (:299-302) */
+    uint64_t n_kept;               /* input points that survive the carve (:470-472) */
+    uint64_t n_surface;            /* generated bottom + slope points appended to them (:487-584) */
+    uint64_t n_area;               /* points of the /excavation_area cloud (:350-455) */
+} plc_excavation_info;
+
+/* Number of points generateExcavatedSurface and generateExcavationArea produce for these parameters (they depend
+ * on the parameters only), for sizing the output buffers: n_terrain <= matched points + *n_surface. */
+plc_status plc_excavation_counts(const plc_excavation_params* prm, uint64_t* n_surface, uint64_t* n_area);
+
+/* Replaces matchedCloudCallback's data path (excavated_surface_generator.cpp:263-325): getTerrainHeight per
+ * point (mean z of the points within terrain_search_radius horizontally, nearest point otherwise, :183-225),
+ * the carve test (:327-348, :457-472), the synthetic pit surface (:487-584) and the /excavation_area cloud
+ * (:350-455).  Upstream rebuilds a KD-tree inside every getTerrainHeight call; here the cloud is bucketed once.
+ * matched: the /matched_point_cloud message (PointXYZRGB); off_rgb: byte offset of its packed rgb field, or
+ * UINT32_MAX when the message has none (pcl::fromROSMsg then leaves r = g = b = 0, a = 255).
+ * base_t, base_q: the transform map <- zx120/base_link (translation, quaternion x y z w) from TF.
+ * out_terrain / out_area: PointXYZRGB wire layout, 32 bytes per point. */
+plc_status plc_excavate(plc_ctx* ctx, const plc_cloud_view* matched, uint32_t off_rgb,
+                        const double* base_t, const double* base_q, const plc_excavation_params* prm,
+                        void* out_terrain, uint64_t cap_terrain, uint64_t* n_terrain,
+                        void* out_area, uint64_t cap_area, uint64_t* n_area, plc_excavation_info* info);
 
 /* ---------------------------------------------------------------- calc_drivable_area -- */
 

@@ -69,6 +69,11 @@ def lib() -> C.CDLL:
     L.orc_voxel_grid.argtypes = [vp, u64, dbl, vp, vp, vp, vp]
     L.orc_transform.argtypes = [vp, u64, vp, vp, vp]
     L.orc_transform.restype = None
+    L.orc_excavate.restype = None
+    L.orc_excavate.argtypes = [vp, vp, u64, vp, vp, C.POINTER(A.ExcavationParams), vp, C.POINTER(u64), vp, C.POINTER(u64),
+                               C.POINTER(A.ExcavationInfo)]
+    L.orc_excavation_frame.restype = None
+    L.orc_excavation_frame.argtypes = [vp, vp, dbl, dbl, vp, vp]
     L.orc_drivable_area.restype = i64
     L.orc_drivable_area.argtypes = [vp, u64, vp, vp, dbl, dbl, dbl, dbl, dbl, dbl, dbl, dbl, C.c_int, dbl, vp,
                                     C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
@@ -217,3 +222,20 @@ def drivable_area(xyz, t, q, robot_xy, start_xy, *, grid_resolution=1.0, map_wid
     if n < 0:
         return None
     return out[: gw * gh].reshape(gh, gw).copy()
+
+
+def excavate(xyz, rgba, base_t, base_q, params, n_surface_bound: int, n_area_bound: int):
+    """excavated_surface_generator.cpp:263-584.  Returns (terrain records (n, 32) uint8, area records, info)."""
+    L = lib()
+    xyz = np.ascontiguousarray(xyz[:, :3], np.float32)
+    rg = None if rgba is None else np.ascontiguousarray(rgba, np.uint32)
+    t = np.ascontiguousarray(base_t, np.float64)
+    q = np.ascontiguousarray(base_q, np.float64)
+    terrain = np.zeros((xyz.shape[0] + n_surface_bound, 32), np.uint8)
+    area = np.zeros((max(n_area_bound, 1), 32), np.uint8)
+    nt, na = C.c_uint64(0), C.c_uint64(0)
+    info = A.ExcavationInfo()
+    L.orc_excavate(xyz.ctypes.data, A.ptr(rg), xyz.shape[0], t.ctypes.data, q.ctypes.data, C.byref(params),
+                   terrain.ctypes.data, C.byref(nt), area.ctypes.data, C.byref(na), C.byref(info))
+    assert nt.value <= terrain.shape[0] and na.value <= area.shape[0]
+    return terrain[: nt.value], area[: na.value], info

@@ -110,6 +110,14 @@ int64_t orc_voxel_grid(const float* xyz, uint64_t n, double leaf, float* out_xyz
 /* tf2::doTransform float affine (§A.3 item 14): t (3 doubles) and quaternion x,y,z,w narrowed to float. */
 void orc_transform(const float* xyz, uint64_t n, const double* t, const double* q, float* out_xyz);
 
+/* excavated_surface_generator.cpp:263-584: the generator node's data path.  xyz / rgba: the /matched_point_cloud
+ * as a PointXYZRGB cloud (rgba NULL: a = 255, r = g = b = 0).  Outputs are 32-byte PointXYZRGB wire records;
+ * out_terrain needs n + n_surface records. */
+void orc_excavation_frame(const double* t, const double* q, double offset_x, double offset_y, double* center_xy, double* yaw);
+void orc_excavate(const float* xyz, const uint32_t* rgba, uint64_t n, const double* base_t, const double* base_q,
+                  const plc_excavation_params* prm, void* out_terrain, uint64_t* n_terrain, void* out_area,
+                  uint64_t* n_area, plc_excavation_info* info);
+
 /* calc_drivable_area.cpp:36-37, 87-232: the occupancy grid (row-major int8, width x height).  t, q: map <- scan
  * frame (NULL: none).  Returns width*height, or -1 for an empty scan (nothing is published, :108-112). */
 int64_t orc_drivable_area(const float* xyz, uint64_t n, const double* t, const double* q, double robot_x,

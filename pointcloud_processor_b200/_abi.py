@@ -59,7 +59,7 @@ class DeviceTimes(C.Structure):
     _fields_ = [("set_terrain_ms", C.c_float), ("set_observed_ms", C.c_float), ("filter_ms", C.c_float),
                 ("merge_ms", C.c_float), ("sweep_kernel_ms", C.c_float), ("normals_ms", C.c_float),
                 ("cells_ms", C.c_float), ("candidates_ms", C.c_float), ("drivable_ms", C.c_float),
-                ("reserved", C.c_float * 3)]
+                ("excavate_ms", C.c_float), ("reserved", C.c_float * 2)]
 
 
 class GridInfo(C.Structure):
@@ -105,6 +105,19 @@ class MergerInput(C.Structure):     # plc_merger_input
                 ("t", C.c_double * 3), ("q", C.c_double * 4)]
 
 
+class ExcavationParams(C.Structure):  # plc_excavation_params
+    _fields_ = [("depth", C.c_double), ("slope_angle_deg", C.c_double), ("offset_x", C.c_double), ("offset_y", C.c_double),
+                ("point_density", C.c_double), ("terrain_search_radius", C.c_double),
+                ("arm1_length", C.c_double), ("arm1_width", C.c_double), ("arm2_length", C.c_double),
+                ("arm2_width", C.c_double), ("width", C.c_double), ("length", C.c_double),
+                ("l_shape_enabled", C.c_int32), ("reserved", C.c_int32)]
+
+
+class ExcavationInfo(C.Structure):    # plc_excavation_info
+    _fields_ = [("center", C.c_double * 3), ("yaw", C.c_double), ("n_kept", C.c_uint64), ("n_surface", C.c_uint64),
+                ("n_area", C.c_uint64)]
+
+
 class DrivableParams(C.Structure):  # plc_drivable_params
     _fields_ = [("grid_resolution", C.c_double), ("map_width", C.c_double), ("map_height", C.c_double),
                 ("max_gradient", C.c_double), ("start_clear_radius", C.c_double),
@@ -132,6 +145,7 @@ EXPORTS = [
     "plc_vl_upload_candidates_strided", "plc_vl_sweep_strided", "plc_filter", "plc_merge",
     "plc_vl_compute_normals", "plc_vl_generate_cells", "plc_vl_generate_candidates",
     "plc_drivable_params_default", "plc_drivable_area",
+    "plc_excavation_params_default", "plc_excavation_counts", "plc_excavate",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
     "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
     "plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback", "plc_vlnode_zx120_points_callback",
@@ -202,6 +216,11 @@ def lib() -> C.CDLL:
     L.plc_vl_generate_cells.argtypes = [vp, C.POINTER(CloudView), vp, dbl, i32, dbl, vp, u64,
                                         C.POINTER(u64), C.POINTER(GridBounds)]
     L.plc_vl_compute_normals.argtypes = [vp, C.POINTER(CloudView), dbl, vp]
+    L.plc_excavation_params_default.argtypes = [C.POINTER(ExcavationParams)]
+    L.plc_excavation_params_default.restype = None
+    L.plc_excavation_counts.argtypes = [C.POINTER(ExcavationParams), C.POINTER(u64), C.POINTER(u64)]
+    L.plc_excavate.argtypes = [vp, C.POINTER(CloudView), C.c_uint32, vp, vp, C.POINTER(ExcavationParams), vp, u64,
+                               C.POINTER(u64), vp, u64, C.POINTER(u64), C.POINTER(ExcavationInfo)]
     L.plc_drivable_params_default.argtypes = [C.POINTER(DrivableParams)]
     L.plc_drivable_params_default.restype = None
     L.plc_drivable_area.argtypes = [vp, C.POINTER(CloudView), vp, vp, dbl, dbl, dbl, dbl, C.POINTER(DrivableParams),
@@ -259,6 +278,22 @@ def memo_params() -> Params:
     p = Params()
     lib().plc_params_memo(C.byref(p))
     return p
+
+
+def excavation_params(**kw) -> ExcavationParams:
+    p = ExcavationParams()
+    lib().plc_excavation_params_default(C.byref(p))
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+def excavation_counts(p: ExcavationParams):
+    ns, na = C.c_uint64(0), C.c_uint64(0)
+    st = lib().plc_excavation_counts(C.byref(p), C.byref(ns), C.byref(na))
+    if st != PLC_OK:
+        raise PlcError(st, "plc_excavation_counts")
+    return ns.value, na.value
 
 
 def cloud_view(buf: np.ndarray, point_step: int | None = None, off=(0, 4, 8)) -> CloudView:

@@ -227,6 +227,29 @@ class Context:
         return merged[: n_out.value], [e[: n_each[i]] for i, e in enumerate(each)]
 
 
+    def excavate(self, matched: np.ndarray, base_t, base_q, params: A.ExcavationParams | None = None,
+                 point_step: int | None = None, off=(0, 4, 8), off_rgb: int | None = None):
+        """excavated_surface_generator's data path (plc_excavate).  matched: (n, 8) float32 PointXYZRGB records
+        (rgb at byte 16) or any layout via point_step/off/off_rgb.  Returns (terrain records (n, 32) uint8,
+        area records (m, 32) uint8, info)."""
+        if params is None:
+            params = A.excavation_params()
+        v = A.cloud_view(matched, point_step, off)
+        if off_rgb is None:
+            off_rgb = 16 if v.point_step >= 20 else 0xFFFFFFFF
+        n_surface, n_area = A.excavation_counts(params)
+        terrain = np.zeros((int(v.n_points) + n_surface, 32), np.uint8)
+        area = np.zeros((n_area, 32), np.uint8)
+        nt, na = C.c_uint64(0), C.c_uint64(0)
+        info = A.ExcavationInfo()
+        t = np.ascontiguousarray(base_t, np.float64)
+        q = np.ascontiguousarray(base_q, np.float64)
+        st = self._L.plc_excavate(self._h, C.byref(v), off_rgb, t.ctypes.data, q.ctypes.data, C.byref(params),
+                                  terrain.ctypes.data, terrain.shape[0], C.byref(nt), area.ctypes.data, area.shape[0],
+                                  C.byref(na), C.byref(info))
+        self._check(st, "plc_excavate")
+        return terrain[: nt.value], area[: na.value], info
+
     def drivable_area(self, scan: np.ndarray, t, q, robot_xy, start_xy, params: A.DrivableParams | None = None,
                       point_step: int | None = None, off=(0, 4, 8)):
         """calc_drivable_area's occupancy grid (plc_drivable_area).  Returns ((height, width) int8 grid or None for an

@@ -89,7 +89,7 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
                            &c->partial_score, &c->partial_cov, &c->scores, &c->covered, &c->mask, &c->result, &c->pose_aux, &c->s_tab,
                            &c->f_keys, &c->f_vals, &c->f_keys2, &c->f_vals2, &c->f_tmp, &c->f_out, &c->f_flags,
                            &c->m_out, &c->su_pts, &c->su_sorted, &c->su_keys, &c->su_start, &c->su_table, &c->su_tmp,
-                           &c->su_flags, &c->su_out, &c->su_normals, &c->su_state};
+                           &c->su_flags, &c->su_out, &c->su_normals, &c->su_state, &c->ex_plan, &c->ex_terrain, &c->ex_area};
     for (plc::DevBuf* b : bufs) b->release();
     if (c->pinned) cudaFreeHost(c->pinned);
     c->timer.destroy();

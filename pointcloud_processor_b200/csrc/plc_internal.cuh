@@ -197,6 +197,7 @@ struct plc_ctx {
     // node setup on the device (plc_setup.cu): loaded points, bucket order, keys/values of the sort, bucket
     // starts, sort table, scan scratch, flags + slots, packed outputs, per-point normals, bounds block
     plc::DevBuf su_pts, su_sorted, su_keys, su_start, su_table, su_tmp, su_flags, su_out, su_normals, su_state;
+    plc::DevBuf ex_plan, ex_terrain, ex_area;     // plc_excavate.cu: lattice plan, output records
 
     void set_error(const char* what, const char* why) {
         last_error = std::string(what) + ": " + why;
