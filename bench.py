@@ -431,6 +431,44 @@ def measure_feeders(ctx, scene, peak, reps: int = 5) -> dict:
     out["voxelise_terrain"] = row(k_ms, w_ms, n * (12 + 16), n, "points")
     out["voxelise_terrain"]["points_in"] = n
     out["setup"] = measure_setup(ctx, scene, peak, best)
+    # the nodes either side of the path on this workload's merged cloud / robot scan
+    base_t, base_q = np.zeros(3), np.array([0.0, 0.0, 0.0, 1.0])
+    (terrain, area, info), k_ms, w_ms = best(lambda: ctx.excavate(merged.reshape(-1), base_t, base_q, None, point_step=32, off_rgb=16),
+                                             "excavate_ms")
+    n_in = int(merged.shape[0])
+    r = row(k_ms, w_ms, n_in * 32 + int(terrain.shape[0]) * 32 + int(area.shape[0]) * 32, n_in, "points")
+    r.update(points_in=n_in, kept=int(info.n_kept), surface=int(info.n_surface), area=int(info.n_area))
+    if not os.environ.get("PLC_BENCH_NO_CPU_FEEDERS"):
+        from oracle import binding as O
+        from pointcloud_processor_b200 import _abi as A
+        prm = A.excavation_params()
+        ns, na = A.excavation_counts(prm)
+        mx = np.ascontiguousarray(merged[:, :12]).view(np.float32).reshape(-1, 3)
+        t0 = time.perf_counter()
+        O.excavate(mx, None, base_t, base_q, prm, ns, na)
+        r["cpu_port_ms"] = (time.perf_counter() - t0) * 1e3      # one shared index; upstream rebuilds a KD-tree per query
+    out["excavate"] = r
+    # the same node on a dense cloud (1 M ground points around the pit), where the bucketed heights matter
+    rng = np.random.default_rng(17)
+    dense = np.zeros((1_000_000, 8), np.float32)
+    dense[:, :2] = rng.uniform((-11.0, -14.0), (19.0, 16.0), (dense.shape[0], 2))
+    dense[:, 2] = 0.15 * np.sin(0.4 * dense[:, 0]) * np.cos(0.3 * dense[:, 1]) + rng.uniform(-0.01, 0.01, dense.shape[0])
+    dense[:, 3] = 1.0
+    (terrain, area, info), k_ms, w_ms = best(lambda: ctx.excavate(dense, base_t, base_q, None), "excavate_ms")
+    r = row(k_ms, w_ms, dense.shape[0] * 32 + int(terrain.shape[0]) * 32 + int(area.shape[0]) * 32, dense.shape[0], "points")
+    r.update(points_in=int(dense.shape[0]), kept=int(info.n_kept), surface=int(info.n_surface), area=int(info.n_area))
+    out["excavate_dense_1M"] = r
+    rxy = scenes.ROBOT_BASE["xyz"][:2]
+    (grid, ginfo), k_ms, w_ms = best(lambda: ctx.drivable_area(filtered[0], rt, rq, rxy, rxy), "drivable_ms")
+    v = int(filtered[0].shape[0])
+    r = row(k_ms, w_ms, v * 16 + int(ginfo.n_cells) * 13, v, "points")
+    r.update(points_in=v, cells=int(ginfo.n_cells))
+    if not os.environ.get("PLC_BENCH_NO_CPU_FEEDERS"):
+        from oracle import binding as O
+        t0 = time.perf_counter()
+        O.drivable_area(filtered[0], rt, rq, rxy, rxy)
+        r["cpu_port_ms"] = (time.perf_counter() - t0) * 1e3
+    out["drivable_area"] = r
     return out
 
 

@@ -170,3 +170,52 @@ def run_pipeline(ctx: Context, inp, leaf: float = 0.2, **sweep_kw):
     times["sweep_kernel_ms"] = ctx.device_times()["sweep_kernel_ms"]
     out["device_ms"] = times
     return out
+
+
+def run_launch_graph(ctx: Context, inp, leaf: float = 0.2, num_candidates: int = 100, grid_resolution: float = 0.1,
+                     vertical_layers: int = 10, sensor_height: float = 1.1, search_radius: float = 3.0,
+                     excavation: A.ExcavationParams | None = None, robot_base_xy=None, **sweep_kw):
+    """The whole dataflow of launch/start.launch.xml for one scan pair, every data-parallel stage on the device:
+    pointcloud_filter (both scans) -> pointcloud_merger -> excavated_surface_generator -> virtual_lidar
+    (normals, evaluation cells, candidate poses, sweep), with calc_drivable_area beside it on the robot's
+    filtered scan.  Unlike run_pipeline, the sweep's terrain and evaluation area are the generator's outputs for
+    the merged cloud, not a synthetic scene.  zx120/base_link sits at the map origin (pointcloud_merger.cpp:218-228).
+    Returns every intermediate product and the kernel time of each stage."""
+    from .scenes import fixed_pose, ROBOT_BASE
+    out, times = {}, {}
+    out["robot_filtered"] = filter_scan(ctx, inp.robot_scan, leaf=leaf)
+    times["filter_robot_ms"] = ctx.device_times()["filter_ms"]
+    out["zx120_filtered"] = filter_scan(ctx, inp.zx120_scan, leaf=leaf)
+    times["filter_zx120_ms"] = ctx.device_times()["filter_ms"]
+    merged, rc, bc = merge_clouds(ctx, dict(cloud=out["robot_filtered"], t=inp.robot_tf[0], q=inp.robot_tf[1]),
+                                  dict(cloud=out["zx120_filtered"], t=inp.zx120_tf[0], q=inp.zx120_tf[1]))
+    times["merge_ms"] = ctx.device_times()["merge_ms"]
+    out.update(merged=merged, robot_coloured=rc, backhoe_coloured=bc)
+    # /matched_point_cloud -> /excavated_terrain + /excavation_area (PointXYZRGB records, rgb at byte 16)
+    base_t, base_q = np.zeros(3), np.array([0.0, 0.0, 0.0, 1.0])
+    terrain, area, info = ctx.excavate(merged.reshape(-1), base_t, base_q, excavation, point_step=32, off_rgb=16)
+    times["excavate_ms"] = ctx.device_times()["excavate_ms"]
+    out.update(terrain=terrain, area=area, excavation_info=info)
+    # virtual_lidar: excavationAreaCallback, terrainCallback, zx120PointsCallback, runOptimization
+    normals = ctx.compute_normals(area.reshape(-1), 1.5, point_step=32)
+    times["normals_ms"] = ctx.device_times()["normals_ms"]
+    cells, bounds = ctx.generate_cells(area.reshape(-1), normals, grid_resolution, vertical_layers, 1.5, point_step=32)
+    times["cells_ms"] = ctx.device_times()["cells_ms"]
+    ctx.set_terrain(terrain.reshape(-1), point_step=32)
+    times["set_terrain_ms"] = ctx.device_times()["set_terrain_ms"]
+    ctx.set_cells(cells)
+    ctx.set_observed(out["zx120_filtered"], point_step=16)
+    times["set_observed_ms"] = ctx.device_times()["set_observed_ms"]
+    fixed = fixed_pose()
+    cands = ctx.generate_candidates(None, bounds, fixed, num_candidates, search_radius, sensor_height)
+    times["candidates_ms"] = ctx.device_times()["candidates_ms"]
+    out.update(normals=normals, cells=cells, bounds=bounds, candidates=cands, fixed=fixed)
+    out["sweep"] = ctx.sweep(A.default_params(), fixed, cands, **sweep_kw)
+    times["sweep_kernel_ms"] = ctx.device_times()["sweep_kernel_ms"]
+    # calc_drivable_area on the robot's filtered scan (its TF into the map is the merger's)
+    rxy = robot_base_xy if robot_base_xy is not None else ROBOT_BASE["xyz"][:2]
+    grid, ginfo = ctx.drivable_area(out["robot_filtered"], inp.robot_tf[0], inp.robot_tf[1], rxy, rxy, point_step=16)
+    times["drivable_ms"] = ctx.device_times()["drivable_ms"]
+    out.update(occupancy_grid=grid, occupancy_info=ginfo)
+    out["device_ms"] = times
+    return out
