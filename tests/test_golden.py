@@ -51,3 +51,35 @@ def test_filter_merge_fixture():
     assert counts.sum() == cropped.shape[0] and np.all(np.diff(keys) > 0)
     moved = O.transform(cent, z["t"], z["q"])
     assert np.array_equal(moved.view(np.uint32), z["transformed"].view(np.uint32))
+
+
+def bounds_of(z):
+    b = A.GridBounds()
+    (b.min_x, b.max_x, b.min_y, b.max_y, b.min_z, b.max_z), b.width, b.height = z["bounds"][:6], int(z["bounds"][6]), int(z["bounds"][7])
+    return b
+
+
+def test_node_stage_fixture():
+    """tests/golden/node_stages.npz (tools/make_golden.py): generator -> setup -> drivable grid.  The oracle
+    reproduces it through its other index kinds, and the product's host twins of the setup steps agree with it."""
+    from pointcloud_processor_b200 import context as ctxmod
+    z = np.load(GOLDEN / "node_stages.npz")
+    prm = A.excavation_params(point_density=float(z["point_density"]))
+    ns, na = A.excavation_counts(prm)
+    terrain, area, info = O.excavate(z["ground"], z["colours"], z["base_t"], z["base_q"], prm, ns, na)
+    assert np.array_equal(terrain, z["terrain"]) and np.array_equal(area, z["area"]) and info.n_kept == int(z["n_kept"])
+    assert terrain.shape[0] == info.n_kept + ns and area.shape[0] == na
+    area_xyz = np.ascontiguousarray(area[:, :12]).view(np.float32).reshape(-1, 3)
+    terrain_xyz = np.ascontiguousarray(terrain[:, :12]).view(np.float32).reshape(-1, 3)
+    cells, b = O.generate_cells(area_xyz, z["normals"], 0.2, 4, 1.5)
+    assert np.array_equal(cells.view(np.uint8), z["cells"].view(np.uint8))
+    hcells, hb = ctxmod.host_generate_cells(area_xyz, z["normals"], 0.2, 4, 1.5)
+    assert np.array_equal(hcells.view(np.uint8), z["cells"].view(np.uint8))
+    for kind in (O.GRID, O.KDTREE):
+        cands = O.generate_candidates(O.Index(terrain_xyz, kind), bounds_of(z), z["fixed"], 49, 3.0, 1.1)
+        assert np.array_equal(cands.view(np.uint8), z["candidates"].view(np.uint8))
+    hc = ctxmod.host_generate_candidates(terrain_xyz, bounds_of(z), z["fixed"], 49, 3.0, 1.1)
+    assert np.array_equal(hc.view(np.uint8), z["candidates"].view(np.uint8))
+    grid = O.drivable_area(z["scan"], z["drivable_t"], z["drivable_q"], (9.0, -3.0), (7.0, -2.0), grid_resolution=0.5,
+                           map_width=30.0, map_height=24.0, min_points_per_cell=3)
+    assert np.array_equal(grid, z["grid"])

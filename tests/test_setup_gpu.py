@@ -183,3 +183,15 @@ def test_full_size_lattices_have_the_reference_properties(ctx, scene_cache):
     for k in ("x", "y", "z"):
         assert np.array_equal(got[k], host[k]), k
     assert np.allclose(got["pitch"], host["pitch"], rtol=0, atol=4e-15)
+
+
+def test_random_stage_scenes_against_oracle(ctx):
+    """tools/fuzz_stages.py, a few iterations: random clouds, parameters, transforms and wire layouts through the
+    generator, the setup steps and the drivable grid."""
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent / "tools"))
+    import fuzz_stages
+    tot = fuzz_stages.run(ctx, 10, 20260105)
+    print(tot)
+    assert tot["clouds"] == 10 and tot["cells"] > 0 and tot["poses"] > 0

@@ -115,9 +115,50 @@ def hand_cases():
     print("hand_cases", len(cases))
 
 
+def node_stage_fixtures():
+    """The nodes either side of the sweep: seeded inputs and the oracle's outputs.
+    Radius searches go through the BRUTE index where the oracle lets the caller choose one."""
+    rng = np.random.default_rng(2024)
+    # N2: a ground cloud around the pit -> /excavated_terrain + /excavation_area (coarser lattice to keep the file small)
+    n = 9000
+    xy = rng.uniform([0.5, -3.5], [8.5, 3.5], (n, 2))
+    z = 0.15 * np.sin(0.4 * xy[:, 0]) * np.cos(0.3 * xy[:, 1]) + rng.uniform(-0.01, 0.01, n)
+    ground = np.column_stack([xy, z]).astype(np.float32)
+    colours = (rng.integers(0, 1 << 24, n).astype(np.uint32) | np.uint32(0xFF000000))
+    prm = A.excavation_params(point_density=0.1)
+    ns, na = A.excavation_counts(prm)
+    base_t, base_q = np.array([0.25, -0.5, 0.0]), np.array([0.0, 0.0, np.sin(0.15), np.cos(0.15)])
+    terrain, area, info = O.excavate(ground, colours, base_t, base_q, prm, ns, na)
+    exc = dict(ground=ground, colours=colours, base_t=base_t, base_q=base_q, point_density=0.1,
+               terrain=terrain, area=area, n_kept=info.n_kept, center=np.array(list(info.center)), yaw=info.yaw)
+    # N1 on the generator's outputs: normals, cells, candidates
+    area_xyz = np.ascontiguousarray(area[:, :12]).view(np.float32).reshape(-1, 3)
+    terrain_xyz = np.ascontiguousarray(terrain[:, :12]).view(np.float32).reshape(-1, 3)
+    normals = O.compute_normals(area_xyz, 1.5)
+    cells, b = O.generate_cells(area_xyz, normals, 0.2, 4, 1.5)
+    fixed = scenes.fixed_pose()
+    cands = O.generate_candidates(O.Index(terrain_xyz, O.BRUTE), b, fixed, 49, 3.0, 1.1)
+    bounds = np.array([b.min_x, b.max_x, b.min_y, b.max_y, b.min_z, b.max_z, b.width, b.height], np.float64)
+    # N4: a scan in the robot's sensor frame -> occupancy grid
+    m = 8000
+    sxy = rng.uniform(-12, 12, (m, 2))
+    sz = -2.0 + 0.2 * np.sin(0.5 * sxy[:, 0]) + rng.normal(0, 0.02, m) + (rng.random(m) < 0.1) * rng.uniform(0, 2, m)
+    scan = np.column_stack([sxy, sz]).astype(np.float32)
+    scan[::131, 1] = np.nan
+    dt, dq = np.array([9.25, -3.0, 2.0]), np.array([-0.06, 0.0166, 0.963, 0.2675])
+    dq = dq / np.linalg.norm(dq)
+    grid = O.drivable_area(scan, dt, dq, (9.0, -3.0), (7.0, -2.0), grid_resolution=0.5, map_width=30.0, map_height=24.0,
+                           min_points_per_cell=3)
+    np.savez_compressed(OUT / "node_stages.npz", normals=normals, cells=cells, bounds=bounds, fixed=fixed, candidates=cands,
+                        scan=scan, drivable_t=dt, drivable_q=dq, grid=grid, **exc)
+    print("node_stages", "ground", n, "kept", info.n_kept, "surface", ns, "area", na, "cells", cells.size, "cands", cands.size,
+          "grid", grid.shape, {int(v): int((grid == v).sum()) for v in np.unique(grid)})
+
+
 def main():
     OUT.mkdir(parents=True, exist_ok=True)
     hand_cases()
+    node_stage_fixtures()
     sweep_fixture("sweep_tiny", scenes.build("tiny"))
     small = scenes.build("small")
     sweep_fixture("sweep_small_first8", small, n_cands=8)
