@@ -1,6 +1,6 @@
 """Turns the raw ncu outputs in gpurun_out/ (scratch) into the tracked summaries under profiles/.
 
-    python tools/make_profiles.py <tag> <launches.csv> <k_sweep.ncu-rep> [command text]
+    python tools/make_profiles.py <tag> <launches.csv> <k_sweep.ncu-rep | -> [command text]
 
   profiles/<tag>_launches.csv         the ncu launch list as captured (gpu__time_duration per launch)
   profiles/<tag>_launch_summary.csv   per kernel: launches, total time, share of the profiled command
@@ -71,6 +71,9 @@ def main():
     command = sys.argv[4] if len(sys.argv) > 4 else "python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-north-star"
     PROF.mkdir(exist_ok=True)
     per, total = launch_summary(tag, launches, command)
+    if rep == "-":              # launch list only (the k_sweep capture is unchanged)
+        print("kernels", len(per), "total_us", round(total, 1))
+        return
     traffic = full_capture(tag, rep, "cfg2 (1930 poses x 57600 rays, 200k terrain points)")
     tfile = PROF / "sweep_dram_traffic.json"
     cur = json.loads(tfile.read_text()) if tfile.exists() else {}
