@@ -27,6 +27,7 @@ def launch_summary(tag, path, command):
     per = OrderedDict()
     for r in rows:
         name = re.sub(r"\(.*$", "", r[4])
+        name = re.sub(r"^(void )?(plc::)?(<?unnamed>::)?", "", name)      # ncu demangles namespaces differently between runs
         t = float(r[14].replace(",", "")) / 1e3          # ns -> us
         n, tot = per.get(name, (0, 0.0))
         per[name] = (n + 1, tot + t)
