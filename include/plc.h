@@ -142,6 +142,21 @@ int plc_abi_version(void);
 /* Blocks until everything queued on the context's stream has finished. */
 plc_status plc_ctx_sync(plc_ctx* ctx);
 
+/* ---------------------------------------------------------------- clouds that stay on the device -- */
+
+/* Device buffers a caller can hand from one stage to the next without a host round trip.  Wherever an entry point
+ * takes a point cloud (plc_cloud_view::data of plc_vl_set_terrain / plc_vl_set_observed / plc_filter / plc_merge /
+ * plc_excavate / plc_drivable_area / plc_vl_compute_normals / plc_vl_generate_cells / plc_vl_generate_candidates),
+ * the per-point normals of plc_vl_generate_cells, or writes a cloud, a normal array, cells or poses (out_* of the
+ * same calls), the pointer may be host memory or memory of the context's device: device inputs are read in place,
+ * device outputs are written with a device-to-device copy.  Counts and info structs always come back to the host.
+ * (plc_vl_set_cells, the candidate list and the result arrays of the sweep are host memory: the node needs them
+ * there for its markers and logs.) */
+plc_status plc_dev_alloc(plc_ctx* ctx, uint64_t bytes, void** dev_ptr);
+void plc_dev_free(plc_ctx* ctx, void* dev_ptr);
+plc_status plc_dev_upload(plc_ctx* ctx, void* dev_dst, const void* host_src, uint64_t bytes);
+plc_status plc_dev_download(plc_ctx* ctx, void* host_dst, const void* dev_src, uint64_t bytes);
+
 /* ---------------------------------------------------------------- virtual_lidar ------------- */
 
 /* Replaces the KD-tree build of terrainCallback (virtual_lidar.cpp:180-192): voxelises the

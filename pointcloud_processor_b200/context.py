@@ -312,6 +312,45 @@ class Context:
         return out[: n.value].copy()
 
 
+class DevBuffer:
+    """plc_dev_alloc: device memory a caller hands from one stage to the next."""
+
+    def __init__(self, ctx: "Context", nbytes: int):
+        self._ctx, self.nbytes = ctx, int(nbytes)
+        p = C.c_void_p()
+        ctx._check(ctx._L.plc_dev_alloc(ctx._h, self.nbytes, C.byref(p)), "plc_dev_alloc")
+        self.ptr = p.value
+
+    def free(self):
+        if getattr(self, "ptr", None) and getattr(self._ctx, "_h", None):
+            self._ctx._L.plc_dev_free(self._ctx._h, self.ptr)
+        self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def upload(self, arr: np.ndarray):
+        arr = np.ascontiguousarray(arr)
+        assert arr.nbytes <= self.nbytes
+        self._ctx._check(self._ctx._L.plc_dev_upload(self._ctx._h, self.ptr, arr.ctypes.data, arr.nbytes), "plc_dev_upload")
+        return self
+
+    def download(self, nbytes: int, dtype=np.uint8) -> np.ndarray:
+        out = np.zeros(int(nbytes) // np.dtype(dtype).itemsize, dtype)
+        self._ctx._check(self._ctx._L.plc_dev_download(self._ctx._h, out.ctypes.data, self.ptr, out.nbytes), "plc_dev_download")
+        return out
+
+    def view(self, n_points: int, point_step: int, off=(0, 4, 8)) -> A.CloudView:
+        v = A.CloudView()
+        v.data = self.ptr if n_points else None
+        v.n_points, v.point_step = int(n_points), int(point_step)
+        v.off_x, v.off_y, v.off_z = off
+        return v
+
+
 # ---- host-side setup (include/plc_host.h) -------------------------------------------------------
 def host_generate_cells(area: np.ndarray, normals: np.ndarray | None, grid_resolution: float,
                         vertical_layers: int, normal_search_radius: float = 1.5):

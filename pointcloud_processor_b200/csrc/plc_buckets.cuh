@@ -215,18 +215,17 @@ plc_status read_bounds(plc_ctx* ctx, const BoundsState* dev, Bounds* out) {
     return PLC_OK;
 }
 
-// H2D of the PointCloud2 bytes and conversion to float4 {x, y, z, index}; bounds come back to the host
+// The PointCloud2 bytes (copied in, or read in place from a device buffer) and their conversion to float4 {x, y, z, index}; bounds come back to the host
 plc_status load_cloud(plc_ctx* ctx, const plc_cloud_view* cloud, Bounds* bounds) {
     const size_t n = cloud->n_points;
     const size_t bytes = n * (size_t)cloud->point_step;
-    PLC_CUDA_TRY(ctx, ctx->upload.reserve(bytes));
     PLC_CUDA_TRY(ctx, ctx->su_pts.reserve(n * sizeof(float4)));
     PLC_CUDA_TRY(ctx, ctx->su_state.reserve(sizeof(BoundsState)));
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, cloud->data, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    PLC_TRY(stage_bytes(ctx, cloud->data, bytes, &ctx->su_raw));
     const bool aligned = cloud->point_step % 4 == 0 && cloud->off_x % 4 == 0 && cloud->off_y % 4 == 0 && cloud->off_z % 4 == 0;
     ctx->timer.begin(ctx->stream);
     k_bounds_init<<<1, 1, 0, ctx->stream>>>(ctx->su_state.as<BoundsState>());
-    k_load_points<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->upload.as<unsigned char>(), (unsigned)n, cloud->point_step,
+    k_load_points<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->su_raw, (unsigned)n, cloud->point_step,
                                                                cloud->off_x, cloud->off_y, cloud->off_z, aligned,
                                                                ctx->su_pts.as<float4>(), ctx->su_state.as<BoundsState>());
     ctx->timer.end(ctx->stream);

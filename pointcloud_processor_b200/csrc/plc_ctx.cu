@@ -108,3 +108,35 @@ extern "C" plc_status plc_ctx_sync(plc_ctx* c) {
     PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return PLC_OK;
 }
+
+// ---- device buffers handed between stages (plc.h)
+extern "C" plc_status plc_dev_alloc(plc_ctx* c, uint64_t bytes, void** dev_ptr) {
+    if (!c || !dev_ptr) return PLC_E_INVALID_ARG;
+    *dev_ptr = nullptr;
+    PLC_CUDA_TRY(c, cudaSetDevice(c->device));
+    PLC_CUDA_TRY(c, cudaMalloc(dev_ptr, bytes ? bytes : 1));
+    return PLC_OK;
+}
+
+extern "C" void plc_dev_free(plc_ctx* c, void* dev_ptr) {
+    if (!c || !dev_ptr) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(dev_ptr);
+}
+
+extern "C" plc_status plc_dev_upload(plc_ctx* c, void* dev_dst, const void* host_src, uint64_t bytes) {
+    if (!c || (bytes && (!dev_dst || !host_src))) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(c, cudaSetDevice(c->device));
+    PLC_CUDA_TRY(c, cudaMemcpyAsync(dev_dst, host_src, bytes, cudaMemcpyHostToDevice, c->stream));
+    PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_dev_download(plc_ctx* c, void* host_dst, const void* dev_src, uint64_t bytes) {
+    if (!c || (bytes && (!host_dst || !dev_src))) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(c, cudaSetDevice(c->device));
+    PLC_CUDA_TRY(c, cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return PLC_OK;
+}

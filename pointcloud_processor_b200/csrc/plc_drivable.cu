@@ -152,10 +152,10 @@ extern "C" plc_status plc_drivable_area(plc_ctx* ctx, const plc_cloud_view* scan
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
     const size_t n = scan->n_points, bytes = n * (size_t)scan->point_step;
-    PLC_CUDA_TRY(ctx, ctx->upload.reserve(bytes));
     PLC_CUDA_TRY(ctx, ctx->su_flags.reserve(n_cells * sizeof(CellState) + 16));
     PLC_CUDA_TRY(ctx, ctx->su_out.reserve(n_cells + 16));
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, scan->data, bytes, cudaMemcpyDefault, s));
+    const unsigned char* raw = nullptr;
+    PLC_TRY(stage_bytes(ctx, scan->data, bytes, &raw));
     CellState* cells = ctx->su_flags.as<CellState>();
     signed char* grid = ctx->su_out.as<signed char>();
     const bool aligned = ((scan->point_step | scan->off_x | scan->off_y | scan->off_z) & 3u) == 0;
@@ -165,7 +165,7 @@ extern "C" plc_status plc_drivable_area(plc_ctx* ctx, const plc_cloud_view* scan
     ctx->timer.begin(s);
     if (n_cells) {
         k_cells_reset<<<(unsigned)((n_cells + 255) / 256), 256, 0, s>>>(cells, (unsigned)n_cells);
-        k_bin_heights<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(ctx->upload.as<unsigned char>(), (unsigned)n, scan->point_step,
+        k_bin_heights<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(raw, (unsigned)n, scan->point_step,
                                                                    scan->off_x, scan->off_y, scan->off_z, aligned, a, t ? 1 : 0,
                                                                    info->origin_x, info->origin_y, prm->grid_resolution,
                                                                    info->width, info->height, cells);

@@ -561,7 +561,7 @@ extern "C" plc_status plc_excavate(plc_ctx* ctx, const plc_cloud_view* matched, 
     double* centre_h = reinterpret_cast<double*>(area + area_total);
     ctx->timer.begin(s);
     if (n && kept)
-        k_emit_kept<<<blocks_for(n, 256), 256, 0, s>>>(pts, (unsigned)n, keep, slot, ctx->upload.as<unsigned char>(),
+        k_emit_kept<<<blocks_for(n, 256), 256, 0, s>>>(pts, (unsigned)n, keep, slot, ctx->su_raw,
                                                        matched->point_step, off_rgb, terrain);
     k_lattice_heights<<<blocks_for(n_entries * 32, 256), 256, 0, s>>>(G, E, (unsigned)n_entries, P, height);
     k_emit_area<<<blocks_for(n_entries, 256), 256, 0, s>>>(E, (unsigned)n_entries, P, height, area);

@@ -200,12 +200,12 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
     const size_t bytes = (size_t)n * in->point_step;
-    PLC_CUDA_TRY(ctx, ctx->upload.reserve(bytes));
     PLC_CUDA_TRY(ctx, ctx->f_flags.reserve(((size_t)n + 1) * 4));
     PLC_CUDA_TRY(ctx, ctx->f_tmp.reserve(scan_tmp_bytes((size_t)n + 1) + scan_tmp_bytes(sort_table_entries(n)) + 64));
     PLC_CUDA_TRY(ctx, ctx->f_out.reserve((size_t)n * sizeof(float4) * 2));   // [cropped | centroids]
     PLC_CUDA_TRY(ctx, ctx->scratch.reserve(4096));
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, in->data, bytes, cudaMemcpyHostToDevice, s));
+    const unsigned char* raw = nullptr;
+    PLC_TRY(stage_bytes(ctx, in->data, bytes, &raw));
 
     const bool aligned = ((in->point_step | in->off_x | in->off_y | in->off_z) & 3u) == 0;
     const CropDev cb{box->x_min, box->x_max, box->y_min, box->y_max, box->z_min, box->z_max};
@@ -220,10 +220,10 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     ctx->times.filter_ms = 0.f;
     ctx->timer.begin(s);
     k_filter_state_init<<<1, 1, 0, s>>>(st);
-    k_crop_flag<<<blocks1, 256, 0, s>>>(ctx->upload.as<unsigned char>(), n, in->point_step, in->off_x, in->off_y,
+    k_crop_flag<<<blocks1, 256, 0, s>>>(raw, n, in->point_step, in->off_x, in->off_y,
                                         in->off_z, aligned, cb, flag);
     scan_exclusive_u32(flag, (size_t)n + 1, scan_tmp, s);
-    k_crop_compact<<<(n + 255) / 256, 256, 0, s>>>(ctx->upload.as<unsigned char>(), n, in->point_step, in->off_x,
+    k_crop_compact<<<(n + 255) / 256, 256, 0, s>>>(raw, n, in->point_step, in->off_x,
                                                    in->off_y, in->off_z, aligned, flag, cropped, st);
     ctx->launches += 6;
     ctx->timer.end(s);
@@ -241,7 +241,7 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
 
     auto copy_out = [&](const float4* src, unsigned count) -> plc_status {
         if (count > capacity) return PLC_E_CAPACITY;
-        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_xyz16, src, (size_t)count * sizeof(float4), cudaMemcpyDeviceToHost, s));
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_xyz16, src, (size_t)count * sizeof(float4), cudaMemcpyDefault, s));
         PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
         *n_out = count;
         return PLC_OK;

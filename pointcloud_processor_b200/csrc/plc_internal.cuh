@@ -198,6 +198,7 @@ struct plc_ctx {
     // starts, sort table, scan scratch, flags + slots, packed outputs, per-point normals, bounds block
     plc::DevBuf su_pts, su_sorted, su_keys, su_start, su_table, su_tmp, su_flags, su_out, su_normals, su_state;
     plc::DevBuf ex_plan, ex_terrain, ex_area;     // plc_excavate.cu: lattice plan, output records
+    const unsigned char* su_raw = nullptr;         // where load_cloud read the caller's records from (upload or the caller's device buffer)
 
     void set_error(const char* what, const char* why) {
         last_error = std::string(what) + ": " + why;
@@ -231,6 +232,25 @@ plc_status fetch_strided(plc_ctx* ctx, plc_sweep_out* out, uint64_t dst_stride);
 // (normally (float)(radius*radius)); march_err + march_err_m: position error of the caller's march, in
 // fine-voxel units, folded into the conservative slack.
 plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err, double march_err_m);
+
+// Where a caller's cloud bytes are read from on the device.  `data` may be host memory (copied into ctx->upload) or
+// device memory of this context's device — a buffer from plc_dev_alloc, typically the output of the previous stage —
+// which is then read in place (clouds stay in HBM between the nodes' stages).
+inline plc_status stage_bytes(plc_ctx* ctx, const void* data, size_t bytes, const unsigned char** dev) {
+    *dev = nullptr;
+    if (bytes == 0) return PLC_OK;
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, data) == cudaSuccess &&
+        (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged)) {
+        *dev = static_cast<const unsigned char*>(data);
+        return PLC_OK;
+    }
+    cudaGetLastError();          // an unregistered host pointer is not an error
+    PLC_CUDA_TRY(ctx, ctx->upload.reserve(bytes));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, data, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    *dev = ctx->upload.as<unsigned char>();
+    return PLC_OK;
+}
 
 inline bool cloud_view_ok(const plc_cloud_view* v) {
     if (!v) return false;

@@ -87,7 +87,6 @@ extern "C" plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_s
     if (total == 0) return PLC_OK;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
-    PLC_CUDA_TRY(ctx, ctx->upload.reserve(raw_bytes));
     PLC_CUDA_TRY(ctx, ctx->m_out.reserve(total * 32 * 2));      // [merged | per-source clouds back to back]
     uint4* merged = ctx->m_out.as<uint4>();
     uint4* each = merged + total * 2;
@@ -99,25 +98,25 @@ extern "C" plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_s
         if (!src.present || src.cloud.n_points == 0) continue;
         const unsigned n = (unsigned)src.cloud.n_points;
         // the staging buffer is reused per source: order the copy after the previous kernel (same stream)
-        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, src.cloud.data, (size_t)n * src.cloud.point_step,
-                                          cudaMemcpyHostToDevice, s));
+        const unsigned char* raw = nullptr;
+        PLC_TRY(stage_bytes(ctx, src.cloud.data, (size_t)n * src.cloud.point_step, &raw));
         const bool aligned = ((src.cloud.point_step | src.cloud.off_x | src.cloud.off_y | src.cloud.off_z) & 3u) == 0;
         const unsigned rgba = 0xff000000u | ((unsigned)src.r << 16) | ((unsigned)src.g << 8) | (unsigned)src.b;
         const bool want_own = out_each && out_each[i];
         ctx->timer.begin(s);
-        k_transform_colour<<<(n + 255) / 256, 256, 0, s>>>(ctx->upload.as<unsigned char>(), n, src.cloud.point_step,
+        k_transform_colour<<<(n + 255) / 256, 256, 0, s>>>(raw, n, src.cloud.point_step,
                                                            src.cloud.off_x, src.cloud.off_y, src.cloud.off_z, aligned,
                                                            make_affine(src.t, src.q), rgba, merged + at * 2,
                                                            want_own ? each + at * 2 : nullptr);
         ctx->launches += 1;
         ctx->timer.end(s);
         if (want_own)
-            PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_each[i], each + at * 2, (size_t)n * 32, cudaMemcpyDeviceToHost, s));
+            PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_each[i], each + at * 2, (size_t)n * 32, cudaMemcpyDefault, s));
         if (n_each) n_each[i] = n;
         at += n;
     }
     PLC_CUDA_TRY(ctx, cudaGetLastError());
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_merged, merged, total * 32, cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out_merged, merged, total * 32, cudaMemcpyDefault, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     ctx->times.merge_ms = ctx->timer.total_ms();
     *n_out = total;

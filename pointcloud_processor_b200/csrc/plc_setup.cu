@@ -338,7 +338,7 @@ extern "C" plc_status plc_vl_compute_normals(plc_ctx* ctx, const plc_cloud_view*
     ctx->timer.end(s);
     ctx->launches += 2;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(normals_out, ctx->su_normals.ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(normals_out, ctx->su_normals.ptr, 3 * n * sizeof(float), cudaMemcpyDefault, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     ctx->times.normals_ms = ctx->timer.total_ms();
     return PLC_OK;
@@ -403,14 +403,14 @@ extern "C" plc_status plc_vl_generate_cells(plc_ctx* ctx, const plc_cloud_view* 
     ctx->launches += 1;
     if (normals) {
         PLC_CUDA_TRY(ctx, ctx->su_normals.reserve(3 * n * sizeof(float)));
-        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->su_normals.ptr, normals, 3 * n * sizeof(float), cudaMemcpyHostToDevice, s));
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->su_normals.ptr, normals, 3 * n * sizeof(float), cudaMemcpyDefault, s));
         k_cell_normals<<<blocks_for(total * 32, 256), 256, 0, s>>>(G, ctx->su_normals.as<float>(), (unsigned)total,
                                                                   radius_sq_f32(normal_radius), widened(normal_radius), cells);
         ctx->launches += 1;
     }
     ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out, cells, total * sizeof(plc_cell), cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out, cells, total * sizeof(plc_cell), cudaMemcpyDefault, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     ctx->times.cells_ms = ctx->timer.total_ms();
     return PLC_OK;
@@ -495,7 +495,7 @@ extern "C" plc_status plc_vl_generate_candidates(plc_ctx* ctx, const plc_cloud_v
     ctx->timer.end(s);
     ctx->launches += 1;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out, packed, total * sizeof(plc_pose), cudaMemcpyDeviceToHost, s));
+    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out, packed, total * sizeof(plc_pose), cudaMemcpyDefault, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     ctx->times.candidates_ms = ctx->timer.total_ms();
     return PLC_OK;

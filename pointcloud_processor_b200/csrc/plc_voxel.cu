@@ -233,16 +233,16 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
     if (cloud->n_points == 0) return PLC_OK;
     if (cloud->n_points > 0xfffffff0ull) return PLC_E_INVALID_ARG;
     size_t bytes = (size_t)cloud->n_points * cloud->point_step;
-    PLC_CUDA_TRY(ctx, ctx->upload.reserve(bytes));
     PLC_CUDA_TRY(ctx, ix.raw.reserve((size_t)cloud->n_points * sizeof(float4)));
     PLC_CUDA_TRY(ctx, ctx->scratch.reserve(4096));
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, cloud->data, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    const unsigned char* raw = nullptr;
+    PLC_TRY(stage_bytes(ctx, cloud->data, bytes, &raw));
     ExtractState* st = ctx->scratch.as<ExtractState>();
     ctx->timer.begin(ctx->stream);
     k_extract_init<<<1, 1, 0, ctx->stream>>>(st);
     bool aligned = ((cloud->point_step | cloud->off_x | cloud->off_y | cloud->off_z) & 3u) == 0;
     unsigned blocks = (unsigned)((cloud->n_points + 255) / 256);
-    k_extract<<<blocks, 256, 0, ctx->stream>>>(ctx->upload.as<unsigned char>(), cloud->n_points, cloud->point_step,
+    k_extract<<<blocks, 256, 0, ctx->stream>>>(raw, cloud->n_points, cloud->point_step,
                                                cloud->off_x, cloud->off_y, cloud->off_z, aligned,
                                                ix.raw.as<float4>(), st);
     ctx->launches += 2;

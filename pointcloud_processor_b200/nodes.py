@@ -219,3 +219,99 @@ def run_launch_graph(ctx: Context, inp, leaf: float = 0.2, num_candidates: int =
     out.update(occupancy_grid=grid, occupancy_info=ginfo)
     out["device_ms"] = times
     return out
+
+
+def run_launch_graph_resident(ctx: Context, inp, leaf: float = 0.2, num_candidates: int = 100, grid_resolution: float = 0.1,
+                              vertical_layers: int = 10, sensor_height: float = 1.1, search_radius: float = 3.0,
+                              excavation: A.ExcavationParams | None = None, robot_base_xy=None, download: bool = False,
+                              **sweep_kw):
+    """run_launch_graph with every cloud between the stages left in HBM: the two scans come from the
+    host (they are sensor input), the evaluation cells, the poses and the results go to the host (the node needs
+    them there); filtered scans, merged cloud, excavated terrain, excavation area and normals only ever exist in
+    device buffers (plc_dev_alloc) that the next stage reads in place.  `download=True` also copies those
+    intermediate clouds back (after the timed part) so that tests can compare them."""
+    import time
+    from .context import DevBuffer
+    from .scenes import fixed_pose, ROBOT_BASE
+    L = A.lib()
+    prm = excavation if excavation is not None else A.excavation_params()
+    chk = ctx._check
+    out, n = {}, {}
+    t0 = time.perf_counter()
+    # pointcloud_filter x2
+    filt = {}
+    for name, scan in (("robot", inp.robot_scan), ("zx120", inp.zx120_scan)):
+        v = A.cloud_view(scan)
+        filt[name] = DevBuffer(ctx, max(int(v.n_points), 1) * 16)
+        cnt = C.c_uint64(0)
+        chk(L.plc_filter_scan(ctx._h, C.byref(v), 15.0, 10.0, 10.0, leaf, filt[name].ptr, int(v.n_points), C.byref(cnt)), "plc_filter_scan")
+        n[name] = cnt.value
+    # pointcloud_merger
+    ins = []
+    for name, tf in (("robot", inp.robot_tf), ("zx120", inp.zx120_tf)):
+        m = A.MergerInput()
+        m.cloud = filt[name].view(n[name], 16)
+        m.has_cloud = m.has_transform = 1
+        m.t[:] = list(map(float, tf[0]))
+        m.q[:] = list(map(float, tf[1]))
+        ins.append(m)
+    n_m = n["robot"] + n["zx120"]
+    merged, own_r, own_b = DevBuffer(ctx, max(n_m, 1) * 32), DevBuffer(ctx, max(n["robot"], 1) * 32), DevBuffer(ctx, max(n["zx120"], 1) * 32)
+    c0, c1, c2 = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+    chk(L.plc_merge_clouds(ctx._h, C.byref(ins[0]), C.byref(ins[1]), merged.ptr, n_m, C.byref(c0), own_r.ptr, n["robot"], C.byref(c1),
+                           own_b.ptr, n["zx120"], C.byref(c2)), "plc_merge_clouds")
+    n["merged"] = c0.value
+    # excavated_surface_generator
+    ns, na = A.excavation_counts(prm)
+    terrain, area = DevBuffer(ctx, (n["merged"] + ns) * 32), DevBuffer(ctx, max(na, 1) * 32)
+    nt, nar = C.c_uint64(0), C.c_uint64(0)
+    info = A.ExcavationInfo()
+    base_t, base_q = np.zeros(3), np.array([0.0, 0.0, 0.0, 1.0])
+    vm = merged.view(n["merged"], 32)
+    chk(L.plc_excavate(ctx._h, C.byref(vm), 16, base_t.ctypes.data, base_q.ctypes.data, C.byref(prm), terrain.ptr,
+                       n["merged"] + ns, C.byref(nt), area.ptr, na, C.byref(nar), C.byref(info)), "plc_excavate")
+    n["terrain"], n["area"] = nt.value, nar.value
+    # virtual_lidar: normals and cells from the area cloud, indices from the terrain and the zx120 scan, poses, sweep
+    va, vt = area.view(n["area"], 32), terrain.view(n["terrain"], 32)
+    normals = DevBuffer(ctx, max(n["area"], 1) * 12)
+    chk(L.plc_vl_compute_normals(ctx._h, C.byref(va), 1.5, normals.ptr), "plc_vl_compute_normals")
+    b = A.GridBounds()
+    cnt = C.c_uint64(0)
+    st = L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, None, 0, C.byref(cnt), C.byref(b))
+    if st not in (A.PLC_OK, A.PLC_E_CAPACITY):
+        chk(st, "plc_vl_generate_cells")
+    cells = np.zeros(cnt.value, A.CELL_DTYPE)
+    if cnt.value:
+        chk(L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, cells.ctypes.data,
+                                    cells.size, C.byref(cnt), C.byref(b)), "plc_vl_generate_cells")
+    chk(L.plc_vl_set_terrain(ctx._h, C.byref(vt)), "plc_vl_set_terrain")
+    ctx.set_cells(cells)
+    vo = filt["zx120"].view(n["zx120"], 16)
+    chk(L.plc_vl_set_observed(ctx._h, C.byref(vo)), "plc_vl_set_observed")
+    fixed = fixed_pose()
+    cands = ctx.generate_candidates(None, b, fixed, num_candidates, search_radius, sensor_height)
+    out["sweep"] = ctx.sweep(A.default_params(), fixed, cands, **sweep_kw)
+    # calc_drivable_area
+    rxy = robot_base_xy if robot_base_xy is not None else ROBOT_BASE["xyz"][:2]
+    dprm = A.DrivableParams()
+    L.plc_drivable_params_default(C.byref(dprm))
+    dinfo = A.DrivableInfo()
+    w, h = int(dprm.map_width / dprm.grid_resolution), int(dprm.map_height / dprm.grid_resolution)
+    grid = np.zeros(max(w * h, 1), np.int8)
+    vr = filt["robot"].view(n["robot"], 16)
+    t_r, q_r = np.ascontiguousarray(inp.robot_tf[0], np.float64), np.ascontiguousarray(inp.robot_tf[1], np.float64)
+    chk(L.plc_drivable_area(ctx._h, C.byref(vr), t_r.ctypes.data, q_r.ctypes.data, rxy[0], rxy[1], rxy[0], rxy[1], C.byref(dprm),
+                            grid.ctypes.data, grid.size, C.byref(dinfo)), "plc_drivable_area")
+    out["wall_ms"] = (time.perf_counter() - t0) * 1e3
+    out.update(cells=cells, bounds=b, candidates=cands, fixed=fixed, excavation_info=info, counts=dict(n),
+               occupancy_grid=grid[: dinfo.n_cells].reshape(dinfo.height, dinfo.width) if dinfo.published else None)
+    if download:
+        out["robot_filtered"] = filt["robot"].download(n["robot"] * 16, np.float32).reshape(-1, 4)
+        out["zx120_filtered"] = filt["zx120"].download(n["zx120"] * 16, np.float32).reshape(-1, 4)
+        out["merged"] = merged.download(n["merged"] * 32).reshape(-1, 32)
+        out["terrain"] = terrain.download(n["terrain"] * 32).reshape(-1, 32)
+        out["area"] = area.download(n["area"] * 32).reshape(-1, 32)
+        out["normals"] = normals.download(n["area"] * 12, np.float32).reshape(-1, 3)
+    for buf in (*filt.values(), merged, own_r, own_b, terrain, area, normals):
+        buf.free()
+    return out

@@ -6,7 +6,7 @@ import pytest
 
 from oracle import binding as O
 from pointcloud_processor_b200 import Context, _abi as A, scenes
-from pointcloud_processor_b200.nodes import run_launch_graph
+from pointcloud_processor_b200.nodes import run_launch_graph, run_launch_graph_resident
 from test_excavate_gpu import assert_clouds_match
 from test_sweep_gpu import assert_same_optimum
 
@@ -93,3 +93,22 @@ def test_launch_graph_full_size(ctx):
     n = np.stack([got["cells"]["nx"], got["cells"]["ny"], got["cells"]["nz"]], 1).astype(np.float64)
     assert np.allclose(np.linalg.norm(n, axis=1), 1.0, atol=1e-6)
     print({k: round(v, 3) for k, v in got["device_ms"].items()})
+
+
+@pytest.mark.parametrize("n_scan,kw", [(150_000, dict(num_candidates=64)),
+                                       (1_000_000, dict(num_candidates=256, grid_resolution=0.05, vertical_layers=12))])
+def test_resident_graph_equals_host_buffer_graph(ctx, n_scan, kw):
+    """with every intermediate cloud left in device buffers (read in place by the next stage) the graph
+    produces the same bytes as with host buffers between the stages."""
+    inp = scenes.pipeline_inputs(n_scan=n_scan, sweep="tiny")
+    host = run_launch_graph(ctx, inp, mask=True, **kw)
+    dev = run_launch_graph_resident(ctx, inp, download=True, mask=True, **kw)
+    for k in ("robot_filtered", "zx120_filtered", "merged", "terrain", "area"):
+        assert np.array_equal(np.ascontiguousarray(host[k]).view(np.uint8).reshape(-1), dev[k].view(np.uint8).reshape(-1)), k
+    assert np.array_equal(host["normals"].view(np.uint32), dev["normals"].view(np.uint32))
+    assert np.array_equal(host["cells"].view(np.uint8), dev["cells"].view(np.uint8))
+    assert np.array_equal(host["candidates"].view(np.uint8), dev["candidates"].view(np.uint8))
+    assert np.array_equal(host["sweep"].mask, dev["sweep"].mask) and host["sweep"].best_index == dev["sweep"].best_index
+    assert np.array_equal(host["sweep"].scores, dev["sweep"].scores)
+    assert np.array_equal(host["occupancy_grid"], dev["occupancy_grid"])
+    print(n_scan, "resident graph wall ms", round(dev["wall_ms"], 2), dev["counts"])
