@@ -469,6 +469,33 @@ def measure_feeders(ctx, scene, peak, reps: int = 5) -> dict:
         O.drivable_area(filtered[0], rt, rq, rxy, rxy)
         r["cpu_port_ms"] = (time.perf_counter() - t0) * 1e3
     out["drivable_area"] = r
+    out["launch_graph"] = measure_launch_graph(ctx)
+    return out
+
+
+def measure_launch_graph(ctx, reps: int = 5) -> dict:
+    """The whole dataflow of launch/start.launch.xml for one scan pair (two 1 M-point scans): wall time through the
+    C ABI with host buffers between the stages, and with every intermediate cloud left in device buffers that the
+    next stage reads in place.  leaf 0.2 is the node's default (a few thousand points after the
+    voxel filter); leaf 0.03 keeps ~100 k points per scan and shows what the hand-over costs when clouds are dense."""
+    from pointcloud_processor_b200 import scenes
+    from pointcloud_processor_b200.nodes import run_launch_graph, run_launch_graph_resident
+    inp = scenes.pipeline_inputs(n_scan=1_000_000, sweep="tiny")
+    out = {"config": "2 x 1M-point scans -> filter -> merger -> generator -> normals/cells/poses (32x32) -> sweep, drivable grid"}
+    for leaf in (0.2, 0.03):
+        kw = dict(leaf=leaf, num_candidates=32 * 32, grid_resolution=0.05, vertical_layers=20)
+        walls = {"host_buffers": [], "device_resident": []}
+        counts = None
+        for _ in range(reps + 1):          # the first round warms allocations up
+            t0 = time.perf_counter()
+            run_launch_graph(ctx, inp, **kw)
+            walls["host_buffers"].append((time.perf_counter() - t0) * 1e3)
+            r = run_launch_graph_resident(ctx, inp, **kw)
+            walls["device_resident"].append(r["wall_ms"])
+            counts = r["counts"]
+        out[f"leaf_{leaf}"] = {"wall_ms_host_buffers": float(np.median(walls["host_buffers"][1:])),
+                               "wall_ms_device_resident": float(np.median(walls["device_resident"][1:])),
+                               "points": {k: int(v) for k, v in counts.items()}}
     return out
 
 

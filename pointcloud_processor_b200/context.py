@@ -50,6 +50,8 @@ class Context:
         self._keep = []
 
     def close(self):
+        for buf in self.__dict__.pop("_graph_pool", {}).values():
+            buf.free()
         if getattr(self, "_h", None):
             self._L.plc_ctx_destroy(self._h)
             self._h = None

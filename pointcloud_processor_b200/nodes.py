@@ -231,12 +231,24 @@ def run_launch_graph_resident(ctx: Context, inp, leaf: float = 0.2, num_candidat
     device buffers (plc_dev_alloc) that the next stage reads in place.  `download=True` also copies those
     intermediate clouds back (after the timed part) so that tests can compare them."""
     import time
-    from .context import DevBuffer
+    from .context import DevBuffer as _DevBuffer
     from .scenes import fixed_pose, ROBOT_BASE
     L = A.lib()
     prm = excavation if excavation is not None else A.excavation_params()
     chk = ctx._check
     out, n = {}, {}
+    # a node keeps its device buffers from one message to the next: grow-only pool on the context
+    pool = ctx.__dict__.setdefault("_graph_pool", {})
+
+    def DevBuffer(_ctx, nbytes, _name=[0]):
+        _name[0] += 1
+        key = _name[0]
+        buf = pool.get(key)
+        if buf is None or buf.nbytes < nbytes:
+            if buf is not None:
+                buf.free()
+            buf = pool[key] = _DevBuffer(ctx, int(nbytes * 1.25) + 256)
+        return buf
     t0 = time.perf_counter()
     # pointcloud_filter x2
     filt = {}
@@ -312,6 +324,4 @@ def run_launch_graph_resident(ctx: Context, inp, leaf: float = 0.2, num_candidat
         out["terrain"] = terrain.download(n["terrain"] * 32).reshape(-1, 32)
         out["area"] = area.download(n["area"] * 32).reshape(-1, 32)
         out["normals"] = normals.download(n["area"] * 12, np.float32).reshape(-1, 3)
-    for buf in (*filt.values(), merged, own_r, own_b, terrain, area, normals):
-        buf.free()
     return out
