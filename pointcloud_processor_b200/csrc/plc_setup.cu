@@ -88,8 +88,19 @@ k_emit_cells(Lattice L, unsigned n_lattice, const uint32_t* __restrict__ flag, c
 
 // computeCellSurfaceNormal (:301-340): sum of the finite normals of the area points within normal_radius of the
 // cell centre, normalised; one warp per cell, lanes stride over each row of buckets
+// per-point normals brought into bucket order once (w = 1 where all three components are finite, :320-324), so that
+// k_cell_normals reads them next to the points instead of gathering by index for every cell
 __global__ void __launch_bounds__(256)
-k_cell_normals(BucketGrid G, const float* __restrict__ normals, unsigned n_cells, float r2f, double reach,
+k_normals_in_bucket_order(BucketGrid G, const float* __restrict__ normals, unsigned n_finite, float4* __restrict__ out) {
+    unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_finite) return;
+    const float* nv = normals + 3 * (size_t)__float_as_uint(G.pts[p].w);
+    const float a = nv[0], b = nv[1], c = nv[2];
+    out[p] = make_float4(a, b, c, (isfinite(a) && isfinite(b) && isfinite(c)) ? 1.f : 0.f);
+}
+
+__global__ void __launch_bounds__(256)
+k_cell_normals(BucketGrid G, const float4* __restrict__ normals, unsigned n_cells, float r2f, double reach,
                plc_cell* __restrict__ cells) {
     const unsigned w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -106,12 +117,11 @@ k_cell_normals(BucketGrid G, const float* __restrict__ normals, unsigned n_cells
                 for (uint32_t p = __ldg(&G.start[row + R.x0]) + lane; p < e; p += 32) {
                     const float4 v = __ldg(&G.pts[p]);
                     if (dist2(qx, qy, qz, v.x, v.y, v.z) < r2f) {
-                        const float* nv = normals + 3 * (size_t)__float_as_uint(v.w);
-                        const float a = __ldg(nv), b = __ldg(nv + 1), c = __ldg(nv + 2);
-                        if (isfinite(a) && isfinite(b) && isfinite(c)) {                 // :320-324
-                            sx = __dadd_rn(sx, (double)a);
-                            sy = __dadd_rn(sy, (double)b);
-                            sz = __dadd_rn(sz, (double)c);
+                        const float4 nv = __ldg(&normals[p]);
+                        if (nv.w != 0.f) {                                               // :320-324
+                            sx = __dadd_rn(sx, (double)nv.x);
+                            sy = __dadd_rn(sy, (double)nv.y);
+                            sz = __dadd_rn(sz, (double)nv.z);
                             ++used;
                         }
                     }
@@ -401,14 +411,24 @@ extern "C" plc_status plc_vl_generate_cells(plc_ctx* ctx, const plc_cloud_view* 
     ctx->timer.begin(s);
     k_emit_cells<<<blocks_for(n_lat, 256), 256, 0, s>>>(L, (unsigned)n_lat, flag, slot, cells);
     ctx->launches += 1;
-    if (normals) {
-        PLC_CUDA_TRY(ctx, ctx->su_normals.reserve(3 * n * sizeof(float)));
-        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->su_normals.ptr, normals, 3 * n * sizeof(float), cudaMemcpyDefault, s));
-        k_cell_normals<<<blocks_for(total * 32, 256), 256, 0, s>>>(G, ctx->su_normals.as<float>(), (unsigned)total,
-                                                                  radius_sq_f32(normal_radius), widened(normal_radius), cells);
-        ctx->launches += 1;
-    }
     ctx->timer.end(s);
+    if (normals) {
+        // the near test wanted buckets of 1.5 res; a ball of normal_radius over those would walk thousands of empty
+        // rows per cell, so the cloud is bucketed again at a quarter of the normal radius (the first grid is done with)
+        PLC_TRY(build_buckets(ctx, ctx->su_pts.as<float4>(), n, b, std::max(normal_radius * 0.25, std::max(near_radius, 1e-3)), &G));
+        uint32_t n_finite = 0;
+        PLC_TRY(finite_count(ctx, G, &n_finite));
+        PLC_CUDA_TRY(ctx, ctx->su_normals.reserve(3 * n * sizeof(float) + 16 + (size_t)(n + 1) * sizeof(float4)));
+        float* raw_normals = ctx->su_normals.as<float>();
+        float4* ordered = reinterpret_cast<float4*>(raw_normals + ((3 * n + 3) & ~(size_t)3));
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(raw_normals, normals, 3 * n * sizeof(float), cudaMemcpyDefault, s));
+        ctx->timer.begin(s);
+        if (n_finite) k_normals_in_bucket_order<<<blocks_for(n_finite, 256), 256, 0, s>>>(G, raw_normals, n_finite, ordered);
+        k_cell_normals<<<blocks_for(total * 32, 256), 256, 0, s>>>(G, ordered, (unsigned)total, radius_sq_f32(normal_radius),
+                                                                  widened(normal_radius), cells);
+        ctx->timer.end(s);
+        ctx->launches += 2;
+    }
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out, cells, total * sizeof(plc_cell), cudaMemcpyDefault, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
