@@ -319,8 +319,12 @@ plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_src,
 
 /* ---------------------------------------------------------------- excavated_surface_generator -- */
 
-/* Parameters of the node (excavated_surface_generator.cpp:28-47); the _L and _square variants are the same
- * algorithm with l_shape_enabled fixed. */
+/* Parameters of the node (excavated_surface_generator.cpp:28-47).  Of the two sources the reference keeps beside it
+ * without building them (CMakeLists.txt:99 compiles only excavated_surface_generator.cpp):
+ * excavated_surface_generator_L.cpp is this algorithm except that the wall points of /excavation_area stand
+ * vertically above the edge (no slope offset, its :399-400) — area_walls_vertical = 1 — and its default offsets are
+ * (5.0, 0.0); excavated_surface_genaerator_square.cpp is an earlier rectangle-only formulation with another lattice
+ * enumeration and is not restated. */
 typedef struct plc_excavation_params {
     double depth;                  /* excavation.depth = 1.0 */
     double slope_angle_deg;        /* excavation.slope_angle = 75.0 */
@@ -330,7 +334,7 @@ typedef struct plc_excavation_params {
     double arm1_length, arm1_width, arm2_length, arm2_width;   /* 2.0, 1.2, 2.0, 1.2 */
     double width, length;          /* rectangle mode: 1.2, 1.8 */
     int32_t l_shape_enabled;       /* excavation.l_shape_enabled = true */
-    int32_t reserved;
+    int32_t area_walls_vertical;   /* 0: the built node (:410-444); 1: excavated_surface_generator_L.cpp:391-407 */
 } plc_excavation_params;
 void plc_excavation_params_default(plc_excavation_params* p);
 

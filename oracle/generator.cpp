@@ -11,7 +11,8 @@
 //   generateExcavationArea    350-455
 //   processExcavation         457-481
 //   generateExcavatedSurface  487-584
-// The _L and _square variants are this algorithm with the shape fixed.
+// excavated_surface_generator_L.cpp (not built upstream) is this algorithm with vertical wall points in the area
+// cloud (its :391-407; plc_excavation_params::area_walls_vertical); the _square file is another formulation, not restated.
 // Parity unpinned: the reference has no tests or fixtures for this node.  KD-tree result order decides
 // the order of the double sum in getTerrainHeight (restated as ascending distance, ties by index) and which of two
 // equidistant points nearestKSearch returns (restated as the lower index).
@@ -186,7 +187,9 @@ void excavation_area(std::vector<Rec>& cloud, const double center[3], double yaw
                     const double xg = center[0] + x_slope * std::cos(yaw) - y_slope * std::sin(yaw);
                     const double yg = center[1] + x_slope * std::sin(yaw) + y_slope * std::cos(yaw);
                     const double z_local = local_terrain_height - P.depth + k * pd;
-                    cloud.push_back(make_rec(xg, yg, z_local, 200, 200, 0));
+                    // excavated_surface_generator_L.cpp:399-400 keeps the wall points straight above the edge
+                    if (P.area_walls_vertical) cloud.push_back(make_rec(x_global, y_global, z_local, 200, 200, 0));
+                    else cloud.push_back(make_rec(xg, yg, z_local, 200, 200, 0));
                 }
             }
         }

@@ -110,7 +110,7 @@ class ExcavationParams(C.Structure):  # plc_excavation_params
                 ("point_density", C.c_double), ("terrain_search_radius", C.c_double),
                 ("arm1_length", C.c_double), ("arm1_width", C.c_double), ("arm2_length", C.c_double),
                 ("arm2_width", C.c_double), ("width", C.c_double), ("length", C.c_double),
-                ("l_shape_enabled", C.c_int32), ("reserved", C.c_int32)]
+                ("l_shape_enabled", C.c_int32), ("area_walls_vertical", C.c_int32)]
 
 
 class ExcavationInfo(C.Structure):    # plc_excavation_info

@@ -8,7 +8,8 @@
 //   processExcavation         457-481  -> k_carve_prefilter, k_carve_heights, scan, k_emit_kept
 //   generateExcavationArea    350-455  -> k_plan_lattice, k_lattice_heights, k_emit_area
 //   generateExcavatedSurface  487-584  -> k_plan_lattice, k_lattice_heights, k_emit_bottoms, k_emit_slopes
-// (the _L and _square variants are the same algorithm with the shape fixed).
+// (excavated_surface_generator_L.cpp, not built upstream, differs only in the area cloud's wall points: see
+// plc_excavation_params::area_walls_vertical.)
 //
 // Parity against the CPU restatement: the kept set, every generated x/y and the output order are bit-identical;
 // a height is a mean of hundreds of float z values summed in double — upstream in KD-tree result order, here in a
@@ -37,6 +38,7 @@ struct ExcavDev {
     int n_x, n_y, n_depth, n_slope;
     float r2f;
     int have_points;                               // the cloud is not empty (:185)
+    int area_walls_vertical;                       // excavated_surface_generator_L.cpp: wall points of the area cloud without the slope offset
     unsigned n_finite;
 };
 
@@ -282,8 +284,8 @@ k_emit_area(ExcavDev E, unsigned n_entries, LatticePlan P, const double* __restr
         const double offset = __dmul_rn(E.slope_offset, ratio);
         // offset_x = +offset, -offset or 0.0 (:417-430): the sign is exact
         const double xs = __dadd_rn(xl, sx * offset), ys = __dadd_rn(yl, sy * offset);
-        double xgs, ygs;
-        to_global(E, xs, ys, xgs, ygs);
+        double xgs = xg, ygs = yg;                                                                 // _L variant: straight above the edge
+        if (!E.area_walls_vertical) to_global(E, xs, ys, xgs, ygs);
         const double z = __dadd_rn(__dsub_rn(h, E.depth), __dmul_rn((double)k, E.pd));             // :437
         o[k] = make_rec(xgs, ygs, z, 0xffc8c800u);                                                 // 200,200,0
     }
@@ -408,7 +410,7 @@ extern "C" void plc_excavation_params_default(plc_excavation_params* p) {
     p->width = 1.2;
     p->length = 1.8;
     p->l_shape_enabled = 1;
-    p->reserved = 0;
+    p->area_walls_vertical = 0;
 }
 
 extern "C" plc_status plc_excavation_counts(const plc_excavation_params* prm, uint64_t* n_surface, uint64_t* n_area) {
@@ -473,6 +475,7 @@ extern "C" plc_status plc_excavate(plc_ctx* ctx, const plc_cloud_view* matched, 
     E.r2f = static_cast<float>(prm->terrain_search_radius * prm->terrain_search_radius);
     E.reach = widened(prm->terrain_search_radius);
     E.have_points = n ? 1 : 0;
+    E.area_walls_vertical = prm->area_walls_vertical ? 1 : 0;
 
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;

@@ -73,6 +73,8 @@ def run_both(ctx, rec, colours, t, q, prm):
     ("rectangle", dict(l_shape_enabled=0), 60_000, (0.0, 0.0, 0.0), 0.0),
     ("L turned", dict(point_density=0.08, terrain_search_radius=0.3, depth=0.7, slope_angle_deg=60.0), 40_000, (1.5, -0.5, 0.2), 0.7),
     ("rectangle turned", dict(l_shape_enabled=0, length=2.4, width=0.9, offset_x=3.0, offset_y=-1.0), 40_000, (-0.5, 1.0, 0.0), -2.2),
+    # excavated_surface_generator_L.cpp: wall points of the area cloud straight above the edge, offsets (5, 0)
+    ("L file variant", dict(area_walls_vertical=1, offset_x=5.0, offset_y=0.0), 40_000, (0.0, 0.0, 0.0), 0.4),
 ])
 def test_generator_matches_oracle(ctx, name, kw, n, t, yaw):
     prm = A.excavation_params(**kw)
