@@ -123,3 +123,28 @@ def test_pca_normals_close_to_oracle_and_analytic():
 def test_empty_area_gives_no_cells():
     cells, _ = ctxmod.host_generate_cells(np.zeros((0, 3), np.float32), None, 0.1, 10, 1.5)
     assert cells.size == 0
+
+
+def test_node_stage_parameter_presets_match_reference_defaults():
+    g = A.excavation_params()          # excavated_surface_generator.cpp:28-47
+    assert (g.depth, g.slope_angle_deg, g.offset_x, g.offset_y, g.point_density, g.terrain_search_radius) == (1.0, 75.0, 4.0, 1.0, 0.05, 0.5)
+    assert (g.arm1_length, g.arm1_width, g.arm2_length, g.arm2_width, g.width, g.length) == (2.0, 1.2, 2.0, 1.2, 1.2, 1.8)
+    assert g.l_shape_enabled == 1 and g.area_walls_vertical == 0
+    d = A.DrivableParams()             # calc_drivable_area.cpp:21-26
+    A.lib().plc_drivable_params_default(C.byref(d))
+    assert (d.grid_resolution, d.map_width, d.map_height, d.max_gradient, d.min_points_per_cell, d.start_clear_radius) == \
+           (1.0, 100.0, 100.0, 0.3, 10, 3.0)
+    assert C.sizeof(A.ExcavationParams) == 12 * 8 + 8 and C.sizeof(A.DrivableParams) == 5 * 8 + 8
+    assert C.sizeof(A.ExcavationInfo) == 4 * 8 + 3 * 8 and C.sizeof(A.DeviceTimes) == 12 * 4
+
+
+def test_generator_sizing_function():
+    # sizes depend on the parameters only (generateExcavatedSurface :487-584, generateExcavationArea :350-455)
+    assert A.excavation_counts(A.excavation_params()) == (3115, 5575)                 # L: 1 680 bottoms + 205 edge points x 7 / x 19
+    assert A.excavation_counts(A.excavation_params(l_shape_enabled=0)) == (1714, 3130)
+    ns, na = A.excavation_counts(A.excavation_params(point_density=0.1))
+    assert 0 < ns < 3115 and 0 < na < 5575
+    for bad in (dict(point_density=0.0), dict(depth=-1.0), dict(slope_angle_deg=float("nan")), dict(slope_angle_deg=120.0),
+                dict(point_density=1e-6)):
+        with pytest.raises(A.PlcError):
+            A.excavation_counts(A.excavation_params(**bad))

@@ -112,3 +112,36 @@ def test_resident_graph_equals_host_buffer_graph(ctx, n_scan, kw):
     assert np.array_equal(host["sweep"].scores, dev["sweep"].scores)
     assert np.array_equal(host["occupancy_grid"], dev["occupancy_grid"])
     print(n_scan, "resident graph wall ms", round(dev["wall_ms"], 2), dev["counts"])
+
+
+@pytest.mark.parametrize("resident", [False, True])
+def test_cpp_host_runs_the_same_graph(ctx, tmp_path, resident):
+    """examples/launch_graph.cpp drives the C ABI from C++ (the reference's language) with no Python in between: same
+    scans in, same sizes, optimal pose and score out as nodes.run_launch_graph."""
+    import json
+    import subprocess
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    exe = root / "examples" / "_build" / "launch_graph"
+    if not exe.exists():
+        subprocess.check_call(["make", "-C", str(root / "examples")])
+    inp = scenes.pipeline_inputs(n_scan=150_000, sweep="tiny")
+    inp.robot_scan.astype("<f4").tofile(tmp_path / "robot.f32")
+    inp.zx120_scan.astype("<f4").tofile(tmp_path / "zx120.f32")
+    cmd = [str(exe), "--robot", str(tmp_path / "robot.f32"), "--zx120", str(tmp_path / "zx120.f32"), "--candidates", "64"]
+    out = subprocess.run(cmd + (["--resident"] if resident else []), capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    got = json.loads(out.stdout.strip().splitlines()[-1])
+    ref = run_launch_graph(ctx, inp, num_candidates=64)
+    assert got["resident"] is resident
+    assert got["robot_filtered"] == ref["robot_filtered"].shape[0] and got["zx120_filtered"] == ref["zx120_filtered"].shape[0]
+    assert got["merged"] == ref["merged"].shape[0] and got["terrain"] == ref["terrain"].shape[0] and got["area"] == ref["area"].shape[0]
+    assert got["kept"] == ref["excavation_info"].n_kept
+    assert got["cells"] == ref["cells"].size and got["candidates"] == ref["candidates"].size
+    r = ref["sweep"]
+    assert got["best_index"] == r.best_index and got["samples"] == r.counters["samples"]
+    assert got["best_score"] == pytest.approx(r.best_score, rel=1e-12)
+    b = ref["candidates"][r.best_index]
+    assert got["best_pose"] == [b["x"], b["y"], b["z"]]
+    assert got["grid_occupied"] == int((ref["occupancy_grid"] == 100).sum()) and got["grid_unknown"] == int((ref["occupancy_grid"] == -1).sum())
+    assert got["kernels_launched"] > 50
