@@ -153,6 +153,7 @@ plc_status plc_ctx_sync(plc_ctx* ctx);
  * (plc_vl_set_cells, the candidate list and the result arrays of the sweep are host memory: the node needs them
  * there for its markers and logs.) */
 plc_status plc_dev_alloc(plc_ctx* ctx, uint64_t bytes, void** dev_ptr);
+/* Waits for the context's stream, then frees.  Call it before plc_ctx_destroy(ctx). */
 void plc_dev_free(plc_ctx* ctx, void* dev_ptr);
 plc_status plc_dev_upload(plc_ctx* ctx, void* dev_dst, const void* host_src, uint64_t bytes);
 plc_status plc_dev_download(plc_ctx* ctx, void* host_dst, const void* dev_src, uint64_t bytes);
