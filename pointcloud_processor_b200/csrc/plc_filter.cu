@@ -222,10 +222,10 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     k_filter_state_init<<<1, 1, 0, s>>>(st);
     k_crop_flag<<<blocks1, 256, 0, s>>>(raw, n, in->point_step, in->off_x, in->off_y,
                                         in->off_z, aligned, cb, flag);
-    scan_exclusive_u32(flag, (size_t)n + 1, scan_tmp, s);
+    ctx->launches += scan_exclusive_u32(flag, (size_t)n + 1, scan_tmp, s);
     k_crop_compact<<<(n + 255) / 256, 256, 0, s>>>(raw, n, in->point_step, in->off_x,
                                                    in->off_y, in->off_z, aligned, flag, cropped, st);
-    ctx->launches += 6;
+    ctx->launches += 3;
     ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
 
@@ -288,7 +288,7 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     const uint32_t* skeys = where ? ctx->f_keys2.as<uint32_t>() : ctx->f_keys.as<uint32_t>();
     const uint32_t* svals = where ? ctx->f_vals2.as<uint32_t>() : ctx->f_vals.as<uint32_t>();
     k_heads<<<(m + 1 + 255) / 256, 256, 0, s>>>(skeys, m, flag);
-    scan_exclusive_u32(flag, (size_t)m + 1, scan_tmp, s);
+    ctx->launches += scan_exclusive_u32(flag, (size_t)m + 1, scan_tmp, s);
     // the unsorted key buffer is free again: it holds the segment starts (at most m + 1 entries)
     uint32_t* seg_start = where ? ctx->f_keys.as<uint32_t>() : ctx->f_keys2.as<uint32_t>();
     k_segment_starts<<<(m + 1 + 255) / 256, 256, 0, s>>>(flag, m, seg_start);
@@ -298,7 +298,7 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     const unsigned n_seg = host->total;
     ctx->timer.begin(s);
     k_centroid<<<(n_seg * 32 + 255) / 256, 256, 0, s>>>(svals, seg_start, n_seg, cropped, centroids);
-    ctx->launches += 6;
+    ctx->launches += 3;
     ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     plc_status rc = copy_out(centroids, n_seg);           // synchronises the stream

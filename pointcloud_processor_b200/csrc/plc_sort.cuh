@@ -104,9 +104,9 @@ inline int radix_sort_pairs(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b
         uint32_t* kout = cur ? keys_a : keys_b;
         uint32_t* vout = cur ? vals_a : vals_b;
         k_radix_hist<<<n_tiles, kSortWarps * 32, 0, s>>>(kin, n, shift, table, n_tiles);
-        scan_exclusive_u32(table, (size_t)256 * n_tiles, scan_tmp, s);
+        const int scan_launches = scan_exclusive_u32(table, (size_t)256 * n_tiles, scan_tmp, s);
         k_radix_scatter<<<n_tiles, kSortWarps * 32, 0, s>>>(kin, vin, n, shift, table, n_tiles, kout, vout);
-        if (launches) *launches += 5;
+        if (launches) *launches += 2 + scan_launches;
         cur ^= 1;
     }
     return cur;
