@@ -213,10 +213,14 @@ int main(int argc, char** argv) {
         plc_cloud_view va = area.view(n_a, 32), vt = terrain.view(n_t, 32), vo = f_zx.view(n_fz, 16);
         CHECK(normals.reserve(ctx, resident, n_a * 12));
         CHECK(plc_vl_compute_normals(ctx, &va, 1.5, static_cast<float*>(normals.data())));
-        plc_status st = plc_vl_generate_cells(ctx, &va, static_cast<const float*>(normals.data()), res, layers, 1.5, nullptr, 0, &n_cells, &bounds);
-        if (st != PLC_OK && st != PLC_E_CAPACITY) CHECK(st);
-        cells.resize(n_cells);
-        if (n_cells) CHECK(plc_vl_generate_cells(ctx, &va, static_cast<const float*>(normals.data()), res, layers, 1.5, cells.data(), n_cells, &n_cells, &bounds));
+        // room for the last count (64 Ki cells on the first pass): one call when it fits, else the count comes back
+        if (cells.size() < (size_t(1) << 16)) cells.resize(size_t(1) << 16);
+        plc_status st = plc_vl_generate_cells(ctx, &va, static_cast<const float*>(normals.data()), res, layers, 1.5, cells.data(), cells.size(), &n_cells, &bounds);
+        if (st == PLC_E_CAPACITY) {
+            cells.resize(n_cells);
+            st = plc_vl_generate_cells(ctx, &va, static_cast<const float*>(normals.data()), res, layers, 1.5, cells.data(), n_cells, &n_cells, &bounds);
+        }
+        CHECK(st);
         CHECK(plc_vl_set_terrain(ctx, &vt));
         CHECK(plc_vl_set_cells(ctx, cells.data(), n_cells));
         CHECK(plc_vl_set_observed(ctx, &vo));

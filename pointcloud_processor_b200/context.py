@@ -287,15 +287,18 @@ class Context:
             normals = np.ascontiguousarray(normals, np.float32)
         b = A.GridBounds()
         n = C.c_uint64(0)
+        # first try with room for the last count (or 64 Ki cells): one pass when it fits, else the count comes back
+        # with PLC_E_CAPACITY and the second call is exact
+        cells = np.zeros(max(getattr(self, "_cells_guess", 0), 1 << 16), A.CELL_DTYPE)
         st = self._L.plc_vl_generate_cells(self._h, C.byref(v), A.ptr(normals), grid_resolution, vertical_layers,
-                                           normal_search_radius, None, 0, C.byref(n), C.byref(b))
-        if st not in (A.PLC_OK, A.PLC_E_CAPACITY):
-            self._check(st, "plc_vl_generate_cells")
-        cells = np.zeros(n.value, A.CELL_DTYPE)
-        if n.value:
+                                           normal_search_radius, cells.ctypes.data, cells.size, C.byref(n), C.byref(b))
+        if st == A.PLC_E_CAPACITY:
+            cells = np.zeros(n.value, A.CELL_DTYPE)
             st = self._L.plc_vl_generate_cells(self._h, C.byref(v), A.ptr(normals), grid_resolution, vertical_layers,
                                                normal_search_radius, cells.ctypes.data, cells.size, C.byref(n), C.byref(b))
-            self._check(st, "plc_vl_generate_cells")
+        self._check(st, "plc_vl_generate_cells")
+        self._cells_guess = int(n.value)
+        cells = cells[: n.value].copy() if n.value != cells.size else cells
         return cells, b
 
     def generate_candidates(self, terrain: np.ndarray | None, bounds: A.GridBounds, fixed: np.ndarray,

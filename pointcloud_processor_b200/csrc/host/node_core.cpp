@@ -6,6 +6,7 @@
 //   plc_vlnode_*      SimplifiedDualLidarOptimizer, /root/reference/src/virtual_lidar.cpp:60-548
 //   plc_filter_scan   SimplifiedScanMatcher::processCloudSimple, src/pointcloud_filter.cpp:64-139
 //   plc_merge_clouds  GnssGicpMatcher::processPointClouds, src/pointcloud_merger.cpp:308-394
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -158,15 +159,17 @@ extern "C" plc_status plc_vlnode_excavation_area_callback(plc_vlnode* n, const p
     if (st != PLC_OK) return st;
     uint64_t count = 0;
     plc_grid_bounds b{};
+    // room for the last count (or 64 Ki cells) makes this one pass; a larger lattice reports its count and is redone
+    std::vector<plc_cell> cells(std::max<size_t>(n->cells.size(), size_t(1) << 16));
     st = plc_vl_generate_cells(dev, cloud, normals.data(), n->grid_resolution, n->vertical_layers, // :174
-                               kNormalSearchRadius, nullptr, 0, &count, &b);
-    if (st != PLC_OK && st != PLC_E_CAPACITY) return st;
-    std::vector<plc_cell> cells(count);
-    if (count) {
+                               kNormalSearchRadius, cells.data(), cells.size(), &count, &b);
+    if (st == PLC_E_CAPACITY) {
+        cells.resize(count);
         st = plc_vl_generate_cells(dev, cloud, normals.data(), n->grid_resolution, n->vertical_layers,
                                    kNormalSearchRadius, cells.data(), count, &count, &b);
-        if (st != PLC_OK) return st;
     }
+    if (st != PLC_OK) return st;
+    cells.resize(count);
     n->cells.swap(cells);                     // excavation_grid_3d_.clear() + refill (:239, :278)
     n->flags.assign(n->cells.size(), 0);      // GridCell(): every flag false
     n->bounds = b;

@@ -289,13 +289,16 @@ def run_launch_graph_resident(ctx: Context, inp, leaf: float = 0.2, num_candidat
     chk(L.plc_vl_compute_normals(ctx._h, C.byref(va), 1.5, normals.ptr), "plc_vl_compute_normals")
     b = A.GridBounds()
     cnt = C.c_uint64(0)
-    st = L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, None, 0, C.byref(cnt), C.byref(b))
-    if st not in (A.PLC_OK, A.PLC_E_CAPACITY):
-        chk(st, "plc_vl_generate_cells")
-    cells = np.zeros(cnt.value, A.CELL_DTYPE)
-    if cnt.value:
-        chk(L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, cells.ctypes.data,
-                                    cells.size, C.byref(cnt), C.byref(b)), "plc_vl_generate_cells")
+    cells = np.zeros(max(getattr(ctx, "_cells_guess", 0), 1 << 16), A.CELL_DTYPE)   # one pass when the last count fits
+    st = L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, cells.ctypes.data,
+                                 cells.size, C.byref(cnt), C.byref(b))
+    if st == A.PLC_E_CAPACITY:
+        cells = np.zeros(cnt.value, A.CELL_DTYPE)
+        st = L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, cells.ctypes.data,
+                                     cells.size, C.byref(cnt), C.byref(b))
+    chk(st, "plc_vl_generate_cells")
+    ctx._cells_guess = int(cnt.value)
+    cells = cells[: cnt.value]
     chk(L.plc_vl_set_terrain(ctx._h, C.byref(vt)), "plc_vl_set_terrain")
     ctx.set_cells(cells)
     vo = filt["zx120"].view(n["zx120"], 16)
