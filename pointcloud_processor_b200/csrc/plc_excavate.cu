@@ -383,6 +383,8 @@ bool lattice_of(const plc_excavation_params& P, ExcavDev* E) {
     const double nx = (hi_x - lo_x) / P.point_density, ny = (hi_y - lo_y) / P.point_density;
     const double nd = P.depth / P.point_density, ns = E->slope_offset / P.point_density;
     if (!(nx >= 0 && ny >= 0 && (nx + 2) * (ny + 2) < 6.0e7 && nd < 1e6 && std::fabs(ns) < 1e6)) return false;
+    // the per-entry counts are scanned in 32 bits and the slope kernel runs one warp per (entry, slope step)
+    if (!((nx + 2) * (ny + 2) * (std::fabs(ns) + 2) < 2.0e9 && (nx + 2) * (ny + 2) * (nd + 1) < 2.0e9)) return false;
     E->n_x = (int)nx + 1;                                                             // :368-370, :507-508
     E->n_y = (int)ny + 1;
     E->n_depth = (int)nd;
@@ -538,7 +540,7 @@ extern "C" plc_status plc_excavate(plc_ctx* ctx, const plc_cloud_view* matched, 
         ctx->timer.begin(s);
         if (n_queue) k_carve_heights<<<blocks_for((size_t)n_queue * 32, 256), 256, 0, s>>>(G, E, pts, queue, n_queue, keep);
         ctx->timer.end(s);
-        ctx->launches += 1;
+        ctx->launches += n_queue ? 1 : 0;
         PLC_TRY(scan_flags(ctx, keep, slot, n, &kept));
     }
     const uint64_t terrain_total = kept + bottoms + slopes;
@@ -572,7 +574,7 @@ extern "C" plc_status plc_excavate(plc_ctx* ctx, const plc_cloud_view* matched, 
                                                                                           terrain + kept + bottoms);
     k_one_height<<<1, 32, 0, s>>>(G, E, E.center_x, E.center_y, centre_h);
     ctx->timer.end(s);
-    ctx->launches += 6;
+    ctx->launches += 5 + ((n && kept) ? 1 : 0);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     double* host_h = reinterpret_cast<double*>(static_cast<char*>(ctx->pinned) + 64);
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(host_h, centre_h, sizeof(double), cudaMemcpyDeviceToHost, s));

@@ -346,7 +346,7 @@ extern "C" plc_status plc_vl_compute_normals(plc_ctx* ctx, const plc_cloud_view*
         k_pca_normals<<<blocks_for((size_t)n_finite * 32, 256), 256, 0, s>>>(G, n_finite, radius_sq_f32(radius), widened(radius),
                                                                              ctx->su_normals.as<float>());
     ctx->timer.end(s);
-    ctx->launches += 2;
+    ctx->launches += n_finite ? 2 : 1;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(normals_out, ctx->su_normals.ptr, 3 * n * sizeof(float), cudaMemcpyDefault, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
@@ -427,7 +427,7 @@ extern "C" plc_status plc_vl_generate_cells(plc_ctx* ctx, const plc_cloud_view* 
         k_cell_normals<<<blocks_for(total * 32, 256), 256, 0, s>>>(G, ordered, (unsigned)total, radius_sq_f32(normal_radius),
                                                                   widened(normal_radius), cells);
         ctx->timer.end(s);
-        ctx->launches += 2;
+        ctx->launches += n_finite ? 2 : 1;
     }
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(out, cells, total * sizeof(plc_cell), cudaMemcpyDefault, s));

@@ -145,6 +145,7 @@ def test_generator_sizing_function():
     ns, na = A.excavation_counts(A.excavation_params(point_density=0.1))
     assert 0 < ns < 3115 and 0 < na < 5575
     for bad in (dict(point_density=0.0), dict(depth=-1.0), dict(slope_angle_deg=float("nan")), dict(slope_angle_deg=120.0),
-                dict(point_density=1e-6)):
+                dict(point_density=1e-6),
+                dict(point_density=0.001, slope_angle_deg=0.01)):        # 3 M entries x 5.7 M slope steps: not walkable
         with pytest.raises(A.PlcError):
             A.excavation_counts(A.excavation_params(**bad))
