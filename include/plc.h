@@ -158,6 +158,22 @@ void plc_dev_free(plc_ctx* ctx, void* dev_ptr);
 plc_status plc_dev_upload(plc_ctx* ctx, void* dev_dst, const void* host_src, uint64_t bytes);
 plc_status plc_dev_download(plc_ctx* ctx, void* host_dst, const void* dev_src, uint64_t bytes);
 
+/* The same hand-over between PROCESSES on one GPU (upstream's stages are separate ROS nodes: pointcloud_filter →
+ * pointcloud_merger → excavated_surface_generator → virtual_lidar each publish a PointCloud2 the next one copies):
+ * the producer exports a buffer it got from plc_dev_alloc, sends the 64 opaque bytes over any channel it has (a topic,
+ * a pipe), the consumer imports them and passes the pointer as plc_cloud_view::data like any device pointer.
+ * The producer keeps the buffer alive (and does not rewrite it) until the consumer has released it; every library call
+ * that wrote the buffer has returned, hence finished on the device, before the handle is sent. */
+typedef struct plc_ipc_handle {
+    unsigned char opaque[64];
+} plc_ipc_handle;
+/* dev_ptr: a pointer plc_dev_alloc returned (the start of the allocation), in this process. */
+plc_status plc_dev_export(plc_ctx* ctx, void* dev_ptr, plc_ipc_handle* handle);
+/* Maps a buffer another process exported on the context's device.  PLC_E_INVALID_ARG in the exporting process itself. */
+plc_status plc_dev_import(plc_ctx* ctx, const plc_ipc_handle* handle, void** dev_ptr);
+/* Unmaps an imported buffer (not plc_dev_free: the memory belongs to the exporter). */
+void plc_dev_release(plc_ctx* ctx, void* dev_ptr);
+
 /* ---------------------------------------------------------------- virtual_lidar ------------- */
 
 /* Replaces the KD-tree build of terrainCallback (virtual_lidar.cpp:180-192): voxelises the

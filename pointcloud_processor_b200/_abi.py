@@ -145,7 +145,8 @@ EXPORTS = [
     "plc_vl_upload_candidates_strided", "plc_vl_sweep_strided", "plc_filter", "plc_merge",
     "plc_vl_compute_normals", "plc_vl_generate_cells", "plc_vl_generate_candidates",
     "plc_drivable_params_default", "plc_drivable_area",
-    "plc_dev_alloc", "plc_dev_free", "plc_dev_upload", "plc_dev_download",
+    "plc_dev_alloc", "plc_dev_free", "plc_dev_upload", "plc_dev_download", "plc_dev_export", "plc_dev_import",
+    "plc_dev_release",
     "plc_excavation_params_default", "plc_excavation_counts", "plc_excavate",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
     "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
@@ -222,6 +223,10 @@ def lib() -> C.CDLL:
     L.plc_dev_free.restype = None
     L.plc_dev_upload.argtypes = [vp, vp, vp, u64]
     L.plc_dev_download.argtypes = [vp, vp, vp, u64]
+    L.plc_dev_export.argtypes = [vp, vp, vp]
+    L.plc_dev_import.argtypes = [vp, vp, C.POINTER(vp)]
+    L.plc_dev_release.argtypes = [vp, vp]
+    L.plc_dev_release.restype = None
     L.plc_excavation_params_default.argtypes = [C.POINTER(ExcavationParams)]
     L.plc_excavation_params_default.restype = None
     L.plc_excavation_counts.argtypes = [C.POINTER(ExcavationParams), C.POINTER(u64), C.POINTER(u64)]

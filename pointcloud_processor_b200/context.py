@@ -355,6 +355,32 @@ class DevBuffer:
         v.off_x, v.off_y, v.off_z = off
         return v
 
+    def export(self) -> bytes:
+        """plc_dev_export: 64 opaque bytes another process on the same GPU turns back into this buffer."""
+        h = (C.c_ubyte * 64)()
+        self._ctx._check(self._ctx._L.plc_dev_export(self._ctx._h, self.ptr, h), "plc_dev_export")
+        return bytes(h)
+
+
+class ImportedBuffer(DevBuffer):
+    """plc_dev_import: a buffer another process exported; released (unmapped), never freed, by this side."""
+
+    def __init__(self, ctx: "Context", handle: bytes, nbytes: int):
+        assert len(handle) == 64
+        self._ctx, self.nbytes = ctx, int(nbytes)
+        p = C.c_void_p()
+        h = (C.c_ubyte * 64).from_buffer_copy(handle)
+        ctx._check(ctx._L.plc_dev_import(ctx._h, h, C.byref(p)), "plc_dev_import")
+        self.ptr = p.value
+
+    def free(self):
+        if getattr(self, "ptr", None) and getattr(self._ctx, "_h", None):
+            self._ctx._L.plc_dev_release(self._ctx._h, self.ptr)
+        self.ptr = None
+
+    def export(self) -> bytes:
+        raise A.PlcError(A.PLC_E_INVALID_ARG, "an imported buffer is exported by its owner")
+
 
 # ---- host-side setup (include/plc_host.h) -------------------------------------------------------
 def host_generate_cells(area: np.ndarray, normals: np.ndarray | None, grid_resolution: float,

@@ -140,3 +140,39 @@ extern "C" plc_status plc_dev_download(plc_ctx* c, void* host_dst, const void* d
     PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return PLC_OK;
 }
+
+// ---- the same buffers across processes (CUDA IPC; one GPU, one handle per plc_dev_alloc allocation)
+static_assert(sizeof(cudaIpcMemHandle_t) == sizeof(plc_ipc_handle), "plc_ipc_handle carries a cudaIpcMemHandle_t");
+
+extern "C" plc_status plc_dev_export(plc_ctx* c, void* dev_ptr, plc_ipc_handle* handle) {
+    if (!c || !dev_ptr || !handle) return PLC_E_INVALID_ARG;
+    PLC_CUDA_TRY(c, cudaSetDevice(c->device));
+    PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));          // whatever wrote the buffer has finished
+    cudaIpcMemHandle_t h;
+    PLC_CUDA_TRY(c, cudaIpcGetMemHandle(&h, dev_ptr));
+    memcpy(handle->opaque, &h, sizeof(h));
+    return PLC_OK;
+}
+
+extern "C" plc_status plc_dev_import(plc_ctx* c, const plc_ipc_handle* handle, void** dev_ptr) {
+    if (!c || !handle || !dev_ptr) return PLC_E_INVALID_ARG;
+    *dev_ptr = nullptr;
+    PLC_CUDA_TRY(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle->opaque, sizeof(h));
+    const cudaError_t e = cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e == cudaErrorInvalidValue || e == cudaErrorInvalidResourceHandle || e == cudaErrorDeviceUninitialized) {
+        cudaGetLastError();                                     // a handle of this very process, or not a handle
+        *dev_ptr = nullptr;
+        return PLC_E_INVALID_ARG;
+    }
+    PLC_CUDA_TRY(c, e);
+    return PLC_OK;
+}
+
+extern "C" void plc_dev_release(plc_ctx* c, void* dev_ptr) {
+    if (!c || !dev_ptr) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaIpcCloseMemHandle(dev_ptr);
+}
