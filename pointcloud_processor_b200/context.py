@@ -298,7 +298,7 @@ class Context:
                                                normal_search_radius, cells.ctypes.data, cells.size, C.byref(n), C.byref(b))
         self._check(st, "plc_vl_generate_cells")
         self._cells_guess = int(n.value)
-        cells = cells[: n.value].copy() if n.value != cells.size else cells
+        cells = cells[: n.value]          # a view: copying a structured array goes field by field
         return cells, b
 
     def generate_candidates(self, terrain: np.ndarray | None, bounds: A.GridBounds, fixed: np.ndarray,
