@@ -65,3 +65,18 @@ def test_exported_buffer_is_another_process_input(tmp_path):
         # the producer still owns the memory after the consumer has let go of it
         assert np.array_equal(buf.download(cloud.nbytes, np.float32).reshape(n, 4), cloud)
         buf.free()
+
+
+def test_import_of_garbage_is_an_error_not_a_crash():
+    from pointcloud_processor_b200 import _abi as A
+    from pointcloud_processor_b200.context import Context, ImportedBuffer
+
+    with Context(0) as ctx:
+        for handle in (bytes(64), bytes(range(64))):
+            with pytest.raises(A.PlcError):
+                ImportedBuffer(ctx, handle, 1024)
+        # the context is still usable afterwards (no sticky error)
+        cloud = np.zeros((100, 4), np.float32)
+        cloud[:, 0] = np.arange(100, dtype=np.float32) * 0.01
+        out, n_crop = ctx.filter(cloud, A.CropBox(-1.0, 2.0, -1.0, 1.0, -1.0, 1.0), 0.05)
+        assert n_crop == 100 and 0 < out.shape[0] <= 100
