@@ -1,6 +1,11 @@
 // plc_ctx.cu — context lifetime, status text, parameter presets.
+#include <atomic>
 #include <cmath>
+#include <cstdlib>
+#include <memory>
 #include <new>
+#include <thread>
+#include <vector>
 
 #include "plc_internal.cuh"
 
@@ -92,6 +97,8 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
                            &c->su_flags, &c->su_out, &c->su_normals, &c->su_state, &c->ex_plan, &c->ex_terrain, &c->ex_area};
     for (plc::DevBuf* b : bufs) b->release();
     if (c->pinned) cudaFreeHost(c->pinned);
+    if (c->stage_pinned) cudaFreeHost(c->stage_pinned);
+    if (c->stage_done) cudaEventDestroy(c->stage_done);
     c->timer.destroy();
     if (c->ev_sweep_begin) cudaEventDestroy(c->ev_sweep_begin);
     if (c->ev_sweep_end) cudaEventDestroy(c->ev_sweep_end);
@@ -108,6 +115,96 @@ extern "C" plc_status plc_ctx_sync(plc_ctx* c) {
     PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return PLC_OK;
 }
+
+// ---- large pageable inputs (a ROS message's byte vector is pageable memory).  cudaMemcpyAsync from pageable memory
+// is staged by the driver on the calling thread (14 GB/s at 64 MB); here a few threads fill page-locked staging piece by piece
+// and each piece goes over the bus as soon as it is there.  PLC_STAGE_THREADS=0 turns it off.
+namespace plc {
+namespace {
+// measured on the B200 box (tools/dev/stage_probe.py): 16 MB 0.84 ms plain / 1.07 ms staged (starting the helper threads
+// is the fixed cost), 64 MB 4.75 ms plain / 2.66 ms staged — so only from 32 MB up
+constexpr size_t kStagePiece = size_t(1) << 20, kStageMin = size_t(32) << 20, kStageMax = size_t(1) << 30;
+
+int stage_threads() {
+    static const int n = [] {
+        if (const char* e = std::getenv("PLC_STAGE_THREADS")) return std::max(0, std::min(atoi(e), 16));
+        const unsigned hw = std::thread::hardware_concurrency();
+        return hw >= 8 ? 4 : hw >= 4 ? 2 : 0;
+    }();
+    return n;
+}
+}  // namespace
+
+bool upload_pageable(plc_ctx* ctx, void* dev_dst, const void* host_src, size_t bytes, plc_status* st) {
+    *st = PLC_OK;
+    const int n_threads = stage_threads();
+    if (n_threads == 0 || bytes < kStageMin || bytes > kStageMax) return false;
+    if (ctx->stage_pending) {                         // the previous staged copy may still be reading the buffer
+        if (cudaEventSynchronize(ctx->stage_done) != cudaSuccess) return false;
+        ctx->stage_pending = false;
+    }
+    if (bytes > ctx->stage_cap) {
+        if (ctx->stage_pinned) cudaFreeHost(ctx->stage_pinned);
+        ctx->stage_pinned = nullptr;
+        ctx->stage_cap = 0;
+        const size_t want = (bytes + kStagePiece - 1) / kStagePiece * kStagePiece;
+        if (cudaMallocHost(&ctx->stage_pinned, want) != cudaSuccess) {
+            cudaGetLastError();
+            ctx->stage_pinned = nullptr;
+            return false;
+        }
+        ctx->stage_cap = want;
+    }
+    if (!ctx->stage_done && cudaEventCreateWithFlags(&ctx->stage_done, cudaEventDisableTiming) != cudaSuccess) {
+        cudaGetLastError();
+        ctx->stage_done = nullptr;
+        return false;
+    }
+    const size_t n_pieces = (bytes + kStagePiece - 1) / kStagePiece;
+    std::unique_ptr<std::atomic<unsigned char>[]> ready(new (std::nothrow) std::atomic<unsigned char>[n_pieces]);
+    if (!ready) return false;
+    for (size_t i = 0; i < n_pieces; ++i) ready[i].store(0, std::memory_order_relaxed);
+    std::atomic<size_t> next{0};
+    const unsigned char* src = static_cast<const unsigned char*>(host_src);
+    unsigned char* stage = static_cast<unsigned char*>(ctx->stage_pinned);
+    auto fill = [&] {
+        for (;;) {
+            const size_t i = next.fetch_add(1, std::memory_order_relaxed);
+            if (i >= n_pieces) return;
+            const size_t off = i * kStagePiece;
+            memcpy(stage + off, src + off, std::min(kStagePiece, bytes - off));
+            ready[i].store(1, std::memory_order_release);
+        }
+    };
+    std::vector<std::thread> helpers;
+    try {
+        for (int t = 0; t < n_threads; ++t) helpers.emplace_back(fill);
+    } catch (...) {
+        // fewer helpers than wanted (or none): this thread fills what is left below
+    }
+    cudaError_t err = cudaSuccess;
+    for (size_t i = 0; i < n_pieces; ++i) {
+        while (!ready[i].load(std::memory_order_acquire)) {
+            if (helpers.empty()) fill();              // no helper could be started: copy here
+            else std::this_thread::yield();
+        }
+        const size_t off = i * kStagePiece;
+        if (err == cudaSuccess)
+            err = cudaMemcpyAsync(static_cast<unsigned char*>(dev_dst) + off, stage + off, std::min(kStagePiece, bytes - off),
+                                  cudaMemcpyHostToDevice, ctx->stream);
+    }
+    for (std::thread& t : helpers) t.join();
+    if (err == cudaSuccess) err = cudaEventRecord(ctx->stage_done, ctx->stream);
+    if (err != cudaSuccess) {
+        ctx->set_error("upload_pageable", cudaGetErrorString(err));
+        cudaGetLastError();
+        *st = PLC_E_CUDA;
+        return true;
+    }
+    ctx->stage_pending = true;
+    return true;
+}
+}  // namespace plc
 
 // ---- device buffers handed between stages (plc.h)
 extern "C" plc_status plc_dev_alloc(plc_ctx* c, uint64_t bytes, void** dev_ptr) {
@@ -128,7 +225,15 @@ extern "C" void plc_dev_free(plc_ctx* c, void* dev_ptr) {
 extern "C" plc_status plc_dev_upload(plc_ctx* c, void* dev_dst, const void* host_src, uint64_t bytes) {
     if (!c || (bytes && (!dev_dst || !host_src))) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(c, cudaSetDevice(c->device));
-    PLC_CUDA_TRY(c, cudaMemcpyAsync(dev_dst, host_src, bytes, cudaMemcpyHostToDevice, c->stream));
+    cudaPointerAttributes attr{};
+    const bool pageable = cudaPointerGetAttributes(&attr, host_src) != cudaSuccess || attr.type == cudaMemoryTypeUnregistered;
+    cudaGetLastError();
+    plc_status st = PLC_OK;
+    if (pageable && plc::upload_pageable(c, dev_dst, host_src, bytes, &st)) {
+        if (st != PLC_OK) return st;
+    } else {
+        PLC_CUDA_TRY(c, cudaMemcpyAsync(dev_dst, host_src, bytes, cudaMemcpyHostToDevice, c->stream));
+    }
     PLC_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return PLC_OK;
 }

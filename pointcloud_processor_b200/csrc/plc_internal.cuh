@@ -158,6 +158,10 @@ struct plc_ctx {
     plc::DevBuf scratch;         // small reductions
     void* pinned = nullptr;      // pinned host scratch for small results
     size_t pinned_cap = 0;
+    void* stage_pinned = nullptr;        // page-locked staging of large pageable inputs (plc::upload_pageable)
+    size_t stage_cap = 0;
+    cudaEvent_t stage_done = nullptr;    // the last staged copy has left the staging buffer
+    bool stage_pending = false;
 
     // virtual_lidar state
     plc::VoxelIndex terrain, observed;
@@ -236,6 +240,10 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
 // Where a caller's cloud bytes are read from on the device.  `data` may be host memory (copied into ctx->upload) or
 // device memory of this context's device — a buffer from plc_dev_alloc, typically the output of the previous stage —
 // which is then read in place (clouds stay in HBM between the nodes' stages).
+// Large pageable host buffer -> device, as a pipeline: a few host threads copy 1 MB pieces into page-locked staging
+// while the pieces already there go over the bus (plc_ctx.cu).  False: not applicable, copy the plain way.
+bool upload_pageable(plc_ctx* ctx, void* dev_dst, const void* host_src, size_t bytes, plc_status* st);
+
 inline plc_status stage_bytes(plc_ctx* ctx, const void* data, size_t bytes, const unsigned char** dev) {
     *dev = nullptr;
     if (bytes == 0) return PLC_OK;
@@ -245,9 +253,15 @@ inline plc_status stage_bytes(plc_ctx* ctx, const void* data, size_t bytes, cons
         *dev = static_cast<const unsigned char*>(data);
         return PLC_OK;
     }
+    const bool pageable = attr.type == cudaMemoryTypeUnregistered;
     cudaGetLastError();          // an unregistered host pointer is not an error
     PLC_CUDA_TRY(ctx, ctx->upload.reserve(bytes));
-    PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, data, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    plc_status st = PLC_OK;
+    if (pageable && upload_pageable(ctx, ctx->upload.ptr, data, bytes, &st)) {
+        if (st != PLC_OK) return st;
+    } else {
+        PLC_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->upload.ptr, data, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
     *dev = ctx->upload.as<unsigned char>();
     return PLC_OK;
 }

@@ -104,7 +104,7 @@ def filter_scan(ctx: Context, scan, front=15.0, side=10.0, height=10.0, leaf=0.2
     L = A.lib()
     v = A.cloud_view(scan, point_step, off)
     cap = max(int(v.n_points), 1)
-    out = np.zeros((cap, 4), np.float32)
+    out = np.empty((cap, 4), np.float32)
     n = C.c_uint64(0)
     st = L.plc_filter_scan(ctx._h, C.byref(v), front, side, height, leaf, out.ctypes.data, cap, C.byref(n))
     if st != A.PLC_OK:
@@ -289,11 +289,11 @@ def run_launch_graph_resident(ctx: Context, inp, leaf: float = 0.2, num_candidat
     chk(L.plc_vl_compute_normals(ctx._h, C.byref(va), 1.5, normals.ptr), "plc_vl_compute_normals")
     b = A.GridBounds()
     cnt = C.c_uint64(0)
-    cells = np.zeros(max(getattr(ctx, "_cells_guess", 0), 1 << 16), A.CELL_DTYPE)   # one pass when the last count fits
+    cells = np.empty(max(getattr(ctx, "_cells_guess", 0), 1 << 16), A.CELL_DTYPE)   # one pass when the last count fits
     st = L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, cells.ctypes.data,
                                  cells.size, C.byref(cnt), C.byref(b))
     if st == A.PLC_E_CAPACITY:
-        cells = np.zeros(cnt.value, A.CELL_DTYPE)
+        cells = np.empty(cnt.value, A.CELL_DTYPE)
         st = L.plc_vl_generate_cells(ctx._h, C.byref(va), normals.ptr, grid_resolution, vertical_layers, 1.5, cells.ctypes.data,
                                      cells.size, C.byref(cnt), C.byref(b))
     chk(st, "plc_vl_generate_cells")
