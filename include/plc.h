@@ -288,7 +288,8 @@ typedef struct plc_device_times {
     float candidates_ms;    /* plc_vl_generate_candidates */
     float drivable_ms;      /* plc_drivable_area */
     float excavate_ms;      /* plc_excavate */
-    float reserved[2];
+    float sweep_fixed_ms;   /* last plc_vl_run_async: everything before k_sweep (reset, fixed-sensor pass k_fixed, k_pose_prep) */
+    float sweep_reduce_ms;  /* last plc_vl_run_async: everything after k_sweep (k_finalize, k_argmax, k_flags if asked for) */
 } plc_device_times;
 plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out);
 

@@ -59,7 +59,7 @@ class DeviceTimes(C.Structure):
     _fields_ = [("set_terrain_ms", C.c_float), ("set_observed_ms", C.c_float), ("filter_ms", C.c_float),
                 ("merge_ms", C.c_float), ("sweep_kernel_ms", C.c_float), ("normals_ms", C.c_float),
                 ("cells_ms", C.c_float), ("candidates_ms", C.c_float), ("drivable_ms", C.c_float),
-                ("excavate_ms", C.c_float), ("reserved", C.c_float * 2)]
+                ("excavate_ms", C.c_float), ("sweep_fixed_ms", C.c_float), ("sweep_reduce_ms", C.c_float)]
 
 
 class GridInfo(C.Structure):

@@ -76,7 +76,8 @@ extern "C" plc_status plc_ctx_create(int device, void* stream, plc_ctx** out) {
         c->own_stream = true;
     }
     if (c->result.reserve(sizeof(plc::SweepResult)) != cudaSuccess || !c->pinned_reserve(1 << 16) ||
-        cudaEventCreate(&c->ev_sweep_begin) != cudaSuccess || cudaEventCreate(&c->ev_sweep_end) != cudaSuccess) {
+        cudaEventCreate(&c->ev_sweep_begin) != cudaSuccess || cudaEventCreate(&c->ev_sweep_end) != cudaSuccess ||
+        cudaEventCreate(&c->ev_run_begin) != cudaSuccess || cudaEventCreate(&c->ev_run_end) != cudaSuccess) {
         plc_ctx_destroy(c);
         return PLC_E_OOM;
     }
@@ -102,6 +103,8 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
     c->timer.destroy();
     if (c->ev_sweep_begin) cudaEventDestroy(c->ev_sweep_begin);
     if (c->ev_sweep_end) cudaEventDestroy(c->ev_sweep_end);
+    if (c->ev_run_begin) cudaEventDestroy(c->ev_run_begin);
+    if (c->ev_run_end) cudaEventDestroy(c->ev_run_end);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }

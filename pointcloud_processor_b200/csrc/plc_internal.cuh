@@ -70,7 +70,8 @@ struct VoxelGeom {
     float inv_g;             // 1/g (power of two)
     float reach;             // real-number radius + slack used by the builder
     int dim_x, dim_y, dim_z; // coarse dims
-    int mdim_x, mdim_y, mdim_z;   // mid dims = 2*coarse
+    int mdim_x, mdim_y, mdim_z;   // mid-voxel dims (candidate lists)
+    int mid_shift;                // fine voxels per mid-voxel edge = 1 << mid_shift (4 at refinement 1, 8 at 2)
     float fdim_xf, fdim_yf, fdim_zf;   // fine dims = 8*coarse, as float for the bounds test
     float clip_lo[3], clip_hi[3];      // box outside which no position is within reach of a point
     float clip_t;                      // slack (m along the ray) the clipped sample range may overshoot by
@@ -90,16 +91,19 @@ struct VoxelIndex {
     float built_thr = 0.0f;       // float32 squared-distance threshold of the "certain" bit
     double built_march_err = 0.0; // position error of the caller's march covered by the slack: in fine voxels ...
     double built_march_err_m = 0.0;   // ... plus in metres
+    int built_refine = 0;         // occupancy refinement the structure was built with (1, 2 or 4) ...
+    int asked_refine = 0;         // ... and the one asked for (the size caps may have lowered it)
     double h = 0.0;
     DevBuf bricks, gstart, cfill, cgrp, scan_tmp;
     VoxelGeom geom{};
-    uint64_t n_vox = 0;       // coarse voxels
+    uint64_t n_vox = 0;       // bricks
+    uint64_t n_mid = 0;       // list voxels
     uint64_t n_groups = 0;    // 4-point groups in cgrp
     bool has_points() const { return n_raw > 0; }
     // the "G" term of the algorithmic bytes: the indexed points, once (a lower bound of what the sweep must read)
     uint64_t bytes() const { return n_raw * 16; }
     // what is actually resident (candidate lists replicate a point into every mid voxel in reach)
-    uint64_t resident_bytes() const { return n_vox * 128 + (n_vox * 8 + 1) * 4 + n_groups * 48; }
+    uint64_t resident_bytes() const { return n_vox * 128 + (n_mid + 1) * 4 + n_groups * 48; }
     void release() {
         raw.release(); bricks.release(); gstart.release(); cfill.release(); cgrp.release();
         scan_tmp.release();
@@ -190,6 +194,10 @@ struct plc_ctx {
     uint64_t mask_words = 0;
     int tiles = 0;
     cudaEvent_t ev_sweep_begin = nullptr, ev_sweep_end = nullptr;   // around k_sweep
+    // occupancy refinement policy (plc_sweep.cu pick_refine): rays swept over the current terrain so far, and the
+    // size of the last sweep as the forecast for a terrain that has just arrived
+    uint64_t terrain_rays_accum = 0, last_sweep_rays = 0;
+    cudaEvent_t ev_run_begin = nullptr, ev_run_end = nullptr;       // around all kernels of plc_vl_run_async
     bool sweep_timed = false;
     plc::DevTimer timer;         // kernels of the call in progress
     plc_device_times times{};    // last completed call of each kind (plc_last_device_times)
@@ -235,7 +243,8 @@ plc_status fetch_strided(plc_ctx* ctx, plc_sweep_out* out, uint64_t dst_stride);
 // Builds (or keeps) the index for `radius`.  thr: float32 squared-distance threshold of the exact test
 // (normally (float)(radius*radius)); march_err + march_err_m: position error of the caller's march, in
 // fine-voxel units, folded into the conservative slack.
-plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err, double march_err_m);
+plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err, double march_err_m,
+                       int refine = 1);
 
 // Where a caller's cloud bytes are read from on the device.  `data` may be host memory (copied into ctx->upload) or
 // device memory of this context's device — a buffer from plc_dev_alloc, typically the output of the previous stage —

@@ -931,7 +931,19 @@ size_t sample_table_size(const plc_params* p) {
     return n;
 }
 
-plc_status build_terrain_index(plc_ctx* ctx, const plc_params* p) {
+// Occupancy refinement (plc_voxel.cu voxel_build): fine voxels of half the edge halve the uncertain shell, hence
+// the samples that take the exact test (cfg2: 2.97 -> 2.42 ms per sweep, cfg5: 1.7x), for about 1.5 ns per
+// point more build time and 8x the brick memory.  A sweep gains ~5 ps per ray at least, so the finer structure
+// pays once the rays swept over one terrain exceed ~300 per point: decided from the rays already swept over
+// this terrain plus the sweep about to run (for a terrain that has just arrived: the size of the last sweep).
+int pick_refine(const plc_ctx* ctx, uint64_t rays_ahead) {
+    static const int forced = getenv("PLC_DEV_REFINE") ? atoi(getenv("PLC_DEV_REFINE")) : 0;
+    if (forced > 0) return forced;
+    const double rays = (double)ctx->terrain_rays_accum + (double)rays_ahead;
+    return rays > 300.0 * (double)ctx->terrain.n_raw ? 2 : 1;
+}
+
+plc_status build_terrain_index(plc_ctx* ctx, const plc_params* p, int refine) {
     // position error of k_sweep's march against the upstream double position:
     //   16.16 fixed point, in fine voxels: origin 1, each step 1/2;
     //   float32 direction (< 1e-6 relative) and sample parameter over a ray of at most max_distance, and the
@@ -942,7 +954,7 @@ plc_status build_terrain_index(plc_ctx* ctx, const plc_params* p) {
     const double cells_radius = std::fmax(16.0, (double)ctx->cells_radius);
     const double march_err_m = 3e-6 * p->max_distance + 2e-6 + 2.5e-7 * (2.0 * cells_radius + 2.0 * p->max_distance) + 1e-7;
     return voxel_build(ctx, ctx->terrain, p->vis_radius * p->block_radius_scale, block_threshold(p), march_err,
-                       march_err_m);
+                       march_err_m, refine);
 }
 plc_status build_observed_index(plc_ctx* ctx, const plc_params* p) {
     return voxel_build(ctx, ctx->observed, p->vis_radius * p->observed_radius_scale, observed_threshold(p), 0.0, 0.0);
@@ -984,7 +996,8 @@ extern "C" plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* clo
     // build for the node's default block radius right away; a sweep with other parameters rebuilds
     plc_params d;
     plc_params_default(&d);
-    PLC_TRY(build_terrain_index(ctx, &d));
+    ctx->terrain_rays_accum = 0;
+    PLC_TRY(build_terrain_index(ctx, &d, pick_refine(ctx, ctx->last_sweep_rays)));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->times.set_terrain_ms = ctx->timer.total_ms();
     return PLC_OK;
@@ -1094,7 +1107,10 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     if (ctx->terrain.n_input == 0) return PLC_E_NO_TERRAIN;             // :455 !terrain_cloud_
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const plc_params& p = ctx->prm;
-    PLC_TRY(build_terrain_index(ctx, &p));
+    const uint64_t rays_ahead = ctx->n_local * ctx->n_cells;
+    PLC_TRY(build_terrain_index(ctx, &p, pick_refine(ctx, rays_ahead)));
+    ctx->terrain_rays_accum += rays_ahead;
+    ctx->last_sweep_rays = rays_ahead;
     PLC_TRY(build_observed_index(ctx, &p));
     PLC_TRY(upload_sample_table(ctx, &p));
 
@@ -1159,6 +1175,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     cudaStream_t s = ctx->stream;
     SweepResult* res = ctx->result.as<SweepResult>();
     double* fixed_totals = ctx->scratch.as<double>();
+    cudaEventRecord(ctx->ev_run_begin, s);
     k_reset_result<<<1, 1, 0, s>>>(res);
     k_fixed<<<fixed_blocks, kSweepThreads, 0, s>>>(P, ctx->fixed, ctx->cells.as<plc_cell>(), M,
                                                    ctx->fixed_scores.as<double>(), ctx->cell_flags.as<uint8_t>(),
@@ -1196,6 +1213,7 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
                                                        ctx->cells.as<plc_cell>(), M, ctx->cell_flags.as<uint8_t>());
         ctx->launches += 1;
     }
+    cudaEventRecord(ctx->ev_run_end, s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ctx->ran = true;
     ctx->ran_mask = want_mask != 0;
@@ -1285,6 +1303,12 @@ extern "C" plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out)
     float ms = 0.f;
     PLC_TRY(plc_vl_last_sweep_kernel_ms(ctx, &ms));
     ctx->times.sweep_kernel_ms = ms;
+    ctx->times.sweep_fixed_ms = ctx->times.sweep_reduce_ms = 0.f;
+    if (ctx->sweep_timed) {      // plc_vl_last_sweep_kernel_ms has synchronised on ev_sweep_end
+        PLC_CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_run_end));
+        PLC_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->times.sweep_fixed_ms, ctx->ev_run_begin, ctx->ev_sweep_begin));
+        PLC_CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->times.sweep_reduce_ms, ctx->ev_sweep_end, ctx->ev_run_end));
+    }
     *out = ctx->times;
     return PLC_OK;
 }

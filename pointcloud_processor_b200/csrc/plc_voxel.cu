@@ -15,6 +15,7 @@
 //   k_dilate    2-bit fine-voxel states within reach of each point                 N*16 rd, ~100 atomicOr/pt
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "plc_voxel_query.cuh"
 #include "plc_scan.cuh"
@@ -256,11 +257,14 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
     return PLC_OK;
 }
 
-plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err, double march_err_m) {
+plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, double march_err, double march_err_m,
+                       int refine) {
     if (!ix.has_points()) return PLC_OK;
     if (ix.built_radius == radius && ix.built_thr == thr && march_err <= ix.built_march_err &&
-        march_err_m <= ix.built_march_err_m)
+        march_err_m <= ix.built_march_err_m && refine <= ix.asked_refine)
         return PLC_OK;
+    ix.asked_refine = refine;
+    refine = refine >= 4 ? 4 : (refine >= 2 ? 2 : 1);
     if (!(radius > 0) || !std::isfinite(radius) || !(thr >= 0) || !(march_err >= 0) || !(march_err_m >= 0))
         return PLC_E_INVALID_ARG;
 
@@ -278,8 +282,9 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     double h = std::max(std::exp2(std::ceil(std::log2(2.0 * (r_out + slack0)))), 1.0 / 64.0);
     double org[3], reach = 0.0, slack = 0.0;
     long long dim[3];
+    int F = refine;      // bricks per list-voxel edge: the occupancy is F times finer than the candidate lists
     for (;;) {
-        slack = slack0 + (h / 8.0) * march_err + march_err_m;
+        slack = slack0 + (h / (8.0 * F)) * march_err + march_err_m;
         reach = r_out + slack;
         if (h < 2.0 * reach) {
             h *= 2.0;
@@ -292,16 +297,21 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
             cells *= (double)dim[a];
         }
         // fine coordinates must fit the march's signed 16.16 fixed point with room to spare
-        bool fits = cells <= 1.6e7 && dim[0] <= 3600 && dim[1] <= 3600 && dim[2] <= 3600;
+        static const double cap = getenv("PLC_DEV_BRICK_CAP") ? atof(getenv("PLC_DEV_BRICK_CAP")) : 1.6e7;
+        bool fits = cells * F * F * F <= cap && dim[0] * F <= 3600 && dim[1] * F <= 3600 && dim[2] * F <= 3600;
         if (fits) break;
+        if (F > 1) {
+            F /= 2;  // the refinement is optional: give it up before coarsening the lists
+            continue;
+        }
         h *= 2.0;    // coarser voxels only make the lists longer, never incomplete
     }
     // "certain" bit: the float32 test accepts every sample of the fine voxel against this point
     const double inner = std::sqrt((double)std::min(thr, r2f)) * (1.0 - 1e-6) - slack;
-    const size_t n_vox = (size_t)dim[0] * dim[1] * dim[2];
-    const size_t n_mid = n_vox * 8;
+    const size_t n_mid = (size_t)dim[0] * dim[1] * dim[2] * 8;      // list voxels: edge h / 2
+    const size_t n_vox = (size_t)dim[0] * dim[1] * dim[2] * F * F * F;   // bricks: edge h / F, 8 fine voxels per edge
     const unsigned n = (unsigned)ix.n_raw;
-    const double gsz = h / 8.0;
+    const double gsz = h / (8.0 * F);
 
     PLC_CUDA_TRY(ctx, ix.gstart.reserve((n_mid + 1) * 4));
     PLC_CUDA_TRY(ctx, ix.cfill.reserve(n_mid * 4));
@@ -311,14 +321,15 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     g.ox = (float)org[0];
     g.oy = (float)org[1];
     g.oz = (float)org[2];
-    g.inv_g = (float)(8.0 / h);
+    g.inv_g = (float)(8.0 * F / h);
     g.reach = (float)reach;
-    g.dim_x = (int)dim[0];
-    g.dim_y = (int)dim[1];
-    g.dim_z = (int)dim[2];
-    g.mdim_x = g.dim_x * 2;
-    g.mdim_y = g.dim_y * 2;
-    g.mdim_z = g.dim_z * 2;
+    g.dim_x = (int)dim[0] * F;
+    g.dim_y = (int)dim[1] * F;
+    g.dim_z = (int)dim[2] * F;
+    g.mdim_x = (int)dim[0] * 2;
+    g.mdim_y = (int)dim[1] * 2;
+    g.mdim_z = (int)dim[2] * 2;
+    g.mid_shift = F == 4 ? 4 : (F == 2 ? 3 : 2);
     g.fdim_xf = (float)(g.dim_x * 8);
     g.fdim_yf = (float)(g.dim_y * 8);
     g.fdim_zf = (float)(g.dim_z * 8);
@@ -372,6 +383,8 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     ix.built_thr = thr;
     ix.built_march_err = march_err;
     ix.built_march_err_m = march_err_m;
+    ix.built_refine = F;
+    ix.n_mid = n_mid;
     return PLC_OK;
 }
 

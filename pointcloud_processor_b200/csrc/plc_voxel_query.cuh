@@ -94,13 +94,17 @@ __device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, 
     PLC_CHECK_OOB((unsigned)(fx >> 16) >= (unsigned)(g.dim_x << kFineShift) || (unsigned)(fy >> 16) >= (unsigned)(g.dim_y << kFineShift) ||
                   (unsigned)(fz >> 16) >= (unsigned)(g.dim_z << kFineShift), 0u)
     const unsigned brick = brick_of(g, fx >> (16 + kFineShift), fy >> (16 + kFineShift), fz >> (16 + kFineShift));
+#ifdef PLC_WIDE_BRICKS
+    const size_t off = ((size_t)brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
+#else
     const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
+#endif
     return ldg_brick_row(reinterpret_cast<const char*>(g.bricks) + off);
 }
 __device__ __forceinline__ unsigned row_shift(int fx) { return ((unsigned)fx >> 15) & 0xeu; }
 
 __device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int iy, int iz) {
-    return (uint32_t)(((size_t)(iz >> 2) * g.mdim_y + (iy >> 2)) * g.mdim_x + (ix >> 2));
+    return (uint32_t)(((size_t)(iz >> g.mid_shift) * g.mdim_y + (iy >> g.mid_shift)) * g.mdim_x + (ix >> g.mid_shift));
 }
 
 // Exact existence test over the candidate list of mid voxel m, four points per iteration.

@@ -85,6 +85,37 @@ def test_parity_config2_candidate_subset(ctx, scene_cache):
     compare(got, ref, s.cells.size, want_flags=False)
 
 
+def test_parity_config2_full(ctx, scene_cache):
+    # BASELINE.json configs[1] at full size: every one of the 1 930 poses x 57 600 rays against the oracle on all
+    # host threads (~111 M rays, 1.1 G samples; tens of seconds of CPU): mask words, covered counts, sample
+    # counters and the optimum
+    import os
+    s = scene_cache("cfg2")
+    got = run_gpu(ctx, s)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, s.params, s.fixed, s.candidates,
+                  threads=os.cpu_count() or 8)
+    assert ref["mask"].shape == (s.candidates.size, 32 * 1800 // 32)
+    compare(got, ref, s.cells.size, want_flags=False)
+    assert got.counters["samples"] > 1_000_000_000
+
+
+def test_parity_config5_candidate_subset(ctx, scene_cache):
+    # BASELINE.json configs[4] geometry (L, 4 M points, 128x128x8 poses, 64x2048 = 131 072 rays per pose): the dense
+    # cloud where the exact radius test (:779-793) dominates.  Two seeded poses from each of the 8 height layers.
+    import os
+    s = scene_cache("cfg5")
+    assert s.cells.size == 64 * 2048 and s.terrain.shape[0] == 4_000_000
+    per_layer = s.candidates.size // 8
+    rng = np.random.default_rng(5)
+    sel = np.sort(np.concatenate([k * per_layer + rng.choice(per_layer, 2, replace=False) for k in range(8)]))
+    cands = s.candidates[sel]
+    assert np.unique(np.round(cands["z"] - cands["z"].min(), 1)).size >= 4       # several sensor heights
+    got = run_gpu(ctx, s, cands=cands)
+    ref = O.sweep(O.Index(s.terrain, O.GRID), None, s.cells, s.params, s.fixed, cands, threads=os.cpu_count() or 8)
+    compare(got, ref, s.cells.size, want_flags=False)
+    assert got.counters["exact_tests"] > 0
+
+
 def test_observed_cloud_and_memo_variant(ctx, scene_cache):
     s = scene_cache("small")
     obs = np.stack([s.cells["x"], s.cells["y"], s.cells["z"]], 1).astype(np.float32)[::5] + np.float32(0.05)

@@ -5,7 +5,9 @@ for name in sys.argv[1:]:
     sc = scenes.build(name)
     with Context(0) as ctx:
         ctx.set_terrain(sc.terrain); ctx.set_cells(sc.cells)
+        r = ctx.sweep(sc.params, sc.fixed, sc.candidates[:8], scores=False)      # builds the index the sweep wants
+        build_ms = ctx.device_times()
         r = ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)
         t0=time.time(); r = ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False); dt=time.time()-t0
         g = ctx.grid_info()[0]
-        print(json.dumps(dict(scene=name, ms=dt*1e3, kernel_ms=ctx.last_sweep_kernel_ms(), **r.counters, grid_bytes=g["grid_bytes"], n_vox=g["n_voxels"])))
+        print(json.dumps(dict(scene=name, ms=dt*1e3, kernel_ms=ctx.last_sweep_kernel_ms(), **r.counters, grid_bytes=g["grid_bytes"], n_vox=g["n_voxels"], set_terrain_ms=build_ms.get("set_terrain_ms"))))
