@@ -10,11 +10,14 @@ cell) ray of this rank's candidate shard, per-candidate scores, argmax and — f
 16-byte-per-rank all-gather.  Metric: rays/s over the whole job (BASELINE.json).  Prints ONE JSON
 line on rank 0.  See DESIGN.md §6 for every field.
 
-Workload: BASELINE.json configs[1] (rectangular pit, 200 k points, 32x32x2 poses, 32x1800 rays per
-pose) at N = 1; at N GPUs the candidate lattice is refined to round(32*sqrt(N))^2 x 2 poses over
-the same region, so every rank keeps a configs[1]-sized shard ("scaling": "weak").  The line also
-carries `north_star_cfg3`: configs[2] (L-shape, 1 M points, 64x64x4 poses) swept by the same N
-ranks, the number the north star's 50 ms target is quoted on.
+Workload: N = 1 — BASELINE.json configs[1] (cfg2: rectangular pit, 200 k points, 32x32x2 poses, 32x1800 rays per
+pose), plus a `north_star_cfg3` block.  N > 1 — configs[2] (cfg3: L-shape, 1 M points, 64x64x4 poses, 32x1800 rays),
+the configuration the north star's 50 ms target is quoted on, strong-scaled over the N ranks ("scaling": "strong");
+extra blocks: `breakdown` (k_sweep / fixed pass / finalize+argmax / all-gather / rank imbalance), `parity` (sharded
+against unsharded on rank 0), `group` (plc_group_* from one process against the rank-sharded result),
+`weak_cfg2_shard` (round 1's weak-scaling line) and, at N = 8, `cfg5` (configs[4]).
+`e2e.value` is measured with PAGEABLE host buffers and the node core's outputs (flags + fixed scores);
+`e2e.variants` has the pinned and scores-only figures beside it.
 """
 from __future__ import annotations
 
@@ -44,20 +47,25 @@ WORKLOADS = {
 
 
 def default_workload(n_gpus: int) -> str:
-    return "cfg2"
+    """N = 1: BASELINE.json configs[1] ("... on 1xB200").  N > 1: configs[2] ("... sharded across 2/4/8 B200"), the
+    configuration the north star's 50 ms target is quoted on, strong-scaled."""
+    return "cfg2" if n_gpus <= 1 else "cfg3"
 
 
-def build_scene(workload: str, world: int):
-    """configs[1] keeps a fixed shard per rank: the pose lattice side grows with sqrt(N)."""
+def build_scene(workload: str, world: int, weak: bool = False, setup=None):
+    """`weak`: configs[1] with a fixed shard per rank (the pose lattice side grows with sqrt(N))."""
     from pointcloud_processor_b200 import scenes
-    if workload == "cfg2" and world > 1:
-        return scenes.build("cfg2", px=int(round(32 * np.sqrt(world))))
-    return scenes.build(workload)
+    kw = {}
+    if setup is not None:
+        kw.update(setup=setup, layers=scenes.LAYERS_FOUND[workload])
+    if weak and world > 1:
+        kw["px"] = int(round(32 * np.sqrt(world)))
+    return scenes.build(workload, **kw)
 
 
-def workload_text(workload: str, world: int) -> str:
+def workload_text(workload: str, world: int, weak: bool = False) -> str:
     text = WORKLOADS.get(workload, workload)
-    if workload == "cfg2" and world > 1:
+    if weak and world > 1:
         side = int(round(32 * np.sqrt(world)))
         text = text.replace("32x32x2 poses", f"{side}x{side}x2 poses (32x32x2 per GPU x {world})")
     return f"{workload}: {text}"
@@ -168,6 +176,24 @@ def algorithmic_bytes(rays: int, samples: int, n_cands: int, grid_bytes: int) ->
     return 32 * rays + 4 * samples + 64 * n_cands + grid_bytes
 
 
+def oracle_setup():
+    """(generate_cells, generate_candidates) of oracle/vl_setup.cpp with the signatures scenes.build expects:
+    the reference arm builds its scene with these, so it never loads the product library."""
+    from oracle import binding as O
+    index = {}
+
+    def gen_cells(area, normals, res, layers, normal_radius):
+        return O.generate_cells(area, normals, res, layers, normal_radius)
+
+    def gen_cands(terrain, bounds, fixed, num_candidates, search_radius, sensor_height):
+        if id(terrain) not in index:
+            index.clear()
+            index[id(terrain)] = O.Index(terrain, O.GRID)
+        return O.generate_candidates(index[id(terrain)], bounds, fixed, num_candidates, search_radius, sensor_height)
+
+    return gen_cells, gen_cands
+
+
 def cpu_reference_sample(scene, budget_s: float, threads: int, seed: int = 1234):
     """Times the CPU restatement of the reference's sweep (KD-tree index, reference loop structure
     incl. the per-candidate fixed-sensor re-evaluation) on a seeded subset of candidates sized to
@@ -192,113 +218,286 @@ def cpu_reference_sample(scene, budget_s: float, threads: int, seed: int = 1234)
     return n * M / dt, n, dt
 
 
-def run_ours(args) -> dict | None:
-    import torch
-    import torch.distributed as dist
+class Rig:
+    """One rank's context, stream and collectives."""
 
-    from pointcloud_processor_b200 import Context, exchange, scenes
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        from pointcloud_processor_b200 import Context, exchange
+        self.torch, self.dist, self.exchange = torch, dist, exchange
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the plc_* path")
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        self.host_group = None
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+            # a CPU-side barrier for the stretch where rank 0 alone drives every GPU (group_block): an NCCL barrier
+            # would leave a kernel spinning on the very devices rank 0 is about to use from another process
+            self.host_group = dist.new_group(backend="gloo")
+        # a non-default torch stream (handle != 0) made current: the library launches on it, NCCL orders
+        # against it, and torch.cuda.Event records see exactly the kernels that are timed
+        self.stream = torch.cuda.Stream(self.dev)
+        torch.cuda.set_stream(self.stream)
+        self.ctx = Context(self.local_rank, stream=self.stream.cuda_stream)
+        assert self.stream.cuda_stream != 0
+        self.pair = None
+        self.gathered = torch.empty((self.world, 2), dtype=torch.int64, device=self.dev)
+        self.flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.int32, device=self.dev)   # 256 MiB > 126 MB L2
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the plc_* path")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    workload = args.workload or default_workload(world)
-    scene = build_scene(workload, world)
-    C, M = int(scene.candidates.size), int(scene.cells.size)
-    # round-robin share of the pose list: rank r evaluates poses r, r + N, r + 2N, ... (neighbouring poses cost
-    # about the same, contiguous blocks of the lattice do not); every pair carries its global index
-    n_local = len(range(rank, C, world))
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
 
-    # a non-default torch stream (handle != 0) made current: the library launches on it, NCCL orders
-    # against it, and torch.cuda.Event records see exactly the kernels that are timed
-    stream = torch.cuda.Stream(dev)
-    torch.cuda.set_stream(stream)
-    ctx = Context(local_rank, stream=stream.cuda_stream)
-    assert stream.cuda_stream != 0
-    ctx.set_terrain(scene.terrain)
-    ctx.set_cells(scene.cells)
-    ctx.upload_candidates_strided(scene.params, scene.fixed, scene.candidates, rank, world)
-    pair = exchange.result_pair_tensor(ctx)
-    gathered = torch.empty((world, 2), dtype=torch.int64, device=dev)
-    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.int32, device=dev)   # 256 MiB > 126 MB L2
+    def host_barrier(self):
+        self.torch.cuda.synchronize(self.dev)
+        if self.world > 1:
+            self.dist.barrier(group=self.host_group)
 
-    def step():
-        ctx.run_async(False, False)
-        if world > 1:
-            exchange.all_gather_best(pair, gathered)
+    def max_over_ranks(self, v: float) -> float:
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def all_values(self, v: float) -> list:
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.dev)
+        out = self.torch.empty(self.world, dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_gather_into_tensor(out, t)
         else:
-            gathered.copy_(pair.view(1, 2))
+            out.copy_(t)
+        return [float(x) for x in out.cpu().numpy()]
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
+    def load(self, scene):
+        """Resident inputs: terrain index, cells, this rank's round-robin share of the pose list (rank r evaluates
+        poses r, r + N, ...: neighbouring poses cost about the same, contiguous blocks of the lattice do not)."""
+        self.ctx.set_terrain(scene.terrain)
+        self.ctx.set_cells(scene.cells)
+        self.ctx.upload_candidates_strided(scene.params, scene.fixed, scene.candidates, self.rank, self.world)
+        self.pair = self.exchange.result_pair_tensor(self.ctx)
 
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
+    def step(self, events=None):
+        """One sweep of the resident workload + the 16-byte exchange.  `events` = (mid,) records between the two."""
+        self.ctx.run_async(False, False)
+        if events is not None:
+            events[0].record(self.stream)
+        if self.world > 1:
+            self.exchange.all_gather_best(self.pair, self.gathered)
+        else:
+            self.gathered.copy_(self.pair.view(1, 2))
 
-    # ---- device-timed region: exactly K steps, L2 flushed between steps (outside the event pairs)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    launches0 = ctx.launch_count
-    kernel_ms = []
-    with ClockSampler(local_rank) as clocks:
-        barrier()
-        for a, b in ev:
-            flush.fill_(1)
-            a.record(stream)
-            step()
-            b.record(stream)
-            kernel_ms.append(None)
-            if args.steps <= 64:                       # per-launch duration of the dominant kernel
-                kernel_ms[-1] = ctx.last_sweep_kernel_ms()
-        barrier()
-    launches = ctx.launch_count - launches0
-    step_ms = [a.elapsed_time(b) for a, b in ev]
-    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)       # max over ranks
-    ms_per_step = float(total_ms.item()) / args.steps
-    best_score, best_index = exchange.pick_best(gathered)
-    res = ctx.fetch(scores=False)
+    def timed(self, steps: int, warmup: int, clocks: bool = False) -> dict:
+        """`steps` device-timed sweeps of the resident workload, L2 flushed before each (outside the event pairs)."""
+        E = lambda: self.torch.cuda.Event(enable_timing=True)
+        for _ in range(warmup):
+            self.step()
+        self.barrier()
+        ev = [(E(), E(), E()) for _ in range(steps)]
+        launches0 = self.ctx.launch_count
+        k_ms, fixed_ms, reduce_ms = [], [], []
+        sampler = ClockSampler(self.local_rank) if clocks else None
+        if sampler:
+            sampler.__enter__()
+        self.barrier()
+        for a, m, b in ev:
+            self.flush.fill_(1)
+            a.record(self.stream)
+            self.step((m,))
+            b.record(self.stream)
+            if steps <= 64:                       # per-launch duration of the dominant kernel and of what surrounds it
+                t = self.ctx.device_times()
+                k_ms.append(t["sweep_kernel_ms"])
+                fixed_ms.append(t["sweep_fixed_ms"])
+                reduce_ms.append(t["sweep_reduce_ms"])
+        self.barrier()
+        if sampler:
+            sampler.__exit__()
+        launches = self.ctx.launch_count - launches0
+        step_ms = [a.elapsed_time(b) for a, _, b in ev]
+        gather_ms = float(np.mean([m.elapsed_time(b) for _, m, b in ev]))
+        ms_per_step = self.max_over_ranks(sum(step_ms)) / steps
+        k_local = float(np.mean(k_ms)) if k_ms else float(np.mean(step_ms))
+        k_all = self.all_values(k_local)
+        g_all = self.all_values(gather_ms)
+        return {"ms_per_step": ms_per_step, "launches": int(launches), "k_sweep_ms_local": k_local,
+                "clocks": sampler.summary() if sampler else None,
+                "breakdown": {"k_sweep_ms": max(k_all), "fixed_ms": self.max_over_ranks(float(np.mean(fixed_ms)) if fixed_ms else 0.0),
+                              "finalize_argmax_ms": self.max_over_ranks(float(np.mean(reduce_ms)) if reduce_ms else 0.0),
+                              # the rank that arrives last does not wait in the collective: its time is the exchange itself
+                              "allgather_ms": min(g_all),
+                              "rank_imbalance_ms": max(k_all) - float(np.mean(k_all)),
+                              "k_sweep_ms_per_rank": [round(x, 4) for x in k_all]},
+                "best": self.exchange.pick_best(self.gathered)}
 
-    # ---- end to end through the C ABI with HOST buffers: set_terrain + set_cells + sweep, every step
-    h2d = scene.terrain.nbytes + scene.cells.nbytes + scene.candidates.nbytes + 40 + 96
-    d2h = n_local * 12 + 112
-    e2e_steps = max(1, min(args.steps, 5))
 
-    def pinned(a: np.ndarray) -> np.ndarray:
-        # the step's inputs live in page-locked host memory, as a node that keeps its message buffers registered would hold them
+def measure_e2e(rig: Rig, scene, steps: int) -> dict:
+    """The same sweep through the C ABI with HOST buffers every step: plc_vl_set_terrain (H2D + index build) +
+    plc_vl_set_cells + plc_vl_sweep_strided (H2D poses, kernels, D2H results), wall clock, max over ranks.
+      pinned           page-locked inputs, scores out (round 1's figure)
+      pageable         plain malloc'ed inputs — what a ROS2 subscriber's PointCloud2::data is
+      node_equivalent  pageable inputs + the outputs plc_vlnode_run_optimization asks for (per-cell flags and fixed
+                       scores: k_flags runs, node_core.cpp) — the headline `e2e.value`"""
+    torch, ctx = rig.torch, rig.ctx
+    C, M = int(scene.candidates.size), int(scene.cells.size)
+    n_local = len(range(rig.rank, C, rig.world))
+    keep = []
+
+    def pinned(a):
         t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
-        keep_alive.append(t)
+        keep.append(t)
         return t.numpy().view(a.dtype).reshape(a.shape)
 
-    keep_alive = []
-    h_terrain, h_cells, h_cands = pinned(scene.terrain), pinned(scene.cells), pinned(scene.candidates)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        ctx.set_terrain(h_terrain)
-        ctx.set_cells(h_cells)
-        r = ctx.sweep_strided(scene.params, scene.fixed, h_cands, rank, world, scores=True)
-        if world > 1:
-            exchange.all_gather_best(exchange.pack_pair(r.best_score, r.best_index, dev), gathered)
-            torch.cuda.synchronize(dev)
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = C * M / (float(e2e_s.item()) / e2e_steps)
+    def run(bufs, node: bool) -> float:
+        terr, cells, cands = bufs
+        rig.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            ctx.set_terrain(terr)
+            ctx.set_cells(cells)
+            r = ctx.sweep_strided(scene.params, scene.fixed, cands, rig.rank, rig.world, scores=True, flags=node,
+                                  fixed_scores=node)
+            if rig.world > 1:
+                rig.exchange.all_gather_best(rig.exchange.pack_pair(r.best_score, r.best_index, rig.dev), rig.gathered)
+                torch.cuda.synchronize(rig.dev)
+        return C * M / (rig.max_over_ranks(time.perf_counter() - t0) / steps)
+
+    pin = (pinned(scene.terrain), pinned(scene.cells), pinned(scene.candidates))
+    page = (np.array(scene.terrain, copy=True), np.array(scene.cells, copy=True), np.array(scene.candidates, copy=True))
+    run(page, True)                                    # warm-up of the staging buffers
+    v_pinned, v_page, v_node = run(pin, False), run(page, False), run(page, True)
+    h2d = scene.terrain.nbytes + scene.cells.nbytes + scene.candidates.nbytes + 40 + 96
+    d2h = n_local * 12 + 112 + M * 9                  # scores + covered, result block, flags + fixed scores
+    # sweep latency as SURVEY D1 defines it: wall time of the sweep call with terrain and cells resident,
+    # host pose list in, NCCL step and D2H of the results included
+    rig.barrier()
+    walls = []
+    for _ in range(max(3, steps)):
+        rig.barrier()
+        t0 = time.perf_counter()
+        r = ctx.sweep_strided(scene.params, scene.fixed, page[2], rig.rank, rig.world, scores=True)
+        if rig.world > 1:
+            rig.exchange.all_gather_best(rig.exchange.pack_pair(r.best_score, r.best_index, rig.dev), rig.gathered)
+            torch.cuda.synchronize(rig.dev)
+        walls.append(time.perf_counter() - t0)
+    wall = rig.max_over_ranks(float(np.median(walls))) * 1e3
+    return {"value": v_node, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": steps,
+            "path": "plc_vl_set_terrain + plc_vl_set_cells + plc_vl_sweep_strided with pageable host buffers, per-cell flags "
+                    "and fixed scores out (what the node core asks for)",
+            "variants": {"pinned": v_pinned, "pageable": v_page, "node_equivalent": v_node},
+            "sweep_wall_ms_resident": wall}
+
+
+def extra_block(rig: Rig, scene, workload: str, steps: int, weak: bool = False, scaling: str = "strong") -> dict:
+    rig.load(scene)
+    t = rig.timed(steps, 2)
+    C, M = int(scene.candidates.size), int(scene.cells.size)
+    return {"workload": workload_text(workload, rig.world, weak), "poses": C, "rays_per_pose": M,
+            "terrain_points": int(scene.terrain.shape[0]), "scaling": scaling, "n_gpus": rig.world, "steps": steps,
+            "sweep_latency_ms": t["ms_per_step"], "rays_per_s": C * M / (t["ms_per_step"] * 1e-3),
+            "k_sweep_ms": t["breakdown"]["k_sweep_ms"], "best_pose_index": t["best"][1], "best_score": t["best"][0]}
+
+
+def parity_block(rig: Rig, scene, n_mask_poses: int = 64) -> dict:
+    """N > 1: the rank-sharded sweep against an unsharded sweep of the same scene on rank 0 — every score bit for
+    bit, the optimum, and the visibility masks of this rank's first poses."""
+    torch, dist, ctx = rig.torch, rig.dist, rig.ctx
+    C, M = int(scene.candidates.size), int(scene.cells.size)
+    rig.load(scene)
+    rig.step()
+    rig.barrier()
+    local = ctx.fetch(scores=True, mask=False)
+    sharded_best = rig.exchange.pick_best(rig.gathered)
+    parts = [None] * rig.world
+    dist.all_gather_object(parts, (local.scores, local.covered))
+    out = None
+    if rank_zero(rig):
+        scores = np.empty(C, np.float64)
+        covered = np.empty(C, np.int32)
+        for r, (s, c) in enumerate(parts):
+            scores[r::rig.world] = s
+            covered[r::rig.world] = c
+        t0 = time.perf_counter()
+        full = ctx.sweep(scene.params, scene.fixed, scene.candidates, scores=True)
+        unsharded_ms = (time.perf_counter() - t0) * 1e3
+        k = min(n_mask_poses, len(range(0, C, rig.world)))
+        mine = ctx.sweep_strided(scene.params, scene.fixed, scene.candidates[: k * rig.world], 0, rig.world, mask=True)
+        whole = ctx.sweep(scene.params, scene.fixed, scene.candidates[: k * rig.world], mask=True)
+        mism = int(np.count_nonzero(np.unpackbits((mine.mask ^ whole.mask[:: rig.world]).view(np.uint8))))
+        out = {"against": "unsharded sweep of the same scene on rank 0", "scores_compared": C,
+               "scores_bit_equal": bool(np.array_equal(scores, full.scores)),
+               "covered_equal": bool(np.array_equal(covered, full.covered)),
+               "argmax_equal": bool(sharded_best[1] == full.best_index and sharded_best[0] == full.best_score),
+               "pairs": int(k * M), "mask_mismatches": mism, "unsharded_wall_ms": unsharded_ms}
+        assert out["scores_bit_equal"] and out["argmax_equal"] and mism == 0, out
+    rig.barrier()
+    return out
+
+
+def group_block(rig: Rig, scene, reps: int = 3) -> dict | None:
+    """plc_group_* — the single-process form the drop-in node uses (one process, N devices, library-side NCCL):
+    rank 0 alone drives all N devices while the other ranks wait; results must equal the rank-sharded ones."""
+    out = None
+    rig.load(scene)
+    rig.step()
+    rig.barrier()
+    sharded_best = rig.exchange.pick_best(rig.gathered)
+    rig.barrier()
+    rig.host_barrier()              # every GPU idle, every other rank waiting on the host from here on
+    if rank_zero(rig):
+        from pointcloud_processor_b200.context import Group
+        try:
+            with Group(list(range(rig.world))) as g:
+                g.set_terrain(scene.terrain)
+                g.set_cells(scene.cells)
+                r = g.sweep(scene.params, scene.fixed, scene.candidates)
+                walls = []
+                for _ in range(reps):
+                    t0 = time.perf_counter()
+                    r = g.sweep(scene.params, scene.fixed, scene.candidates)
+                    walls.append((time.perf_counter() - t0) * 1e3)
+            out = {"group_sweep_wall_ms": float(np.median(walls)), "devices": rig.world,
+                   "group_equals_ranks": bool(r.best_index == sharded_best[1] and r.best_score == sharded_best[0]),
+                   "best_pose_index": int(r.best_index)}
+        except Exception as e:          # reported, not fatal: the rank-sharded numbers above stand on their own
+            out = {"error": repr(e)[:200]}
+    rig.host_barrier()
+    rig.barrier()
+    return out
+
+
+def rank_zero(rig: Rig) -> bool:
+    return rig.rank == 0
+
+
+def run_ours(args) -> dict | None:
+    from pointcloud_processor_b200 import scenes
+
+    rig = Rig()
+    world, ctx = rig.world, rig.ctx
+    workload = args.workload or default_workload(world)
+    weak = workload == "cfg2" and world > 1
+    scene = build_scene(workload, world, weak=weak)
+    C, M = int(scene.candidates.size), int(scene.cells.size)
+    n_local = len(range(rig.rank, C, world))
+
+    rig.load(scene)
+    main = rig.timed(args.steps, max(args.warmup, 3), clocks=True)
+    ms_per_step = main["ms_per_step"]
+    best_score, best_index = main["best"]
+    res = ctx.fetch(scores=False)
+    grid = ctx.grid_info()[0]
+
+    e2e = measure_e2e(rig, scene, max(1, min(args.steps, 5)))
 
     # ---- roofline of the dominant kernel (k_sweep) on this rank
-    grid = ctx.grid_info()[0]
     peak, peak_src = measured_peaks()
-    k_ms = [k for k in kernel_ms if k]
-    k_avg = float(np.mean(k_ms)) if k_ms else ms_per_step
+    k_avg = main["k_sweep_ms_local"]
     alg = algorithmic_bytes(res.counters["rays"], res.counters["samples"], n_local, grid["grid_bytes"])
     achieved = alg / (k_avg * 1e-3) / 1e9
     traffic = None
@@ -309,56 +508,44 @@ def run_ours(args) -> dict | None:
         except ValueError:
             traffic = None
 
-    # ---- the north star's target configuration (configs[2]) on the same N ranks, strong-scaled
-    north = None
-    if workload == "cfg2" and not args.no_north_star:
-        s3 = scenes.build("cfg3")
-        C3, M3 = int(s3.candidates.size), int(s3.cells.size)
-        ctx.set_terrain(s3.terrain)
-        ctx.set_cells(s3.cells)
-        ctx.upload_candidates_strided(s3.params, s3.fixed, s3.candidates, rank, world)
-        for _ in range(2):
-            step()
-        barrier()
-        ev3 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(3)]
-        for a, b in ev3:
-            flush.fill_(1)
-            a.record(stream)
-            step()
-            b.record(stream)
-        barrier()
-        t3 = torch.tensor([sum(a.elapsed_time(b) for a, b in ev3) / len(ev3)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t3, op=dist.ReduceOp.MAX)
-        s3_score, s3_index = exchange.pick_best(gathered)
-        north = {"workload": f"cfg3: {WORKLOADS['cfg3']}", "poses": C3, "rays_per_pose": M3,
-                 "terrain_points": int(s3.terrain.shape[0]), "scaling": "strong", "n_gpus": world,
-                 "sweep_latency_ms": float(t3.item()), "rays_per_s": C3 * M3 / (float(t3.item()) * 1e-3),
-                 "target_ms_on_8_gpus": 50.0, "best_pose_index": s3_index, "best_score": s3_score}
+    extras = {}
+    if world == 1:
+        if workload == "cfg2" and not args.no_north_star:
+            extras["north_star_cfg3"] = extra_block(rig, scenes.build("cfg3"), "cfg3", 3)
+            extras["north_star_cfg3"]["target_ms_on_8_gpus"] = 50.0
+    else:
+        if not args.no_parity:
+            extras["parity"] = parity_block(rig, scene)
+            extras["group"] = group_block(rig, scene)
+        if workload == "cfg3" and not args.no_north_star:
+            extras["weak_cfg2_shard"] = extra_block(rig, build_scene("cfg2", world, weak=True), "cfg2", 5, weak=True,
+                                                    scaling="weak")
+            if world >= 8 or args.cfg5:
+                extras["cfg5"] = extra_block(rig, scenes.build("cfg5"), "cfg5", 3)
 
-    if world > 1:
-        dist.barrier()
-    if rank != 0:
+    rig.barrier()
+    if rig.rank != 0:
         if world > 1:
-            dist.destroy_process_group()
+            rig.dist.destroy_process_group()
         return None
 
+    strong = world > 1 and not weak
     line = {
         "metric": METRIC, "value": C * M / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
         "dtype": "f64 geometry / f32 distance test", "data": "synthetic",
-        "config": {"workload": workload_text(workload, world), "poses": C, "rays_per_pose": M,
+        "config": {"workload": workload_text(workload, world, weak), "poses": C, "rays_per_pose": M,
                    "terrain_points": int(scene.terrain.shape[0]), "rays_per_step": C * M,
                    "samples_per_ray": res.counters["samples"] / max(res.counters["rays"], 1),
                    "parallelism": f"candidate poses dealt round-robin over {world} GPU(s), grid replicated",
                    "cache": "L2 flushed (256 MiB fill) before every timed step",
                    "best_pose_index": best_index, "best_score": best_score},
         "sweep_latency_ms": ms_per_step,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "steps": e2e_steps, "path": "plc_vl_set_terrain + plc_vl_set_cells + plc_vl_sweep, pinned host buffers in, host results out"},
-        "gpu_launches": int(launches),
-        "clocks": clocks.summary(),
+        "breakdown": main["breakdown"],
+        "e2e": e2e,
+        "gpu_launches": main["launches"],
+        "clocks": main["clocks"],
         "roofline": {"bound": "hbm", "kernel": "k_sweep", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg), "kernel_ms": k_avg,
@@ -366,9 +553,11 @@ def run_ours(args) -> dict | None:
                      "note": "algorithmic bytes = 32 B/ray + 4 B/evaluated sample + 64 B/pose + grid (SURVEY D4); "
                              "the grid is L2-resident, so the kernel is issue/latency bound, not DRAM bound"},
     }
-    if north is not None:
-        line["north_star_cfg3"] = north
-    if not args.no_feeders:
+    if strong:
+        line["config"]["note"] = ("N > 1 lines strong-scale configs[2]; the N = 1 line is configs[1] (cfg2), so the same-"
+                                  "workload one-GPU time is parity.unsharded_wall_ms / north_star_cfg3 of the N = 1 line")
+    line.update({k: v for k, v in extras.items() if v is not None})
+    if world == 1 and not args.no_feeders:
         line["feeders"] = measure_feeders(ctx, scene, peak)
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
@@ -380,7 +569,7 @@ def run_ours(args) -> dict | None:
                                 "value_1_thread": v1, "sample_1_thread": f"{n1} poses ({dt1:.1f} s)",
                                 "full_sweep_extrapolated_s": C * M / v}
     if world > 1:
-        dist.destroy_process_group()
+        rig.dist.destroy_process_group()
     return line
 
 
@@ -545,7 +734,10 @@ def run_reference(args) -> dict | None:
     if rank != 0:
         return None                      # rank 0 alone runs and prints; the others exit 0
     workload = args.workload or default_workload(world)
-    scene = build_scene(workload, world)
+    weak = workload == "cfg2" and world > 1
+    # the scene comes from oracle/vl_setup.cpp (identical arrays to the plc_host_* route, checked in
+    # tests/test_oracle.py): this arm never loads the product library
+    scene = build_scene(workload, world, weak=weak, setup=oracle_setup())
     C, M = int(scene.candidates.size), int(scene.cells.size)
     threads = os.cpu_count() or 1
     steps = max(1, args.steps)
@@ -563,9 +755,9 @@ def run_reference(args) -> dict | None:
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * C * M / value, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64 geometry / f32 distance test",
-        "data": "synthetic",
-        "config": {"workload": workload_text(workload, world), "poses": C, "rays_per_pose": M,
+        "scaling": "weak" if (weak or world == 1) else "strong", "vs_baseline": None,
+        "dtype": "f64 geometry / f32 distance test", "data": "synthetic",
+        "config": {"workload": workload_text(workload, world, weak), "poses": C, "rays_per_pose": M,
                    "terrain_points": int(scene.terrain.shape[0]), "rays_per_step": C * M,
                    "note": "ms_per_step is the full sweep extrapolated from the timed sample"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
@@ -581,11 +773,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default=None,
-                    help="default: cfg2 (BASELINE.json configs[1]), one configs[1]-sized shard per GPU")
+                    help="default: cfg2 (BASELINE.json configs[1]) on one GPU, cfg3 (configs[2]) strong-scaled on N > 1")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-north-star", action="store_true", help="skip the extra configs[2] measurement")
     ap.add_argument("--no-feeders", action="store_true", help="skip the crop/voxel/merge/voxelise measurements (config 4)")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the sharded-vs-unsharded and plc_group checks")
+    ap.add_argument("--cfg5", action="store_true", help="N > 1: add the configs[4] block below 8 GPUs too")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: anything libraries write to fd 1 meanwhile (NCCL prints its version
     # banner there) is sent to stderr

@@ -182,6 +182,11 @@ void plc_dev_release(plc_ctx* ctx, void* dev_ptr);
  * visible, :727), matching the reference's empty-cloud guard (:184). */
 plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* cloud);
 /* Replaces zx120PointsCallback (virtual_lidar.cpp:194-207): the cloud observed by the fixed sensor. */
+/* terrainCallback with an EMPTY message (virtual_lidar.cpp:180-192): terrain_cloud_ becomes non-null, so
+ * runOptimization's guard (:455) passes, but no KD-tree exists — checkVisibility then answers `true` for every
+ * gated ray (:721, :727).  If no terrain has been indexed yet, sweeps run in that state instead of returning
+ * PLC_E_NO_TERRAIN; an index that exists is kept, as upstream keeps its tree. */
+plc_status plc_vl_set_terrain_unindexed(plc_ctx* ctx);
 plc_status plc_vl_set_observed(plc_ctx* ctx, const plc_cloud_view* cloud);
 /* Hands over excavation_grid_3d_ (built by generateExcavationGrid3D, :236-287). Resets cell flags. */
 plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint64_t n_cells);
@@ -268,6 +273,7 @@ plc_ctx* plc_group_ctx(plc_group* group, int i);
 const char* plc_group_last_error(const plc_group* group);
 /* plc_vl_set_* on every device (one host thread each). */
 plc_status plc_group_set_terrain(plc_group* group, const plc_cloud_view* cloud);
+plc_status plc_group_set_terrain_unindexed(plc_group* g);   /* plc_vl_set_terrain_unindexed on every device */
 plc_status plc_group_set_observed(plc_group* group, const plc_cloud_view* cloud);
 plc_status plc_group_set_cells(plc_group* group, const plc_cell* cells, uint64_t n_cells);
 /* plc_vl_sweep over the whole candidate list; the optional arrays of `out` are indexed by GLOBAL candidate. */

@@ -155,6 +155,7 @@ EXPORTS = [
     "plc_vlnode_get_cells", "plc_vlnode_get_bounds", "plc_vlnode_take_log", "plc_filter_scan", "plc_merge_clouds",
     "plc_group_create", "plc_group_destroy", "plc_group_size", "plc_group_ctx", "plc_group_last_error",
     "plc_group_set_terrain", "plc_group_set_observed", "plc_group_set_cells", "plc_group_sweep",
+    "plc_vl_set_terrain_unindexed", "plc_group_set_terrain_unindexed",
 ]
 
 _lib = None
@@ -313,6 +314,8 @@ def cloud_view(buf: np.ndarray, point_step: int | None = None, off=(0, 4, 8)) ->
     ``buf`` is either an (n, k) float32 array whose first three columns are x, y, z (point_step =
     4k) or a flat uint8 array with an explicit ``point_step``.  The caller keeps ``buf`` alive.
     """
+    if isinstance(buf, CloudView):          # already a view (e.g. DevBuffer.view(): device memory)
+        return buf
     if buf.dtype == np.uint8 and buf.ndim == 1:
         if not point_step:
             raise ValueError("point_step required for a byte buffer")

@@ -20,16 +20,14 @@
 
 namespace {
 
-// A PointCloud2 data buffer kept by value between callbacks (the message goes away).
+// What the node remembers of the last /excavated_terrain message.  The points themselves live in the context
+// (plc_vl_set_terrain copied or read them during the callback; plc_cloud_view::data may be device memory, which
+// the host must not touch): only the count and the reference's "cloud pointer is non-null" are kept.
 struct StoredCloud {
-    std::vector<unsigned char> bytes;
-    plc_cloud_view view{};
-    bool present = false;      // the reference's "cloud pointer is non-null"
+    uint64_t n_points = 0;
+    bool present = false;
     void store(const plc_cloud_view& v) {
-        const size_t n = static_cast<size_t>(v.n_points) * v.point_step;
-        bytes.assign(static_cast<const unsigned char*>(v.data), static_cast<const unsigned char*>(v.data) + n);
-        view = v;
-        view.data = bytes.data();
+        n_points = v.n_points;
         present = true;
     }
 };
@@ -56,6 +54,7 @@ struct plc_vlnode {
     plc_group* group = nullptr;      // set instead of ctx when the node drives several GPUs
     plc_ctx* setup_ctx() { return group ? plc_group_ctx(group, 0) : ctx; }
     plc_status set_terrain(const plc_cloud_view* c) { return group ? plc_group_set_terrain(group, c) : plc_vl_set_terrain(ctx, c); }
+    plc_status set_terrain_unindexed() { return group ? plc_group_set_terrain_unindexed(group) : plc_vl_set_terrain_unindexed(ctx); }
     plc_status set_observed(const plc_cloud_view* c) { return group ? plc_group_set_observed(group, c) : plc_vl_set_observed(ctx, c); }
     plc_status set_cells(const plc_cell* c, uint64_t m) { return group ? plc_group_set_cells(group, c, m) : plc_vl_set_cells(ctx, c, m); }
     // declared parameters (:66-71) and the copies updateParameters() refreshes (:155-162)
@@ -182,7 +181,8 @@ extern "C" plc_status plc_vlnode_excavation_area_callback(plc_vlnode* n, const p
 extern "C" plc_status plc_vlnode_terrain_callback(plc_vlnode* n, const plc_cloud_view* cloud) {
     if (!n || !view_ok(cloud)) return PLC_E_INVALID_ARG;
     n->terrain.store(*cloud);
-    if (cloud->n_points == 0) return PLC_OK;
+    // an empty message replaces the cloud but builds no tree: before any tree exists every ray is visible (:721, :727)
+    if (cloud->n_points == 0) return n->terrain_indexed ? PLC_OK : n->set_terrain_unindexed();
     plc_status st = n->set_terrain(cloud);
     if (st == PLC_OK) n->terrain_indexed = true;
     return st;
@@ -251,7 +251,6 @@ extern "C" plc_status plc_vlnode_run_optimization(plc_vlnode* n, plc_vlnode_resu
     out->best_score = -std::numeric_limits<double>::infinity();
     if (n->cells.empty() || !n->terrain.present || !n->have_tf) return PLC_OK;     // :455
     n->update_parameters();                                                         // :457
-    if (!n->terrain_indexed) return PLC_E_NO_TERRAIN;      // only empty terrain clouds so far: nothing to trace against
 
     plc_pose fixed{n->base[0] + kFixedOffset[0], n->base[1] + kFixedOffset[1], n->base[2] + kFixedOffset[2],
                    kFixedPitch, kFixedYaw};                                         // :347-351
@@ -262,7 +261,8 @@ extern "C" plc_status plc_vlnode_run_optimization(plc_vlnode* n, plc_vlnode_resu
     uint64_t n_cands = 0;
     // on the device, against the terrain plc_vl_set_terrain left there; an empty cloud that arrived after it
     // replaced terrain_cloud_ but not the tree (:180-192), so getGroundHeight answers 0 everywhere (:601)
-    const plc_cloud_view* ground = n->terrain.view.n_points ? nullptr : &n->terrain.view;
+    const plc_cloud_view empty_cloud{};
+    const plc_cloud_view* ground = n->terrain.n_points ? nullptr : &empty_cloud;
     plc_status st = plc_vl_generate_candidates(n->setup_ctx(), ground, &n->bounds, &fixed, n->num_candidates,
                                                n->search_radius, n->sensor_height, cands.data(), cands.size(),
                                                &n_cands);

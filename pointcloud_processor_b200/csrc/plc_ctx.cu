@@ -58,6 +58,7 @@ extern "C" void plc_params_memo(plc_params* p) {
 }
 
 extern "C" plc_status plc_ctx_create(int device, void* stream, plc_ctx** out) {
+    PLC_RANGE();
     if (!out) return PLC_E_INVALID_ARG;
     *out = nullptr;
     int n = 0;
@@ -226,6 +227,7 @@ extern "C" void plc_dev_free(plc_ctx* c, void* dev_ptr) {
 }
 
 extern "C" plc_status plc_dev_upload(plc_ctx* c, void* dev_dst, const void* host_src, uint64_t bytes) {
+    PLC_RANGE();
     if (!c || (bytes && (!dev_dst || !host_src))) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(c, cudaSetDevice(c->device));
     cudaPointerAttributes attr{};
@@ -242,6 +244,7 @@ extern "C" plc_status plc_dev_upload(plc_ctx* c, void* dev_dst, const void* host
 }
 
 extern "C" plc_status plc_dev_download(plc_ctx* c, void* host_dst, const void* dev_src, uint64_t bytes) {
+    PLC_RANGE();
     if (!c || (bytes && (!host_dst || !dev_src))) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(c, cudaSetDevice(c->device));
     PLC_CUDA_TRY(c, cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, c->stream));

@@ -132,6 +132,7 @@ extern "C" plc_status plc_drivable_area(plc_ctx* ctx, const plc_cloud_view* scan
                                         double robot_x, double robot_y, double start_x, double start_y,
                                         const plc_drivable_params* prm, int8_t* out_grid, uint64_t capacity,
                                         plc_drivable_info* info) {
+    PLC_RANGE();
     if (!ctx || !cloud_view_ok(scan) || !prm || !info || (t == nullptr) != (q == nullptr)) return PLC_E_INVALID_ARG;
     if (!(prm->grid_resolution > 0) || !(prm->map_width >= 0) || !(prm->map_height >= 0)) return PLC_E_INVALID_ARG;
     if (scan->n_points > 0x7fffff00ull) return PLC_E_INVALID_ARG;

@@ -442,6 +442,7 @@ extern "C" plc_status plc_excavate(plc_ctx* ctx, const plc_cloud_view* matched, 
                                    const double* base_q, const plc_excavation_params* prm, void* out_terrain,
                                    uint64_t cap_terrain, uint64_t* n_terrain, void* out_area, uint64_t cap_area,
                                    uint64_t* n_area, plc_excavation_info* info) {
+    PLC_RANGE();
     if (!ctx || !cloud_view_ok(matched) || !base_t || !base_q || !params_ok(prm) || !n_terrain || !n_area)
         return PLC_E_INVALID_ARG;
     if (matched->n_points > 0x7fffff00ull) return PLC_E_INVALID_ARG;

@@ -191,6 +191,7 @@ using namespace plc;
 
 extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const plc_crop_box* box, double leaf,
                                  void* out_xyz16, uint64_t capacity, uint64_t* n_out, uint64_t* n_cropped) {
+    PLC_RANGE();
     if (!ctx || !cloud_view_ok(in) || !box || !n_out || (capacity && !out_xyz16)) return PLC_E_INVALID_ARG;
     if (in->n_points > 0x7ffffff0ull) return PLC_E_INVALID_ARG;
     *n_out = 0;

@@ -105,6 +105,7 @@ plc_status nccl_fail(plc_group* g, const char* what, int rc) {
 }  // namespace
 
 extern "C" plc_status plc_group_create(const int* devices, int n_devices, plc_group** out) {
+    PLC_RANGE();
     if (!out || n_devices < 1 || n_devices > 64 || !devices) return PLC_E_INVALID_ARG;
     *out = nullptr;
     for (int i = 0; i < n_devices; ++i)
@@ -165,24 +166,35 @@ extern "C" plc_ctx* plc_group_ctx(plc_group* g, int i) {
 extern "C" const char* plc_group_last_error(const plc_group* g) { return g ? g->last_error.c_str() : ""; }
 
 extern "C" plc_status plc_group_set_terrain(plc_group* g, const plc_cloud_view* cloud) {
+    PLC_RANGE();
     if (!g) return PLC_E_INVALID_ARG;
     return on_all(g, [&](int i) { return plc_vl_set_terrain(g->ctx[i], cloud); });
 }
+extern "C" plc_status plc_group_set_terrain_unindexed(plc_group* g) {
+    if (!g) return PLC_E_INVALID_ARG;
+    return on_all(g, [&](int i) { return plc_vl_set_terrain_unindexed(g->ctx[i]); });
+}
 extern "C" plc_status plc_group_set_observed(plc_group* g, const plc_cloud_view* cloud) {
+    PLC_RANGE();
     if (!g) return PLC_E_INVALID_ARG;
     return on_all(g, [&](int i) { return plc_vl_set_observed(g->ctx[i], cloud); });
 }
 extern "C" plc_status plc_group_set_cells(plc_group* g, const plc_cell* cells, uint64_t n_cells) {
+    PLC_RANGE();
     if (!g) return PLC_E_INVALID_ARG;
     return on_all(g, [&](int i) { return plc_vl_set_cells(g->ctx[i], cells, n_cells); });
 }
 
 extern "C" plc_status plc_group_sweep(plc_group* g, const plc_params* prm, const plc_pose* fixed, const plc_pose* cands,
                                       uint64_t n_cands, plc_sweep_out* out) {
+    PLC_RANGE();
     if (!g || !out) return PLC_E_INVALID_ARG;
     const int n = (int)g->ctx.size();
+    int launched = 0;           // devices whose sweep is in flight
+    // a failure on one device must not leave the others running a sweep nobody collects: wait for them first
     auto fail = [&](int i, plc_status st) {
         g->last_error = "device " + std::to_string(g->dev[i]) + ": " + plc_last_error(g->ctx[i]);
+        for (int k = 0; k < launched; ++k) plc_ctx_sync(g->ctx[k]);
         return st;
     };
     // upload + launch on every device without waiting for any of them
@@ -192,23 +204,30 @@ extern "C" plc_status plc_group_sweep(plc_group* g, const plc_params* prm, const
         // the stale-flag bytes depend on the whole candidate list, which every context holds: device 0 makes them
         st = plc_vl_run_async(g->ctx[i], out->mask != nullptr, i == 0 && out->cell_flags != nullptr);
         if (st != PLC_OK) return fail(i, st);
+        launched = i + 1;
     }
     // the one exchange: all-gather of {best_score, best_global_index}, ordered after the sweep on each stream
     if (n > 1) {
-        int rc = g->nccl.GroupStart();
-        if (rc != 0) return nccl_fail(g, "ncclGroupStart", rc);
+        // everything that can fail without NCCL is done before the NCCL group opens, and the group is closed on
+        // every path: an open group would leave the communicators unusable
+        std::vector<void*> pair(n, nullptr);
         for (int i = 0; i < n; ++i) {
-            void* pair = nullptr;
-            plc_status st = plc_vl_result_device_ptr(g->ctx[i], &pair);
+            plc_status st = plc_vl_result_device_ptr(g->ctx[i], &pair[i]);
             if (st != PLC_OK) return fail(i, st);
-            rc = g->nccl.AllGather(pair, g->gathered[i], sizeof(Pair), kNcclInt8, g->comms[i], g->ctx[i]->stream);
-            if (rc != 0) {
-                g->nccl.GroupEnd();
-                return nccl_fail(g, "ncclAllGather", rc);
-            }
         }
+        int rc = g->nccl.GroupStart();
+        if (rc != 0) {
+            for (int k = 0; k < launched; ++k) plc_ctx_sync(g->ctx[k]);
+            return nccl_fail(g, "ncclGroupStart", rc);
+        }
+        int rc_gather = 0;
+        for (int i = 0; i < n && rc_gather == 0; ++i)
+            rc_gather = g->nccl.AllGather(pair[i], g->gathered[i], sizeof(Pair), kNcclInt8, g->comms[i], g->ctx[i]->stream);
         rc = g->nccl.GroupEnd();
-        if (rc != 0) return nccl_fail(g, "ncclGroupEnd", rc);
+        if (rc_gather != 0 || rc != 0) {
+            for (int k = 0; k < launched; ++k) plc_ctx_sync(g->ctx[k]);
+            return rc_gather != 0 ? nccl_fail(g, "ncclAllGather", rc_gather) : nccl_fail(g, "ncclGroupEnd", rc);
+        }
     }
     // results: each shard's arrays are interleaved straight into the caller's global arrays
     plc_sweep_out total = *out;

@@ -10,6 +10,19 @@
 
 #include "plc.h"
 
+// NVTX ranges around the C-ABI entry points (SURVEY §5 tracing row): header-only NVTX 3, a no-op unless a
+// profiler injects its library, so timelines show which plc_* call the kernels below belong to.
+#include <nvtx3/nvToolsExt.h>
+namespace plc {
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
+}  // namespace plc
+#define PLC_RANGE() plc::NvtxRange plc_nvtx_range_(__func__)
+
 #define PLC_CUDA_TRY(ctx, expr)                                                              \
     do {                                                                                     \
         cudaError_t e__ = (expr);                                                            \
@@ -197,6 +210,8 @@ struct plc_ctx {
     // occupancy refinement policy (plc_sweep.cu pick_refine): rays swept over the current terrain so far, and the
     // size of the last sweep as the forecast for a terrain that has just arrived
     uint64_t terrain_rays_accum = 0, last_sweep_rays = 0;
+    bool terrain_unindexed = false;   // plc_vl_set_terrain_unindexed: a terrain cloud exists, no index does (every ray visible)
+    bool sweep_attr_set = false;      // k_sweep's shared-memory carve-out has been set on this context's device
     cudaEvent_t ev_run_begin = nullptr, ev_run_end = nullptr;       // around all kernels of plc_vl_run_async
     bool sweep_timed = false;
     plc::DevTimer timer;         // kernels of the call in progress
@@ -259,6 +274,14 @@ inline plc_status stage_bytes(plc_ctx* ctx, const void* data, size_t bytes, cons
     cudaPointerAttributes attr{};
     if (cudaPointerGetAttributes(&attr, data) == cudaSuccess &&
         (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged)) {
+        if (attr.type == cudaMemoryTypeDevice && attr.device != ctx->device) {
+            // another GPU's buffer (plc_group_* hand the same view to every context): kernels here cannot
+            // dereference it without peer access, so it is copied device to device into this context's staging
+            PLC_CUDA_TRY(ctx, ctx->upload.reserve(bytes));
+            PLC_CUDA_TRY(ctx, cudaMemcpyPeerAsync(ctx->upload.ptr, ctx->device, data, attr.device, bytes, ctx->stream));
+            *dev = ctx->upload.as<unsigned char>();
+            return PLC_OK;
+        }
         *dev = static_cast<const unsigned char*>(data);
         return PLC_OK;
     }

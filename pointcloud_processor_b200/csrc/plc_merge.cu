@@ -72,6 +72,7 @@ using namespace plc;
 
 extern "C" plc_status plc_merge(plc_ctx* ctx, const plc_merge_src* srcs, int n_src, void* out_merged,
                                 uint64_t capacity, uint64_t* n_out, void* const* out_each, uint64_t* n_each) {
+    PLC_RANGE();
     if (!ctx || n_src < 0 || (n_src && !srcs) || !n_out) return PLC_E_INVALID_ARG;
     *n_out = 0;
     uint64_t total = 0, raw_bytes = 0;

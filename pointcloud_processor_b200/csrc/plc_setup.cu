@@ -326,6 +326,7 @@ k_emit_poses(unsigned n_slots, const uint32_t* __restrict__ keep, const uint32_t
 using namespace plc;
 
 extern "C" plc_status plc_vl_compute_normals(plc_ctx* ctx, const plc_cloud_view* area, double radius, float* normals_out) {
+    PLC_RANGE();
     if (!ctx || !cloud_view_ok(area) || !normals_out || !(radius > 0) || area->n_points > 0x7fffff00ull)
         return PLC_E_INVALID_ARG;
     const size_t n = area->n_points;
@@ -357,6 +358,7 @@ extern "C" plc_status plc_vl_compute_normals(plc_ctx* ctx, const plc_cloud_view*
 extern "C" plc_status plc_vl_generate_cells(plc_ctx* ctx, const plc_cloud_view* area, const float* normals, double res,
                                             int32_t layers, double normal_radius, plc_cell* out, uint64_t capacity,
                                             uint64_t* n_out, plc_grid_bounds* bounds) {
+    PLC_RANGE();
     if (!ctx || !cloud_view_ok(area) || !n_out || !(res > 0) || (capacity && !out) || area->n_points > 0x7fffff00ull)
         return PLC_E_INVALID_ARG;
     if (normals && !(normal_radius > 0)) return PLC_E_INVALID_ARG;
@@ -439,6 +441,7 @@ extern "C" plc_status plc_vl_generate_cells(plc_ctx* ctx, const plc_cloud_view* 
 extern "C" plc_status plc_vl_generate_candidates(plc_ctx* ctx, const plc_cloud_view* terrain, const plc_grid_bounds* gb,
                                                  const plc_pose* fixed, int32_t num_candidates, double search_radius,
                                                  double sensor_height, plc_pose* out, uint64_t capacity, uint64_t* n_out) {
+    PLC_RANGE();
     if (!ctx || !gb || !fixed || !n_out || (capacity && !out)) return PLC_E_INVALID_ARG;
     if (terrain && (!cloud_view_ok(terrain) || terrain->n_points > 0x7fffff00ull)) return PLC_E_INVALID_ARG;
     *n_out = 0;

@@ -989,9 +989,11 @@ plc_status upload_sample_table(plc_ctx* ctx, const plc_params* p) {
 using namespace plc;
 
 extern "C" plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* cloud) {
+    PLC_RANGE();
     if (!ctx || !cloud_view_ok(cloud)) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     ctx->timer.reset();
+    ctx->terrain_unindexed = false;
     PLC_TRY(voxel_set_cloud(ctx, ctx->terrain, cloud));
     // build for the node's default block radius right away; a sweep with other parameters rebuilds
     plc_params d;
@@ -1003,7 +1005,14 @@ extern "C" plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* clo
     return PLC_OK;
 }
 
+extern "C" plc_status plc_vl_set_terrain_unindexed(plc_ctx* ctx) {
+    if (!ctx) return PLC_E_INVALID_ARG;
+    if (ctx->terrain.n_input == 0) ctx->terrain_unindexed = true;     // an index that exists stays (:183-191)
+    return PLC_OK;
+}
+
 extern "C" plc_status plc_vl_set_observed(plc_ctx* ctx, const plc_cloud_view* cloud) {
+    PLC_RANGE();
     if (!ctx || !cloud_view_ok(cloud)) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     ctx->timer.reset();
@@ -1017,6 +1026,7 @@ extern "C" plc_status plc_vl_set_observed(plc_ctx* ctx, const plc_cloud_view* cl
 }
 
 extern "C" plc_status plc_vl_set_cells(plc_ctx* ctx, const plc_cell* cells, uint64_t n_cells) {
+    PLC_RANGE();
     if (!ctx || (n_cells && !cells) || n_cells > 0x7fffff00ull) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     ctx->n_cells = 0;
@@ -1086,6 +1096,7 @@ plc_status upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose
 extern "C" plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
                                                const plc_pose* cands, uint64_t n_cands, uint64_t cand_begin,
                                                uint64_t cand_end) {
+    PLC_RANGE();
     if (!ctx || !params_ok(prm) || !fixed || (n_cands && !cands)) return PLC_E_INVALID_ARG;
     if (cand_begin > cand_end || cand_end > n_cands || n_cands > 0x7fffff00ull) return PLC_E_INVALID_ARG;
     return upload_candidates(ctx, prm, fixed, cands, n_cands, cand_begin, 1, cand_end - cand_begin);
@@ -1094,6 +1105,7 @@ extern "C" plc_status plc_vl_upload_candidates(plc_ctx* ctx, const plc_params* p
 extern "C" plc_status plc_vl_upload_candidates_strided(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed,
                                                        const plc_pose* cands, uint64_t n_cands, uint64_t first,
                                                        uint64_t stride) {
+    PLC_RANGE();
     if (!ctx || !params_ok(prm) || !fixed || (n_cands && !cands)) return PLC_E_INVALID_ARG;
     if (stride == 0 || stride > 0xffff || n_cands > 0x7fffff00ull) return PLC_E_INVALID_ARG;
     const uint64_t n_local = first < n_cands ? (n_cands - first + stride - 1) / stride : 0;
@@ -1101,10 +1113,11 @@ extern "C" plc_status plc_vl_upload_candidates_strided(plc_ctx* ctx, const plc_p
 }
 
 extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_flags) {
+    PLC_RANGE();
     if (!ctx) return PLC_E_INVALID_ARG;
     if (!ctx->have_job) return PLC_E_NO_CANDIDATES;
     if (ctx->n_cells == 0) return PLC_E_NO_CELLS;                       // :455 excavation_grid_3d_.empty()
-    if (ctx->terrain.n_input == 0) return PLC_E_NO_TERRAIN;             // :455 !terrain_cloud_
+    if (ctx->terrain.n_input == 0 && !ctx->terrain_unindexed) return PLC_E_NO_TERRAIN;   // :455 !terrain_cloud_
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const plc_params& p = ctx->prm;
     const uint64_t rays_ahead = ctx->n_local * ctx->n_cells;
@@ -1186,11 +1199,10 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
         k_pose_prep<<<(n_local + 127) / 128, 128, 0, s>>>(P, ctx->cands.as<plc_pose>(), (unsigned)ctx->cand_begin,
                                                           (unsigned)ctx->cand_stride, n_local, ctx->pose_aux.as<PoseAux>());
         // measured on cfg2/cfg3: a 50 % carve-out (L1 kept large) beats full occupancy of the 5.25 KB blocks
-        static bool carveout_set = false;
-        if (!carveout_set) {
+        if (!ctx->sweep_attr_set) {          // a per-device attribute: once per context, not per process
             const char* ev = getenv("PLC_DEV_CARVEOUT");
             cudaFuncSetAttribute(k_sweep, cudaFuncAttributePreferredSharedMemoryCarveout, ev ? atoi(ev) : 50);
-            carveout_set = true;
+            ctx->sweep_attr_set = true;
         }
         cudaEventRecord(ctx->ev_sweep_begin, s);
         k_sweep<<<(n_local * tiles + kSweepWarps - 1) / kSweepWarps, 32 * kSweepWarps, 0, s>>>(
@@ -1266,6 +1278,7 @@ extern "C" plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out) { return pl
 
 extern "C" plc_status plc_vl_sweep(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed, const plc_pose* cands,
                                    uint64_t n_cands, uint64_t cand_begin, uint64_t cand_end, plc_sweep_out* out) {
+    PLC_RANGE();
     if (!out) return PLC_E_INVALID_ARG;
     PLC_TRY(plc_vl_upload_candidates(ctx, prm, fixed, cands, n_cands, cand_begin, cand_end));
     PLC_TRY(plc_vl_run_async(ctx, out->mask != nullptr, out->cell_flags != nullptr));
@@ -1274,6 +1287,7 @@ extern "C" plc_status plc_vl_sweep(plc_ctx* ctx, const plc_params* prm, const pl
 
 extern "C" plc_status plc_vl_sweep_strided(plc_ctx* ctx, const plc_params* prm, const plc_pose* fixed, const plc_pose* cands,
                                            uint64_t n_cands, uint64_t first, uint64_t stride, plc_sweep_out* out) {
+    PLC_RANGE();
     if (!out) return PLC_E_INVALID_ARG;
     PLC_TRY(plc_vl_upload_candidates_strided(ctx, prm, fixed, cands, n_cands, first, stride));
     PLC_TRY(plc_vl_run_async(ctx, out->mask != nullptr, out->cell_flags != nullptr));

@@ -184,7 +184,7 @@ def fixed_pose() -> np.ndarray:
     return f
 
 
-def make_cells(area, normals, m_target: int | None, res: float, layers: int | None):
+def make_cells(area, normals, m_target: int | None, res: float, layers: int | None, host_generate_cells=host_generate_cells):
     if layers is None:
         # smallest vertical_layers whose lattice yields at least m_target valid cells
         lo, hi = 1, 8
@@ -204,10 +204,12 @@ def make_cells(area, normals, m_target: int | None, res: float, layers: int | No
         if cells.size < m_target:
             raise RuntimeError(f"lattice res={res} layers={layers} gives {cells.size} < {m_target} cells")
         cells = cells[:m_target].copy()    # truncate in reference order (D1)
+    make_cells.last_layers = layers
     return cells, bounds
 
 
-def make_candidates(terrain_xyz, bounds, fixed, px: int, pz: int, search_radius=3.0, base_height=1.1):
+def make_candidates(terrain_xyz, bounds, fixed, px: int, pz: int, search_radius=3.0, base_height=1.1,
+                    host_generate_candidates=host_generate_candidates):
     layers = [host_generate_candidates(terrain_xyz, bounds, fixed, px * px, search_radius, base_height + 0.4 * k)
               for k in range(pz)]
     return np.concatenate(layers) if layers else np.zeros(0, A.POSE_DTYPE)
@@ -226,20 +228,26 @@ CONFIGS = {
     "cfg3": dict(shape="L", n=1_000_000, px=64, pz=4, m=32 * 1800, seed=3, side=30.0, res=0.03, layers=None),
     "cfg5": dict(shape="L", n=4_000_000, px=128, pz=8, m=64 * 2048, seed=6, side=40.0, res=0.025, layers=None),
 }
+# what the search for the smallest sufficient vertical_layers finds (checked by tests/test_oracle.py); a caller whose
+# cell generator is slow (the single-threaded oracle in bench.py's reference arm) passes these instead of searching
+LAYERS_FOUND = {"cfg1": 18, "cfg2": 74, "cfg3": 50, "cfg5": 99}
 
 
-def build(name: str, **override) -> Scene:
+def build(name: str, setup=None, **override) -> Scene:
+    """`setup` = (generate_cells, generate_candidates) replaces the plc_host_* steps with functions of the same
+    signature (bench.py's reference arm passes the oracle's, so that it never loads the product library)."""
     cfg = dict(CONFIGS[name])
     cfg.update(override)
+    gen_cells, gen_cands = setup if setup is not None else (host_generate_cells, host_generate_candidates)
     terr = terrain(cfg["shape"], cfg["n"], cfg["seed"], cfg["side"])
     area, normals = excavation_area(cfg["shape"], 0.05)
     fixed = fixed_pose()
-    cells, bounds = make_cells(area, normals, cfg["m"], cfg["res"], cfg["layers"])
-    cands = make_candidates(terr, bounds, fixed, cfg["px"], cfg["pz"])
+    cells, bounds = make_cells(area, normals, cfg["m"], cfg["res"], cfg["layers"], gen_cells)
+    cands = make_candidates(terr, bounds, fixed, cfg["px"], cfg["pz"], host_generate_candidates=gen_cands)
     prm = A.default_params()
     meta = dict(cfg)
     meta.update(layers_used=int(round((bounds.max_z - bounds.min_z) / max(cells["z"][1] - cells["z"][0], 1e-12))) if cells.size > 1 and cells["x"][0] == cells["x"][1] else None,
-                n_cells=int(cells.size), n_candidates=int(cands.size), n_terrain=int(terr.shape[0]),
+                layers_found=int(make_cells.last_layers), n_cells=int(cells.size), n_candidates=int(cands.size), n_terrain=int(terr.shape[0]),
                 n_area=int(area.shape[0]))
     return Scene(name, terr, area, normals, cells, bounds, fixed, cands, prm, meta)
 

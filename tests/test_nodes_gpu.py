@@ -119,6 +119,74 @@ def test_virtual_lidar_node_cycle(ctx, shape, n_pts, num_candidates):
     node.close()
 
 
+def test_node_callbacks_take_device_buffers(ctx):
+    """Every plc_cloud_view::data may be device memory (plc.h, INTEGRATION.md): the node core must hand the pointer
+    on without reading it on the host (StoredCloud used to memcpy from it)."""
+    from pointcloud_processor_b200.context import DevBuffer
+    terrain = xyzrgb_records(scenes.terrain("rect", 30_000, seed=22, side=24.0))
+    area = xyzrgb_records(scenes.excavation_area("rect", 0.05)[0])
+    obs = xyzrgb_records((area[::9, :3] + np.float32(0.02)).astype(np.float32))
+
+    def cycle(make):
+        node = VirtualLidarNode(ctx)
+        node.set_parameter("num_candidates", 36)
+        node.excavation_area_callback(make(area))
+        node.terrain_callback(make(terrain))
+        node.zx120_points_callback(make(obs))
+        node.set_base_transform((0.0, 0.0, 0.0))
+        res = node.run_optimization()
+        out = (res.ran, res.best_score, res.fixed_total, (res.best.x, res.best.y, res.best.z), node.cells()[1].copy(),
+               node.candidates().copy())
+        node.close()
+        return out
+
+    keep = []
+
+    def on_device(rec):
+        b = DevBuffer(ctx, rec.nbytes).upload(rec)
+        keep.append(b)
+        return b.view(rec.shape[0], 32)
+
+    host, dev = cycle(lambda rec: rec), cycle(on_device)
+    assert host[0] == dev[0] == 1
+    assert host[1] == dev[1] and host[2] == dev[2] and host[3] == dev[3]
+    assert np.array_equal(host[4], dev[4]) and np.array_equal(host[5], dev[5])
+    for b in keep:
+        b.free()
+
+
+def test_node_with_only_empty_terrain_messages(ctx):
+    """Upstream's guard is `!terrain_cloud_` (:455): an EMPTY /excavated_terrain message makes the pointer non-null
+    while no KD-tree exists, so the cycle runs with every gated ray visible (:721, :727) and ground height 0 (:601)."""
+    area, _ = scenes.excavation_area("rect", 0.05)
+    node = VirtualLidarNode(ctx)
+    node.set_parameter("num_candidates", 49)
+    node.excavation_area_callback(xyzrgb_records(area))
+    node.set_base_transform((0.0, 0.0, 0.0))
+    assert node.run_optimization().ran == 0                      # no terrain message at all: guard holds
+    node.terrain_callback(np.zeros((0, 8), np.float32))
+    res = node.run_optimization()
+    assert res.ran == 1
+    cells, flags = node.cells()
+    cands = node.candidates()
+    assert cands.size > 0 and np.all(cands["z"] == 0.0 + 1.1)    # getGroundHeight -> 0.0
+    fixed = np.zeros(1, A.POSE_DTYPE)
+    fixed["x"], fixed["y"], fixed["z"], fixed["pitch"] = 0.4, 0.5, 3.5, -np.pi / 6
+    ref = O.sweep(None, None, cells, A.default_params(), fixed, cands)
+    assert ref["counters"]["rays_visible"] == ref["counters"]["rays_gated_in"] > 0
+    assert res.best_score == pytest.approx(ref["best_score"], rel=1e-12)
+    assert np.array_equal(flags, ref["flags"])
+    # a real terrain arrives, then another empty message: the index stays (upstream keeps its tree), heights go to 0
+    terrain = scenes.terrain("rect", 30_000, seed=23, side=24.0)
+    node.terrain_callback(xyzrgb_records(terrain))
+    with_terrain = node.run_optimization()
+    assert with_terrain.best_score < res.best_score              # occlusion now counts
+    node.terrain_callback(np.zeros((0, 8), np.float32))
+    node.run_optimization()
+    assert np.all(node.candidates()["z"] == 1.1)
+    node.close()
+
+
 def test_filter_and_merger_nodes(ctx):
     from test_filter_merge_gpu import scan
     pts = scan(120_000, 8)
