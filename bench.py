@@ -559,6 +559,7 @@ def run_ours(args) -> dict | None:
     line.update({k: v for k, v in extras.items() if v is not None})
     if world == 1 and not args.no_feeders:
         line["feeders"] = measure_feeders(ctx, scene, peak)
+        line["feeders_large"] = measure_feeders_large(ctx, peak)
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         v, n, dt = cpu_reference_sample(scene, args.cpu_budget, threads)
@@ -659,6 +660,60 @@ def measure_feeders(ctx, scene, peak, reps: int = 5) -> dict:
         r["cpu_port_ms"] = (time.perf_counter() - t0) * 1e3
     out["drivable_area"] = r
     out["launch_graph"] = measure_launch_graph(ctx)
+    return out
+
+
+def measure_feeders_large(ctx, peak, reps: int = 4) -> dict:
+    """The same secondary kernels at a size where launch latency amortises: an 8 M-point scan through
+    crop + voxel downsample at leaf 0.05, two 4 M-point clouds through the merger's transform, a 4 M-point terrain
+    through the voxeliser.  Algorithmic bytes per SURVEY D4 (sort traffic excluded => a lower bound for K7)."""
+    from pointcloud_processor_b200 import scenes
+    from pointcloud_processor_b200.nodes import filter_scan, merge_clouds
+    rng = np.random.default_rng(41)
+    n = 8_000_000
+    scan = np.ones((n, 4), np.float32)
+    scan[:, 0] = rng.uniform(-6.0, 24.0, n)
+    scan[:, 1] = rng.uniform(-14.0, 14.0, n)
+    scan[:, 2] = 0.15 * np.sin(0.4 * scan[:, 0]) * np.cos(0.3 * scan[:, 1]) + rng.normal(0.0, 0.02, n).astype(np.float32) - 2.0
+
+    def best(fn, key):
+        ks, ws, out = [], [], None
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            out = fn()
+            ws.append((time.perf_counter() - t0) * 1e3)
+            ks.append(ctx.device_times()[key])
+        return out, float(np.median(ks[1:])), float(np.median(ws[1:]))
+
+    def row(kernel_ms, wall_ms, alg_bytes, units):
+        gbs = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+        return {"kernel_ms": kernel_ms, "wall_ms": wall_ms, "points_per_s": units / (kernel_ms * 1e-3) if kernel_ms > 0 else 0.0,
+                "algorithmic_bytes": int(alg_bytes), "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / peak}
+
+    out = {"config": "8M-point scan -> crop 15/10/10 -> voxel 0.05; 2 x 4M-point clouds -> merge; 4M-point terrain -> voxelise"}
+    p = scan[:, :3].astype(np.float64)
+    m_crop = int(np.count_nonzero((p[:, 0] > 0) & (p[:, 0] < 15) & (np.abs(p[:, 1]) < 10) & (p[:, 2] > -1.5) & (p[:, 2] < 10)))
+    del p
+    f, k_ms, w_ms = best(lambda: filter_scan(ctx, scan, leaf=0.0), "filter_ms")
+    out["crop_only"] = row(k_ms, w_ms, n * 12 + m_crop * 12, n)
+    out["crop_only"].update(points_in=n, cropped=m_crop)
+    f, k_ms, w_ms = best(lambda: filter_scan(ctx, scan, leaf=0.05), "filter_ms")
+    v = int(f.shape[0])
+    out["filter"] = row(k_ms, w_ms, n * 12 + m_crop * 12 + m_crop * 12 + v * 12, n)
+    out["filter"].update(points_in=n, cropped=m_crop, voxels=v,
+                         note="K7 sorts (key, index) pairs in 8-bit passes: each pass moves 24 B per cropped point on top of "
+                              "the algorithmic bytes")
+    half = scan[: n // 2]
+    ident_t, ident_q = np.array([1.0, 2.0, 0.5]), np.array([0.0, 0.0, 0.38268343, 0.92387953])
+    (merged, _, _), k_ms, w_ms = best(lambda: merge_clouds(ctx, dict(cloud=half, t=ident_t, q=ident_q),
+                                                          dict(cloud=scan[n // 2:], t=ident_t, q=ident_q)), "merge_ms")
+    mv = int(merged.shape[0])
+    out["merge"] = row(k_ms, w_ms, mv * 12 + mv * 16 * 2, mv)
+    out["merge"]["points_in"] = mv
+    terr = scenes.terrain("L", 4_000_000, 6, 40.0)
+    _, k_ms, w_ms = best(lambda: ctx.set_terrain(terr), "set_terrain_ms")
+    out["voxelise_terrain"] = row(k_ms, w_ms, terr.shape[0] * (12 + 16), terr.shape[0])
+    out["voxelise_terrain"]["points_in"] = int(terr.shape[0])
     return out
 
 

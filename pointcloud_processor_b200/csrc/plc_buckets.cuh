@@ -274,9 +274,9 @@ plc_status build_buckets(plc_ctx* ctx, const float4* pts, size_t n, const Bounds
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(start, 0, (n_buckets + 1) * sizeof(uint32_t), s));
     if (n) {
         k_bucket_keys<<<blocks_for(n, 256), 256, 0, s>>>(pts, (unsigned)n, G, keys_a, vals_a, start);
-        ctx->launches += scan_exclusive_u32(start, n_buckets + 1, ctx->su_tmp.as<uint32_t>(), s);
+        ctx->launches += scan_exclusive_u32(start, n_buckets + 1, ctx->lb, s);
         const int where = radix_sort_pairs(keys_a, vals_a, keys_b, vals_b, (unsigned)n, key_bits, ctx->su_table.as<uint32_t>(),
-                                           ctx->su_tmp.as<uint32_t>(), s, &ctx->launches);
+                                           ctx->lb, s, &ctx->launches);
         k_gather_points<<<blocks_for(n, 256), 256, 0, s>>>(pts, where ? vals_b : vals_a, (unsigned)n, ctx->su_sorted.as<float4>());
         ctx->launches += 2;
     }
@@ -306,7 +306,7 @@ plc_status scan_flags(plc_ctx* ctx, const uint32_t* flags, uint32_t* slot, size_
     PLC_CUDA_TRY(ctx, ctx->su_tmp.reserve(scan_tmp_bytes(n + 1) + 64));
     k_copy_u32<<<blocks_for(n, 256), 256, 0, s>>>(flags, n, slot);
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(slot + n, 0, sizeof(uint32_t), s));
-    ctx->launches += 1 + scan_exclusive_u32(slot, n + 1, ctx->su_tmp.as<uint32_t>(), s);
+    ctx->launches += 1 + scan_exclusive_u32(slot, n + 1, ctx->lb, s);
     uint32_t* host = static_cast<uint32_t*>(ctx->pinned_reserve(sizeof(uint32_t)));
     if (!host) return PLC_E_OOM;
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(host, slot + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));

@@ -78,7 +78,8 @@ extern "C" plc_status plc_ctx_create(int device, void* stream, plc_ctx** out) {
     }
     if (c->result.reserve(sizeof(plc::SweepResult)) != cudaSuccess || !c->pinned_reserve(1 << 16) ||
         cudaEventCreate(&c->ev_sweep_begin) != cudaSuccess || cudaEventCreate(&c->ev_sweep_end) != cudaSuccess ||
-        cudaEventCreate(&c->ev_run_begin) != cudaSuccess || cudaEventCreate(&c->ev_run_end) != cudaSuccess) {
+        cudaEventCreate(&c->ev_run_begin) != cudaSuccess || cudaEventCreate(&c->ev_run_end) != cudaSuccess ||
+        c->lb.reserve(size_t(1) << 20) != cudaSuccess) {     // status words for scans of up to 2^31 items (8 MB)
         plc_ctx_destroy(c);
         return PLC_E_OOM;
     }
@@ -90,6 +91,7 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    c->lb.release();
     c->terrain.release();
     c->observed.release();
     plc::DevBuf* bufs[] = {&c->upload, &c->scratch, &c->cells, &c->cells_f, &c->tile_boxes, &c->cell_flags, &c->fixed_scores, &c->cands,

@@ -507,9 +507,9 @@ extern "C" plc_status plc_excavate(plc_ctx* ctx, const plc_cloud_view* matched, 
     ctx->timer.begin(s);
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(P.area_off, 0, plan_words * sizeof(uint32_t), s));
     k_plan_lattice<<<blocks_for(n_entries, 256), 256, 0, s>>>(E, (unsigned)n_entries, P);
-    ctx->launches += 1 + scan_exclusive_u32(P.area_off, n_entries + 1, ctx->su_tmp.as<uint32_t>(), s);
-    ctx->launches += scan_exclusive_u32(P.bottom_off, n_entries + 1, ctx->su_tmp.as<uint32_t>(), s);
-    ctx->launches += scan_exclusive_u32(P.slope_off, n_entries + 1, ctx->su_tmp.as<uint32_t>(), s);
+    ctx->launches += 1 + scan_exclusive_u32(P.area_off, n_entries + 1, ctx->lb, s);
+    ctx->launches += scan_exclusive_u32(P.bottom_off, n_entries + 1, ctx->lb, s);
+    ctx->launches += scan_exclusive_u32(P.slope_off, n_entries + 1, ctx->lb, s);
     // ---- carve: height-independent rejection, then heights for the rest
     unsigned* queue_n = nullptr;
     uint32_t *keep = nullptr, *slot = nullptr, *queue = nullptr;

@@ -22,6 +22,7 @@ struct NvtxRange {
 };
 }  // namespace plc
 #define PLC_RANGE() plc::NvtxRange plc_nvtx_range_(__func__)
+#include "plc_scan.cuh"
 
 #define PLC_CUDA_TRY(ctx, expr)                                                              \
     do {                                                                                     \
@@ -219,6 +220,7 @@ struct plc_ctx {
 
     // filter / merge scratch
     plc::DevBuf f_keys, f_vals, f_keys2, f_vals2, f_tmp, f_out, f_flags;
+    plc::LookbackWs lb;          // status words and ticket counter of the single-pass scans (plc_scan.cuh)
     plc::DevBuf m_out;
 
     // node setup on the device (plc_setup.cu): loaded points, bucket order, keys/values of the sort, bucket

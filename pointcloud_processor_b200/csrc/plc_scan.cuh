@@ -1,5 +1,9 @@
-// plc_scan.cuh — exclusive prefix sum over uint32 on the device (3 passes, 2048 items per block; one block for short arrays).
-// Used by the voxeliser (voxel start offsets), the crop compaction and the radix sort.
+// plc_scan.cuh — exclusive prefix sum over uint32 on the device.
+// Arrays up to 8192 items: one block (k_scan_small).  Longer ones: ONE launch of a single-pass scan with decoupled
+// look-back (every tile publishes its total, then its inclusive prefix, in a 64-bit status word; a tile adds up the
+// words of its predecessors, 32 at a time, until it meets an inclusive one) — N*4 read + N*4 written, instead of the
+// three launches and 2x traffic of a tile-sums scan.  Used by the voxeliser (list offsets), the ordered
+// compactions (crop, voxel segment heads, lattice plans) and the radix sort's digit tables.
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
@@ -39,48 +43,6 @@ static __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint
     return r;
 }
 
-static __global__ void __launch_bounds__(kScanThreads)
-k_scan_tiles(uint32_t* __restrict__ data, size_t n, uint32_t* __restrict__ tile_sums) {
-    size_t base = (size_t)blockIdx.x * kScanTile + (size_t)threadIdx.x * kScanItems;
-    uint32_t v[kScanItems], sum = 0;
-#pragma unroll
-    for (int k = 0; k < kScanItems; ++k) {
-        v[k] = (base + k < n) ? data[base + k] : 0;
-        sum += v[k];
-    }
-    uint32_t total;
-    uint32_t ex = block_exclusive_scan(sum, &total);
-#pragma unroll
-    for (int k = 0; k < kScanItems; ++k) {
-        if (base + k < n) data[base + k] = ex;
-        ex += v[k];
-    }
-    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
-}
-
-// single block: exclusive scan of the tile sums (any count)
-static __global__ void __launch_bounds__(kScanThreads)
-k_scan_sums(uint32_t* __restrict__ sums, size_t n) {
-    uint32_t carry = 0;
-    for (size_t base = 0; base < n; base += kScanThreads) {
-        size_t i = base + threadIdx.x;
-        uint32_t v = i < n ? sums[i] : 0, total;
-        uint32_t ex = block_exclusive_scan(v, &total);
-        if (i < n) sums[i] = carry + ex;
-        carry += total;
-    }
-}
-
-static __global__ void __launch_bounds__(kScanThreads)
-k_scan_add(uint32_t* __restrict__ data, size_t n, const uint32_t* __restrict__ tile_sums) {
-    size_t base = (size_t)blockIdx.x * kScanTile + (size_t)threadIdx.x * kScanItems;
-    uint32_t add = tile_sums[blockIdx.x];
-#pragma unroll
-    for (int k = 0; k < kScanItems; ++k)
-        if (base + k < n) data[base + k] += add;
-}
-
-
 // One block walks the whole array, 2048 items per round with a running carry: for the short arrays that dominate
 // the node-side stages (sort tables, lattice plans) one launch instead of three.
 static __global__ void __launch_bounds__(kScanThreads)
@@ -106,21 +68,145 @@ k_scan_small(uint32_t* __restrict__ data, size_t n) {
 }
 constexpr size_t kScanSmallLimit = 4 * kScanTile;      // 8192 items: four rounds of one block
 
+// ---- decoupled look-back ----------------------------------------------------------------------
+// Status word of a tile: [63:34] epoch of the launch that wrote it, [33:32] 1 = tile total, 2 = inclusive prefix,
+// [31:0] the value.  Words of earlier launches carry an older epoch and read as "not there yet", so the array is
+// never cleared.  Tiles take their index from a ticket counter in the order they start, which is what makes
+// waiting on lower tiles safe.
+struct LookbackWs {
+    unsigned long long* status = nullptr;
+    unsigned* ticket = nullptr;
+    size_t capacity = 0;            // status words
+    unsigned tickets_issued = 0;    // host mirror of *ticket: every launched block takes exactly one
+    unsigned epoch = 0;
+    cudaError_t reserve(size_t tiles) {
+        if (tiles <= capacity && status) return cudaSuccess;
+        if (status) cudaFree(status);          // synchronises with whatever still reads it
+        status = nullptr;
+        capacity = 0;
+        const size_t want = tiles + tiles / 4 + 1024;
+        cudaError_t e = cudaMalloc(&status, want * sizeof(unsigned long long));
+        if (e != cudaSuccess) return e;
+        e = cudaMemset(status, 0, want * sizeof(unsigned long long));      // epoch 0 = never written
+        if (e != cudaSuccess) return e;
+        if (!ticket) {
+            e = cudaMalloc(&ticket, sizeof(unsigned));
+            if (e != cudaSuccess) return e;
+            e = cudaMemset(ticket, 0, sizeof(unsigned));
+            if (e != cudaSuccess) return e;
+            tickets_issued = 0;
+        }
+        capacity = want;
+        return cudaSuccess;
+    }
+    void release() {
+        if (status) cudaFree(status);
+        if (ticket) cudaFree(ticket);
+        status = nullptr;
+        ticket = nullptr;
+        capacity = 0;
+    }
+    // bookkeeping of one launch of `blocks` blocks: returns (ticket base, epoch) for the kernel
+    void begin(unsigned blocks, unsigned* base, unsigned* ep) {
+        *base = tickets_issued;
+        tickets_issued += blocks;
+        epoch = (epoch + 1) & 0x3fffffffu;
+        if (epoch == 0) epoch = 1;
+        *ep = epoch;
+    }
+};
+
+struct LookbackArgs {
+    unsigned long long* status;
+    unsigned* ticket;
+    unsigned ticket_base, epoch;
+};
+
+// The block's tile index, in start order (call with all threads; one __syncthreads inside).
+static __device__ __forceinline__ unsigned lookback_tile(const LookbackArgs& a) {
+    __shared__ unsigned s_tile;
+    if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u) - a.ticket_base;
+    __syncthreads();
+    return s_tile;
+}
+
+// Called by all 32 lanes of ONE warp with the tile's total: publishes it, waits for the predecessors and
+// returns the exclusive prefix of the tile (the sum of all lower tiles' totals) in every lane.
+static __device__ __forceinline__ uint32_t lookback_exclusive(const LookbackArgs& a, unsigned tile, uint32_t total) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned long long ep = (unsigned long long)a.epoch << 34;
+    volatile unsigned long long* st = a.status;
+    if (tile == 0) {
+        if (lane == 0) st[0] = ep | (2ull << 32) | total;
+        return 0;
+    }
+    if (lane == 0) st[tile] = ep | (1ull << 32) | total;
+    uint32_t excl = 0;
+    int t = (int)tile - 1;
+    for (;;) {
+        const int idx = t - lane;
+        unsigned long long w = 2ull << 32;              // below tile 0: an inclusive prefix of zero
+        if (idx >= 0) {
+            do {
+                w = st[idx];
+            } while ((w >> 34) != (unsigned long long)a.epoch || ((w >> 32) & 3ull) == 0);
+        }
+        const unsigned inc = __ballot_sync(FULL, ((w >> 32) & 3ull) == 2ull);
+        const int first = inc ? __ffs(inc) - 1 : 32;      // nearest predecessor that already knows its prefix
+        uint32_t v = lane <= first ? (uint32_t)w : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+        excl += v;
+        if (inc) break;
+        t -= 32;
+    }
+    if (lane == 0) st[tile] = ep | (2ull << 32) | (uint32_t)(excl + total);
+    return excl;
+}
+
+static __global__ void __launch_bounds__(kScanThreads)
+k_scan_lookback(uint32_t* __restrict__ data, size_t n, LookbackArgs lb) {
+    __shared__ uint32_t s_excl;
+    const unsigned tile = lookback_tile(lb);
+    const size_t base = (size_t)tile * kScanTile + (size_t)threadIdx.x * kScanItems;
+    uint32_t v[kScanItems], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        v[k] = (base + k < n) ? data[base + k] : 0;
+        sum += v[k];
+    }
+    uint32_t total;
+    uint32_t ex = block_exclusive_scan(sum, &total);
+    if (threadIdx.x < 32) {
+        const uint32_t e = lookback_exclusive(lb, tile, total);
+        if (threadIdx.x == 0) s_excl = e;
+    }
+    __syncthreads();
+    ex += s_excl;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        if (base + k < n) data[base + k] = ex;
+        ex += v[k];
+    }
+}
+
 inline size_t scan_tmp_bytes(size_t n) { return ((n + kScanTile - 1) / kScanTile + 1) * sizeof(uint32_t); }
 
-// In-place exclusive scan of data[0..n); tmp needs scan_tmp_bytes(n).  Returns the number of kernels launched
-// (1 for short arrays, else 3).
-inline int scan_exclusive_u32(uint32_t* data, size_t n, uint32_t* tmp, cudaStream_t s) {
+// In-place exclusive scan of data[0..n).  Returns the number of kernels launched (1), or -1 if the look-back
+// workspace could not be allocated.
+inline int scan_exclusive_u32(uint32_t* data, size_t n, LookbackWs& ws, cudaStream_t s) {
     if (n == 0) return 0;
     if (n <= kScanSmallLimit) {
         k_scan_small<<<1, kScanThreads, 0, s>>>(data, n);
         return 1;
     }
-    size_t tiles = (n + kScanTile - 1) / kScanTile;
-    k_scan_tiles<<<(unsigned)tiles, kScanThreads, 0, s>>>(data, n, tmp);
-    k_scan_sums<<<1, kScanThreads, 0, s>>>(tmp, tiles);
-    k_scan_add<<<(unsigned)tiles, kScanThreads, 0, s>>>(data, n, tmp);
-    return 3;
+    const size_t tiles = (n + kScanTile - 1) / kScanTile;
+    if (ws.reserve(tiles) != cudaSuccess) return -1;
+    LookbackArgs a{ws.status, ws.ticket, 0, 0};
+    ws.begin((unsigned)tiles, &a.ticket_base, &a.epoch);
+    k_scan_lookback<<<(unsigned)tiles, kScanThreads, 0, s>>>(data, n, a);
+    return 1;
 }
 
 }  // namespace plc

@@ -18,9 +18,10 @@ constexpr int kSortRounds = 8;
 constexpr int kSortTile = kSortWarps * 32 * kSortRounds;   // 2048
 
 static __global__ void __launch_bounds__(kSortWarps * 32)
-k_radix_hist(const uint32_t* __restrict__ keys, unsigned n, int shift, uint32_t* __restrict__ table,
-             unsigned n_tiles) {
+k_radix_hist(const uint32_t* __restrict__ keys, unsigned n, const unsigned* __restrict__ n_dev, int shift,
+             uint32_t* __restrict__ table, unsigned n_tiles) {
     __shared__ uint32_t hist[256];
+    if (n_dev) n = min(n, *n_dev);          // the count lives on the device: `n` sized the grid, tiles past it count zero
     hist[threadIdx.x] = 0;
     __syncthreads();
     unsigned base = blockIdx.x * kSortTile;
@@ -34,10 +35,12 @@ k_radix_hist(const uint32_t* __restrict__ keys, unsigned n, int shift, uint32_t*
 }
 
 static __global__ void __launch_bounds__(kSortWarps * 32)
-k_radix_scatter(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals, unsigned n, int shift,
-                const uint32_t* __restrict__ table, unsigned n_tiles, uint32_t* __restrict__ out_keys,
-                uint32_t* __restrict__ out_vals) {
+k_radix_scatter(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals, unsigned n,
+                const unsigned* __restrict__ n_dev, int shift, const uint32_t* __restrict__ table, unsigned n_tiles,
+                uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_vals) {
     __shared__ uint32_t wbase[kSortWarps][256];
+    if (n_dev) n = min(n, *n_dev);
+    if (blockIdx.x * kSortTile >= n) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int k = threadIdx.x; k < kSortWarps * 256; k += blockDim.x) (&wbase[0][0])[k] = 0;
     __syncthreads();
@@ -88,13 +91,14 @@ k_radix_scatter(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ 
 
 inline size_t sort_table_entries(size_t n) { return 256 * ((n + kSortTile - 1) / kSortTile); }
 
-// Sorts n pairs by the low `key_bits` bits of the key.  (keys_a, vals_a) hold the input; the result
+// Sorts n pairs by the low `key_bits` bits of the key.  With `n_dev` the number of pairs is min(n, *n_dev), read on
+// the device (n then only sizes the launches), so a pipeline need not come back to the host for it.  (keys_a, vals_a) hold the input; the result
 // lands in whichever buffer pair the returned index names (0 = a, 1 = b).  `table` needs
-// sort_table_entries(n) uint32, `scan_tmp` needs scan_tmp_bytes(sort_table_entries(n)).
+// sort_table_entries(n) uint32; `lb` is the context\'s look-back workspace (plc_scan.cuh).
 // Returns the number of kernel launches through *launches.
 inline int radix_sort_pairs(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, unsigned n,
-                            int key_bits, uint32_t* table, uint32_t* scan_tmp, cudaStream_t s,
-                            uint64_t* launches) {
+                            int key_bits, uint32_t* table, LookbackWs& lb, cudaStream_t s,
+                            uint64_t* launches, const unsigned* n_dev = nullptr) {
     if (n == 0) return 0;
     unsigned n_tiles = (n + kSortTile - 1) / kSortTile;
     int cur = 0;
@@ -103,9 +107,9 @@ inline int radix_sort_pairs(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b
         const uint32_t* vin = cur ? vals_b : vals_a;
         uint32_t* kout = cur ? keys_a : keys_b;
         uint32_t* vout = cur ? vals_a : vals_b;
-        k_radix_hist<<<n_tiles, kSortWarps * 32, 0, s>>>(kin, n, shift, table, n_tiles);
-        const int scan_launches = scan_exclusive_u32(table, (size_t)256 * n_tiles, scan_tmp, s);
-        k_radix_scatter<<<n_tiles, kSortWarps * 32, 0, s>>>(kin, vin, n, shift, table, n_tiles, kout, vout);
+        k_radix_hist<<<n_tiles, kSortWarps * 32, 0, s>>>(kin, n, n_dev, shift, table, n_tiles);
+        const int scan_launches = scan_exclusive_u32(table, (size_t)256 * n_tiles, lb, s);
+        k_radix_scatter<<<n_tiles, kSortWarps * 32, 0, s>>>(kin, vin, n, n_dev, shift, table, n_tiles, kout, vout);
         if (launches) *launches += 2 + scan_launches;
         cur ^= 1;
     }

@@ -353,7 +353,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     uint32_t* totals = static_cast<uint32_t*>(ctx->pinned);
     k_counts_to_groups<<<(unsigned)((n_mid + 255) / 256), 256, 0, s>>>(ix.gstart.as<uint32_t>(), n_mid);
-    ctx->launches += 1 + scan_exclusive_u32(ix.gstart.as<uint32_t>(), n_mid + 1, ix.scan_tmp.as<uint32_t>(), s);
+    ctx->launches += 1 + scan_exclusive_u32(ix.gstart.as<uint32_t>(), n_mid + 1, ctx->lb, s);
     ctx->timer.end(s);
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ix.gstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
