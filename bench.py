@@ -674,7 +674,7 @@ def measure_feeders_large(ctx, peak, reps: int = 4) -> dict:
     scan = np.ones((n, 4), np.float32)
     scan[:, 0] = rng.uniform(-6.0, 24.0, n)
     scan[:, 1] = rng.uniform(-14.0, 14.0, n)
-    scan[:, 2] = 0.15 * np.sin(0.4 * scan[:, 0]) * np.cos(0.3 * scan[:, 1]) + rng.normal(0.0, 0.02, n).astype(np.float32) - 2.0
+    scan[:, 2] = 0.15 * np.sin(0.4 * scan[:, 0]) * np.cos(0.3 * scan[:, 1]) + rng.normal(0.0, 0.02, n).astype(np.float32) - 1.2
 
     def best(fn, key):
         ks, ws, out = [], [], None

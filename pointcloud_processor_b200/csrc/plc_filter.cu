@@ -77,7 +77,7 @@ constexpr int kCropTile = 256 * kCropRounds;
 // — when the key is fixed by the crop box — the voxel key of every kept point.  N*12 read, M'*(16 + 8) written.
 __global__ void __launch_bounds__(256)
 k_crop_onepass(const unsigned char* __restrict__ data, unsigned n, unsigned n_tiles, unsigned step, unsigned ox,
-               unsigned oy, unsigned oz, bool aligned, CropDev b, VoxDev vox, float4* __restrict__ out,
+               unsigned oy, unsigned oz, bool aligned, bool vec16, CropDev b, VoxDev vox, float4* __restrict__ out,
                uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, FilterState* __restrict__ st, LookbackArgs lb) {
     __shared__ unsigned wcount[kCropRounds * 8];      // kept points per (round, warp), then their exclusive prefix
     __shared__ unsigned s_excl, s_total;
@@ -97,9 +97,16 @@ k_crop_onepass(const unsigned char* __restrict__ data, unsigned n, unsigned n_ti
         x[r] = y[r] = z[r] = 0.f;
         if (i < n) {
             const unsigned char* p = data + (size_t)i * step;
-            x[r] = ld_f32(p + ox, aligned);
-            y[r] = ld_f32(p + oy, aligned);
-            z[r] = ld_f32(p + oz, aligned);
+            if (vec16) {          // x, y, z in one 16-byte word of the record (PointXYZ, PointXYZRGB): one load
+                const float4 v = *reinterpret_cast<const float4*>(p + ox);
+                x[r] = v.x;
+                y[r] = v.y;
+                z[r] = v.z;
+            } else {
+                x[r] = ld_f32(p + ox, aligned);
+                y[r] = ld_f32(p + oy, aligned);
+                z[r] = ld_f32(p + oz, aligned);
+            }
             const double dx = x[r], dy = y[r], dz = z[r];
             keep = dx > b.x_min && dx < b.x_max && dy > b.y_min && dy < b.y_max && dz > b.z_min && dz < b.z_max;
         }
@@ -357,8 +364,10 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
     {
         LookbackArgs la{ctx->lb.status, ctx->lb.ticket, 0, 0};
         ctx->lb.begin(n_tiles, &la.ticket_base, &la.epoch);
+        const bool vec16 = in->point_step % 16 == 0 && in->off_x % 16 == 0 && in->off_y == in->off_x + 4 &&
+                           in->off_z == in->off_x + 8 && reinterpret_cast<uintptr_t>(raw) % 16 == 0;
         k_crop_onepass<<<n_tiles, 256, 0, s>>>(raw, n, n_tiles, in->point_step, in->off_x, in->off_y, in->off_z, aligned,
-                                               cb, vd, cropped, ctx->f_keys.as<uint32_t>(), ctx->f_vals.as<uint32_t>(),
+                                               vec16, cb, vd, cropped, ctx->f_keys.as<uint32_t>(), ctx->f_vals.as<uint32_t>(),
                                                st, la);
     }
     ctx->launches += 2;

@@ -116,6 +116,8 @@ struct LookbackWs {
     }
 };
 
+constexpr int kLookbackPerLane = 4;      // predecessors each lane of the look-back warp reads per step
+
 struct LookbackArgs {
     unsigned long long* status;
     unsigned* ticket;
@@ -142,24 +144,38 @@ static __device__ __forceinline__ uint32_t lookback_exclusive(const LookbackArgs
         return 0;
     }
     if (lane == 0) st[tile] = ep | (1ull << 32) | total;
+    // 128 predecessors per step, four per lane (eight per lane measured slower: 0.109 -> 0.154 ms on an 8 M-point crop) (the loads overlap): when a whole wave of tiles starts at once the
+    // walk back is as long as the wave, and its length in L2 round trips is what the kernel then waits for
     uint32_t excl = 0;
     int t = (int)tile - 1;
     for (;;) {
-        const int idx = t - lane;
-        unsigned long long w = 2ull << 32;              // below tile 0: an inclusive prefix of zero
-        if (idx >= 0) {
-            do {
-                w = st[idx];
-            } while ((w >> 34) != (unsigned long long)a.epoch || ((w >> 32) & 3ull) == 0);
+        unsigned long long w[kLookbackPerLane];
+        bool ready;
+        do {
+            ready = true;
+#pragma unroll
+            for (int j = 0; j < kLookbackPerLane; ++j) {
+                const int idx = t - lane - 32 * j;
+                w[j] = idx >= 0 ? st[idx] : (2ull << 32);          // below tile 0: an inclusive prefix of zero
+                ready = ready && (idx < 0 || ((w[j] >> 34) == (unsigned long long)a.epoch && ((w[j] >> 32) & 3ull) != 0));
+            }
+        } while (!ready);
+        bool done = false;
+        uint32_t v = 0;
+#pragma unroll
+        for (int j = 0; j < kLookbackPerLane; ++j) {
+            const unsigned inc = __ballot_sync(FULL, ((w[j] >> 32) & 3ull) == 2ull);
+            if (!done) {
+                const int first = inc ? __ffs(inc) - 1 : 32;      // nearest predecessor that already knows its prefix
+                if (lane <= first) v += (uint32_t)w[j];
+                done = inc != 0;
+            }
         }
-        const unsigned inc = __ballot_sync(FULL, ((w >> 32) & 3ull) == 2ull);
-        const int first = inc ? __ffs(inc) - 1 : 32;      // nearest predecessor that already knows its prefix
-        uint32_t v = lane <= first ? (uint32_t)w : 0u;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
         excl += v;
-        if (inc) break;
-        t -= 32;
+        if (done) break;
+        t -= 32 * kLookbackPerLane;
     }
     if (lane == 0) st[tile] = ep | (2ull << 32) | (uint32_t)(excl + total);
     return excl;

@@ -438,10 +438,13 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     //   plc_q_tag      uint32[kQueueCap]  ring of (ray slot << 16 | sample index)
     static_assert(kQueueCap == 128, "sizes are spelled out in the PTX declaration below");
 #if PLC_RAYS_PER_THREAD == 8
+#define PLC_TILE_F4_BYTES "4096"
 #define PLC_RAY_STATE_BYTES "1024"
 #elif PLC_RAYS_PER_THREAD == 16
+#define PLC_TILE_F4_BYTES "8192"
 #define PLC_RAY_STATE_BYTES "2048"
 #elif PLC_RAYS_PER_THREAD == 32
+#define PLC_TILE_F4_BYTES "16384"
 #define PLC_RAY_STATE_BYTES "4096"
 #else
 #error "PLC_RAYS_PER_THREAD must be 8, 16 or 32"
@@ -455,6 +458,27 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                  : "=r"(ray_state), "=r"(q_tag));
     const unsigned wid = blockIdx.x;         // this warp's (candidate, tile) index
     if (wid >= n_work) return;
+#if defined(PLC_TMA_CELLS)
+    // Experiment: the tile's float32 cell records staged in shared memory by one bulk copy
+    // (cp.async.bulk, completion counted on an mbarrier) instead of one 16-byte load per ray.
+    unsigned cells_s, bar_s;
+    asm volatile(".shared .align 128 .b8 plc_cells_s[" PLC_TILE_F4_BYTES "];\n\t"
+                 ".shared .align 8 .b64 plc_cells_bar;\n\t"
+                 "mov.u32 %0, plc_cells_s;\n\t"
+                 "mov.u32 %1, plc_cells_bar;"
+                 : "=r"(cells_s), "=r"(bar_s));
+    if ((threadIdx.x & 31) == 0) {
+        const unsigned tile0 = wid - (wid / tiles) * tiles;
+        const float4* src = P.cells_f + (size_t)tile0 * kTileCells;
+        const unsigned bytes = kTileCells * 16;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(cells_s), "l"(src), "r"(bytes), "r"(bar_s) : "memory");
+    }
+    __syncwarp();
+#endif
 
     const unsigned FULL = 0xffffffffu;
     unsigned local = wid / tiles, tile = wid - local * tiles;
@@ -575,12 +599,22 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         q_n -= take;
     };
 
+#if defined(PLC_TMA_CELLS)
+    asm volatile("{\n\t.reg .pred p;\n\tPLC_WAIT_CELLS:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
+                 "@!p bra PLC_WAIT_CELLS;\n\t}" ::"r"(bar_s) : "memory");
+#endif
 #pragma unroll 1
     for (int r = 0; r < kRaysPerThread; ++r) {
         const int slot = r * 32 + lane;
         unsigned j = tile * kTileCells + slot;
         // ---- evaluateCellScore gates (:656-678): range
+#if defined(PLC_TMA_CELLS)
+        float4 cf;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(cf.x), "=f"(cf.y), "=f"(cf.z), "=f"(cf.w) : "r"(cells_s + 16u * slot));
+#else
         const float4 cf = __ldg(&P.cells_f[j]);          // padded to whole tiles: no bounds test
+#endif
         const float df[3] = {cf.x - A.sr[0], cf.y - A.sr[1], cf.z - A.sr[2]};
         const float hd2 = df[0] * df[0] + df[1] * df[1];
         const float L2f = hd2 + df[2] * df[2];
