@@ -421,6 +421,27 @@ plc_status plc_drivable_area(plc_ctx* ctx, const plc_cloud_view* scan, const dou
                              const plc_drivable_params* prm, int8_t* out_grid, uint64_t capacity,
                              plc_drivable_info* info);
 
+/* plc_drivable_area without any allocation.  It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments, same grid as plc_drivable_area, with these differences:
+ *   - the per-cell (count, min z, max z) scratch is a static __device__ array inside the library, sized for
+ *     PLC_DRIVABLE_STATIC_MAX_CELLS cells (12 MiB that every GPU loading the library holds until exit); a grid
+ *     with more cells is refused with PLC_E_CAPACITY (plc_last_error names the limit) and nothing is written;
+ *   - scan->data and out_grid must be device memory of the context's device (plc_dev_alloc or the caller's own):
+ *     no staging buffer exists, so host pointers are PLC_E_INVALID_ARG;
+ *   - the three kernels are enqueued on the context's stream and the call returns without synchronising:
+ *     out_grid is complete after plc_ctx_sync (or after whatever the caller orders behind that stream);
+ *   - no cudaMalloc / cudaFree / allocating routine is called, no events are recorded (plc_last_device_times
+ *     is not updated).  The first call on a device resolves the array's device address (cudaGetSymbolAddress).
+ * Every call on a device shares the one array, which keeps the last call's contents (each call resets the cells
+ * it uses before binning): calls that overlap on the GPU — two contexts or streams on one device — race; order
+ * them on one stream. */
+#define PLC_DRIVABLE_STATIC_MAX_CELLS 1048576u
+plc_status plc_drivable_area_static(plc_ctx* ctx, const plc_cloud_view* scan, const double* t, const double* q,
+                                    double robot_x, double robot_y, double start_x, double start_y,
+                                    const plc_drivable_params* prm, int8_t* out_grid, uint64_t capacity,
+                                    plc_drivable_info* info);
+
 #ifdef __cplusplus
 }
 #endif

@@ -144,7 +144,7 @@ EXPORTS = [
     "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times",
     "plc_vl_upload_candidates_strided", "plc_vl_sweep_strided", "plc_filter", "plc_merge",
     "plc_vl_compute_normals", "plc_vl_generate_cells", "plc_vl_generate_candidates",
-    "plc_drivable_params_default", "plc_drivable_area",
+    "plc_drivable_params_default", "plc_drivable_area", "plc_drivable_area_static",
     "plc_dev_alloc", "plc_dev_free", "plc_dev_upload", "plc_dev_download", "plc_dev_export", "plc_dev_import",
     "plc_dev_release",
     "plc_excavation_params_default", "plc_excavation_counts", "plc_excavate",
@@ -237,6 +237,7 @@ def lib() -> C.CDLL:
     L.plc_drivable_params_default.restype = None
     L.plc_drivable_area.argtypes = [vp, C.POINTER(CloudView), vp, vp, dbl, dbl, dbl, dbl, C.POINTER(DrivableParams),
                                     vp, u64, C.POINTER(DrivableInfo)]
+    L.plc_drivable_area_static.argtypes = L.plc_drivable_area.argtypes
     L.plc_vl_generate_candidates.argtypes = [vp, C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
                                              dbl, dbl, vp, u64, C.POINTER(u64)]
     L.plc_host_generate_candidates.argtypes = [C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,

@@ -272,6 +272,19 @@ class Context:
             return None, info
         return grid[: info.n_cells].reshape(info.height, info.width), info
 
+    def drivable_area_static(self, scan_view: A.CloudView, t, q, robot_xy, start_xy, params: A.DrivableParams,
+                             out_dev_ptr: int, capacity: int) -> A.DrivableInfo:
+        """plc_drivable_area_static: the allocation-free variant.  `scan_view.data` and `out_dev_ptr` are device memory
+        (DevBuffer); the grid is complete after sync().  Returns info."""
+        tp = None if t is None else np.ascontiguousarray(t, np.float64)
+        qp = None if q is None else np.ascontiguousarray(q, np.float64)
+        info = A.DrivableInfo()
+        st = self._L.plc_drivable_area_static(self._h, C.byref(scan_view), A.ptr(tp), A.ptr(qp), robot_xy[0], robot_xy[1],
+                                              start_xy[0], start_xy[1], C.byref(params), out_dev_ptr, capacity,
+                                              C.byref(info))
+        self._check(st, "plc_drivable_area_static")
+        return info
+
     # ---- node setup on the device (SURVEY §8 N1): same results as the host_* functions below
     def compute_normals(self, area: np.ndarray, radius: float = 1.5, point_step: int | None = None, off=(0, 4, 8)) -> np.ndarray:
         v = A.cloud_view(area, point_step, off)

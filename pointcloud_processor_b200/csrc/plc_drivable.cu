@@ -10,6 +10,13 @@
 // N*point_step bytes read once, W*H*(12 + 1) bytes of cell state.
 #include "plc_internal.cuh"
 
+#include <mutex>
+
+// Scratch of plc_drivable_area_static (bottom of this file): the per-cell (count, min z, max z) state lives in this
+// array instead of a cudaMalloc'd buffer.  Every GPU that loads the library holds these 12 MiB until exit.  In host
+// code the name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, per device.
+static __device__ __align__(256) unsigned char g_drivable_static_scratch[(size_t)PLC_DRIVABLE_STATIC_MAX_CELLS * 12u];
+
 namespace plc {
 namespace {
 
@@ -182,6 +189,106 @@ extern "C" plc_status plc_drivable_area(plc_ctx* ctx, const plc_cloud_view* scan
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     ctx->times.drivable_ms = ctx->timer.total_ms();
     info->n_cells = n_cells;
+    info->published = 1;
+    return PLC_OK;
+}
+
+// ---- the allocation-free variant ------------------------------------------------------------------------------------
+namespace plc {
+namespace {
+
+static_assert(sizeof(CellState) == 12, "g_drivable_static_scratch is sized for 12-byte cell states");
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mu;
+CellState* g_static_cells[kMaxStaticDevices] = {};       // device address of the scratch array, per device
+
+// Device address of the static scratch on the context's device (which must be current): resolved once per device.
+plc_status static_cells(plc_ctx* ctx, CellState** out) {
+    if (ctx->device < 0 || ctx->device >= kMaxStaticDevices) {
+        ctx->set_error("plc_drivable_area_static", "device ordinal beyond the per-device address table (64)");
+        return PLC_E_INVALID_ARG;
+    }
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_cells[ctx->device]) {
+        void* p = nullptr;
+        PLC_CUDA_TRY(ctx, cudaGetSymbolAddress(&p, g_drivable_static_scratch));
+        g_static_cells[ctx->device] = static_cast<CellState*>(p);
+    }
+    *out = g_static_cells[ctx->device];
+    return PLC_OK;
+}
+
+// true when `p` is memory kernels on `device` may dereference without any staging copy
+bool device_resident(const void* p, int device) {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    if (attr.type == cudaMemoryTypeManaged) return true;
+    return attr.type == cudaMemoryTypeDevice && attr.device == device;
+}
+
+}  // namespace
+}  // namespace plc
+
+extern "C" plc_status plc_drivable_area_static(plc_ctx* ctx, const plc_cloud_view* scan, const double* t, const double* q,
+                                               double robot_x, double robot_y, double start_x, double start_y,
+                                               const plc_drivable_params* prm, int8_t* out_grid, uint64_t capacity,
+                                               plc_drivable_info* info) {
+    if (!ctx || !cloud_view_ok(scan) || !prm || !info || (t == nullptr) != (q == nullptr)) return PLC_E_INVALID_ARG;
+    if (!(prm->grid_resolution > 0) || !(prm->map_width >= 0) || !(prm->map_height >= 0)) return PLC_E_INVALID_ARG;
+    if (scan->n_points > 0x7fffff00ull) return PLC_E_INVALID_ARG;
+    const double wd = prm->map_width / prm->grid_resolution, hd = prm->map_height / prm->grid_resolution;
+    if (!(wd < 46000.0 && hd < 46000.0)) return PLC_E_INVALID_ARG;
+    memset(info, 0, sizeof(*info));
+    info->width = (int32_t)wd;
+    info->height = (int32_t)hd;
+    info->origin_x = robot_x - prm->map_width / 2.0;
+    info->origin_y = robot_y - prm->map_height / 2.0;
+    info->resolution = prm->grid_resolution;
+    const uint64_t n_cells = (uint64_t)info->width * (uint64_t)info->height;
+    if (scan->n_points == 0) return PLC_OK;
+    info->n_cells = n_cells;
+    if (n_cells > (uint64_t)PLC_DRIVABLE_STATIC_MAX_CELLS) {
+        ctx->set_error("plc_drivable_area_static",
+                       ("grid of " + std::to_string(n_cells) + " cells exceeds the static scratch of " +
+                        std::to_string((uint64_t)PLC_DRIVABLE_STATIC_MAX_CELLS) +
+                        " cells (PLC_DRIVABLE_STATIC_MAX_CELLS); use plc_drivable_area").c_str());
+        return PLC_E_CAPACITY;
+    }
+    if (n_cells > capacity || (n_cells && !out_grid)) return PLC_E_CAPACITY;
+    if (n_cells == 0) {
+        info->published = 1;
+        return PLC_OK;
+    }
+    PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (!device_resident(scan->data, ctx->device) || !device_resident(out_grid, ctx->device)) {
+        ctx->set_error("plc_drivable_area_static",
+                       "scan->data and out_grid must be device memory of the context's device (no staging buffer is allocated)");
+        return PLC_E_INVALID_ARG;
+    }
+    CellState* cells = nullptr;
+    PLC_TRY(static_cells(ctx, &cells));
+    cudaStream_t s = ctx->stream;
+    const size_t n = scan->n_points;
+    const bool aligned = ((scan->point_step | scan->off_x | scan->off_y | scan->off_z) & 3u) == 0 &&
+                         (reinterpret_cast<uintptr_t>(scan->data) & 3u) == 0;
+    Affine3 a{};
+    if (t) a = affine_of(t, q);
+    // the array keeps the previous call's cell states: every cell this call reads is reset first
+    k_cells_reset<<<(unsigned)((n_cells + 255) / 256), 256, 0, s>>>(cells, (unsigned)n_cells);
+    k_bin_heights<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(static_cast<const unsigned char*>(scan->data), (unsigned)n,
+                                                               scan->point_step, scan->off_x, scan->off_y, scan->off_z,
+                                                               aligned, a, t ? 1 : 0, info->origin_x, info->origin_y,
+                                                               prm->grid_resolution, info->width, info->height, cells);
+    k_classify<<<(unsigned)((n_cells + 255) / 256), 256, 0, s>>>(cells, info->width, info->height, info->origin_x,
+                                                                info->origin_y, prm->grid_resolution, start_x, start_y,
+                                                                prm->start_clear_radius, prm->max_gradient,
+                                                                prm->min_points_per_cell,
+                                                                reinterpret_cast<signed char*>(out_grid));
+    ctx->launches += 3;
+    PLC_CUDA_TRY(ctx, cudaGetLastError());
     info->published = 1;
     return PLC_OK;
 }
