@@ -113,6 +113,9 @@ struct VoxelIndex {
     uint64_t n_vox = 0;       // bricks
     uint64_t n_mid = 0;       // list voxels
     uint64_t n_groups = 0;    // 4-point groups in cgrp
+    // `bricks` holds zeros everywhere except in the bricks of the list voxels that (geom, gstart, n_mid) of the
+    // last build describe as non-empty: the next build clears just those (k_clear_touched) instead of the whole array
+    bool bricks_sparse_dirty = false;
     bool has_points() const { return n_raw > 0; }
     // the "G" term of the algorithmic bytes: the indexed points, once (a lower bound of what the sweep must read)
     uint64_t bytes() const { return n_raw * 16; }
@@ -121,6 +124,7 @@ struct VoxelIndex {
     void release() {
         raw.release(); bricks.release(); gstart.release(); cfill.release(); cgrp.release();
         scan_tmp.release();
+        bricks_sparse_dirty = false;
     }
 };
 

@@ -225,17 +225,51 @@ k_dilate(VoxelGeom g, const float4* __restrict__ raw, unsigned n, double reach, 
                 xd = min(xb, bx + (int)ceilf(lx + wi) - 2);
             }
         }
-        const int word = ((z & 7) << 2) | ((y & 7) >> 1);
-        const int yshift = (y & 1) << 4;
         for (int v = xa >> kFineShift; v <= (xb >> kFineShift); ++v) {
             const int lo = v << kFineShift;
             const int a = max(xa, lo) - lo, b = min(xb, lo + 7) - lo;                    // fields a..b of this brick row
             uint32_t bits = (((1u << (2 * (b + 1))) - 1u) ^ ((1u << (2 * a)) - 1u)) & 0x5555u;
             const int c = max(xc, lo) - lo, d = min(xd, lo + 7) - lo;
             if (c <= d) bits |= (((1u << (2 * (d + 1))) - 1u) ^ ((1u << (2 * c)) - 1u)) & 0xAAAAu;
-            atomicOr(&bricks[(size_t)brick_of(g, v, y >> kFineShift, z >> kFineShift) * 32 + word], bits << yshift);
+            const unsigned row = row_index(g, v, y, z);                                  // two 16-bit rows per word
+            // Bits are only ever set, so a plain read that already shows them makes the atomic redundant (a stale
+            // read merely repeats it).  Every voxel near a surface lies within reach of tens to hundreds of points:
+            // nine atomics in ten go away (L2 read instead of L2 read-modify-write).
+            uint32_t* wp = &bricks[row >> 1];
+            const uint32_t want = bits << ((row & 1u) << 4);
+            if ((__ldcg(wp) & want) != want) atomicOr(wp, want);
         }
     }
+}
+
+// Zeroes the bricks the previous build can have written: those of its non-empty list voxels (a fine voxel only gets
+// bits within `reach` of a point, which puts that point into the list of the voxel's list voxel; the lists are
+// built with a slightly larger reach than the dilation uses, see voxel_build).  One thread per 16 bytes of a list
+// voxel's bricks would be finer; a thread per list voxel writing its (at most 8) bricks is enough at 20-150 MB.
+__global__ void __launch_bounds__(256)
+k_clear_touched(VoxelGeom g, size_t n_mid, const uint32_t* __restrict__ gstart, uint4* __restrict__ bricks) {
+    const size_t m = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n_mid || gstart[m + 1] == gstart[m]) return;
+    const int mx = (int)(m % (size_t)g.mdim_x), my = (int)((m / (size_t)g.mdim_x) % (size_t)g.mdim_y),
+              mz = (int)(m / ((size_t)g.mdim_x * g.mdim_y));
+    // list voxel edge = 2^mid_shift fine voxels; brick edge = 8 fine voxels
+    const int fine = 1 << g.mid_shift;
+    const int bx0 = (mx * fine) >> kFineShift, by0 = (my * fine) >> kFineShift, bz0 = (mz * fine) >> kFineShift;
+    const int nb = fine > 8 ? fine >> kFineShift : 1;
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    for (int z = 0; z < nb; ++z)
+        for (int y = 0; y < nb; ++y)
+            for (int x = 0; x < nb; ++x) {
+#if PLC_LAYOUT == 0
+                uint4* b = bricks + (size_t)brick_of(g, bx0 + x, by0 + y, bz0 + z) * 8;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) b[q] = zero;
+#else
+                for (int fz = 0; fz < 8; ++fz)
+                    for (int fy = 0; fy < 8; ++fy)
+                        reinterpret_cast<unsigned short*>(bricks)[row_index(g, bx0 + x, ((by0 + y) << 3) + fy, ((bz0 + z) << 3) + fz)] = 0;
+#endif
+            }
 }
 
 }  // namespace
@@ -329,6 +363,17 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     const unsigned n = (unsigned)ix.n_raw;
     const double gsz = h / (8.0 * F);
 
+    // Before anything of the previous build is freed or overwritten: un-set the bricks it wrote
+    bool bricks_zero = false;
+    if (ix.bricks_sparse_dirty && ix.bricks.ptr && ix.gstart.ptr && ix.n_mid) {
+        ctx->timer.begin(ctx->stream);
+        k_clear_touched<<<(unsigned)((ix.n_mid + 255) / 256), 256, 0, ctx->stream>>>(ix.geom, ix.n_mid, ix.gstart.as<uint32_t>(),
+                                                                                      ix.bricks.as<uint4>());
+        ctx->timer.end(ctx->stream);
+        ctx->launches += 1;
+        bricks_zero = true;
+    }
+    ix.bricks_sparse_dirty = false;
     PLC_CUDA_TRY(ctx, ix.gstart.reserve((n_mid + 1) * 4));
     PLC_CUDA_TRY(ctx, ix.cfill.reserve(n_mid * 4));
     PLC_CUDA_TRY(ctx, ix.scan_tmp.reserve(scan_tmp_bytes(n_mid + 1)));
@@ -360,10 +405,14 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
 
     cudaStream_t s = ctx->stream;
     unsigned pb = (n + 255) / 256;
+    // The lists take every point within reach_l, a hair beyond the dilation's float32 reach (k_dilate widens its
+    // radius by a thousandth of a fine voxel): every brick the dilation writes then belongs to a non-empty list
+    // voxel, which is what lets the next build clear the occupancy sparsely.  Longer lists are harmless.
+    const double reach_l = reach * (1.0 + 4e-6) + 4e-3 * gsz;
     // ---- candidate lists: counts -> offsets
     ctx->timer.begin(s);
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.gstart.ptr, 0, (n_mid + 1) * 4, s));
-    k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.gstart.as<uint32_t>(),
+    k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach_l, h / 2.0, ix.gstart.as<uint32_t>(),
                                            nullptr, nullptr);
     ctx->launches += 1;
     PLC_CUDA_TRY(ctx, cudaGetLastError());
@@ -374,19 +423,23 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ix.gstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     const size_t n_groups = totals[0];
-    PLC_CUDA_TRY(ctx, ix.bricks.reserve(n_vox * 128));
+    {
+        const void* before = ix.bricks.ptr;
+        PLC_CUDA_TRY(ctx, ix.bricks.reserve(n_vox * 128));
+        if (ix.bricks.ptr != before) bricks_zero = false;            // a new allocation holds anything
+    }
     PLC_CUDA_TRY(ctx, ix.cgrp.reserve(std::max<size_t>(n_groups, 1) * 48));
     g.bricks = ix.bricks.as<uint32_t>();
     g.cgrp = ix.cgrp.as<float4>();
     ctx->timer.begin(s);
     k_fill_f32<<<148 * 8, 256, 0, s>>>(ix.cgrp.as<float>(), n_groups * 12, INFINITY);
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, n_vox * 128, s));
+    if (!bricks_zero) PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, n_vox * 128, s));
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
     const int slices = (int)std::floor(2.0 * reach / gsz) + 2;
     const unsigned long long dthreads = (unsigned long long)n * (unsigned)slices;
     k_dilate<<<(unsigned)((dthreads + 255) / 256), 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, inner, gsz, slices,
                                                                 ix.bricks.as<uint32_t>());
-    k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, h / 2.0, ix.cfill.as<uint32_t>(),
+    k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach_l, h / 2.0, ix.cfill.as<uint32_t>(),
                                           ix.gstart.as<uint32_t>(), ix.cgrp.as<float>());
     ctx->launches += 3;
     ctx->timer.end(s);
@@ -401,6 +454,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     ix.built_march_err_m = march_err_m;
     ix.built_refine = F;
     ix.n_mid = n_mid;
+    ix.bricks_sparse_dirty = true;
     return PLC_OK;
 }
 

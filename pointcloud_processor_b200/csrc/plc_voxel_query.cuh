@@ -72,27 +72,40 @@ __device__ __forceinline__ uint32_t brick_of(const VoxelGeom& g, int cx, int cy,
     return (uint32_t)((cz * g.dim_y + cy) * g.dim_x + cx);
 }
 
-// State of fine voxel (ix, iy, iz): 0 clear, 1 uncertain (run the exact test), 3 certainly blocked.
-// One load: brick word ((iz&7)*4 + (iy&7)/2) of the voxel's coarse cell.
+// Index of the 16-bit occupancy row that holds fine voxels (8 cx .. 8 cx + 7, y, z).  PLC_LAYOUT picks how the rows
+// are ordered in memory (the builder, the point queries and k_sweep's march all go through this one function):
+//   0  bricks: 8x8x8 fine voxels per 128-byte line, bricks x-fastest           [cz][cy][cx][z&7][y&7]
+//   1  rows in plain z, y, cx order (a 128-byte line is 512 voxels along x)    [z][y][cx]
+//   2  flat bricks: 64x8x1 fine voxels per 128-byte line                        [z][cy][cx][y&7]
+#ifndef PLC_LAYOUT
+#define PLC_LAYOUT 0
+#endif
+__device__ __forceinline__ unsigned row_index(const VoxelGeom& g, int cx, int y, int z) {
+#if PLC_LAYOUT == 0
+    return (brick_of(g, cx, y >> kFineShift, z >> kFineShift) << 6) | (unsigned)((z & 7) << 3) | (unsigned)(y & 7);
+#elif PLC_LAYOUT == 1
+    return (unsigned)((z * (g.dim_y << kFineShift) + y) * g.dim_x + cx);
+#else
+    return ((unsigned)((z * g.dim_y + (y >> kFineShift)) * g.dim_x + cx) << 3) | (unsigned)(y & 7);
+#endif
+}
+
+__device__ __forceinline__ unsigned ldg_row(const VoxelGeom& g, unsigned idx) {
+    return ldg_brick_row(reinterpret_cast<const char*>(reinterpret_cast<const unsigned short*>(g.bricks) + idx));
+}
+
+// State of fine voxel (ix, iy, iz): 0 clear, 1 uncertain (run the exact test), 3 certainly blocked.  One load.
 __device__ __forceinline__ unsigned voxel_state(const VoxelGeom& g, int ix, int iy, int iz) {
-    unsigned brick = brick_of(g, ix >> kFineShift, iy >> kFineShift, iz >> kFineShift);
-    uint32_t w = __ldg(&g.bricks[(size_t)brick * 32 + (((iz & 7) << 2) | ((iy & 7) >> 1))]);
-    return (w >> (2 * (((iy & 1) << 3) | (ix & 7)))) & 3u;
+    return (ldg_row(g, row_index(g, ix >> kFineShift, iy, iz)) >> (2 * (ix & 7))) & 3u;
 }
 
-// The same for a position in 16.16 fixed-point fine-voxel units (k_sweep's march).  A brick is 8 z-slabs of
-// 16 bytes, each 8 y-rows of 2 bytes, each 8 x-fields of 2 bits, so the row is one aligned 16-bit load at a
-// byte offset made of bit fields of the coordinates.
-__device__ __forceinline__ unsigned voxel_state_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
-    const unsigned brick = brick_of(g, fx >> (16 + kFineShift), fy >> (16 + kFineShift), fz >> (16 + kFineShift));
-    const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
-    return ((unsigned)ldg_brick_row(reinterpret_cast<const char*>(g.bricks) + off) >> (((unsigned)fx >> 15) & 0xeu)) & 3u;
-}
-
-// Split form for software pipelining: the row of the voxel holding (fx, fy, fz), and the state from a row.
+// The same for a position in 16.16 fixed-point fine-voxel units (k_sweep's march), split for software pipelining:
+// the row of the voxel holding (fx, fy, fz), and the state from a row.  In the brick layout the row's byte offset is
+// assembled from bit fields of the three coordinates.
 __device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
     PLC_CHECK_OOB((unsigned)(fx >> 16) >= (unsigned)(g.dim_x << kFineShift) || (unsigned)(fy >> 16) >= (unsigned)(g.dim_y << kFineShift) ||
                   (unsigned)(fz >> 16) >= (unsigned)(g.dim_z << kFineShift), 0u)
+#if PLC_LAYOUT == 0
     const unsigned brick = brick_of(g, fx >> (16 + kFineShift), fy >> (16 + kFineShift), fz >> (16 + kFineShift));
 #ifdef PLC_WIDE_BRICKS
     const size_t off = ((size_t)brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
@@ -100,6 +113,9 @@ __device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, 
     const unsigned off = (brick << 7) | (((unsigned)fz >> 12) & 0x70u) | (((unsigned)fy >> 15) & 0xeu);
 #endif
     return ldg_brick_row(reinterpret_cast<const char*>(g.bricks) + off);
+#else
+    return ldg_row(g, row_index(g, fx >> (16 + kFineShift), fy >> 16, fz >> 16));
+#endif
 }
 __device__ __forceinline__ unsigned row_shift(int fx) { return ((unsigned)fx >> 15) & 0xeu; }
 

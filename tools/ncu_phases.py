@@ -13,11 +13,11 @@ stall_cols = [(i, c) for i, c in enumerate(h) if c.startswith("stall_") and "Not
 # phase markers are comments in plc_sweep.cu: "// PHASE name" lines give the line ranges
 # phase boundaries: first line of each phase in plc_sweep.cu AS CAPTURED ("name:line,name:line,..." as argv[3])
 marks = [(int(b), a) for a, b in (kv.split(":") for kv in (sys.argv[3] if len(sys.argv) > 3 else
-         "prologue:456,drain:515,setup:578,march:686,final:721").split(","))]
+         "prologue:459,drain:542,setup:607,march:719,final:756").split(","))]
 marks.sort()
 def phase_of(f, ln):
     if f == "plc_voxel_query.cuh":
-        return "march" if ln >= 86 and ln <= 101 else ("exact" if 54 <= ln <= 60 else "vq_other")
+        return "march" if 86 <= ln <= 104 else ("exact" if 54 <= ln <= 60 else "vq_other")
     if f != "plc_sweep.cu":
         return "intrinsics"
     p = "pre"
