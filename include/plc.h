@@ -179,7 +179,10 @@ void plc_dev_release(plc_ctx* ctx, void* dev_ptr);
 /* Replaces the KD-tree build of terrainCallback (virtual_lidar.cpp:180-192): voxelises the
  * /excavated_terrain cloud into the occupancy grid the sweep traverses.  Non-finite points are
  * dropped, as KdTreeFLANN::setInputCloud does.  n_points == 0 leaves "no terrain" (every ray
- * visible, :727), matching the reference's empty-cloud guard (:184). */
+ * visible, :727), matching the reference's empty-cloud guard (:184).
+ * The caller's buffer has been consumed when the call returns, but the last kernels of the index build may still be
+ * running on the context's stream (later calls on the context are ordered behind them; plc_ctx_sync or
+ * plc_last_device_times waits for them): a device fault in them is reported by the next call that synchronises. */
 plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* cloud);
 /* Replaces zx120PointsCallback (virtual_lidar.cpp:194-207): the cloud observed by the fixed sensor. */
 /* terrainCallback with an EMPTY message (virtual_lidar.cpp:180-192): terrain_cloud_ becomes non-null, so

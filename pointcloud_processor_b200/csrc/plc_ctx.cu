@@ -104,6 +104,7 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
     if (c->stage_pinned) cudaFreeHost(c->stage_pinned);
     if (c->stage_done) cudaEventDestroy(c->stage_done);
     c->timer.destroy();
+    c->terrain_timer.destroy();
     if (c->ev_sweep_begin) cudaEventDestroy(c->ev_sweep_begin);
     if (c->ev_sweep_end) cudaEventDestroy(c->ev_sweep_end);
     if (c->ev_run_begin) cudaEventDestroy(c->ev_run_begin);

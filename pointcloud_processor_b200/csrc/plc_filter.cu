@@ -69,73 +69,95 @@ __device__ __forceinline__ uint32_t voxel_key(const VoxDev& v, float x, float y,
     return (uint32_t)(i0 + i1 * v.mul_y + i2 * v.mul_z);
 }
 
-constexpr int kCropRounds = 8;
+#ifndef PLC_CROP_ROUNDS
+#define PLC_CROP_ROUNDS 16
+#endif
+constexpr int kCropRounds = PLC_CROP_ROUNDS;      // points per thread of k_crop_onepass (a tile is 256 x this many points)
 constexpr int kCropTile = 256 * kCropRounds;
+constexpr int kHeadRounds = 8;
+constexpr int kHeadTile = 256 * kHeadRounds;
 
 // K6 in one pass (pointcloud_filter.cpp:106-116): strict six-sided test on the float promoted to double (NaN fails),
 // order-preserving compaction through a decoupled look-back over the tiles' counts, the cropped cloud's bounds, and
 // — when the key is fixed by the crop box — the voxel key of every kept point.  N*12 read, M'*(16 + 8) written.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 8)
 k_crop_onepass(const unsigned char* __restrict__ data, unsigned n, unsigned n_tiles, unsigned step, unsigned ox,
                unsigned oy, unsigned oz, bool aligned, bool vec16, CropDev b, VoxDev vox, float4* __restrict__ out,
                uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, FilterState* __restrict__ st, LookbackArgs lb) {
     __shared__ unsigned wcount[kCropRounds * 8];      // kept points per (round, warp), then their exclusive prefix
+    __shared__ unsigned wkeep[kCropRounds * 8];       // which lanes of (round, warp) kept their point
     __shared__ unsigned s_excl, s_total;
     __shared__ int red[6][8];
     const unsigned tile = lookback_tile(lb);
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
-    float x[kCropRounds], y[kCropRounds], z[kCropRounds];
-    unsigned keep_bits = 0, rank[kCropRounds];
     const int lo_id = 0x7fffffff, hi_id = (int)0x80000000;
     int k[6] = {lo_id, lo_id, lo_id, hi_id, hi_id, hi_id};
+    // One record's coordinates.  The tile is read twice — here for the test, after the look-back for the copy (an
+    // L2 hit by then) — so that no thread holds eight points in registers across the two barriers: half the
+    // registers, twice the resident blocks, and it is the resident blocks that keep HBM busy while others wait.
+    auto load_xyz = [&](unsigned i, float& x, float& y, float& z) {
+        const unsigned char* p = data + (size_t)i * step;
+        if (vec16) {              // x, y, z in one 16-byte word of the record (PointXYZ, PointXYZRGB): one load
+            const float4 v = *reinterpret_cast<const float4*>(p + ox);
+            x = v.x;
+            y = v.y;
+            z = v.z;
+        } else {
+            x = ld_f32(p + ox, aligned);
+            y = ld_f32(p + oy, aligned);
+            z = ld_f32(p + oz, aligned);
+        }
+    };
 #pragma unroll
     for (int r = 0; r < kCropRounds; ++r) {
         const unsigned i = tile * kCropTile + r * 256 + threadIdx.x;
         bool keep = false;
-        x[r] = y[r] = z[r] = 0.f;
+        float x = 0.f, y = 0.f, z = 0.f;
         if (i < n) {
-            const unsigned char* p = data + (size_t)i * step;
-            if (vec16) {          // x, y, z in one 16-byte word of the record (PointXYZ, PointXYZRGB): one load
-                const float4 v = *reinterpret_cast<const float4*>(p + ox);
-                x[r] = v.x;
-                y[r] = v.y;
-                z[r] = v.z;
-            } else {
-                x[r] = ld_f32(p + ox, aligned);
-                y[r] = ld_f32(p + oy, aligned);
-                z[r] = ld_f32(p + oz, aligned);
-            }
-            const double dx = x[r], dy = y[r], dz = z[r];
+            load_xyz(i, x, y, z);
+            const double dx = x, dy = y, dz = z;
             keep = dx > b.x_min && dx < b.x_max && dy > b.y_min && dy < b.y_max && dz > b.z_min && dz < b.z_max;
         }
         const unsigned bal = __ballot_sync(FULL, keep);
-        rank[r] = __popc(bal & lt);
-        if (lane == 0) wcount[r * 8 + warp] = __popc(bal);
+        if (lane == 0) {
+            wcount[r * 8 + warp] = __popc(bal);
+            wkeep[r * 8 + warp] = bal;
+        }
         if (keep) {
-            keep_bits |= 1u << r;
-            k[0] = min(k[0], order_key(x[r]));
-            k[1] = min(k[1], order_key(y[r]));
-            k[2] = min(k[2], order_key(z[r]));
-            k[3] = max(k[3], order_key(x[r]));
-            k[4] = max(k[4], order_key(y[r]));
-            k[5] = max(k[5], order_key(z[r]));
+            k[0] = min(k[0], order_key(x));
+            k[1] = min(k[1], order_key(y));
+            k[2] = min(k[2], order_key(z));
+            k[3] = max(k[3], order_key(x));
+            k[4] = max(k[4], order_key(y));
+            k[5] = max(k[5], order_key(z));
         }
     }
     __syncthreads();
     if (warp == 0) {
-        // exclusive prefix over the 64 (round, warp) counts, two per lane, then the tile's place among the tiles
-        const unsigned a0 = wcount[2 * lane], a1 = wcount[2 * lane + 1];
-        unsigned inc = a0 + a1;
+        // exclusive prefix over the (round, warp) counts, kPer consecutive ones per lane, then the tile's place
+        // among the tiles
+        constexpr int kPer = kCropRounds * 8 / 32;
+        unsigned c[kPer], sum = 0;
+#pragma unroll
+        for (int q = 0; q < kPer; ++q) {
+            c[q] = wcount[kPer * lane + q];
+            sum += c[q];
+        }
+        unsigned inc = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const unsigned t = __shfl_up_sync(FULL, inc, o);
             if (lane >= o) inc += t;
         }
         const unsigned total = __shfl_sync(FULL, inc, 31);
-        wcount[2 * lane] = inc - a0 - a1;
-        wcount[2 * lane + 1] = inc - a1;
+        unsigned run = inc - sum;
+#pragma unroll
+        for (int q = 0; q < kPer; ++q) {
+            wcount[kPer * lane + q] = run;
+            run += c[q];
+        }
         const unsigned e = lookback_exclusive(lb, tile, total);
         if (lane == 0) {
             s_excl = e;
@@ -146,11 +168,14 @@ k_crop_onepass(const unsigned char* __restrict__ data, unsigned n, unsigned n_ti
     const unsigned base = s_excl;
 #pragma unroll
     for (int r = 0; r < kCropRounds; ++r) {
-        if (!((keep_bits >> r) & 1u)) continue;
-        const unsigned pos = base + wcount[r * 8 + warp] + rank[r];
-        out[pos] = make_float4(x[r], y[r], z[r], 1.0f);          // pcl::PointXYZ keeps 1.0f in data[3]
+        const unsigned bal = wkeep[r * 8 + warp];
+        if (!((bal >> lane) & 1u)) continue;
+        float x, y, z;
+        load_xyz(tile * kCropTile + r * 256 + threadIdx.x, x, y, z);
+        const unsigned pos = base + wcount[r * 8 + warp] + __popc(bal & lt);
+        out[pos] = make_float4(x, y, z, 1.0f);          // pcl::PointXYZ keeps 1.0f in data[3]
         if (vox.fixed) {
-            keys[pos] = voxel_key(vox, x[r], y[r], z[r]);
+            keys[pos] = voxel_key(vox, x, y, z);
             vals[pos] = pos;
         }
     }
@@ -190,20 +215,20 @@ k_voxel_keys(const float4* __restrict__ pts, unsigned n, VoxDev v, uint32_t* __r
 
 // First element of every run of equal keys, in order: seg_start[j] = index of the j-th voxel's first point,
 // seg_start[n_seg] = m.  One pass: head flags, look-back over the tiles' head counts, scatter.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 8)
 k_heads_onepass(const uint32_t* __restrict__ keys, unsigned n_max, unsigned n_tiles, uint32_t* __restrict__ seg_start,
                 FilterState* __restrict__ st, LookbackArgs lb) {
-    __shared__ unsigned wcount[kCropRounds * 8];
+    __shared__ unsigned wcount[kHeadRounds * 8];
     __shared__ unsigned s_excl, s_total;
     const unsigned tile = lookback_tile(lb);
     const unsigned m = min(n_max, st->m);
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
-    unsigned head_bits = 0, rank[kCropRounds];
+    unsigned head_bits = 0, rank[kHeadRounds];
 #pragma unroll
-    for (int r = 0; r < kCropRounds; ++r) {
-        const unsigned i = tile * kCropTile + r * 256 + threadIdx.x;
+    for (int r = 0; r < kHeadRounds; ++r) {
+        const unsigned i = tile * kHeadTile + r * 256 + threadIdx.x;
         const bool head = i < m && (i == 0 || keys[i] != keys[i - 1]);
         const unsigned bal = __ballot_sync(FULL, head);
         rank[r] = __popc(bal & lt);
@@ -230,8 +255,8 @@ k_heads_onepass(const uint32_t* __restrict__ keys, unsigned n_max, unsigned n_ti
     }
     __syncthreads();
 #pragma unroll
-    for (int r = 0; r < kCropRounds; ++r)
-        if ((head_bits >> r) & 1u) seg_start[s_excl + wcount[r * 8 + warp] + rank[r]] = tile * kCropTile + r * 256 + threadIdx.x;
+    for (int r = 0; r < kHeadRounds; ++r)
+        if ((head_bits >> r) & 1u) seg_start[s_excl + wcount[r * 8 + warp] + rank[r]] = tile * kHeadTile + r * 256 + threadIdx.x;
     if (threadIdx.x == 0 && tile == n_tiles - 1) {
         st->n_seg = s_excl + s_total;
         seg_start[s_excl + s_total] = m;          // end sentinel
@@ -348,7 +373,7 @@ extern "C" plc_status plc_filter(plc_ctx* ctx, const plc_cloud_view* in, const p
                                      count_dev);
         const uint32_t* skeys = where ? ctx->f_keys2.as<uint32_t>() : ctx->f_keys.as<uint32_t>();
         const uint32_t* svals = where ? ctx->f_vals2.as<uint32_t>() : ctx->f_vals.as<uint32_t>();
-        const unsigned tiles = (count_max + kCropTile - 1) / kCropTile;
+        const unsigned tiles = (count_max + kHeadTile - 1) / kHeadTile;
         LookbackArgs la{ctx->lb.status, ctx->lb.ticket, 0, 0};
         ctx->lb.begin(tiles, &la.ticket_base, &la.epoch);
         k_heads_onepass<<<tiles, 256, 0, s>>>(skeys, count_max, tiles, seg_start, st, la);

@@ -220,6 +220,13 @@ struct plc_ctx {
     cudaEvent_t ev_run_begin = nullptr, ev_run_end = nullptr;       // around all kernels of plc_vl_run_async
     bool sweep_timed = false;
     plc::DevTimer timer;         // kernels of the call in progress
+    // plc_vl_set_terrain returns with the tail of its index build still in flight (the caller's next host work —
+    // staging the cells, the pose list — overlaps it), so its kernels are timed by a timer of their own that
+    // plc_last_device_times reads after synchronising
+    plc::DevTimer terrain_timer;
+    plc::DevTimer* timer_override = nullptr;
+    bool terrain_time_pending = false;
+    plc::DevTimer& T() { return timer_override ? *timer_override : timer; }
     plc_device_times times{};    // last completed call of each kind (plc_last_device_times)
 
     // filter / merge scratch

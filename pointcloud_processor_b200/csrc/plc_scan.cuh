@@ -181,7 +181,7 @@ static __device__ __forceinline__ uint32_t lookback_exclusive(const LookbackArgs
     return excl;
 }
 
-static __global__ void __launch_bounds__(kScanThreads)
+static __global__ void __launch_bounds__(kScanThreads, 8)
 k_scan_lookback(uint32_t* __restrict__ data, size_t n, LookbackArgs lb) {
     __shared__ uint32_t s_excl;
     const unsigned tile = lookback_tile(lb);

@@ -1067,16 +1067,24 @@ extern "C" plc_status plc_vl_set_terrain(plc_ctx* ctx, const plc_cloud_view* clo
     PLC_RANGE();
     if (!ctx || !cloud_view_ok(cloud)) return PLC_E_INVALID_ARG;
     PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    ctx->timer.reset();
     ctx->terrain_unindexed = false;
+    ctx->terrain_timer.reset();
+    ctx->terrain_time_pending = false;
+    ctx->times.set_terrain_ms = 0.f;
+    struct UseTerrainTimer {
+        plc_ctx* c;
+        explicit UseTerrainTimer(plc_ctx* c_) : c(c_) { c->timer_override = &c->terrain_timer; }
+        ~UseTerrainTimer() { c->timer_override = nullptr; }
+    } guard(ctx);
     PLC_TRY(voxel_set_cloud(ctx, ctx->terrain, cloud));
     // build for the node's default block radius right away; a sweep with other parameters rebuilds
     plc_params d;
     plc_params_default(&d);
     ctx->terrain_rays_accum = 0;
     PLC_TRY(build_terrain_index(ctx, &d, pick_refine(ctx, ctx->last_sweep_rays)));
-    PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->times.set_terrain_ms = ctx->timer.total_ms();
+    // No synchronisation here: the counts the host needed were read inside the build; the occupancy dilation and
+    // the list fill that follow them run while the caller prepares its next call on the same stream.
+    ctx->terrain_time_pending = true;
     return PLC_OK;
 }
 
@@ -1389,6 +1397,12 @@ extern "C" unsigned long long plc_dev_oob_count() {
 
 extern "C" plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out) {
     if (!ctx || !out) return PLC_E_INVALID_ARG;
+    if (ctx->terrain_time_pending) {
+        PLC_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+        PLC_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->times.set_terrain_ms = ctx->terrain_timer.total_ms();
+        ctx->terrain_time_pending = false;
+    }
     float ms = 0.f;
     PLC_TRY(plc_vl_last_sweep_kernel_ms(ctx, &ms));
     ctx->times.sweep_kernel_ms = ms;

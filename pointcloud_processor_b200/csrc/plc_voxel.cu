@@ -289,7 +289,7 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
     const unsigned char* raw = nullptr;
     PLC_TRY(stage_bytes(ctx, cloud->data, bytes, &raw));
     ExtractState* st = ctx->scratch.as<ExtractState>();
-    ctx->timer.begin(ctx->stream);
+    ctx->T().begin(ctx->stream);
     k_extract_init<<<1, 1, 0, ctx->stream>>>(st);
     bool aligned = ((cloud->point_step | cloud->off_x | cloud->off_y | cloud->off_z) & 3u) == 0;
     unsigned blocks = (unsigned)((cloud->n_points + 255) / 256);
@@ -297,7 +297,7 @@ plc_status voxel_set_cloud(plc_ctx* ctx, VoxelIndex& ix, const plc_cloud_view* c
                                                cloud->off_x, cloud->off_y, cloud->off_z, aligned,
                                                ix.raw.as<float4>(), st);
     ctx->launches += 2;
-    ctx->timer.end(ctx->stream);
+    ctx->T().end(ctx->stream);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ExtractState* host = static_cast<ExtractState*>(ctx->pinned);
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(host, st, sizeof(ExtractState), cudaMemcpyDeviceToHost, ctx->stream));
@@ -366,10 +366,10 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     // Before anything of the previous build is freed or overwritten: un-set the bricks it wrote
     bool bricks_zero = false;
     if (ix.bricks_sparse_dirty && ix.bricks.ptr && ix.gstart.ptr && ix.n_mid) {
-        ctx->timer.begin(ctx->stream);
+        ctx->T().begin(ctx->stream);
         k_clear_touched<<<(unsigned)((ix.n_mid + 255) / 256), 256, 0, ctx->stream>>>(ix.geom, ix.n_mid, ix.gstart.as<uint32_t>(),
                                                                                       ix.bricks.as<uint4>());
-        ctx->timer.end(ctx->stream);
+        ctx->T().end(ctx->stream);
         ctx->launches += 1;
         bricks_zero = true;
     }
@@ -410,7 +410,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     // voxel, which is what lets the next build clear the occupancy sparsely.  Longer lists are harmless.
     const double reach_l = reach * (1.0 + 4e-6) + 4e-3 * gsz;
     // ---- candidate lists: counts -> offsets
-    ctx->timer.begin(s);
+    ctx->T().begin(s);
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.gstart.ptr, 0, (n_mid + 1) * 4, s));
     k_candidates<false><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach_l, h / 2.0, ix.gstart.as<uint32_t>(),
                                            nullptr, nullptr);
@@ -419,7 +419,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     uint32_t* totals = static_cast<uint32_t*>(ctx->pinned);
     k_counts_to_groups<<<(unsigned)((n_mid + 255) / 256), 256, 0, s>>>(ix.gstart.as<uint32_t>(), n_mid);
     ctx->launches += 1 + scan_exclusive_u32(ix.gstart.as<uint32_t>(), n_mid + 1, ctx->lb, s);
-    ctx->timer.end(s);
+    ctx->T().end(s);
     PLC_CUDA_TRY(ctx, cudaMemcpyAsync(totals, ix.gstart.as<uint32_t>() + n_mid, 4, cudaMemcpyDeviceToHost, s));
     PLC_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     const size_t n_groups = totals[0];
@@ -431,7 +431,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     PLC_CUDA_TRY(ctx, ix.cgrp.reserve(std::max<size_t>(n_groups, 1) * 48));
     g.bricks = ix.bricks.as<uint32_t>();
     g.cgrp = ix.cgrp.as<float4>();
-    ctx->timer.begin(s);
+    ctx->T().begin(s);
     k_fill_f32<<<148 * 8, 256, 0, s>>>(ix.cgrp.as<float>(), n_groups * 12, INFINITY);
     if (!bricks_zero) PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, n_vox * 128, s));
     PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
@@ -442,7 +442,7 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach_l, h / 2.0, ix.cfill.as<uint32_t>(),
                                           ix.gstart.as<uint32_t>(), ix.cgrp.as<float>());
     ctx->launches += 3;
-    ctx->timer.end(s);
+    ctx->T().end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ix.geom = g;
     ix.h = h;
