@@ -250,12 +250,12 @@ int main(int argc, char** argv) {
     const plc_pose best = so.best_index >= 0 ? cands[static_cast<size_t>(so.best_index)] : plc_pose{0, 0, 10, -M_PI / 2, 0};
     std::printf("{\"resident\": %s, \"robot_filtered\": %llu, \"zx120_filtered\": %llu, \"merged\": %llu, \"terrain\": %llu, "
                 "\"kept\": %llu, \"area\": %llu, \"cells\": %llu, \"candidates\": %llu, \"best_index\": %lld, "
-                "\"best_pose\": [%.17g, %.17g, %.17g], \"best_score\": %.17g, \"fixed_total\": %.17g, \"samples\": %llu, "
+                "\"best_pose\": [%.17g, %.17g, %.17g], \"best_score\": %.17g, \"fixed_total\": %.17g, \"rays_visible\": %llu, "
                 "\"grid_occupied\": %ld, \"grid_unknown\": %ld, \"kernels_launched\": %llu, \"wall_ms\": %.3f}\n",
                 resident ? "true" : "false", (unsigned long long)n_fr, (unsigned long long)n_fz, (unsigned long long)n_m,
                 (unsigned long long)n_t, (unsigned long long)einfo.n_kept, (unsigned long long)n_a, (unsigned long long)n_cells,
                 (unsigned long long)n_cands, (long long)so.best_index, best.x, best.y, best.z, so.best_score, so.fixed_total,
-                (unsigned long long)so.counters.samples, occupied, unknown, (unsigned long long)plc_launch_count(ctx), wall_ms);
+                (unsigned long long)so.counters.rays_visible, occupied, unknown, (unsigned long long)plc_launch_count(ctx), wall_ms);
     for (Cloud* c : {&f_robot, &f_zx, &merged, &own_r, &own_b, &terrain, &area, &normals}) c->release();   // before their context goes
     plc_ctx_destroy(ctx);
     return 0;

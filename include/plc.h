@@ -105,7 +105,8 @@ typedef struct plc_counters {
     uint64_t rays;            /* candidates evaluated * cells */
     uint64_t rays_gated_in;   /* rays that passed range and FOV */
     uint64_t rays_visible;    /* rays with the visibility bit set */
-    uint64_t samples;         /* sample positions the reference would evaluate (up to and incl. first blocked) */
+    uint64_t samples;         /* sample positions the reference would evaluate (up to and incl. first blocked);
+                                 0 unless plc_vl_count_samples(ctx, 1) */
     uint64_t fixed_samples;   /* same, for the hoisted fixed-sensor pass (M rays) */
     uint64_t exact_tests;     /* samples that needed the exact point test (implementation detail, informational) */
 } plc_counters;
@@ -219,6 +220,17 @@ plc_status plc_vl_sweep_strided(plc_ctx* ctx, const plc_params* prm, const plc_p
                                 uint64_t first, uint64_t stride, plc_sweep_out* out);
 plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_flags);
 plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out);
+/* How the traversal treats a ray once one of its samples is known to be blocked.  The reference walks a ray from the
+ * sensor outwards and returns at the first blocked sample (virtual_lidar.cpp:769-797); only "is any sample blocked"
+ * reaches its outputs (visibility, scores, flags, optimum).
+ *   on == 0 (default)  any-hit: samples are visited from the target end, and nothing of a ray is tested again once
+ *                      a blocked sample is known.  Same masks, scores, flags and optimum, bit for bit;
+ *                      plc_sweep_out::samples is reported as 0.
+ *   on != 0            counting: the first blocked sample index of every ray is established, and
+ *                      plc_sweep_out::samples is the number of sample positions the reference's loop evaluates
+ *                      (what SURVEY D4's algorithmic-bytes figure is made of).  3-17 % slower.
+ * No counterpart in the reference (it has no counters). */
+plc_status plc_vl_count_samples(plc_ctx* ctx, int on);
 /* Device address of this context's {double best_score; int64 best_global_index} pair (16 bytes),
  * valid after plc_vl_run_async; the multi-GPU exchange all-gathers it. */
 plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr);

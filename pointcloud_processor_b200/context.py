@@ -47,6 +47,7 @@ class Context:
         self._h = h
         self.device = device
         self.n_cells = 0
+        self.counting = False        # plc_vl_count_samples: any-hit traversal by default
         self._keep = []
 
     def close(self):
@@ -174,6 +175,12 @@ class Context:
         ms = C.c_float(0)
         self._check(self._L.plc_vl_last_sweep_kernel_ms(self._h, C.byref(ms)), "plc_vl_last_sweep_kernel_ms")
         return float(ms.value)
+
+    def count_samples(self, on: bool = True):
+        """plc_vl_count_samples: counting mode (the reference's evaluated-sample count in `counters["samples"]`)
+        instead of the default any-hit traversal."""
+        self._check(self._L.plc_vl_count_samples(self._h, 1 if on else 0), "plc_vl_count_samples")
+        self.counting = bool(on)
 
     def device_times(self) -> dict:
         """Kernel time (ms) of the last call of each kind, host<->device copies excluded."""

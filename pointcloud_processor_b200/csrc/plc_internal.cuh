@@ -219,6 +219,7 @@ struct plc_ctx {
     bool sweep_attr_set = false;      // k_sweep's shared-memory carve-out has been set on this context's device
     cudaEvent_t ev_run_begin = nullptr, ev_run_end = nullptr;       // around all kernels of plc_vl_run_async
     bool sweep_timed = false;
+    bool count_samples = false;  // k_sweep in counting mode (plc_vl_count_samples) instead of any-hit mode
     plc::DevTimer timer;         // kernels of the call in progress
     // plc_vl_set_terrain returns with the tail of its index build still in flight (the caller's next host work —
     // staging the cells, the pose list — overlaps it), so its kernels are timed by a timer of their own that

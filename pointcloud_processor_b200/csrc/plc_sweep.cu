@@ -425,6 +425,7 @@ constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not bloc
 #define PLC_SWEEP_BLOCKS_PER_SM 32
 #endif
 constexpr int kSweepWarps = 1;                  // one warp per block: no block-level synchronisation anywhere
+template <bool kAnyHit>
 __global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin, unsigned cand_stride,
         unsigned tiles, unsigned n_work, const plc_cell* __restrict__ cells, unsigned n_cells,
@@ -456,19 +457,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                  "mov.u32 %0, plc_ray_state;\n\t"
                  "mov.u32 %1, plc_q_tag;"
                  : "=r"(ray_state), "=r"(q_tag));
-#if defined(PLC_SM_AFFINE)
-    // experiment: the block scheduler hands the first blocks out round-robin over the SMs, so this permutation puts
-    // 32 consecutive work items (one tile, adjacent poses) on one SM for the first wave at least
-    unsigned wid = blockIdx.x;
-    if (wid >= n_work) return;
-    {
-        const unsigned W = PLC_SM_AFFINE * 32u, wave = wid / W, r = wid - wave * W;
-        if ((wave + 1) * W <= n_work) wid = wave * W + (r % PLC_SM_AFFINE) * 32u + r / PLC_SM_AFFINE;
-    }
-#else
     const unsigned wid = blockIdx.x;         // this warp's (tile, candidate) index
     if (wid >= n_work) return;
-#endif
     // Blocks run in (tile, candidate) order: the ~4 700 blocks resident at one time sweep two or three tiles from
     // every pose, so the warps that share an SM's L1 (and the L2) march towards the same cells (candidate-major
     // order measured 1.8 % slower on cfg2, 0.5 % on cfg3).  Results are stored candidate-major for k_finalize.
@@ -566,7 +556,9 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         if (lane < take) {
             tag = lds_u32(q_tag + 4u * ((q_head + lane) & (kQueueCap - 1)));
             int eslot = (int)(tag >> 16), ek = (int)(tag & 0xffffu);
-            if ((int)lds_u32(ray_state + 4u * eslot) > ek) {             // not already blocked earlier on the ray
+            // counting mode: skip a sample only if the ray is already blocked EARLIER (the first blocked index is an
+            // output); any-hit mode: any blocked sample decides the ray, so nothing of a blocked ray is tested again
+            if ((int)lds_u32(ray_state + 4u * eslot) > (kAnyHit ? kOpen - 1 : ek)) {
                 ++exact;
                 double ex, ey, ez;
                 exact_d(tile * kTileCells + eslot, ex, ey, ez);
@@ -705,7 +697,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             if (k < k_hi) {
                 // fixed-point fine-voxel coordinate of sample k and its per-step increment; the 2^16 scale is
                 // folded into the (power-of-two) voxel pitch and the pose offset, which changes no rounding
-                const float t0 = fmaf((float)k, P.stepf, P.startf);
+                // any-hit mode marches from the far end (blockers sit near the target more often than not)
+                const float t0 = fmaf((float)(kAnyHit ? k_hi - 1 : k), P.stepf, P.startf);
                 const float ug[3] = {uf[0] * P.inv_g16, uf[1] * P.inv_g16, uf[2] * P.inv_g16};
                 fx = __float2int_rd(fmaf(ug[0], t0, sof[0]));
                 fy = __float2int_rd(fmaf(ug[1], t0, sof[1]));
@@ -713,6 +706,11 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 dfx = __float2int_rn(uf[0] * P.step_fine);
                 dfy = __float2int_rn(uf[1] * P.step_fine);
                 dfz = __float2int_rn(uf[2] * P.step_fine);
+                if (kAnyHit) {
+                    dfx = -dfx;
+                    dfy = -dfy;
+                    dfz = -dfz;
+                }
                 // Both ends of the clipped range lie inside the grid by construction as long as float32
                 // resolves clip_t at the scene's coordinates (trust_limit).  Beyond that the ends are checked,
                 // and a ray that leaves the grid is marched sample by sample with bounds-checked lookups.
@@ -737,34 +735,16 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         }
         __syncwarp();
         // a lane is marching while k < k_hi; a blocked ray jumps to k = k_hi
-        const unsigned tag_base = ((unsigned)slot << 16) - 1u;
+        // step counter k visits sample k (counting mode) or sample k_rev - k (any-hit mode, far end first); a tag is
+        // written after k has moved on by one
+        const int k_rev = k + k_hi - 1;
+        const unsigned tag_base = kAnyHit ? ((unsigned)slot << 16) + (unsigned)k_rev + 1u : ((unsigned)slot << 16) - 1u;
         bool more = __any_sync(FULL, k < k_hi);
         // software pipeline of depth one: the occupancy row of the next sample is requested before the current
         // one is examined, so each marching lane keeps a load in flight through the whole step
         unsigned row = 0;
         if (k < k_hi) row = brick_row_fixed(G, fx, fy, fz);
         while (more) {
-#if defined(PLC_MARCH_PRED)
-            while (q_n + 32 <= kQueueCap) {               // room for one more push from every lane
-                // branch-free step: lanes that are done carry k = k_hi and a zero row, so every update below is a no-op
-                const unsigned st = (row >> row_shift(fx)) & 3u;
-                fx += dfx;
-                fy += dfy;
-                fz += dfz;
-                const int k1 = min(k + 1, k_hi);
-                row = 0;
-                if (k1 < k_hi) row = brick_row_fixed(G, fx, fy, fz);
-                if (st == 3u) reds_min_s32(ray_state + 4u * slot, k);
-                k = st == 3u ? k_hi : k1;
-                const unsigned ub = __ballot_sync(FULL, st == 1u);
-                if (ub) {
-                    if (st == 1u) sts_u32(q_tag + 4u * ((q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)), tag_base + (unsigned)k);
-                    q_n += __popc(ub);
-                }
-                more = __any_sync(FULL, k < k_hi);
-                if (!more) break;
-            }
-#else
             while (q_n + 32 <= kQueueCap) {               // room for one more push from every lane
                 unsigned st = 0;
                 if (k < k_hi) {
@@ -775,7 +755,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     row = 0;
                     if (k + 1 < k_hi) row = brick_row_fixed(G, fx, fy, fz);      // in flight through the rest of the step
                     if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
-                        reds_min_s32(ray_state + 4u * slot, k);
+                        reds_min_s32(ray_state + 4u * slot, kAnyHit ? k_rev - k : k);
                         k = k_hi;
                     } else {
                         ++k;
@@ -783,13 +763,12 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 }
                 const unsigned ub = __ballot_sync(FULL, st == 1u);     // lanes whose sample k - 1 was uncertain
                 if (ub) {
-                    if (st == 1u) sts_u32(q_tag + 4u * ((q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)), tag_base + (unsigned)k);
+                    if (st == 1u) sts_u32(q_tag + 4u * ((q_head + q_n + __popc(ub & lt_mask)) & (kQueueCap - 1)), kAnyHit ? tag_base - (unsigned)k : tag_base + (unsigned)k);
                     q_n += __popc(ub);
                 }
                 more = __any_sync(FULL, k < k_hi);
                 if (!more) break;
             }
-#endif
             if (q_n >= 32) drain();
         }
     }
@@ -807,7 +786,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
         unsigned j = tile * kTileCells + slot;
         int st = (int)lds_u32(ray_state + 4u * slot);
         bool vis = st >= kOpen;
-        if (st >= 0 && P.have_terrain) samples += (unsigned)(vis ? st - kOpen : st + 1);
+        if (!kAnyHit && st >= 0 && P.have_terrain) samples += (unsigned)(vis ? st - kOpen : st + 1);
         if (j < n_cells) {
             const double fixed = __ldg(&fixed_scores[j]);                // requested before the score arithmetic
             double mobile = 0.0;
@@ -1284,11 +1263,14 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
         // measured on cfg2/cfg3: a 50 % carve-out (L1 kept large) beats full occupancy of the 5.25 KB blocks
         if (!ctx->sweep_attr_set) {          // a per-device attribute: once per context, not per process
             const char* ev = getenv("PLC_DEV_CARVEOUT");
-            cudaFuncSetAttribute(k_sweep, cudaFuncAttributePreferredSharedMemoryCarveout, ev ? atoi(ev) : 50);
+            cudaFuncSetAttribute(k_sweep<false>, cudaFuncAttributePreferredSharedMemoryCarveout, ev ? atoi(ev) : 50);
+            cudaFuncSetAttribute(k_sweep<true>, cudaFuncAttributePreferredSharedMemoryCarveout, ev ? atoi(ev) : 50);
             ctx->sweep_attr_set = true;
         }
         cudaEventRecord(ctx->ev_sweep_begin, s);
-        k_sweep<<<(n_local * tiles + kSweepWarps - 1) / kSweepWarps, 32 * kSweepWarps, 0, s>>>(
+        // any-hit unless the caller wants the reference's evaluated-sample count (plc_vl_count_samples)
+        auto kernel = ctx->count_samples ? k_sweep<false> : k_sweep<true>;
+        kernel<<<(n_local * tiles + kSweepWarps - 1) / kSweepWarps, 32 * kSweepWarps, 0, s>>>(
             P, ctx->cands.as<plc_pose>(), ctx->pose_aux.as<PoseAux>(), (unsigned)ctx->cand_begin, (unsigned)ctx->cand_stride,
             tiles, n_local * tiles,
             ctx->cells.as<plc_cell>(), M,
@@ -1394,6 +1376,12 @@ extern "C" unsigned long long plc_dev_oob_count() {
     return v;
 }
 #endif
+
+extern "C" plc_status plc_vl_count_samples(plc_ctx* ctx, int on) {
+    if (!ctx) return PLC_E_INVALID_ARG;
+    ctx->count_samples = on != 0;
+    return PLC_OK;
+}
 
 extern "C" plc_status plc_last_device_times(plc_ctx* ctx, plc_device_times* out) {
     if (!ctx || !out) return PLC_E_INVALID_ARG;

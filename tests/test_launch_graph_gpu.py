@@ -15,12 +15,6 @@ pytestmark = pytest.mark.gpu
 BOX = A.CropBox(0.0, 15.0, -10.0, 10.0, -1.5, 10.0)
 
 
-@pytest.fixture(scope="module")
-def ctx():
-    with Context(0) as c:
-        yield c
-
-
 def xyz(rec):
     return np.ascontiguousarray(rec[:, :12]).view(np.float32).reshape(-1, 3)
 
@@ -139,7 +133,7 @@ def test_cpp_host_runs_the_same_graph(ctx, tmp_path, resident):
     assert got["kept"] == ref["excavation_info"].n_kept
     assert got["cells"] == ref["cells"].size and got["candidates"] == ref["candidates"].size
     r = ref["sweep"]
-    assert got["best_index"] == r.best_index and got["samples"] == r.counters["samples"]
+    assert got["best_index"] == r.best_index and got["rays_visible"] == r.counters["rays_visible"]
     assert got["best_score"] == pytest.approx(r.best_score, rel=1e-12)
     b = ref["candidates"][r.best_index]
     assert got["best_pose"] == [b["x"], b["y"], b["z"]]

@@ -13,12 +13,6 @@ pytestmark = pytest.mark.gpu
 BOX = A.CropBox(0.0, 15.0, -10.0, 10.0, -1.5, 10.0)      # pointcloud_filter.cpp:30-36, :106-116
 
 
-@pytest.fixture(scope="module")
-def ctx():
-    with Context(0) as c:
-        yield c
-
-
 def xyz(rec):
     return rec[:, :12].copy().view(np.float32).reshape(-1, 3)
 

@@ -5,6 +5,7 @@ for name in sys.argv[1:]:
     sc = scenes.build(name)
     with Context(0) as ctx:
         ctx.set_terrain(sc.terrain); ctx.set_cells(sc.cells)
+        if os.environ.get("PLC_COUNT"): ctx.count_samples(True)     # counting mode instead of the default any-hit
         r = ctx.sweep(sc.params, sc.fixed, sc.candidates[:8], scores=False)      # builds the index the sweep wants
         build_ms = ctx.device_times()
         r = ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)

@@ -9,6 +9,7 @@ sel = np.sort(np.random.default_rng(3).choice(sc.candidates.size, min(n, sc.cand
 cands = sc.candidates[sel]
 with Context(0) as ctx:
     ctx.set_terrain(sc.terrain); ctx.set_cells(sc.cells)
+    if os.environ.get("PLC_COUNT"): ctx.count_samples(True)     # counting mode instead of the default any-hit
     for _ in range(2):
         r = ctx.sweep(sc.params, sc.fixed, cands, scores=False)
     g = ctx.grid_info()[0]

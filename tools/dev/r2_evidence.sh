@@ -11,3 +11,6 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_sweep -s 1 -c 1 -f -o gpurun_out/${tag}_k_sweep \
   python tools/counters.py cfg2 > gpurun_out/${tag}_ncu_full.log 2>&1; echo "full capture rc=$?"
 tail -3 gpurun_out/${tag}_gpu_tests.txt; cat gpurun_out/${tag}_bench_n1.json | cut -c1-1500
+# cfg5 (4000 seeded poses, refinement as the full config gets it): full capture of k_sweep
+PLC_DEV_REFINE=2 timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_sweep -s 1 -c 1 -f -o gpurun_out/${tag}_k_sweep_cfg5 \
+  python tools/counters_subset.py cfg5 4000 > gpurun_out/${tag}_ncu_cfg5.log 2>&1; echo "cfg5 capture rc=$?"

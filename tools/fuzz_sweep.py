@@ -79,6 +79,7 @@ def main():
     tot = dict(rays=0, gated=0, visible=0, samples=0, exact=0)
     t0 = time.time()
     with Context(0) as ctx:
+        ctx.count_samples(True)          # the evaluated-sample counter is compared below
         for it in range(iters):
             rng = np.random.default_rng(seed * 100003 + it)
             terrain, observed, cells, poses, fixed, prm = scene(rng)

@@ -88,6 +88,7 @@ def check_filter_merge(ctx):
 if __name__ == "__main__":
     names = sys.argv[1:] or ["tiny", "small", "ref_default", "cfg1"]
     with Context(0) as ctx:
+        ctx.count_samples(True)          # the evaluated-sample counter is compared below
         check_filter_merge(ctx)
         for nm in names:
             check_scene(nm, ctx, full=nm not in ("cfg3", "cfg5"))

@@ -10,14 +10,30 @@ hi = next(i for i, r in enumerate(rows) if "Instructions Executed" in r)
 h = rows[hi]
 iI, iS = h.index("Instructions Executed"), h.index("# Samples")
 stall_cols = [(i, c) for i, c in enumerate(h) if c.startswith("stall_") and "Not Issued" not in c]
-# phase markers are comments in plc_sweep.cu: "// PHASE name" lines give the line ranges
-# phase boundaries: first line of each phase in plc_sweep.cu AS CAPTURED ("name:line,name:line,..." as argv[3])
-marks = [(int(b), a) for a, b in (kv.split(":") for kv in (sys.argv[3] if len(sys.argv) > 3 else
-         "prologue:459,drain:542,setup:607,march:719,final:756").split(","))]
+# Phase boundaries = the lines of these statements in the CURRENT sources (the capture must come from the same
+# revision: --import-source embeds line numbers, not the text), or "name:line,..." as argv[3].
+import os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+def find_lines(path, needles):
+    lines = open(os.path.join(ROOT, "pointcloud_processor_b200", "csrc", path)).read().split("\n")
+    out = {}
+    for name, needle in needles:
+        out[name] = next(i + 1 for i, l in enumerate(lines) if needle in l and name not in out)
+    return out
+if len(sys.argv) > 3:
+    marks = [(int(b), a) for a, b in (kv.split(":") for kv in sys.argv[3].split(","))]
+else:
+    m = find_lines("plc_sweep.cu", [("prologue", "const unsigned wid = blockIdx.x"), ("drain", "auto drain = [&]()"),
+                                    ("setup", "for (int r = 0; r < kRaysPerThread; ++r) {"),
+                                    ("march", "a lane is marching while k < k_hi"), ("final", "---- score (:689-700)")])
+    marks = [(l, n) for n, l in m.items()]
 marks.sort()
+vq = find_lines("plc_voxel_query.cuh", [("dist_lo", "float dist2_f32("), ("row_lo", "unsigned ldg_row("), ("row_hi", "unsigned row_shift(int fx)"),
+                                        ("ldrow", "unsigned ldg_brick_row(")])
 def phase_of(f, ln):
     if f == "plc_voxel_query.cuh":
-        return "march" if 86 <= ln <= 104 else ("exact" if 54 <= ln <= 60 else "vq_other")
+        if vq["row_lo"] <= ln <= vq["row_hi"] + 1 or vq["ldrow"] <= ln <= vq["ldrow"] + 5: return "march"
+        return "exact" if vq["dist_lo"] <= ln <= vq["dist_lo"] + 6 else "vq_other"
     if f != "plc_sweep.cu":
         return "intrinsics"
     p = "pre"

@@ -24,13 +24,17 @@ def gpu_sweep(ctx, sc, reps=3):
     ctx.set_terrain(sc.terrain)
     ctx.set_cells(sc.cells)
     ctx.set_observed(np.zeros((0, 3), np.float32))
-    ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)
+    ctx.count_samples(True)                 # one counting sweep: the reference's evaluated-sample count (D4's bytes)
+    r = ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)
+    r.extra["k_sweep_ms_counting"] = ctx.last_sweep_kernel_ms()
+    ctx.count_samples(False)                # timed in the library's default any-hit mode
     wall, kern = [], []
     for _ in range(reps):
         t0 = time.perf_counter()
-        r = ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)
+        fast = ctx.sweep(sc.params, sc.fixed, sc.candidates, scores=False)
         wall.append((time.perf_counter() - t0) * 1e3)
         kern.append(ctx.last_sweep_kernel_ms())
+    assert (fast.best_index, fast.best_score) == (r.best_index, r.best_score)
     return r, float(np.median(wall)), float(np.median(kern))
 
 
@@ -48,7 +52,7 @@ def sweep_row(ctx, name, budget):
     r, wall_ms, kern_ms = gpu_sweep(ctx, sc)
     row = dict(config=name, poses=C, rays_per_pose=M, terrain_points=N, sweep_ms=wall_ms, k_sweep_ms=kern_ms,
                rays_per_s=C * M / (wall_ms * 1e-3), samples=r.counters["samples"], best_index=int(r.best_index),
-               best_score=float(r.best_score))
+               best_score=float(r.best_score), k_sweep_ms_counting=r.extra["k_sweep_ms_counting"])
     alg = 32 * r.counters["rays"] + 4 * r.counters["samples"] + 64 * C + 16 * N
     row["algorithmic_GBps"] = alg / (kern_ms * 1e-3) / 1e9
     # parity + CPU baseline on a seeded pose subset sized to the budget (cfg1: everything)
@@ -65,12 +69,16 @@ def sweep_row(ctx, name, budget):
     subm = np.sort(rng.permutation(C)[:nmt])
     ref, row["cpu_mt_rays_per_s"], dtm = cpu_rate(sc, kd, subm, threads)
     row["cpu_mt_sample"] = f"{nmt} of {C} poses, {dtm:.1f} s, {threads} threads"
-    got = ctx.sweep(sc.params, sc.fixed, sc.candidates[subm], mask=True)
+    got = ctx.sweep(sc.params, sc.fixed, sc.candidates[subm], mask=True)                # any-hit: what was timed
+    ctx.count_samples(True)
+    cnt = ctx.sweep(sc.params, sc.fixed, sc.candidates[subm], mask=True)
+    ctx.count_samples(False)
+    row["any_hit_equals_counting"] = bool(np.array_equal(got.mask, cnt.mask) and np.array_equal(got.scores, cnt.scores))
     row["pairs_compared"] = int(subm.size * M)
     row["mask_mismatches"] = int(np.count_nonzero(np.unpackbits((got.mask ^ ref["mask"]).view(np.uint8))))
     row["score_max_rel_err"] = float(np.max(np.abs(got.scores - ref["scores"]) / np.maximum(1.0, np.abs(ref["scores"]))))
     row["argmax_equal_on_subset"] = bool(got.best_index == ref["best_index"])
-    row["samples_equal_on_subset"] = bool(got.counters["samples"] == ref["counters"]["samples"])
+    row["samples_equal_on_subset"] = bool(cnt.counters["samples"] == ref["counters"]["samples"])
     return row
 
 

@@ -15,6 +15,7 @@ from pointcloud_processor_b200 import Context, _abi as A, scenes  # noqa: E402
 from pointcloud_processor_b200.nodes import run_pipeline  # noqa: E402
 
 with Context(0) as ctx:
+    ctx.count_samples(True)          # the evaluated-sample counter is compared below
     for name in ("tiny", "small", "cfg1"):
         sc = scenes.build(name)
         ctx.set_terrain(sc.terrain)
