@@ -92,6 +92,7 @@ struct VoxelGeom {
     const uint32_t* __restrict__ bricks;
     const uint32_t* __restrict__ gstart;
     const float4* __restrict__ cgrp;
+    unsigned long long occ_tex;        // PLC_TEX_MARCH experiment: the occupancy rows as a 3-D texture (x/8, y, z) of 16-bit texels
 };
 
 struct VoxelIndex {
@@ -116,6 +117,11 @@ struct VoxelIndex {
     // `bricks` holds zeros everywhere except in the bricks of the list voxels that (geom, gstart, n_mid) of the
     // last build describe as non-empty: the next build clears just those (k_clear_touched) instead of the whole array
     bool bricks_sparse_dirty = false;
+    // PLC_TEX_MARCH experiment: a 3-D array copy of the occupancy rows for k_sweep's march
+    cudaArray_t occ_array = nullptr;
+    cudaTextureObject_t occ_tex = 0;
+    cudaSurfaceObject_t occ_surf = 0;
+    int occ_dims[3] = {0, 0, 0};
     bool has_points() const { return n_raw > 0; }
     // the "G" term of the algorithmic bytes: the indexed points, once (a lower bound of what the sweep must read)
     uint64_t bytes() const { return n_raw * 16; }

@@ -272,6 +272,35 @@ k_clear_touched(VoxelGeom g, size_t n_mid, const uint32_t* __restrict__ gstart, 
             }
 }
 
+#if defined(PLC_TEX_MARCH)
+// experiment: copies the bricks of the non-empty list voxels into the 3-D array the march reads through a texture
+__global__ void __launch_bounds__(256)
+k_rows_to_surface(VoxelGeom g, size_t n_mid, const uint32_t* __restrict__ gstart, const unsigned short* __restrict__ rows,
+                  cudaSurfaceObject_t surf) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t m = t >> 6;
+    const int r = (int)(t & 63);                 // row of the brick: (z & 7) * 8 + (y & 7)
+    if (m >= n_mid || gstart[m + 1] == gstart[m]) return;
+    const int mx = (int)(m % (size_t)g.mdim_x), my = (int)((m / (size_t)g.mdim_x) % (size_t)g.mdim_y),
+              mz = (int)(m / ((size_t)g.mdim_x * g.mdim_y));
+    const int fine = 1 << g.mid_shift;
+    const int bx0 = (mx * fine) >> kFineShift, by0 = (my * fine) >> kFineShift, bz0 = (mz * fine) >> kFineShift;
+    const int nb = fine > 8 ? fine >> kFineShift : 1;
+    for (int z = 0; z < nb; ++z)
+        for (int y = 0; y < nb; ++y)
+            for (int x = 0; x < nb; ++x) {
+                const int fy = ((by0 + y) << 3) + (r & 7), fz = ((bz0 + z) << 3) + (r >> 3);
+                const unsigned short v = rows[row_index(g, bx0 + x, fy, fz)];
+                surf3Dwrite(v, surf, (bx0 + x) * 2, fy, fz);
+            }
+}
+__global__ void __launch_bounds__(256) k_surface_zero(cudaSurfaceObject_t surf, int dx, int dy, int dz) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int x = (int)(t % (size_t)dx), y = (int)((t / (size_t)dx) % (size_t)dy), z = (int)(t / ((size_t)dx * dy));
+    if (z < dz) surf3Dwrite((unsigned short)0, surf, x * 2, y, z);
+}
+#endif
+
 }  // namespace
 
 // Uploads the cloud, drops non-finite points, records bbox.  The voxel index itself is (re)built
@@ -442,6 +471,35 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach_l, h / 2.0, ix.cfill.as<uint32_t>(),
                                           ix.gstart.as<uint32_t>(), ix.cgrp.as<float>());
     ctx->launches += 3;
+#if defined(PLC_TEX_MARCH)
+    {
+        const int dx = g.dim_x, dy = g.dim_y << kFineShift, dz = g.dim_z << kFineShift;
+        if (ix.occ_dims[0] != dx || ix.occ_dims[1] != dy || ix.occ_dims[2] != dz) {
+            if (ix.occ_tex) cudaDestroyTextureObject(ix.occ_tex);
+            if (ix.occ_surf) cudaDestroySurfaceObject(ix.occ_surf);
+            if (ix.occ_array) cudaFreeArray(ix.occ_array);
+            ix.occ_tex = 0; ix.occ_surf = 0; ix.occ_array = nullptr;
+            cudaChannelFormatDesc cd = cudaCreateChannelDesc(16, 0, 0, 0, cudaChannelFormatKindUnsigned);
+            PLC_CUDA_TRY(ctx, cudaMalloc3DArray(&ix.occ_array, &cd, make_cudaExtent(dx, dy, dz), cudaArraySurfaceLoadStore));
+            cudaResourceDesc rd{};
+            rd.resType = cudaResourceTypeArray;
+            rd.res.array.array = ix.occ_array;
+            cudaTextureDesc td{};
+            td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+            td.filterMode = cudaFilterModePoint;
+            td.readMode = cudaReadModeElementType;
+            td.normalizedCoords = 0;
+            PLC_CUDA_TRY(ctx, cudaCreateTextureObject(&ix.occ_tex, &rd, &td, nullptr));
+            PLC_CUDA_TRY(ctx, cudaCreateSurfaceObject(&ix.occ_surf, &rd));
+            ix.occ_dims[0] = dx; ix.occ_dims[1] = dy; ix.occ_dims[2] = dz;
+        }
+        const size_t total = (size_t)dx * dy * dz;
+        k_surface_zero<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(ix.occ_surf, dx, dy, dz);
+        k_rows_to_surface<<<(unsigned)((n_mid * 64 + 255) / 256), 256, 0, s>>>(g, n_mid, ix.gstart.as<uint32_t>(),
+                                                                                ix.bricks.as<unsigned short>(), ix.occ_surf);
+        g.occ_tex = ix.occ_tex;
+    }
+#endif
     ctx->T().end(s);
     PLC_CUDA_TRY(ctx, cudaGetLastError());
     ix.geom = g;

@@ -102,6 +102,16 @@ __device__ __forceinline__ unsigned voxel_state(const VoxelGeom& g, int ix, int 
 // The same for a position in 16.16 fixed-point fine-voxel units (k_sweep's march), split for software pipelining:
 // the row of the voxel holding (fx, fy, fz), and the state from a row.  In the brick layout the row's byte offset is
 // assembled from bit fields of the three coordinates.
+#if defined(PLC_TEX_MARCH)
+// experiment: the row through the texture unit, which does the 3-D address arithmetic (integer texel coordinates)
+__device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
+    unsigned r0, r1, r2, r3;
+    asm("tex.3d.v4.u32.s32 {%0,%1,%2,%3}, [%4, {%5,%6,%7,%8}];"
+        : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+        : "l"(g.occ_tex), "r"(fx >> (16 + kFineShift)), "r"(fy >> 16), "r"(fz >> 16), "r"(0));
+    return r0;
+}
+#else
 __device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, int fy, int fz) {
     PLC_CHECK_OOB((unsigned)(fx >> 16) >= (unsigned)(g.dim_x << kFineShift) || (unsigned)(fy >> 16) >= (unsigned)(g.dim_y << kFineShift) ||
                   (unsigned)(fz >> 16) >= (unsigned)(g.dim_z << kFineShift), 0u)
@@ -117,6 +127,7 @@ __device__ __forceinline__ unsigned brick_row_fixed(const VoxelGeom& g, int fx, 
     return ldg_row(g, row_index(g, fx >> (16 + kFineShift), fy >> 16, fz >> 16));
 #endif
 }
+#endif
 __device__ __forceinline__ unsigned row_shift(int fx) { return ((unsigned)fx >> 15) & 0xeu; }
 
 __device__ __forceinline__ uint32_t mid_voxel_of(const VoxelGeom& g, int ix, int iy, int iz) {
