@@ -122,7 +122,7 @@ def _pit_count(shape, density):
 
 def terrain(shape: str, n_points: int, seed: int, side: float = 30.0, pit_fraction: float = 0.10):
     """/excavated_terrain with exactly n_points points (float32 xyz)."""
-    rng = np.random.default_rng(seed)
+    rng = np.random.Generator(np.random.PCG64(seed))      # an explicit bit generator: the stream is fixed by NumPy's compatibility policy
     # pit density so that the pit surface is ~pit_fraction of the cloud
     target = max(64, int(n_points * pit_fraction))
     lo, hi = 0.002, 0.5
@@ -293,7 +293,7 @@ def lidar_scan(t: np.ndarray, q: np.ndarray, n_points: int, seed: int, shape: st
     the pad) in firing order (azimuth-major, ring-minor).  Range noise N(0, sigma).  Rays that hit nothing
     within max_range give no point (as a velodyne driver does), so azimuth steps are added until n_points
     returns exist and the list is cut to exactly n_points."""
-    rng = np.random.default_rng(seed)
+    rng = np.random.Generator(np.random.PCG64(seed))      # an explicit bit generator: the stream is fixed by NumPy's compatibility policy
     R = _rot(q)
     elev = np.deg2rad(np.linspace(-25.0, 15.0, rings))
     boxes = pit_boxes(shape)
