@@ -103,6 +103,7 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
     if (c->pinned) cudaFreeHost(c->pinned);
     if (c->stage_pinned) cudaFreeHost(c->stage_pinned);
     if (c->stage_done) cudaEventDestroy(c->stage_done);
+    if (c->sweep_graph_exec) cudaGraphExecDestroy(c->sweep_graph_exec);
     c->timer.destroy();
     c->terrain_timer.destroy();
     if (c->ev_sweep_begin) cudaEventDestroy(c->ev_sweep_begin);

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "plc.h"
 
@@ -226,6 +227,12 @@ struct plc_ctx {
     cudaEvent_t ev_run_begin = nullptr, ev_run_end = nullptr;       // around all kernels of plc_vl_run_async
     bool sweep_timed = false;
     bool count_samples = false;  // k_sweep in counting mode (plc_vl_count_samples) instead of any-hit mode
+    // the instantiated CUDA graph of the last repeated sweep, the launch signature it was recorded for, the signature
+    // of the previous sweep (a graph is recorded when a signature repeats), kernels per replay, replays so far
+    cudaGraphExec_t sweep_graph_exec = nullptr;
+    std::vector<unsigned char> sweep_graph_sig, sweep_graph_candidate;
+    unsigned sweep_graph_launches = 0;
+    uint64_t sweep_graph_replays = 0;
     plc::DevTimer timer;         // kernels of the call in progress
     // plc_vl_set_terrain returns with the tail of its index build still in flight (the caller's next host work —
     // staging the cells, the pose list — overlaps it), so its kernels are timed by a timer of their own that
