@@ -231,6 +231,12 @@ plc_status plc_vl_fetch(plc_ctx* ctx, plc_sweep_out* out);
  *                      (what SURVEY D4's algorithmic-bytes figure is made of).  3-17 % slower.
  * No counterpart in the reference (it has no counters). */
 plc_status plc_vl_count_samples(plc_ctx* ctx, int on);
+/* A sweep that repeats the previous one's launch signature (same device buffers, sizes, parameters and outputs asked
+ * for: the timer ticks of the node between two terrain messages, a benchmark's resident loop) is recorded into a CUDA
+ * graph, and every further repeat replays it as one launch (the context owns its graphs; any
+ * set_* / upload that moves a buffer or changes a size makes the next sweep record anew).  *n = replays so far.
+ * PLC_NO_GRAPH in the environment turns the mechanism off.  No counterpart in the reference. */
+plc_status plc_vl_graph_replays(plc_ctx* ctx, uint64_t* n);
 /* Device address of this context's {double best_score; int64 best_global_index} pair (16 bytes),
  * valid after plc_vl_run_async; the multi-GPU exchange all-gathers it. */
 plc_status plc_vl_result_device_ptr(plc_ctx* ctx, void** ptr);

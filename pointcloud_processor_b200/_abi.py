@@ -141,7 +141,7 @@ EXPORTS = [
     "plc_last_error", "plc_launch_count", "plc_abi_version", "plc_ctx_sync",
     "plc_vl_set_terrain", "plc_vl_set_observed", "plc_vl_set_cells", "plc_vl_sweep",
     "plc_vl_upload_candidates", "plc_vl_run_async", "plc_vl_fetch", "plc_vl_result_device_ptr",
-    "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times", "plc_vl_count_samples",
+    "plc_vl_grid_info", "plc_vl_last_sweep_kernel_ms", "plc_last_device_times", "plc_vl_count_samples", "plc_vl_graph_replays",
     "plc_vl_upload_candidates_strided", "plc_vl_sweep_strided", "plc_filter", "plc_merge",
     "plc_vl_compute_normals", "plc_vl_generate_cells", "plc_vl_generate_candidates",
     "plc_drivable_params_default", "plc_drivable_area", "plc_drivable_area_static",
@@ -239,6 +239,7 @@ def lib() -> C.CDLL:
                                     vp, u64, C.POINTER(DrivableInfo)]
     L.plc_drivable_area_static.argtypes = L.plc_drivable_area.argtypes
     L.plc_vl_count_samples.argtypes = [vp, C.c_int]
+    L.plc_vl_graph_replays.argtypes = [vp, C.POINTER(u64)]
     L.plc_vl_generate_candidates.argtypes = [vp, C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,
                                              dbl, dbl, vp, u64, C.POINTER(u64)]
     L.plc_host_generate_candidates.argtypes = [C.POINTER(CloudView), C.POINTER(GridBounds), vp, i32,

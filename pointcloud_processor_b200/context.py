@@ -182,6 +182,13 @@ class Context:
         self._check(self._L.plc_vl_count_samples(self._h, 1 if on else 0), "plc_vl_count_samples")
         self.counting = bool(on)
 
+    @property
+    def graph_replays(self) -> int:
+        """plc_vl_graph_replays: sweeps that were replayed from the context's CUDA graph."""
+        n = C.c_uint64(0)
+        self._check(self._L.plc_vl_graph_replays(self._h, C.byref(n)), "plc_vl_graph_replays")
+        return int(n.value)
+
     def device_times(self) -> dict:
         """Kernel time (ms) of the last call of each kind, host<->device copies excluded."""
         t = A.DeviceTimes()

@@ -1446,6 +1446,12 @@ extern "C" unsigned long long plc_dev_oob_count() {
 }
 #endif
 
+extern "C" plc_status plc_vl_graph_replays(plc_ctx* ctx, uint64_t* n) {
+    if (!ctx || !n) return PLC_E_INVALID_ARG;
+    *n = ctx->sweep_graph_replays;
+    return PLC_OK;
+}
+
 extern "C" plc_status plc_vl_count_samples(plc_ctx* ctx, int on) {
     if (!ctx) return PLC_E_INVALID_ARG;
     ctx->count_samples = on != 0;

@@ -368,3 +368,55 @@ def test_random_scenes_against_oracle(ctx):
             assert got.counters[k] == ref["counters"][k], (it, k)
         gated += ref["counters"]["rays_gated_in"]
     assert gated > 100_000
+
+
+def test_repeated_sweeps_replay_a_graph_and_see_new_data(scene_cache):
+    """A sweep with an unchanged launch signature is recorded into a CUDA graph on its second run and replayed from the
+    third; new poses written into the same device buffer, or new cells of the same count, must show in a replay, and a
+    changed parameter must not be served by the old graph."""
+    import os
+    from pointcloud_processor_b200 import Context
+    s = scene_cache("small")
+
+    def fresh(cands, cells, params):
+        with Context(0) as c:
+            c.set_terrain(s.terrain); c.set_cells(cells)
+            return c.sweep(params, s.fixed, cands, mask=True, flags=True, fixed_scores=True)
+
+    def same(a, b):
+        assert (a.best_index, a.best_score, a.best_covered, a.fixed_total) == (b.best_index, b.best_score, b.best_covered, b.fixed_total)
+        for k in ("scores", "covered", "mask", "cell_flags", "fixed_scores"):
+            assert np.array_equal(getattr(a, k), getattr(b, k)), k
+
+    with Context(0) as c:
+        c.set_terrain(s.terrain); c.set_cells(s.cells)
+        want = fresh(s.candidates, s.cells, s.params)
+        for i in range(4):
+            c.upload_candidates(s.params, s.fixed, s.candidates)
+            c.run_async(True, True)
+            same(c.fetch(mask=True, flags=True, fixed_scores=True), want)
+        if not os.environ.get("PLC_NO_GRAPH"):
+            assert c.graph_replays == 2                   # run 1 direct, run 2 records (and plays), runs 3 and 4 replay
+        moved = s.candidates.copy()
+        moved["x"] += 0.37
+        moved["z"] += 0.21
+        c.upload_candidates(s.params, s.fixed, moved)     # same buffer, same count: the replay reads the new poses
+        c.run_async(True, True)
+        same(c.fetch(mask=True, flags=True, fixed_scores=True), fresh(moved, s.cells, s.params))
+        cells2 = s.cells.copy()
+        cells2["z"] -= 0.05
+        c.set_cells(cells2)                               # same count, same buffers, new contents (and cell flags reset)
+        c.upload_candidates(s.params, s.fixed, moved)
+        c.run_async(True, True)
+        same(c.fetch(mask=True, flags=True, fixed_scores=True), fresh(moved, cells2, s.params))
+        replays = c.graph_replays
+        p2 = A.default_params()
+        for f, _ in A.Params._fields_:
+            setattr(p2, f, getattr(s.params, f))
+        p2.max_distance = s.params.max_distance * 0.8     # another signature: served by direct launches, then a new graph
+        for i in range(3):
+            c.upload_candidates(p2, s.fixed, moved)
+            c.run_async(True, True)
+            same(c.fetch(mask=True, flags=True, fixed_scores=True), fresh(moved, cells2, p2))
+        if not os.environ.get("PLC_NO_GRAPH"):
+            assert c.graph_replays == replays + 1
