@@ -424,9 +424,12 @@ constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not bloc
 #ifndef PLC_SWEEP_BLOCKS_PER_SM
 #define PLC_SWEEP_BLOCKS_PER_SM 32
 #endif
-constexpr int kSweepWarps = 1;                  // one warp per block: no block-level synchronisation anywhere
+#ifndef PLC_SWEEP_WARPS
+#define PLC_SWEEP_WARPS 1
+#endif
+constexpr int kSweepWarps = PLC_SWEEP_WARPS;    // one warp per block: no block-level synchronisation anywhere (2 and 4: experiment)
 template <bool kAnyHit>
-__global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM)
+__global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM / kSweepWarps)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin, unsigned cand_stride,
         unsigned tiles, unsigned n_work, const plc_cell* __restrict__ cells, unsigned n_cells,
         const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
@@ -452,12 +455,34 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
 #endif
     static_assert(kTileCells * 4 == PLC_RAYS_PER_THREAD * 128, "ray state bytes");
     unsigned q_tag, ray_state;
+#if PLC_SWEEP_WARPS == 1
     asm volatile(".shared .align 16 .b8 plc_ray_state[" PLC_RAY_STATE_BYTES "];\n\t"
                  ".shared .align 16 .b8 plc_q_tag[512];\n\t"
                  "mov.u32 %0, plc_ray_state;\n\t"
                  "mov.u32 %1, plc_q_tag;"
                  : "=r"(ray_state), "=r"(q_tag));
     const unsigned wid = blockIdx.x;         // this warp's (tile, candidate) index
+#else
+    // experiment: several warps per block, each with its own arrays; in tile-major order they are neighbouring poses
+    // of one tile, which share an SM by construction
+#if PLC_SWEEP_WARPS == 2 && PLC_RAYS_PER_THREAD == 16
+#define PLC_RS_ALL "4096"
+#define PLC_QT_ALL "1024"
+#elif PLC_SWEEP_WARPS == 4 && PLC_RAYS_PER_THREAD == 16
+#define PLC_RS_ALL "8192"
+#define PLC_QT_ALL "2048"
+#else
+#error "PLC_SWEEP_WARPS 2 or 4 with 16 rays per thread"
+#endif
+    asm volatile(".shared .align 16 .b8 plc_ray_state[" PLC_RS_ALL "];\n\t"
+                 ".shared .align 16 .b8 plc_q_tag[" PLC_QT_ALL "];\n\t"
+                 "mov.u32 %0, plc_ray_state;\n\t"
+                 "mov.u32 %1, plc_q_tag;"
+                 : "=r"(ray_state), "=r"(q_tag));
+    ray_state += (threadIdx.x >> 5) * (kTileCells * 4);
+    q_tag += (threadIdx.x >> 5) * 512;
+    const unsigned wid = blockIdx.x * kSweepWarps + (threadIdx.x >> 5);
+#endif
     if (wid >= n_work) return;
     // Blocks run in (tile, candidate) order: the ~4 700 blocks resident at one time sweep two or three tiles from
     // every pose, so the warps that share an SM's L1 (and the L2) march towards the same cells (candidate-major
