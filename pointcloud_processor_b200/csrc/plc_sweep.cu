@@ -486,14 +486,14 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     if (wid >= n_work) return;
     // Blocks run in (tile, candidate) order: the ~4 700 blocks resident at one time sweep two or three tiles from
     // every pose, so the warps that share an SM's L1 (and the L2) march towards the same cells (candidate-major
-    // order measured 1.8 % slower on cfg2, 0.5 % on cfg3).  Results are stored candidate-major for k_finalize.
+    // order measured 5 % slower with the any-hit traversal).  Partial results are stored tile-major too.
 #if defined(PLC_POSE_MAJOR)
     const unsigned local = wid / tiles, tile = wid - local * tiles;
 #else
     const unsigned n_loc = n_work / tiles;
     const unsigned tile = wid / n_loc, local = wid - tile * n_loc;
 #endif
-    const unsigned out_idx = local * tiles + tile;
+    const unsigned out_idx = tile * (n_work / tiles) + local;      // tile-major: k_finalize reads it coalesced
 #if defined(PLC_TMA_CELLS)
     // Experiment: the tile's float32 cell records staged in shared memory by one bulk copy
     // (cp.async.bulk, completion counted on an mbarrier) instead of one 16-byte load per ray.
@@ -861,7 +861,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     }
 }
 
-// per candidate: tiles summed in tile order
+// per candidate: tiles summed in tile order.  The partials are stored tile-major, so a warp's loads are contiguous;
+// eight are requested ahead of the (sequential, order-defining) additions.
 __global__ void __launch_bounds__(256)
 k_finalize(const double* __restrict__ partial_score, const int* __restrict__ partial_cov, unsigned n_local,
            unsigned tiles, double* __restrict__ scores, int* __restrict__ covered) {
@@ -869,9 +870,24 @@ k_finalize(const double* __restrict__ partial_score, const int* __restrict__ par
     if (c >= n_local) return;
     double t = 0.0;
     int cv = 0;
-    for (unsigned k = 0; k < tiles; ++k) {
-        t = __dadd_rn(t, partial_score[(size_t)c * tiles + k]);
-        cv += partial_cov[(size_t)c * tiles + k];
+    unsigned k = 0;
+    for (; k + 8 <= tiles; k += 8) {
+        double v[8];
+        int w[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            v[j] = partial_score[(size_t)(k + j) * n_local + c];
+            w[j] = partial_cov[(size_t)(k + j) * n_local + c];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            t = __dadd_rn(t, v[j]);
+            cv += w[j];
+        }
+    }
+    for (; k < tiles; ++k) {
+        t = __dadd_rn(t, partial_score[(size_t)k * n_local + c]);
+        cv += partial_cov[(size_t)k * n_local + c];
     }
     scores[c] = t;
     covered[c] = cv;
@@ -924,9 +940,15 @@ k_argmax(const double* __restrict__ scores, const int* __restrict__ covered, uns
         res->best_score = best;
         res->best_index = idx >= 0 ? (long long)(cand_begin + (unsigned long long)idx * cand_stride) : -1;
         res->best_covered = idx >= 0 ? covered[idx] : 0;
+    }
+    // fixed-sensor total: the block totals of k_fixed in a fixed summation shape (lane l adds blocks l, l + 32, ... in
+    // order, then a shuffle tree) — deterministic, and 14 + 5 dependent double additions instead of one per block
+    if (warp == 1) {
         double ft = 0.0;
-        for (unsigned b = 0; b < n_fixed_blocks; ++b) ft = __dadd_rn(ft, fixed_block_totals[b]);
-        res->fixed_total = ft;
+        for (unsigned b = lane; b < n_fixed_blocks; b += 32) ft = __dadd_rn(ft, fixed_block_totals[b]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ft = __dadd_rn(ft, __shfl_down_sync(0xffffffffu, ft, o));
+        if (lane == 0) res->fixed_total = ft;
     }
 }
 
