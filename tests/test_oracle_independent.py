@@ -114,3 +114,123 @@ def test_hand_scene_block_tunnel_and_radius():
         assert gated[0, 0] and not graz[0, 0]
         assert vis[0, 0] == expect_visible
         assert bool(ref["mask"][0, 0] & 1) == expect_visible
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The node's setup steps restated with cKDTree: the evaluation-cell lattice with its cell
+# normals (/root/reference/src/virtual_lidar.cpp:236-340) and the candidate-pose lattice with its ground heights
+# (:550-625).  PCL's radius search works on the float32-narrowed query in float32; the tree here answers in float64,
+# so a decision that hangs on a point within BAND of a search radius is not checked (counted, asserted rare).
+def independent_cells(area, normals, res, layers, normal_radius):
+    pts = np.asarray(area[:, :3], np.float32).astype(np.float64)
+    tree = scipy_spatial.cKDTree(pts)
+    lo, hi = pts.min(axis=0) - res, pts.max(axis=0) + res                       # :239-254
+    width = int(np.ceil((hi[0] - lo[0]) / res)) + 1
+    height = int(np.ceil((hi[1] - lo[1]) / res)) + 1
+    z_step = (hi[2] - lo[2]) / max(1, layers)
+    i, j, k = np.meshgrid(np.arange(height), np.arange(width), np.arange(layers), indexing="ij")   # loop order :265-271
+    x, y, z = lo[0] + j.ravel() * res, lo[1] + i.ravel() * res, lo[2] + k.ravel() * z_step + z_step / 2.0
+    q = np.column_stack([x, y, z]).astype(np.float32).astype(np.float64)       # PointXYZRGB search point
+    d, _ = tree.query(q, k=1)
+    near, graze = d < res * 1.5, np.abs(d - res * 1.5) < BAND                   # :273, :289-299
+    keep = near & ~graze
+    out = dict(x=x, y=y, z=z, near=near, graze=graze, normals=np.zeros((x.size, 3)), normal_graze=np.zeros(x.size, bool))
+    nrm = normals.astype(np.float64)
+    finite = np.all(np.isfinite(nrm), axis=1)
+    for c in np.flatnonzero(keep):                                              # :301-340
+        idx = np.array(tree.query_ball_point(q[c], normal_radius + BAND), int)
+        dd = np.linalg.norm(pts[idx] - q[c], axis=1)
+        out["normal_graze"][c] = bool(np.any(np.abs(dd - normal_radius) < BAND))
+        use = idx[(dd < normal_radius) & finite[idx]]
+        s = nrm[use].sum(axis=0)
+        n = np.linalg.norm(s)
+        out["normals"][c] = s / n if use.size and n > 1e-6 else (0.0, 0.0, 1.0)  # GridCell's default normal (:31-35)
+    return out, (lo, hi, width, height)
+
+
+def test_cell_lattice_matches_independent_restatement():
+    from pointcloud_processor_b200 import scenes
+    area, analytic = scenes.excavation_area("L", 0.05)
+    normals = O.compute_normals(area, 1.5)
+    res, layers = 0.1, 10
+    cells, b = O.generate_cells(area, normals, res, layers, 1.5)
+    ind, (lo, hi, width, height) = independent_cells(area, normals, res, layers, 1.5)
+    assert (b.width, b.height) == (width, height)
+    assert (b.min_x, b.max_x, b.min_y, b.max_y, b.min_z, b.max_z) == (lo[0], hi[0], lo[1], hi[1], lo[2], hi[2])
+    # membership: the oracle's cells are exactly the lattice points the tree calls near, outside the grazing band
+    key = lambda x, y, z: set(zip(x.tolist(), y.tolist(), z.tolist()))
+    mine_sure = key(*(ind[k][ind["near"] & ~ind["graze"]] for k in "xyz"))
+    mine_maybe = key(*(ind[k][ind["graze"]] for k in "xyz"))
+    theirs = key(cells["x"], cells["y"], cells["z"])
+    assert mine_sure <= theirs <= (mine_sure | mine_maybe)
+    assert len(mine_maybe) <= 1e-3 * len(theirs) and len(theirs) > 3000
+    # order: the reference's i (y), j (x), k (z) loop order
+    order = np.lexsort((cells["z"], cells["x"], cells["y"]))
+    assert np.array_equal(order, np.arange(cells.size))
+    # normals of the cells whose neighbour set does not hang on a grazing point
+    pos = {p: c for c, p in enumerate(zip(ind["x"].tolist(), ind["y"].tolist(), ind["z"].tolist()))}
+    at = np.array([pos[p] for p in zip(cells["x"].tolist(), cells["y"].tolist(), cells["z"].tolist())])
+    ok = ~ind["normal_graze"][at] & ~ind["graze"][at]
+    got = np.column_stack([cells["nx"], cells["ny"], cells["nz"]]).astype(np.float64)
+    assert ok.mean() > 0.9          # lattice cells over a lattice-sampled area: exact-radius neighbours are common
+    assert np.max(np.abs(got[ok] - ind["normals"][at][ok])) < 2e-7          # float32 storage of a double unit vector
+    print(f"cells {cells.size}, grazing lattice points {len(mine_maybe)}, cells with a grazing neighbour {int((~ok).sum())}")
+
+
+def independent_candidates(terrain, bounds, fixed_xy, num, search_radius, sensor_height):
+    pts = np.asarray(terrain[:, :3], np.float32).astype(np.float64)
+    tree2 = scipy_spatial.cKDTree(pts[:, :2])
+    lo_x, hi_x, lo_y, hi_y = bounds.min_x, bounds.max_x, bounds.min_y, bounds.max_y
+    ex = (lo_x - search_radius, hi_x + search_radius, lo_y - search_radius, hi_y + search_radius)
+    cx, cy, cz = (lo_x + hi_x) / 2.0, (lo_y + hi_y) / 2.0, (bounds.min_z + bounds.max_z) / 2.0
+    side = int(np.ceil(np.sqrt(float(num))))
+    xs, ys = (ex[1] - ex[0]) / (side - 1), (ex[3] - ex[2]) / (side - 1)
+    out, grazing = [], 0
+    for i in range(side):
+        for j in range(side):
+            x, y = ex[0] + i * xs, ex[2] + j * ys
+            if np.sqrt((x - fixed_xy[0]) ** 2 + (y - fixed_xy[1]) ** 2) < 0.5:                       # :570-572
+                continue
+            if lo_x <= x <= hi_x and lo_y <= y <= hi_y:                                              # :574
+                continue
+            # getGroundHeight (:599-625): points within 2 m of (x, y, 0) in 3-D AND within 1 m horizontally -> max z
+            qf = np.array([np.float32(x), np.float32(y)], np.float64)
+            idx = np.array(tree2.query_ball_point([x, y], 1.0 + 1e-3), int)
+            g = 0.0
+            if idx.size:
+                dh = np.hypot(pts[idx, 0] - x, pts[idx, 1] - y)
+                d3 = np.sqrt((pts[idx, 0] - qf[0]) ** 2 + (pts[idx, 1] - qf[1]) ** 2 + pts[idx, 2] ** 2)
+                sure = (dh < 1.0 - BAND) & (d3 < 2.0 - BAND)
+                maybe = (dh < 1.0 + BAND) & (d3 < 2.0 + BAND)
+                zs, zm = pts[idx[sure], 2], pts[idx[maybe], 2]
+                if zm.size and (not zs.size or zm.max() != zs.max()):
+                    grazing += 1
+                    out.append(None)
+                    continue
+                g = zs.max() if zs.size else 0.0
+            z = g + sensor_height
+            dx, dy, dz = cx - x, cy - y, cz - z
+            hd = np.sqrt(dx * dx + dy * dy)
+            if hd < 0.1:
+                continue
+            elev = np.arctan2(-dz, hd)
+            if np.deg2rad(-85.0) <= elev <= np.deg2rad(85.0):
+                out.append((x, y, z, -np.pi / 2 + elev, np.arctan2(dy, dx)))
+    return out, grazing
+
+
+def test_candidate_lattice_matches_independent_restatement():
+    from pointcloud_processor_b200 import scenes
+    area, _ = scenes.excavation_area("L", 0.05)
+    terrain = scenes.terrain("L", 50_000, seed=21, side=24.0)
+    _, b = O.generate_cells(area, O.compute_normals(area, 1.5), 0.1, 10, 1.5)
+    fixed = np.zeros(1, O.A.POSE_DTYPE)
+    fixed["x"], fixed["y"], fixed["z"] = 0.4, 0.5, 3.5
+    got = O.generate_candidates(O.Index(terrain, O.GRID), b, fixed, 400, 3.0, 1.1)
+    want, grazing = independent_candidates(terrain, b, (0.4, 0.5), 400, 3.0, 1.1)
+    assert len(want) == got.size > 200 and grazing <= 2
+    for g, w in zip(got, want):
+        if w is None:
+            continue
+        assert (g["x"], g["y"], g["z"]) == w[:3]
+        assert abs(g["pitch"] - w[3]) < 1e-12 and abs(g["yaw"] - w[4]) < 1e-12
