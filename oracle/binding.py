@@ -13,7 +13,8 @@ import numpy as np
 from pointcloud_processor_b200 import _abi as A   # shared POD layouts only (include/plc.h)
 
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "_build" / "liboracle.so"
+# PLC_ORACLE_LIB: another build of the same sources (the ASan/UBSan one of `make -C oracle asan`)
+LIB_PATH = Path(os.environ.get("PLC_ORACLE_LIB") or _HERE / "_build" / "liboracle.so")
 
 BRUTE, GRID, KDTREE = 0, 1, 2
 

@@ -245,7 +245,7 @@ extern "C" int orc_vl_sweep(orc_sweep_args* a) {
     a->best_index = best_i;
     a->best_score = best;
     a->best_covered = best_i >= 0 ? covered[best_i] : 0;
-    if (a->scores) std::memcpy(a->scores, scores.data(), C * sizeof(double));
-    if (a->covered) std::memcpy(a->covered, covered.data(), C * sizeof(int32_t));
+    if (a->scores && C) std::memcpy(a->scores, scores.data(), C * sizeof(double));       // an empty vector's data() may be null
+    if (a->covered && C) std::memcpy(a->covered, covered.data(), C * sizeof(int32_t));
     return 0;
 }

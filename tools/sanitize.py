@@ -4,7 +4,7 @@ empty clouds, scenes far from the origin), for a build with bounds checks on the
     make -C pointcloud_processor_b200/csrc DEV_FLAGS=-DPLC_BOUNDS_CHECK ..., then
     PLC_DEV_LIB=.../dev_chk.so python tools/sanitize.py      -> prints the out-of-range access count (must be 0)
 
-(compute-sanitizer is not available on the GPU pool.)"""
+(compute-sanitizer is closed on the GPU pool: its wrapper there refuses to run and says so.)"""
 import os
 import sys
 
@@ -15,7 +15,8 @@ from pointcloud_processor_b200 import Context, _abi as A, scenes  # noqa: E402
 from pointcloud_processor_b200.nodes import run_pipeline  # noqa: E402
 
 with Context(0) as ctx:
-    ctx.count_samples(True)          # the evaluated-sample counter is compared below
+  for counting in (True, False):       # both traversal modes of k_sweep
+    ctx.count_samples(counting)
     for name in ("tiny", "small", "cfg1"):
         sc = scenes.build(name)
         ctx.set_terrain(sc.terrain)
