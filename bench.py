@@ -425,6 +425,9 @@ def parity_block(rig: Rig, scene, n_mask_poses: int = 64) -> dict:
         t0 = time.perf_counter()
         full = ctx.sweep(scene.params, scene.fixed, scene.candidates, scores=True)
         unsharded_ms = (time.perf_counter() - t0) * 1e3
+        ctx.sweep(scene.params, scene.fixed, scene.candidates, scores=False)      # warm (index at its final refinement)
+        dt = ctx.device_times()      # the same workload on ONE GPU in this run: the base of the strong-scaling figure
+        unsharded_dev_ms = dt["sweep_kernel_ms"] + dt["sweep_fixed_ms"] + dt["sweep_reduce_ms"]
         k = min(n_mask_poses, len(range(0, C, rig.world)))
         mine = ctx.sweep_strided(scene.params, scene.fixed, scene.candidates[: k * rig.world], 0, rig.world, mask=True)
         whole = ctx.sweep(scene.params, scene.fixed, scene.candidates[: k * rig.world], mask=True)
@@ -433,7 +436,8 @@ def parity_block(rig: Rig, scene, n_mask_poses: int = 64) -> dict:
                "scores_bit_equal": bool(np.array_equal(scores, full.scores)),
                "covered_equal": bool(np.array_equal(covered, full.covered)),
                "argmax_equal": bool(sharded_best[1] == full.best_index and sharded_best[0] == full.best_score),
-               "pairs": int(k * M), "mask_mismatches": mism, "unsharded_wall_ms": unsharded_ms}
+               "pairs": int(k * M), "mask_mismatches": mism, "unsharded_wall_ms": unsharded_ms,
+               "one_gpu_sweep_ms_same_workload": unsharded_dev_ms}
         assert out["scores_bit_equal"] and out["argmax_equal"] and mism == 0, out
     rig.barrier()
     return out

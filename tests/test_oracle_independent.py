@@ -234,3 +234,97 @@ def test_candidate_lattice_matches_independent_restatement():
             continue
         assert (g["x"], g["y"], g["z"]) == w[:3]
         assert abs(g["pitch"] - w[3]) < 1e-12 and abs(g["yaw"] - w[4]) < 1e-12
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The terrain generator's carve, restated from /root/reference/src/excavated_surface_generator.cpp:
+#   :183-225  getTerrainHeight: 3-D radius search around (x, y, 0), mean z of the hits within the radius in 2-D, nearest
+#             neighbour's z if there are none
+#   :284-300  pit centre = zx120 transform * (offset_x, offset_y, 0), its z from getTerrainHeight, yaw from getRPY
+#   :326-348  isInsideExcavationArea: the boxes grown by the slope offset at that depth
+#   :457-476  processExcavation: a point stays unless it is inside
+def independent_kept(pts32, t, q, prm):
+    pts = pts32.astype(np.float64)
+    ok = np.all(np.isfinite(pts), axis=1)
+    tree = scipy_spatial.cKDTree(pts[ok])
+    pz = pts[ok, 2]
+    R = prm.terrain_search_radius
+
+    def height(x, y):
+        """(mean z, grazing) as getTerrainHeight forms it."""
+        qf = np.array([np.float32(x), np.float32(y), 0.0], np.float64)
+        idx = np.array(tree.query_ball_point(qf, R + BAND), int)
+        if idx.size:
+            p = tree.data[idx]
+            d3 = np.linalg.norm(p - qf, axis=1)
+            d2 = np.hypot(p[:, 0] - x, p[:, 1] - y)
+            graze = bool(np.any(np.abs(d3 - R) < BAND) or np.any(np.abs(d2 - R) < BAND))
+            use = (d3 < R) & (d2 <= R)
+            if use.any():
+                return float(pz[idx[use]].mean()), graze
+            if graze:
+                return 0.0, True
+        _, j = tree.query(qf, k=1)
+        return float(pz[j]), False
+
+    x, y, z, w = q
+    yaw = np.arctan2(2.0 * (w * z + x * y), 1.0 - 2.0 * (y * y + z * z))                 # getRPY's yaw of a unit quaternion
+    rot = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w)], [2 * (x * y + z * w), 1 - 2 * (x * x + z * z)]])
+    cxy = rot @ np.array([prm.offset_x, prm.offset_y]) + np.asarray(t[:2], float)       # z of the offset is 0: the tilt terms vanish for a yaw-only base
+    cz, _ = height(cxy[0], cxy[1])
+    if prm.l_shape_enabled:                                                             # getExcavationBoxes :137-181
+        boxes = [(0.0, -prm.arm1_length / 2.0, prm.arm1_width, prm.arm1_length),
+                 (prm.arm2_length / 2.0, -prm.arm1_length + prm.arm2_width / 2.0, prm.arm2_length, prm.arm2_width)]
+    else:
+        boxes = [(0.0, 0.0, prm.length, prm.width)]
+    slope_offset = prm.depth / np.tan(np.deg2rad(prm.slope_angle_deg))
+    grow_max = max(slope_offset, 0.0) + 1e-6
+
+    def inside(xl, yl, zr):
+        if zr < -prm.depth or zr > 0:
+            return False
+        cur = slope_offset * ((prm.depth + zr) / prm.depth)
+        return any(abs(xl - bx) <= bl / 2.0 + cur and abs(yl - by) <= bw / 2.0 + cur for bx, by, bl, bw in boxes)
+
+    kept, grazing = np.ones(pts.shape[0], bool), np.zeros(pts.shape[0], bool)
+    c, s = np.cos(-yaw), np.sin(-yaw)
+    for i in np.flatnonzero(ok):
+        dx, dy = pts[i, 0] - cxy[0], pts[i, 1] - cxy[1]
+        xl, yl = dx * c - dy * s, dx * s + dy * c
+        if not any(abs(xl - bx) <= bl / 2.0 + grow_max and abs(yl - by) <= bw / 2.0 + grow_max for bx, by, bl, bw in boxes):
+            continue                                                                    # outside the widest outline whatever the height
+        h, g = height(pts[i, 0], pts[i, 1])
+        zr = pts[i, 2] - h
+        a, b_, c_ = inside(xl, yl, zr), inside(xl, yl, zr - 1e-6), inside(xl, yl, zr + 1e-6)
+        kept[i] = not a
+        grazing[i] = g or not (a == b_ == c_)
+    return kept, grazing, (cxy[0], cxy[1], cz), yaw
+
+
+@pytest.mark.parametrize("shape,yaw", [("L", 0.0), ("rect", 0.4)])
+def test_generator_carve_matches_independent_restatement(shape, yaw):
+    from pointcloud_processor_b200 import scenes, _abi as A
+    rng = np.random.default_rng(8)
+    n = 12_000
+    pts = np.zeros((n, 3), np.float32)                                                   # rolling ground, un-carved, around the pit
+    pts[:, :2] = rng.uniform(-2.0, 7.0, (n, 2))
+    pts[:, 2] = 0.15 * np.sin(0.4 * pts[:, 0]) * np.cos(0.3 * pts[:, 1]) + rng.normal(0, 0.01, n) - rng.uniform(0, 1.2, n) * (rng.random(n) < 0.3)
+    pts[rng.choice(n, 8, replace=False), rng.integers(0, 3, 8)] = np.nan
+    prm = A.excavation_params(l_shape_enabled=1 if shape == "L" else 0)
+    t = np.array([0.3, -0.2, 0.0])
+    q = np.array([0.0, 0.0, np.sin(yaw / 2), np.cos(yaw / 2)])
+    ns, na = A.excavation_counts(prm)
+    terrain, area, info = O.excavate(pts, np.zeros(n, np.uint32), t, q, prm, ns, na)
+    kept, grazing, centre, ind_yaw = independent_kept(pts, t, q, prm)
+    assert abs(info.yaw - ind_yaw) < 1e-12
+    assert abs(info.center[0] - centre[0]) < 1e-12 and abs(info.center[1] - centre[1]) < 1e-12 and abs(info.center[2] - centre[2]) < 1e-9
+    got_xyz = np.ascontiguousarray(terrain[: info.n_kept, :12]).view(np.float32).reshape(-1, 3)
+    # the oracle's kept points, in input order, are the independently kept ones, give or take the grazing ones
+    sure_kept, sure_cut = kept & ~grazing, ~kept & ~grazing
+    got_set = set(map(bytes, got_xyz.view(np.uint8).reshape(-1, 12)))
+    as_bytes = lambda m: set(map(bytes, pts[m].view(np.uint8).reshape(-1, 12)))
+    assert as_bytes(sure_kept) <= got_set and not (as_bytes(sure_cut) & got_set)
+    assert grazing.sum() <= 0.01 * n and (~kept).sum() > 100 and info.n_kept < n
+    order = [bytes(b) for b in pts[np.isin(np.arange(n), np.flatnonzero(kept | grazing))].view(np.uint8).reshape(-1, 12) if bytes(b) in got_set]
+    assert order == [bytes(b) for b in got_xyz.view(np.uint8).reshape(-1, 12)]           # input order kept (:470-472)
+    print(f"{shape}: {n} points, {int((~kept).sum())} carved, {int(grazing.sum())} grazing, kept {info.n_kept}")
