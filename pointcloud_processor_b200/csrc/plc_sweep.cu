@@ -77,6 +77,14 @@ __device__ __forceinline__ unsigned lds_u32(unsigned addr) {
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
     return v;
 }
+__device__ __forceinline__ void sts_u8(unsigned addr, unsigned v) {
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned lds_u8(unsigned addr) {
+    unsigned v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
 __device__ __forceinline__ void reds_min_s32(unsigned addr, int v) {
     asm volatile("red.shared.min.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
@@ -424,12 +432,9 @@ constexpr int kOpen = 0x40000000;                // ray_state >= kOpen: not bloc
 #ifndef PLC_SWEEP_BLOCKS_PER_SM
 #define PLC_SWEEP_BLOCKS_PER_SM 32
 #endif
-#ifndef PLC_SWEEP_WARPS
-#define PLC_SWEEP_WARPS 1
-#endif
-constexpr int kSweepWarps = PLC_SWEEP_WARPS;    // one warp per block: no block-level synchronisation anywhere (2 and 4: experiment)
+constexpr int kSweepWarps = 1;                  // one warp per block: no block-level synchronisation anywhere
 template <bool kAnyHit>
-__global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM / kSweepWarps)
+__global__ void __launch_bounds__(32 * kSweepWarps, PLC_SWEEP_BLOCKS_PER_SM)
 k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restrict__ aux, unsigned cand_begin, unsigned cand_stride,
         unsigned tiles, unsigned n_work, const plc_cell* __restrict__ cells, unsigned n_cells,
         const double* __restrict__ fixed_scores, double* __restrict__ partial_score,
@@ -444,45 +449,38 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
 #if PLC_RAYS_PER_THREAD == 8
 #define PLC_TILE_F4_BYTES "4096"
 #define PLC_RAY_STATE_BYTES "1024"
+#define PLC_RAY_BYTE_BYTES "256"
 #elif PLC_RAYS_PER_THREAD == 16
 #define PLC_TILE_F4_BYTES "8192"
 #define PLC_RAY_STATE_BYTES "2048"
+#define PLC_RAY_BYTE_BYTES "512"
 #elif PLC_RAYS_PER_THREAD == 32
 #define PLC_TILE_F4_BYTES "16384"
 #define PLC_RAY_STATE_BYTES "4096"
+#define PLC_RAY_BYTE_BYTES "1024"
 #else
 #error "PLC_RAYS_PER_THREAD must be 8, 16 or 32"
 #endif
     static_assert(kTileCells * 4 == PLC_RAYS_PER_THREAD * 128, "ray state bytes");
     unsigned q_tag, ray_state;
-#if PLC_SWEEP_WARPS == 1
-    asm volatile(".shared .align 16 .b8 plc_ray_state[" PLC_RAY_STATE_BYTES "];\n\t"
-                 ".shared .align 16 .b8 plc_q_tag[512];\n\t"
-                 "mov.u32 %0, plc_ray_state;\n\t"
-                 "mov.u32 %1, plc_q_tag;"
-                 : "=r"(ray_state), "=r"(q_tag));
+    if constexpr (kAnyHit) {
+        // any-hit needs three states per ray — gated out (0), open (1), known to be blocked (2) — kept as one byte
+        // each: "blocked" is a plain byte store of a constant (every writer writes the same value), so there is no
+        // shared-memory atomic in this mode, and the block is 1 KB instead of 2.5 KB: 32 blocks fit the 32 KB
+        // shared-memory configuration, which leaves the occupancy rows a 224 KB L1 instead of 124 KB.
+        asm volatile(".shared .align 16 .b8 plc_ray_byte[" PLC_RAY_BYTE_BYTES "];\n\t"
+                     ".shared .align 16 .b8 plc_q_tag_a[512];\n\t"
+                     "mov.u32 %0, plc_ray_byte;\n\t"
+                     "mov.u32 %1, plc_q_tag_a;"
+                     : "=r"(ray_state), "=r"(q_tag));
+    } else {
+        asm volatile(".shared .align 16 .b8 plc_ray_state[" PLC_RAY_STATE_BYTES "];\n\t"
+                     ".shared .align 16 .b8 plc_q_tag[512];\n\t"
+                     "mov.u32 %0, plc_ray_state;\n\t"
+                     "mov.u32 %1, plc_q_tag;"
+                     : "=r"(ray_state), "=r"(q_tag));
+    }
     const unsigned wid = blockIdx.x;         // this warp's (tile, candidate) index
-#else
-    // experiment: several warps per block, each with its own arrays; in tile-major order they are neighbouring poses
-    // of one tile, which share an SM by construction
-#if PLC_SWEEP_WARPS == 2 && PLC_RAYS_PER_THREAD == 16
-#define PLC_RS_ALL "4096"
-#define PLC_QT_ALL "1024"
-#elif PLC_SWEEP_WARPS == 4 && PLC_RAYS_PER_THREAD == 16
-#define PLC_RS_ALL "8192"
-#define PLC_QT_ALL "2048"
-#else
-#error "PLC_SWEEP_WARPS 2 or 4 with 16 rays per thread"
-#endif
-    asm volatile(".shared .align 16 .b8 plc_ray_state[" PLC_RS_ALL "];\n\t"
-                 ".shared .align 16 .b8 plc_q_tag[" PLC_QT_ALL "];\n\t"
-                 "mov.u32 %0, plc_ray_state;\n\t"
-                 "mov.u32 %1, plc_q_tag;"
-                 : "=r"(ray_state), "=r"(q_tag));
-    ray_state += (threadIdx.x >> 5) * (kTileCells * 4);
-    q_tag += (threadIdx.x >> 5) * 512;
-    const unsigned wid = blockIdx.x * kSweepWarps + (threadIdx.x >> 5);
-#endif
     if (wid >= n_work) return;
     // Blocks run in (tile, candidate) order: the ~4 700 blocks resident at one time sweep two or three tiles from
     // every pose, so the warps that share an SM's L1 (and the L2) march towards the same cells (candidate-major
@@ -583,7 +581,7 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             int eslot = (int)(tag >> 16), ek = (int)(tag & 0xffffu);
             // counting mode: skip a sample only if the ray is already blocked EARLIER (the first blocked index is an
             // output); any-hit mode: any blocked sample decides the ray, so nothing of a blocked ray is tested again
-            if ((int)lds_u32(ray_state + 4u * eslot) > (kAnyHit ? kOpen - 1 : ek)) {
+            if (kAnyHit ? lds_u8(ray_state + (unsigned)eslot) != 2u : (int)lds_u32(ray_state + 4u * eslot) > ek) {
                 ++exact;
                 double ex, ey, ez;
                 exact_d(tile * kTileCells + eslot, ex, ey, ez);
@@ -627,7 +625,10 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                 const float d0 = dist2_f32(ox, oy, oz, X.x, Y.x, Z.x), d1 = dist2_f32(ox, oy, oz, X.y, Y.y, Z.y);
                 const float d2 = dist2_f32(ox, oy, oz, X.z, Y.z, Z.z), d3 = dist2_f32(ox, oy, oz, X.w, Y.w, Z.w);
                 if (fminf(fminf(d0, d1), fminf(d2, d3)) < P.thr_block)
-                    reds_min_s32(ray_state + 4u * (o_tag >> 16), (int)(o_tag & 0xffffu));
+                {
+                    if (kAnyHit) sts_u8(ray_state + (o_tag >> 16), 2u);
+                    else reds_min_s32(ray_state + 4u * (o_tag >> 16), (int)(o_tag & 0xffffu));
+                }
             }
         }
         __syncwarp();
@@ -691,7 +692,9 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
             }
         }
         gated += n >= 0 ? 1u : 0u;
-        sts_u32(ray_state + 4u * slot, (unsigned)(n >= 0 ? kOpen + n : -1));      // published before any of the ray's samples can be queued
+        // published before any of the ray's samples can be queued
+        if (kAnyHit) sts_u8(ray_state + (unsigned)slot, n >= 0 ? 1u : 0u);
+        else sts_u32(ray_state + 4u * slot, (unsigned)(n >= 0 ? kOpen + n : -1));
 
         // ---- checkVisibilityWithRaycasting (:754-800): clear / certain samples here, uncertain ones queued
         int k = 0, k_hi = 0;
@@ -751,7 +754,10 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                         double dx, dy, dz;
                         exact_d(j, dx, dy, dz);
                         bool clear = ray_clear(P, s.x, s.y, s.z, dx, dy, dz, ray_length(dx, dy, dz), st);
-                        if (!clear) sts_u32(ray_state + 4u * slot, st.samples - 1u);
+                        if (!clear) {
+                            if (kAnyHit) sts_u8(ray_state + (unsigned)slot, 2u);
+                            else sts_u32(ray_state + 4u * slot, st.samples - 1u);
+                        }
                         exact += st.exact;
                         k = k_hi = 0;
                     }
@@ -780,7 +786,8 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
                     row = 0;
                     if (k + 1 < k_hi) row = brick_row_fixed(G, fx, fy, fz);      // in flight through the rest of the step
                     if (st == 3u) {                       // certainly blocked: nothing later on the ray matters
-                        reds_min_s32(ray_state + 4u * slot, kAnyHit ? k_rev - k : k);
+                        if (kAnyHit) sts_u8(ray_state + (unsigned)slot, 2u);
+                        else reds_min_s32(ray_state + 4u * slot, k);
                         k = k_hi;
                     } else {
                         ++k;
@@ -809,8 +816,14 @@ k_sweep(SweepDev P, const plc_pose* __restrict__ cands, const PoseAux* __restric
     for (int r = 0; r < kRaysPerThread; ++r) {
         const int slot = r * 32 + lane;
         unsigned j = tile * kTileCells + slot;
-        int st = (int)lds_u32(ray_state + 4u * slot);
-        bool vis = st >= kOpen;
+        int st = 0;
+        bool vis;
+        if (kAnyHit) {
+            vis = lds_u8(ray_state + (unsigned)slot) == 1u;
+        } else {
+            st = (int)lds_u32(ray_state + 4u * slot);
+            vis = st >= kOpen;
+        }
         if (!kAnyHit && st >= 0 && P.have_terrain) samples += (unsigned)(vis ? st - kOpen : st + 1);
         if (j < n_cells) {
             const double fixed = __ldg(&fixed_scores[j]);                // requested before the score arithmetic
@@ -1298,11 +1311,14 @@ extern "C" plc_status plc_vl_run_async(plc_ctx* ctx, int want_mask, int want_fla
     SweepResult* res = ctx->result.as<SweepResult>();
     double* fixed_totals = ctx->scratch.as<double>();
     if (n_local) {
-        // measured on cfg2/cfg3: a 50 % carve-out (L1 kept large) beats full occupancy of the 5.25 KB blocks
+        // counting kernel (2.5 KB per block): a 50 % carve-out measured best on cfg2/cfg3
         if (!ctx->sweep_attr_set) {          // a per-device attribute: once per context, not per process
             const char* ev = getenv("PLC_DEV_CARVEOUT");
             cudaFuncSetAttribute(k_sweep<false>, cudaFuncAttributePreferredSharedMemoryCarveout, ev ? atoi(ev) : 50);
-            cudaFuncSetAttribute(k_sweep<true>, cudaFuncAttributePreferredSharedMemoryCarveout, ev ? atoi(ev) : 50);
+            const char* ev_a = getenv("PLC_DEV_CARVEOUT_ANYHIT");
+            // the any-hit kernel's 32 blocks need 32 KB of shared memory: the smallest configuration that holds them
+            // (carve-out 10-15 %: 2.19 ms on cfg2; 25 %: 2.21; 50 %: 2.27; 5 %: 3.24, half the blocks)
+            cudaFuncSetAttribute(k_sweep<true>, cudaFuncAttributePreferredSharedMemoryCarveout, ev_a ? atoi(ev_a) : 12);
             ctx->sweep_attr_set = true;
         }
     }
