@@ -328,3 +328,38 @@ def test_generator_carve_matches_independent_restatement(shape, yaw):
     order = [bytes(b) for b in pts[np.isin(np.arange(n), np.flatnonzero(kept | grazing))].view(np.uint8).reshape(-1, 12) if bytes(b) in got_set]
     assert order == [bytes(b) for b in got_xyz.view(np.uint8).reshape(-1, 12)]           # input order kept (:470-472)
     print(f"{shape}: {n} points, {int((~kept).sum())} carved, {int(grazing.sum())} grazing, kept {info.n_kept}")
+
+
+# PCA normals of /excavation_area (/root/reference/src/virtual_lidar.cpp:209-234, pcl::NormalEstimation with a radius
+# search): neighbours within the radius, covariance about their centroid, eigenvector of the smallest eigenvalue,
+# flipped towards the viewpoint (0, 0, 0) by PCL and then to n_z >= 0 by the node.
+def test_pca_normals_match_independent_restatement():
+    from pointcloud_processor_b200 import scenes
+    area, analytic = scenes.excavation_area("L", 0.05)
+    got = O.compute_normals(area, 1.5).astype(np.float64)
+    pts = np.asarray(area[:, :3], np.float32).astype(np.float64)
+    tree = scipy_spatial.cKDTree(pts)
+    rng = np.random.default_rng(4)
+    checked = grazing = 0
+    for i in rng.choice(pts.shape[0], 400, replace=False):
+        idx = np.array(tree.query_ball_point(pts[i], 1.5 + BAND), int)
+        d = np.linalg.norm(pts[idx] - pts[i], axis=1)
+        if np.any(np.abs(d - 1.5) < BAND):
+            grazing += 1
+            continue
+        nb = pts[idx[d < 1.5]]
+        assert nb.shape[0] >= 3
+        c = nb - nb.mean(axis=0)
+        w, v = np.linalg.eigh(c.T @ c / nb.shape[0])
+        n = v[:, 0]                                            # smallest eigenvalue first
+        if np.dot(-pts[i], n) < 0:                             # flipNormalTowardsViewpoint, viewpoint (0, 0, 0)
+            n = -n
+        if n[2] < 0:                                           # :223-229 (the second flip decides the final sign)
+            n = -n
+        gap = w[1] - w[0]
+        if gap < 1e-6 * max(w[2], 1e-12):                      # a degenerate neighbourhood has no defined normal
+            continue
+        assert abs(np.dot(n, got[i])) > 1 - 1e-6 and np.dot(n, got[i]) > 0, (i, n, got[i])
+        checked += 1
+    assert checked > 300
+    print(f"normals: {checked} checked, {grazing} with a neighbour at the search radius")
