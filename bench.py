@@ -510,7 +510,7 @@ def run_ours(args) -> dict | None:
         raise SystemExit("any-hit and counting traversals disagree")
     res.counters["samples"] = counted.counters["samples"]
 
-    e2e = measure_e2e(rig, scene, max(1, min(args.steps, 5)))
+    e2e = measure_e2e(rig, scene, max(5, min(args.steps, 20)))
 
     # ---- roofline of the dominant kernel (k_sweep) on this rank
     peak, peak_src = measured_peaks()
