@@ -104,6 +104,9 @@ extern "C" void plc_ctx_destroy(plc_ctx* c) {
     if (c->stage_pinned) cudaFreeHost(c->stage_pinned);
     if (c->stage_done) cudaEventDestroy(c->stage_done);
     if (c->sweep_graph_exec) cudaGraphExecDestroy(c->sweep_graph_exec);
+    if (c->side_fork) cudaEventDestroy(c->side_fork);
+    if (c->side_join) cudaEventDestroy(c->side_join);
+    if (c->side_stream) cudaStreamDestroy(c->side_stream);
     c->timer.destroy();
     c->terrain_timer.destroy();
     if (c->ev_sweep_begin) cudaEventDestroy(c->ev_sweep_begin);

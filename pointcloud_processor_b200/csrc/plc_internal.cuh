@@ -227,6 +227,9 @@ struct plc_ctx {
     cudaEvent_t ev_run_begin = nullptr, ev_run_end = nullptr;       // around all kernels of plc_vl_run_async
     bool sweep_timed = false;
     bool count_samples = false;  // k_sweep in counting mode (plc_vl_count_samples) instead of any-hit mode
+    // index build: the candidate-list fill runs on this stream beside the dilation (fork / join by events)
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t side_fork = nullptr, side_join = nullptr;
     // the instantiated CUDA graph of the last repeated sweep, the launch signature it was recorded for, the signature
     // of the previous sweep (a graph is recorded when a signature repeats), kernels per replay, replays so far
     cudaGraphExec_t sweep_graph_exec = nullptr;

@@ -461,15 +461,29 @@ plc_status voxel_build(plc_ctx* ctx, VoxelIndex& ix, double radius, float thr, d
     g.bricks = ix.bricks.as<uint32_t>();
     g.cgrp = ix.cgrp.as<float4>();
     ctx->T().begin(s);
-    k_fill_f32<<<148 * 8, 256, 0, s>>>(ix.cgrp.as<float>(), n_groups * 12, INFINITY);
+    // The occupancy dilation (issue-bound) and the list fill (bound by its scattered stores) touch different
+    // structures: the fill runs on a side stream beside the dilation and is joined back before anything reads it.
+    cudaStream_t side = s;
+    if (ctx->side_stream || (cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking) == cudaSuccess &&
+                             cudaEventCreateWithFlags(&ctx->side_fork, cudaEventDisableTiming) == cudaSuccess &&
+                             cudaEventCreateWithFlags(&ctx->side_join, cudaEventDisableTiming) == cudaSuccess)) {
+        if (ctx->side_fork && ctx->side_join && getenv("PLC_NO_SIDE_STREAM") == nullptr) side = ctx->side_stream;
+    }
+    if (side != s) {
+        PLC_CUDA_TRY(ctx, cudaEventRecord(ctx->side_fork, s));
+        PLC_CUDA_TRY(ctx, cudaStreamWaitEvent(side, ctx->side_fork, 0));
+    }
+    k_fill_f32<<<148 * 8, 256, 0, side>>>(ix.cgrp.as<float>(), n_groups * 12, INFINITY);
+    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, side));
+    k_candidates<true><<<pb, 256, 0, side>>>(g, ix.raw.as<float4>(), n, reach_l, h / 2.0, ix.cfill.as<uint32_t>(),
+                                             ix.gstart.as<uint32_t>(), ix.cgrp.as<float>());
+    if (side != s) PLC_CUDA_TRY(ctx, cudaEventRecord(ctx->side_join, side));
     if (!bricks_zero) PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.bricks.ptr, 0, n_vox * 128, s));
-    PLC_CUDA_TRY(ctx, cudaMemsetAsync(ix.cfill.ptr, 0, n_mid * 4, s));
     const int slices = (int)std::floor(2.0 * reach / gsz) + 2;
     const unsigned long long dthreads = (unsigned long long)n * (unsigned)slices;
     k_dilate<<<(unsigned)((dthreads + 255) / 256), 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach, inner, gsz, slices,
                                                                 ix.bricks.as<uint32_t>());
-    k_candidates<true><<<pb, 256, 0, s>>>(g, ix.raw.as<float4>(), n, reach_l, h / 2.0, ix.cfill.as<uint32_t>(),
-                                          ix.gstart.as<uint32_t>(), ix.cgrp.as<float>());
+    if (side != s) PLC_CUDA_TRY(ctx, cudaStreamWaitEvent(s, ctx->side_join, 0));
     ctx->launches += 3;
 #if defined(PLC_TEX_MARCH)
     {
