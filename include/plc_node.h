@@ -57,6 +57,11 @@ void plc_vlnode_destroy(plc_vlnode* node);
  * do upstream: at the next runOptimization (updateParameters, :457).  Unknown name: INVALID_ARG. */
 plc_status plc_vlnode_set_parameter_double(plc_vlnode* node, const char* name, double value);
 plc_status plc_vlnode_set_parameter_int(plc_vlnode* node, const char* name, int64_t value);
+/* updateParameters() (:154-162): makes the values set so far the ones the callbacks use.  The reference calls it at the
+ * end of its constructor (:73), so that parameter overrides given at launch hold from the first message on, and at
+ * the start of every runOptimization (:457), which plc_vlnode_run_optimization does itself.  A wrapper calls this once,
+ * after handing over the declared parameter values. */
+plc_status plc_vlnode_update_parameters(plc_vlnode* node);
 
 /* Subscription callbacks (:164-207).  `cloud` is the message's data buffer with the offsets of its
  * x/y/z fields (pcl::fromROSMsg matches fields by name). */

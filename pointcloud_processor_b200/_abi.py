@@ -149,7 +149,7 @@ EXPORTS = [
     "plc_dev_release",
     "plc_excavation_params_default", "plc_excavation_counts", "plc_excavate",
     "plc_host_generate_cells", "plc_host_compute_normals", "plc_host_generate_candidates",
-    "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int",
+    "plc_vlnode_create", "plc_vlnode_create_on_group", "plc_vlnode_destroy", "plc_vlnode_set_parameter_double", "plc_vlnode_set_parameter_int", "plc_vlnode_update_parameters",
     "plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback", "plc_vlnode_zx120_points_callback",
     "plc_vlnode_set_base_transform", "plc_vlnode_run_optimization", "plc_vlnode_get_candidates",
     "plc_vlnode_get_cells", "plc_vlnode_get_bounds", "plc_vlnode_take_log", "plc_filter_scan", "plc_merge_clouds",
@@ -250,6 +250,7 @@ def lib() -> C.CDLL:
     L.plc_vlnode_destroy.restype = None
     L.plc_vlnode_set_parameter_double.argtypes = [vp, C.c_char_p, dbl]
     L.plc_vlnode_set_parameter_int.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.plc_vlnode_update_parameters.argtypes = [vp]
     for name in ("plc_vlnode_excavation_area_callback", "plc_vlnode_terrain_callback",
                  "plc_vlnode_zx120_points_callback"):
         getattr(L, name).argtypes = [vp, C.POINTER(CloudView)]

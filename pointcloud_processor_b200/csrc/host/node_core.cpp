@@ -147,6 +147,12 @@ extern "C" plc_status plc_vlnode_set_parameter_int(plc_vlnode* n, const char* na
     return PLC_OK;
 }
 
+extern "C" plc_status plc_vlnode_update_parameters(plc_vlnode* n) {
+    if (!n) return PLC_E_INVALID_ARG;
+    n->update_parameters();     // :73 — launch-time overrides hold from the first message on
+    return PLC_OK;
+}
+
 // excavationAreaCallback (:164-178): normals, then the evaluation grid, with the parameter values of
 // the last updateParameters().  An empty cloud leaves the previous grid in place (:168).
 extern "C" plc_status plc_vlnode_excavation_area_callback(plc_vlnode* n, const plc_cloud_view* cloud) {

@@ -48,6 +48,10 @@ class VirtualLidarNode:
             st = self._L.plc_vlnode_set_parameter_double(self._h, name.encode(), float(value))
         self._check(st, f"set_parameter({name})")
 
+    def update_parameters(self):
+        """updateParameters() as the reference's constructor calls it (:73): launch-time overrides hold from the first message."""
+        self._check(self._L.plc_vlnode_update_parameters(self._h), "update_parameters")
+
     def excavation_area_callback(self, cloud, point_step=None, off=(0, 4, 8)):
         v = A.cloud_view(cloud, point_step, off)
         self._check(self._L.plc_vlnode_excavation_area_callback(self._h, C.byref(v)), "excavation_area_callback")

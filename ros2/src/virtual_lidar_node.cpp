@@ -86,6 +86,7 @@ public:
             throw std::runtime_error("plc context creation failed");
         }
         push_parameters();
+        plc_vlnode_update_parameters(core_);        // updateParameters() at the end of the constructor (:73)
 
         auto sub = [this](const char* topic, plc_status (*cb)(plc_vlnode*, const plc_cloud_view*), const char* what) {
             return create_subscription<PointCloud2>(topic, 10, [this, cb, what](PointCloud2::SharedPtr msg) {

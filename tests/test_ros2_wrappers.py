@@ -197,6 +197,7 @@ def test_virtual_lidar_node(ctx, tmp_path):
     node = VirtualLidarNode(ctx)
     node.set_parameter("num_candidates", 49)
     node.set_parameter("vertical_layers", 6)
+    node.update_parameters()
     node.excavation_area_callback(area)
     node.terrain_callback(terrain)
     cells0, flags0 = node.cells()
