@@ -19,6 +19,7 @@
 #include <cstring>
 #include <limits>
 #include <memory>
+#include <string>
 #include <unordered_map>
 #include <vector>
 
@@ -26,12 +27,19 @@
 
 namespace pcl {
 
-struct PointXYZ { float x = 0.f, y = 0.f, z = 0.f; };
+// PCL's 16-byte-aligned layouts: data[4] = {x, y, z, 1}; PointXYZRGB adds data_c[4] with the packed colour in [0]
+struct PointXYZ { float x = 0.f, y = 0.f, z = 0.f, data3 = 1.f; };
 struct PointXYZRGB {
-    float x = 0.f, y = 0.f, z = 0.f;
-    union { float rgb; uint32_t rgba; };
+    float x = 0.f, y = 0.f, z = 0.f, data3 = 1.f;
+    union {
+        float rgb;
+        uint32_t rgba;
+        struct { uint8_t b, g, r, a; };
+    };
+    float pad_c[3] = {0.f, 0.f, 0.f};
     PointXYZRGB() : rgba(0xff000000u) {}
 };
+static_assert(sizeof(PointXYZ) == 16 && sizeof(PointXYZRGB) == 32, "PCL point sizes");
 struct Normal { float normal_x = 0.f, normal_y = 0.f, normal_z = 0.f, curvature = 0.f; };
 
 template <class T>
@@ -39,9 +47,11 @@ class PointCloud {
 public:
     using Ptr = std::shared_ptr<PointCloud<T>>;
     using ConstPtr = std::shared_ptr<const PointCloud<T>>;
+    struct Header { uint32_t seq = 0; uint64_t stamp = 0; std::string frame_id; } header;     // pcl::PCLHeader
     std::vector<T> points;
     uint32_t width = 0, height = 0;
     bool is_dense = true;
+    void reserve(size_t n) { points.reserve(n); }
     bool empty() const { return points.empty(); }
     size_t size() const { return points.size(); }
     void clear() { points.clear(); width = height = 0; }
@@ -254,10 +264,96 @@ void fromROSMsg(const sensor_msgs::msg::PointCloud2& msg, PointCloud<T>& cloud) 
         if (ox >= 0) std::memcpy(&q.x, p + ox, 4);
         if (oy >= 0) std::memcpy(&q.y, p + oy, 4);
         if (oz >= 0) std::memcpy(&q.z, p + oz, 4);
-        if constexpr (sizeof(T) > 12) {
+        if constexpr (sizeof(T) > 16) {
             if (orgb >= 0) std::memcpy(&q.rgba, p + orgb, 4);
         }
     }
 }
+
+// pcl::toROSMsg: the point struct's bytes with its registered fields (x, y, z at 0 / 4 / 8; rgb at 16 for PointXYZRGB)
+template <class T>
+void toROSMsg(const PointCloud<T>& cloud, sensor_msgs::msg::PointCloud2& msg) {
+    auto field = [](const char* name, uint32_t offset) {
+        sensor_msgs::msg::PointField f;
+        f.name = name; f.offset = offset; f.datatype = sensor_msgs::msg::PointField::FLOAT32; f.count = 1;
+        return f;
+    };
+    msg.fields = {field("x", 0), field("y", 4), field("z", 8)};
+    if constexpr (sizeof(T) > 16) msg.fields.push_back(field("rgb", 16));
+    // pcl::PointCloud::push_back keeps width = size, height = 1; a cloud never touched has width = height = 0 and
+    // toPCLPointCloud2 then takes width = size, height = 1 as well
+    msg.height = 1;
+    msg.width = static_cast<uint32_t>(cloud.points.size());
+    msg.point_step = sizeof(T);
+    msg.row_step = msg.point_step * msg.width;
+    msg.is_bigendian = false;
+    msg.is_dense = cloud.is_dense;
+    msg.data.resize(cloud.points.size() * sizeof(T));
+    if (!cloud.points.empty()) std::memcpy(msg.data.data(), cloud.points.data(), msg.data.size());
+}
+
+// pcl::VoxelGrid<PointT>::applyFilter with the defaults the reference leaves (downsample_all_data, no field filter,
+// min_points_per_voxel 0), SURVEY A.3 item 13: float inverse leaf, bounds over the finite points, index
+// i + j dx + k dx dy from floor(p * inv) - min_b, one centroid per index in ascending order, float running sums in the
+// order the (index, point) pairs come out of the sort — taken as ascending point index, the order the oracle fixes
+// (the real sort is not stable: SURVEY flags this), divided by the count.
+template <class T>
+class VoxelGrid {
+public:
+    void setInputCloud(const typename PointCloud<T>::ConstPtr& cloud) { input_ = cloud; }
+    void setLeafSize(float lx, float ly, float lz) { leaf_[0] = lx; leaf_[1] = ly; leaf_[2] = lz; }
+    void filter(PointCloud<T>& out) {
+        out.points.clear();
+        out.height = 1;
+        out.is_dense = true;
+        const float inv[3] = {1.0f / leaf_[0], 1.0f / leaf_[1], 1.0f / leaf_[2]};
+        float mn[3] = {std::numeric_limits<float>::max(), std::numeric_limits<float>::max(), std::numeric_limits<float>::max()};
+        float mx[3] = {-mn[0], -mn[1], -mn[2]};
+        for (const T& p : input_->points) {
+            if (!(std::isfinite(p.x) && std::isfinite(p.y) && std::isfinite(p.z))) continue;
+            const float v[3] = {p.x, p.y, p.z};
+            for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], v[a]); mx[a] = std::max(mx[a], v[a]); }
+        }
+        int64_t d64[3];
+        for (int a = 0; a < 3; ++a) d64[a] = static_cast<int64_t>((mx[a] - mn[a]) * inv[a]) + 1;
+        if (d64[0] * d64[1] * d64[2] > static_cast<int64_t>(std::numeric_limits<int32_t>::max())) {
+            out = *input_;                    // "Leaf size is too small for the input dataset"
+            return;
+        }
+        int min_b[3], div_b[3];
+        for (int a = 0; a < 3; ++a) {
+            min_b[a] = static_cast<int>(std::floor(mn[a] * inv[a]));
+            div_b[a] = static_cast<int>(std::floor(mx[a] * inv[a])) - min_b[a] + 1;
+        }
+        const int mul[3] = {1, div_b[0], div_b[0] * div_b[1]};
+        std::vector<std::pair<unsigned, unsigned>> order;      // (voxel index, point index)
+        for (size_t i = 0; i < input_->points.size(); ++i) {
+            const T& p = input_->points[i];
+            if (!(std::isfinite(p.x) && std::isfinite(p.y) && std::isfinite(p.z))) continue;
+            const int ijk0 = static_cast<int>(std::floor(p.x * inv[0]) - static_cast<float>(min_b[0]));
+            const int ijk1 = static_cast<int>(std::floor(p.y * inv[1]) - static_cast<float>(min_b[1]));
+            const int ijk2 = static_cast<int>(std::floor(p.z * inv[2]) - static_cast<float>(min_b[2]));
+            order.emplace_back(static_cast<unsigned>(ijk0 * mul[0] + ijk1 * mul[1] + ijk2 * mul[2]), static_cast<unsigned>(i));
+        }
+        std::sort(order.begin(), order.end());
+        for (size_t a = 0; a < order.size();) {
+            size_t b = a;
+            float sx = 0.f, sy = 0.f, sz = 0.f;
+            for (; b < order.size() && order[b].first == order[a].first; ++b) {
+                const T& p = input_->points[order[b].second];
+                sx += p.x; sy += p.y; sz += p.z;
+            }
+            T c;
+            const float n = static_cast<float>(b - a);
+            c.x = sx / n; c.y = sy / n; c.z = sz / n;
+            out.points.push_back(c);
+            a = b;
+        }
+        out.width = static_cast<uint32_t>(out.points.size());
+    }
+private:
+    typename PointCloud<T>::ConstPtr input_;
+    float leaf_[3] = {0.f, 0.f, 0.f};
+};
 
 }  // namespace pcl

@@ -87,6 +87,7 @@ class Time {
 public:
     Time() = default;
     explicit Time(int64_t ns) : ns_(ns) {}
+    Time(const builtin_interfaces::msg::Time& t) : ns_(static_cast<int64_t>(t.sec) * 1000000000LL + t.nanosec) {}
     operator builtin_interfaces::msg::Time() const {
         builtin_interfaces::msg::Time t;
         t.sec = static_cast<int32_t>(ns_ / 1000000000LL);

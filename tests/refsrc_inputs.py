@@ -1,0 +1,60 @@
+"""Seeded inputs of the reference-source fixtures for the nodes around the sweep (tests/golden/refsrc_*.npz): built
+here, identically, by tools/make_refsrc_golden.py (which feeds them to the reference's own nodes) and by the tests
+(which feed them to the oracle and to the CUDA path).  The fixtures store a SHA-256 of each input next to the outputs."""
+import hashlib
+
+import numpy as np
+
+
+def digest(a: np.ndarray) -> str:
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def quat_zyx(yaw, pitch):
+    cy, sy, cp, sp = np.cos(yaw / 2), np.sin(yaw / 2), np.cos(pitch / 2), np.sin(pitch / 2)
+    return np.array([-sy * sp, cy * sp, sy * cp, cy * cp])
+
+
+def filter_scans():
+    """Two LiDAR scans in their sensor frames: x y z intensity records (point_step 16), some non-finite points, a few
+    points exactly on the crop box's faces."""
+    out = {}
+    for name, seed, n in (("robot", 31, 40_000), ("backhoe", 32, 30_000)):
+        rng = np.random.Generator(np.random.PCG64(seed))
+        p = np.zeros((n, 4), np.float32)
+        p[:, :3] = rng.uniform(-22, 22, (n, 3))
+        p[:, 2] = rng.uniform(-3, 12, n)
+        p[:, 3] = rng.uniform(0, 255, n)
+        p[rng.choice(n, 25, replace=False), rng.integers(0, 3, 25)] = np.nan
+        p[:6, :3] = [[0.0, 1.0, 1.0], [15.0, 1.0, 1.0], [3.0, 10.0, 1.0], [3.0, -10.0, 1.0], [3.0, 1.0, -1.5], [3.0, 1.0, 10.0]]
+        out[name] = p
+    return out
+
+
+FILTER_PARAMS = {"voxel_leaf_size": 0.2, "robot_front_range": 12.0, "backhoe_height_range": 6.0}
+
+
+def drivable_scan():
+    """A filtered robot scan in the sensor frame (point_step 16) and the two transforms the node looks up."""
+    rng = np.random.Generator(np.random.PCG64(33))
+    n = 60_000
+    p = np.zeros((n, 4), np.float32)
+    p[:, :2] = rng.uniform(-25, 25, (n, 2))
+    p[:, 2] = 0.2 * np.sin(0.3 * p[:, 0]) * np.cos(0.2 * p[:, 1]) - 2.0 + np.where(rng.random(n) < 0.15, rng.uniform(0, 2.5, n), 0.0)
+    p[rng.choice(n, 20, replace=False), rng.integers(0, 3, 20)] = np.nan
+    return p, (np.array([9.25, -3.0, 2.0]), quat_zyx(2.6, 0.1245)), (9.0, -3.0)
+
+
+DRIVABLE_PARAMS = {"grid_resolution": 0.5, "map_width": 60.0, "map_height": 50.0, "min_points_per_cell": 4}
+
+
+def generator_cloud(shape):
+    """/matched_point_cloud: un-carved rolling ground around where the pit will be, PointXYZRGB records (point_step 32)."""
+    rng = np.random.Generator(np.random.PCG64(34 if shape == "L" else 35))
+    n = 9_000
+    r = np.zeros((n, 8), np.float32)
+    r[:, :2] = rng.uniform(-2.0, 7.0, (n, 2))
+    r[:, 2] = 0.15 * np.sin(0.4 * r[:, 0]) * np.cos(0.3 * r[:, 1]) + rng.normal(0, 0.01, n) - rng.uniform(0, 1.2, n) * (rng.random(n) < 0.3)
+    r[:, 4] = np.where(rng.random(n) < 0.5, np.uint32(0xFFFF0000), np.uint32(0xFF0000FF)).astype(np.uint32).view(np.float32)
+    base = (np.array([0.3, -0.2, 0.0]), np.array([0.0, 0.0, np.sin(0.2), np.cos(0.2)]) if shape == "rect" else np.array([0.0, 0.0, 0.0, 1.0]))
+    return r, base

@@ -151,3 +151,137 @@ def test_drop_in_executable_publishes_what_the_reference_publishes(name, tmp_pat
         if any(k in body for k in ("cells (", "Total cells:", "Best Mobile LiDAR Position:", "Total Score", "ZX120 Position:",
                                    "Cells in range:", "Cells in FOV:", "Cells visible:", "Red/Green Ratio:", "Generated 3D grid:")):
             assert body in text, body
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The nodes around the sweep: what the reference's own pointcloud_filter.cpp, calc_drivable_area.cpp and
+# excavated_surface_generator.cpp publish for the seeded inputs of tests/refsrc_inputs.py.
+import json
+
+import refsrc_inputs as R
+
+
+def ulp_apart(a, b):
+    """Distance in float32 ulps between two float32 arrays of equal sign-magnitude ordering."""
+    ia, ib = a.view(np.int32).astype(np.int64), b.view(np.int32).astype(np.int64)
+    ia, ib = np.where(ia < 0, -(ia & 0x7fffffff), ia), np.where(ib < 0, -(ib & 0x7fffffff), ib)
+    return np.abs(ia - ib)
+
+
+def filter_reference():
+    z = np.load(GOLDEN / "refsrc_filter.npz")
+    scans = R.filter_scans()
+    for who in ("robot", "backhoe"):
+        assert R.digest(scans[who]) == str(z[f"{who}_input_sha256"])
+    P = R.FILTER_PARAMS
+    ranges = {"robot": (P["robot_front_range"], 10.0, 10.0), "backhoe": (15.0, 10.0, P["backhoe_height_range"])}
+    return z, scans, ranges, P["voxel_leaf_size"]
+
+
+def check_filter_output(z, who, xyz, frame, stamp):
+    rec, meta = z[f"{who}_records"], json.loads(str(z[f"{who}_meta"]))
+    assert rec.shape[0] == xyz.shape[0] > 500 and np.array_equal(rec[:, :3].view(np.uint32), np.ascontiguousarray(xyz[:, :3]).view(np.uint32))
+    assert np.all(rec[:, 3] == 1.0)                                   # pcl::PointXYZ keeps 1.0f in data[3]
+    assert (meta["point_step"], meta["height"], meta["width"], meta["frame_id"], meta["stamp"]) == (16, 1, rec.shape[0], frame, stamp)
+    assert meta["fields"] == [["x", 0, 7, 1], ["y", 4, 7, 1], ["z", 8, 7, 1]]
+
+
+def test_oracle_reproduces_the_reference_filter_node():
+    z, scans, ranges, leaf = filter_reference()
+    for who, frame, stamp in (("robot", "four_wheel_robot/velodyne", [100, 7]), ("backhoe", "zx120/velodyne", [101, 8])):
+        front, side, height = ranges[who]
+        cropped, _ = O.crop(scans[who], A.CropBox(0.0, front, -side, side, -1.5, height))      # :106-116
+        check_filter_output(z, who, O.voxel_grid(cropped, leaf)[0], frame, stamp)
+
+
+@pytest.mark.gpu
+def test_cuda_filter_reproduces_the_reference_filter_node(ctx, tmp_path):
+    from pointcloud_processor_b200.nodes import filter_scan
+    from test_ros2_wrappers import cloud_line, play
+    z, scans, ranges, leaf = filter_reference()
+    for who, frame, stamp in (("robot", "four_wheel_robot/velodyne", [100, 7]), ("backhoe", "zx120/velodyne", [101, 8])):
+        check_filter_output(z, who, filter_scan(ctx, scans[who], *ranges[who], leaf, 16), frame, stamp)
+    # and the drop-in executable on the same script
+    msgs, _ = play("pointcloud_filter", [f"param {k} double {v!r}" for k, v in R.FILTER_PARAMS.items()] + [
+        cloud_line(tmp_path, "/four_wheel_robot/velodyne_points", scans["robot"], "four_wheel_robot/velodyne", (100, 7), "x:0 y:4 z:8 intensity:12"),
+        cloud_line(tmp_path, "/zx120/velodyne_points", scans["backhoe"], "zx120/velodyne", (101, 8), "x:0 y:4 z:8 intensity:12")], tmp_path)
+    for who, (m, b) in zip(("robot", "backhoe"), msgs):
+        want = json.loads(str(z[f"{who}_meta"]))
+        assert {k: m[k] for k in want if k != "is_dense"} == {k: v for k, v in want.items() if k != "is_dense"}
+        assert b == z[f"{who}_records"].tobytes()                     # the published bytes, data[3] = 1.0f included
+
+
+def drivable_reference():
+    z = np.load(GOLDEN / "refsrc_drivable.npz")
+    scan, (t, q), robot = R.drivable_scan()
+    assert R.digest(scan) == str(z["input_sha256"])
+    return z, scan, t, q, robot
+
+
+def check_drivable(z, k, grid, robot):
+    meta = json.loads(str(z[f"meta{k}"]))
+    assert grid.shape == (meta["height"], meta["width"]) == (100, 120) and np.array_equal(grid.ravel(), z[f"grid{k}"])
+    assert meta["origin"] == [robot[0] - 30.0, robot[1] - 25.0, 0.0] and meta["resolution"] == 0.5 and meta["frame_id"] == "map"
+    assert set(np.unique(grid)) == {-1, 0, 100}
+
+
+def test_oracle_reproduces_the_reference_drivable_area_node():
+    z, scan, t, q, robot = drivable_reference()
+    P = R.DRIVABLE_PARAMS
+    for k, rb in enumerate((robot, (robot[0] + 2.0, robot[1] + 1.0))):            # the start position stays where it was set (:127-134)
+        grid = O.drivable_area(scan, t, q, rb, robot, grid_resolution=P["grid_resolution"], map_width=P["map_width"],
+                               map_height=P["map_height"], min_points_per_cell=P["min_points_per_cell"])
+        check_drivable(z, k, grid, rb)
+    assert "Transform from four_wheel_robot/velodyne to map not available yet" in str(z["log"])
+
+
+@pytest.mark.gpu
+def test_cuda_grid_reproduces_the_reference_drivable_area_node(ctx):
+    z, scan, t, q, robot = drivable_reference()
+    prm = A.DrivableParams()
+    A.lib().plc_drivable_params_default(prm)
+    for k, v in R.DRIVABLE_PARAMS.items():
+        setattr(prm, k, v)
+    for k, rb in enumerate((robot, (robot[0] + 2.0, robot[1] + 1.0))):
+        grid, info = ctx.drivable_area(scan, t, q, rb, robot, prm, 16)
+        check_drivable(z, k, grid, rb)
+
+
+def generator_reference(shape):
+    z = np.load(GOLDEN / f"refsrc_generator_{shape}.npz")
+    rec, (bt, bq) = R.generator_cloud(shape)
+    assert R.digest(rec) == str(z["input_sha256"])
+    prm = A.excavation_params(l_shape_enabled=1 if shape == "L" else 0)
+    return z, rec, bt, bq, prm
+
+
+def check_generator(z, terrain, area, n_kept):
+    want_t, want_a = z["terrain"], z["area"]
+    tm, am = json.loads(str(z["terrain_meta"])), json.loads(str(z["area_meta"]))
+    assert terrain.shape == want_t.shape and area.shape == want_a.shape and tm["point_step"] == am["point_step"] == 32
+    assert (tm["frame_id"], tm["stamp"], am["frame_id"], am["stamp"]) == ("map", [55, 66], "map", [55, 66])       # :312-322
+    f = lambda r: np.ascontiguousarray(r).view(np.float32).reshape(-1, 8)
+    for got, want, name in ((f(terrain), f(want_t), "terrain"), (f(area), f(want_a), "area")):
+        assert np.array_equal(got[:, :2].view(np.uint32), want[:, :2].view(np.uint32)), name       # x, y: exact
+        assert np.array_equal(got[:, 4].view(np.uint32), want[:, 4].view(np.uint32)), name         # packed colour
+        # z: the kept input points exactly; generated points carry a mean of terrain heights, summed by the reference
+        # in its search's result order and here in another one: one float32 ulp at most
+        assert ulp_apart(got[:, 2], want[:, 2]).max() <= 1, name
+    assert np.array_equal(f(terrain)[:n_kept, 2].view(np.uint32), f(want_t)[:n_kept, 2].view(np.uint32))
+    assert 0 < n_kept < terrain.shape[0]
+
+
+@pytest.mark.parametrize("shape", ["L", "rect"])
+def test_oracle_reproduces_the_reference_generator_node(shape):
+    z, rec, bt, bq, prm = generator_reference(shape)
+    ns, na = A.excavation_counts(prm)
+    terrain, area, info = O.excavate(rec[:, :3], np.ascontiguousarray(rec[:, 4]).view(np.uint32), bt, bq, prm, ns, na)
+    check_generator(z, terrain, area, int(info.n_kept))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", ["L", "rect"])
+def test_cuda_generator_reproduces_the_reference_generator_node(ctx, shape):
+    z, rec, bt, bq, prm = generator_reference(shape)
+    terrain, area, info = ctx.excavate(rec, bt, bq, prm)
+    check_generator(z, terrain, area, int(info.n_kept))

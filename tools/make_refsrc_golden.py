@@ -1,6 +1,7 @@
-"""Golden vectors from the reference's OWN source: runs oracle/_ref/virtual_lidar_ref — /root/reference/src/virtual_lidar.cpp,
-unmodified, compiled against stand-in PCL / ROS2 headers (`make -C oracle ref`) — on seeded scenes and stores what the
-node publishes and logs in tests/golden/refsrc_<name>.npz, next to the inputs.  Needs /root/reference (this container);
+"""Golden vectors from the reference's OWN source: runs oracle/_ref/<node>_ref — /root/reference/src/{virtual_lidar,
+pointcloud_filter, calc_drivable_area, excavated_surface_generator}.cpp, unmodified, compiled against stand-in PCL / tf2 /
+ROS2 headers (`make -C oracle ref`) — on seeded inputs and stores what the nodes publish and log in
+tests/golden/refsrc_<name>.npz, next to the inputs (or their SHA-256 where tests/refsrc_inputs.py rebuilds them).  Needs /root/reference (this container);
 the fixtures travel, the binary's sources do not.
 
     python tools/make_refsrc_golden.py            # rewrites every fixture
@@ -35,27 +36,91 @@ def records(xyz):
     return r
 
 
-def run_reference(area, terrain, observed, num_candidates, layers, base):
+def play(node, make_lines):
+    """Runs oracle/_ref/<node>_ref over the script `make_lines(tmp)` returns; (published messages, log text)."""
     subprocess.check_call(["make", "-C", os.fspath(ROOT / "oracle"), "ref"], stdout=subprocess.DEVNULL)
     with tempfile.TemporaryDirectory() as tmp:
         tmp = Path(tmp)
-        lines = [f"param num_candidates int {num_candidates}", f"param vertical_layers int {layers}"]
-        for topic, cloud in (("/excavation_area", area), ("/excavated_terrain", terrain), ("/zx120/filtered_points", observed)):
-            if cloud is None:
-                continue
-            f = tmp / (topic.strip("/").replace("/", "_") + ".bin")
-            cloud.tofile(f)
-            lines.append(f"cloud {topic} {f} {cloud.shape[0]} 32 map 10 20 x:0 y:4 z:8 rgb:16")
-        lines += ["tf map zx120/base_link " + " ".join(repr(float(v)) for v in base) + " 0 0 0 1", "timers"]
-        (tmp / "script.txt").write_text("\n".join(lines) + "\n")
+        (tmp / "script.txt").write_text("\n".join(make_lines(tmp)) + "\n")
         env = dict(os.environ, MOCK_ROS_SCRIPT=os.fspath(tmp / "script.txt"), MOCK_ROS_OUT=os.fspath(tmp))
-        subprocess.run([os.fspath(EXE)], env=env, check=True, capture_output=True)
+        subprocess.run([os.fspath(ROOT / "oracle" / "_ref" / f"{node}_ref")], env=env, check=True, capture_output=True)
         msgs = []
         for j in sorted(tmp.glob("[0-9][0-9][0-9].json")):
             b = j.with_suffix(".bin")
             msgs.append((json.loads(j.read_text()), b.read_bytes() if b.exists() else b""))
-        log = (tmp / "log.txt").read_text()
+        log = (tmp / "log.txt").read_text() if (tmp / "log.txt").exists() else ""
     return msgs, log
+
+
+def cloud_line(tmp, topic, rec, frame, stamp, fields):
+    f = tmp / f"cloud_{len(list(tmp.glob('cloud_*')))}.bin"
+    np.ascontiguousarray(rec).tofile(f)
+    step = rec.shape[1] * rec.itemsize
+    return f"cloud {topic} {f} {rec.shape[0]} {step} {frame} {stamp[0]} {stamp[1]} {fields}"
+
+
+def tf_line(target, source, t, q):
+    return f"tf {target} {source} " + " ".join(repr(float(v)) for v in (*t, *q))
+
+
+def run_reference(area, terrain, observed, num_candidates, layers, base):
+    def lines(tmp):
+        out = [f"param num_candidates int {num_candidates}", f"param vertical_layers int {layers}"]
+        for topic, cloud in (("/excavation_area", area), ("/excavated_terrain", terrain), ("/zx120/filtered_points", observed)):
+            if cloud is not None:
+                out.append(cloud_line(tmp, topic, cloud, "map", (10, 20), "x:0 y:4 z:8 rgb:16"))
+        return out + [tf_line("map", "zx120/base_link", base, (0, 0, 0, 1)), "timers"]
+    return play("virtual_lidar", lines)
+
+
+def param_lines(params):
+    return [f"param {k} {'int' if isinstance(v, int) else 'double'} {v!r}" for k, v in params.items()]
+
+
+def other_nodes():
+    """pointcloud_filter, calc_drivable_area and excavated_surface_generator of the reference on the seeded inputs of
+    tests/refsrc_inputs.py."""
+    sys.path.insert(0, os.fspath(ROOT / "tests"))
+    import refsrc_inputs as R
+    gold = ROOT / "tests" / "golden"
+    # ---- pointcloud_filter (src/pointcloud_filter.cpp): crop + VoxelGrid of both scans
+    scans = R.filter_scans()
+    msgs, _ = play("pointcloud_filter", lambda tmp: param_lines(R.FILTER_PARAMS) + [
+        cloud_line(tmp, "/four_wheel_robot/velodyne_points", scans["robot"], "four_wheel_robot/velodyne", (100, 7), "x:0 y:4 z:8 intensity:12"),
+        cloud_line(tmp, "/zx120/velodyne_points", scans["backhoe"], "zx120/velodyne", (101, 8), "x:0 y:4 z:8 intensity:12")])
+    assert [m["topic"] for m, _ in msgs] == ["/four_wheel_robot/filtered_points", "/zx120/filtered_points"]
+    out = {}
+    for who, (m, b) in zip(("robot", "backhoe"), msgs):
+        out[f"{who}_records"] = np.frombuffer(b, np.float32).reshape(-1, m["point_step"] // 4).copy()
+        out[f"{who}_meta"] = json.dumps(m)
+        out[f"{who}_input_sha256"] = R.digest(scans[who])
+    np.savez_compressed(gold / "refsrc_filter.npz", **out)
+    print("filter", {k: v.shape for k, v in out.items() if hasattr(v, "shape") and v.ndim == 2})
+    # ---- calc_drivable_area (src/calc_drivable_area.cpp)
+    scan, (t, q), robot = R.drivable_scan()
+    line = lambda tmp: cloud_line(tmp, "/four_wheel_robot/filtered_points", scan, "four_wheel_robot/velodyne", (5, 6), "x:0 y:4 z:8 intensity:12")
+    msgs, log = play("calc_drivable_area", lambda tmp: param_lines(R.DRIVABLE_PARAMS) + [
+        line(tmp),                                                           # no TF yet: nothing published
+        tf_line("map", "four_wheel_robot/velodyne", t, q), tf_line("map", "four_wheel_robot/base_link", (*robot, 0.0), (0, 0, 0, 1)),
+        line(tmp),
+        tf_line("map", "four_wheel_robot/base_link", (robot[0] + 2.0, robot[1] + 1.0, 0.0), (0, 0, 0, 1)), line(tmp)])
+    assert [m["type"] for m, _ in msgs] == ["OccupancyGrid", "OccupancyGrid"]
+    np.savez_compressed(gold / "refsrc_drivable.npz", grid0=np.frombuffer(msgs[0][1], np.int8).copy(), grid1=np.frombuffer(msgs[1][1], np.int8).copy(),
+                        meta0=json.dumps(msgs[0][0]), meta1=json.dumps(msgs[1][0]), log=log, input_sha256=R.digest(scan))
+    print("drivable", msgs[0][0]["width"], msgs[0][0]["height"], {v: int((np.frombuffer(msgs[0][1], np.int8) == v).sum()) for v in (-1, 0, 100)})
+    # ---- excavated_surface_generator (src/excavated_surface_generator.cpp)
+    for shape in ("L", "rect"):
+        rec, (bt, bq) = R.generator_cloud(shape)
+        msgs, log = play("excavated_surface_generator", lambda tmp: [f"param excavation.l_shape_enabled bool {'true' if shape == 'L' else 'false'}",
+                                                                     tf_line("map", "zx120/base_link", bt, bq),
+                                                                     cloud_line(tmp, "/matched_point_cloud", rec, "map", (55, 66), "x:0 y:4 z:8 rgb:16")])
+        by = {m["topic"]: (m, b) for m, b in msgs}
+        tm, tb = by["/excavated_terrain"]
+        am, ab = by["/excavation_area"]
+        np.savez_compressed(gold / f"refsrc_generator_{shape}.npz", terrain=np.frombuffer(tb, np.uint8).reshape(-1, tm["point_step"]).copy(),
+                            area=np.frombuffer(ab, np.uint8).reshape(-1, am["point_step"]).copy(), terrain_meta=json.dumps(tm),
+                            area_meta=json.dumps(am), input_sha256=R.digest(rec), topics=json.dumps([m["topic"] for m, _ in msgs]))
+        print("generator", shape, "terrain", tm["width"], "area", am["width"], [m["topic"] for m, _ in msgs])
 
 
 def parse(msgs, log):
@@ -94,3 +159,4 @@ def main():
 
 if __name__ == "__main__":
     main()
+    other_nodes()
