@@ -7,7 +7,8 @@
 //   binning of z values                137-160
 //   occupancy decision                 178-222
 //   calculateGradient                  238-250
-// Parity unpinned: the reference has no tests or fixtures for this node.
+// Parity: the reference has no tests or fixtures for this node; tests/golden/refsrc_drivable.npz holds what
+// its own calc_drivable_area.cpp (unmodified, stand-in PCL / tf2 / ROS2 headers, oracle/_ref) publishes, which this file reproduces.
 #include <algorithm>
 #include <cmath>
 #include <vector>

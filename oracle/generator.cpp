@@ -13,7 +13,8 @@
 //   generateExcavatedSurface  487-584
 // excavated_surface_generator_L.cpp (not built upstream) is this algorithm with vertical wall points in the area
 // cloud (its :391-407; plc_excavation_params::area_walls_vertical); the _square file is another formulation, not restated.
-// Parity unpinned: the reference has no tests or fixtures for this node.  KD-tree result order decides
+// Parity: the reference has no tests or fixtures for this node; tests/golden/refsrc_generator_*.npz hold what
+// its own excavated_surface_generator.cpp (unmodified, stand-in headers, oracle/_ref) publishes, which this file reproduces.  KD-tree result order decides
 // the order of the double sum in getTerrainHeight (restated as ascending distance, ties by index) and which of two
 // equidistant points nearestKSearch returns (restated as the lower index).
 #include <algorithm>

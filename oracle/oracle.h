@@ -4,16 +4,20 @@
  * or called from the product library (pointcloud_processor_b200/).  Only tests/,
  * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs use it.
  *
- * PARITY UNPINNED: the reference ships no tests, fixtures or golden vectors, and it
- * cannot be built here (needs rclcpp, tf2, PCL, FLANN, Eigen, GeographicLib).  The arithmetic that
- * decides a visibility bit lives in third-party code that is not under /root/reference:
+ * PARITY: pinned against the reference's own sources, unpinned on its third-party binaries.  The reference ships no
+ * tests, fixtures or golden vectors and its build cannot run here (rclcpp, tf2, PCL, FLANN, Eigen,
+ * GeographicLib are absent), but four of its nodes compile unmodified against the stand-in headers of
+ * oracle/ref_shim/ and tests/mock_ros2/ (`make -C oracle ref` -> oracle/_ref/), and tests/golden/refsrc_*.npz hold
+ * what they publish on seeded inputs (tools/make_refsrc_golden.py); tests/test_reference_source.py requires this
+ * restatement to reproduce them.  The arithmetic that lives in third-party code outside /root/reference stays
+ * restated, in the stand-ins as here:
  *   PCL 1.12.1  KdTreeFLANN<PointXYZRGB>::radiusSearch   (call sites virtual_lidar.cpp:298,312,611,745,782)
  *   FLANN 1.9.1 KDTreeSingleIndex + L2_Simple<float>
- *   PCL 1.12.1  VoxelGrid<PointXYZ>::applyFilter          (pointcloud_filter.cpp:129-136)
- *   tf2_sensor_msgs 0.25.x doTransform<PointCloud2>       (pointcloud_merger.cpp:370)
- * (versions inferred from "ROS2 Humble", not pinned by the reference).  Their published algorithms
- * are restated here and the restatement is pinned only by self-consistency:
- * brute-force == grid == kd-tree, bit for bit, plus hand-checkable fixtures in tests/golden/.
+ *   PCL 1.12.1  NormalEstimation, VoxelGrid<PointXYZ>::applyFilter   (pointcloud_filter.cpp:129-136)
+ *   tf2_sensor_msgs 0.25.x doTransform<PointCloud2>       (pointcloud_merger.cpp:370, calc_drivable_area.cpp:91)
+ * (versions inferred from "ROS2 Humble", not pinned by the reference); it is also checked by self-consistency
+ * (brute-force == grid == kd-tree, bit for bit), hand-checkable fixtures and independent SciPy / NumPy
+ * restatements (tests/test_oracle_independent*.py).
  *
  * POD types are shared with include/plc.h (the boundary declaration) so that the same bytes feed
  * both sides.

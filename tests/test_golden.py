@@ -1,7 +1,7 @@
 """The oracle against the committed golden fixtures (CPU).  tests/golden/*.npz hold the outputs of
 the oracle's brute-force index (O(N) scan, one thread) on seeded inputs; hand_cases.json holds
 answers derived by hand from the reference source.  The reference itself ships no vectors
-(parity unpinned), so these are what pins the oracle."""
+(SURVEY §8c), so these — beside the reference-source fixtures of test_reference_source.py — are what pins the oracle."""
 import numpy as np
 import pytest
 

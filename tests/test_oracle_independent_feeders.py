@@ -2,7 +2,8 @@
 
 The sweep has its SciPy twin in test_oracle_independent.py; this file does the same for the stages around it, so that
 every oracle function the GPU parity tests lean on is pinned by a second implementation that shares no code with
-oracle/*.cpp or with the CUDA path (it still is not the upstream binary: the status stays "parity unpinned").
+oracle/*.cpp or with the CUDA path (it is the check on the third-party arithmetic that the reference-source fixtures of
+test_reference_source.py leave restated).
 
 Restated from /root/reference (arithmetic of the third-party calls as listed in SURVEY section A.3):
   src/pointcloud_filter.cpp:106-116   crop: strict six-sided box on the float promoted to double
