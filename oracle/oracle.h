@@ -6,7 +6,7 @@
  *
  * PARITY: pinned against the reference's own sources, unpinned on its third-party binaries.  The reference ships no
  * tests, fixtures or golden vectors and its build cannot run here (rclcpp, tf2, PCL, FLANN, Eigen,
- * GeographicLib are absent), but four of its nodes compile unmodified against the stand-in headers of
+ * GeographicLib are absent), but five of its nodes compile unmodified against the stand-in headers of
  * oracle/ref_shim/ and tests/mock_ros2/ (`make -C oracle ref` -> oracle/_ref/), and tests/golden/refsrc_*.npz hold
  * what they publish on seeded inputs (tools/make_refsrc_golden.py); tests/test_reference_source.py requires this
  * restatement to reproduce them.  The arithmetic that lives in third-party code outside /root/reference stays

@@ -21,6 +21,7 @@ public:
     double y() const { return v_[1]; }
     double z() const { return v_[2]; }
     double dot(const Vector3& o) const { return v_[0] * o.v_[0] + v_[1] * o.v_[1] + v_[2] * o.v_[2]; }
+    void setValue(double x, double y, double z) { v_[0] = x; v_[1] = y; v_[2] = z; }
     Vector3 operator+(const Vector3& o) const { return Vector3(v_[0] + o.v_[0], v_[1] + o.v_[1], v_[2] + o.v_[2]); }
 private:
     double v_[3] = {0, 0, 0};
@@ -35,6 +36,14 @@ public:
     double z() const { return q_[2]; }
     double w() const { return q_[3]; }
     double length2() const { return q_[0] * q_[0] + q_[1] * q_[1] + q_[2] * q_[2] + q_[3] * q_[3]; }
+    Quaternion inverse() const { return Quaternion(-q_[0], -q_[1], -q_[2], q_[3]); }
+    Quaternion operator*(const Quaternion& b) const {              // tf2/LinearMath/Quaternion.h operator*(q1, q2)
+        const Quaternion& a = *this;
+        return Quaternion(a.w() * b.x() + a.x() * b.w() + a.y() * b.z() - a.z() * b.y(),
+                          a.w() * b.y() + a.y() * b.w() + a.z() * b.x() - a.x() * b.z(),
+                          a.w() * b.z() + a.z() * b.w() + a.x() * b.y() - a.y() * b.x(),
+                          a.w() * b.w() - a.x() * b.x() - a.y() * b.y() - a.z() * b.z());
+    }
     void setRPY(double roll, double pitch, double yaw) {          // tf2/LinearMath/Quaternion.h
         const double hy = yaw * 0.5, hp = pitch * 0.5, hr = roll * 0.5;
         const double cy = std::cos(hy), sy = std::sin(hy), cp = std::cos(hp), sp = std::sin(hp), cr = std::cos(hr), sr = std::sin(hr);
@@ -46,6 +55,13 @@ public:
 private:
     double q_[4] = {0, 0, 0, 1};
 };
+
+inline Vector3 quatRotate(const Quaternion& q, const Vector3& v) {  // q * v * q^-1, as tf2 (quaternion x pure vector)
+    const Quaternion t(q.w() * v.x() + q.y() * v.z() - q.z() * v.y(), q.w() * v.y() + q.z() * v.x() - q.x() * v.z(),
+                       q.w() * v.z() + q.x() * v.y() - q.y() * v.x(), -q.x() * v.x() - q.y() * v.y() - q.z() * v.z());
+    const Quaternion r = t * q.inverse();
+    return Vector3(r.x(), r.y(), r.z());
+}
 
 class Matrix3x3 {
 public:

@@ -4,6 +4,7 @@
 //   setparam NAME int|double|bool VALUE     parameter change while the node runs
 //   tf TARGET SOURCE tx ty tz qx qy qz qw   make a transform available;   notf TARGET SOURCE   withdraw it
 //   cloud TOPIC FILE N STEP FRAME SEC NSEC name:offset ...   deliver a PointCloud2 (FLOAT32 fields) read from FILE
+//   fix TOPIC LAT LON ALT STATUS            deliver a NavSatFix;   heading TOPIC qx qy qz qw   deliver a QuaternionStamped
 //   timers                                  fire every wall timer once
 // Every published message becomes NNN.json (+ NNN.bin for clouds and grids) under MOCK_ROS_OUT, log lines go to log.txt.
 #include "mock_ros2.hpp"
@@ -155,6 +156,21 @@ void dump(const std::string& topic, const nav_msgs::msg::OccupancyGrid& m) {
                 m.data.size());
 }
 
+void dump(const std::string& topic, const geometry_msgs::msg::TransformStamped& m) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "\"child_frame_id\": \"%s\", \"translation\": [%.17g, %.17g, %.17g], \"rotation\": [%.17g, %.17g, %.17g, %.17g]",
+             esc(m.child_frame_id).c_str(), m.transform.translation.x, m.transform.translation.y, m.transform.translation.z,
+             m.transform.rotation.x, m.transform.rotation.y, m.transform.rotation.z, m.transform.rotation.w);
+    write_files("{\"topic\": \"" + topic + "\", \"type\": \"TransformStamped\", " + header_json(m.header) + ", " + buf + "}", nullptr, 0);
+}
+
+template <class T>
+static void deliver(const std::string& topic, const std::shared_ptr<T>& msg) {
+    auto range = subs().equal_range(topic);
+    for (auto it = range.first; it != range.second; ++it)
+        if (it->second.type == std::type_index(typeid(T))) it->second.cb(msg);
+}
+
 void run_script(const std::function<void(const std::string&, const ParamValue&)>& set_param) {
     load();
     for (const std::string& line : script()) {
@@ -202,9 +218,21 @@ void run_script(const std::function<void(const std::string&, const ParamValue&)>
             }
             msg->data.resize(static_cast<size_t>(n) * step);
             std::ifstream(file, std::ios::binary).read(reinterpret_cast<char*>(msg->data.data()), (std::streamsize)msg->data.size());
-            auto range = subs().equal_range(topic);
-            for (auto it = range.first; it != range.second; ++it)
-                if (it->second.type == std::type_index(typeid(sensor_msgs::msg::PointCloud2))) it->second.cb(msg);
+            deliver(topic, msg);
+        } else if (cmd == "fix") {
+            std::string topic;
+            int status = 0;
+            auto msg = std::make_shared<sensor_msgs::msg::NavSatFix>();
+            in >> topic >> msg->latitude >> msg->longitude >> msg->altitude >> status;
+            msg->status.status = static_cast<int8_t>(status);
+            msg->header.stamp = rclcpp::Time(now_ns());
+            deliver(topic, msg);
+        } else if (cmd == "heading") {
+            std::string topic;
+            auto msg = std::make_shared<geometry_msgs::msg::QuaternionStamped>();
+            in >> topic >> msg->quaternion.x >> msg->quaternion.y >> msg->quaternion.z >> msg->quaternion.w;
+            msg->header.stamp = rclcpp::Time(now_ns());
+            deliver(topic, msg);
         } else {
             throw std::runtime_error("unknown script command: " + line);
         }

@@ -32,11 +32,17 @@ struct Pose { Point position; Quaternion orientation; };
 struct Transform { Vector3 translation; Quaternion rotation; };
 struct PointStamped { std_msgs::msg::Header header; Point point; using SharedPtr = std::shared_ptr<PointStamped>; };
 struct TransformStamped { std_msgs::msg::Header header; std::string child_frame_id; Transform transform; };
+struct QuaternionStamped { std_msgs::msg::Header header; Quaternion quaternion; using SharedPtr = std::shared_ptr<QuaternionStamped>; };
 }}
 namespace sensor_msgs { namespace msg {
 struct PointField {
     enum : uint8_t { INT8 = 1, UINT8 = 2, INT16 = 3, UINT16 = 4, INT32 = 5, UINT32 = 6, FLOAT32 = 7, FLOAT64 = 8 };
     std::string name; uint32_t offset = 0; uint8_t datatype = 0; uint32_t count = 0;
+};
+struct NavSatStatus { int8_t status = 0; uint16_t service = 0; };
+struct NavSatFix {
+    std_msgs::msg::Header header; NavSatStatus status; double latitude = 0, longitude = 0, altitude = 0;
+    using SharedPtr = std::shared_ptr<NavSatFix>;
 };
 struct PointCloud2 {
     std_msgs::msg::Header header;
@@ -70,6 +76,7 @@ void dump(const std::string& topic, const sensor_msgs::msg::PointCloud2& m);
 void dump(const std::string& topic, const geometry_msgs::msg::PointStamped& m);
 void dump(const std::string& topic, const visualization_msgs::msg::MarkerArray& m);
 void dump(const std::string& topic, const nav_msgs::msg::OccupancyGrid& m);
+void dump(const std::string& topic, const geometry_msgs::msg::TransformStamped& m);      // TransformBroadcaster: topic "/tf"
 void log_line(const char* level, const std::string& text);
 struct ParamValue { enum Kind { INT, DOUBLE, BOOL } kind = INT; long long i = 0; double d = 0; bool b = false; };
 bool override_of(const std::string& name, ParamValue* out);          // `param` lines of the script
@@ -209,6 +216,7 @@ inline std::string mock_format(const char* fmt, ...) {
 #define RCLCPP_WARN(logger, ...) mock_ros::log_line("WARN", rclcpp::mock_format(__VA_ARGS__))
 #define RCLCPP_ERROR(logger, ...) mock_ros::log_line("ERROR", rclcpp::mock_format(__VA_ARGS__))
 #define RCLCPP_FATAL(logger, ...) mock_ros::log_line("FATAL", rclcpp::mock_format(__VA_ARGS__))
+#define RCLCPP_INFO_ONCE(logger, ...) do { static bool mock_once = false; if (!mock_once) { mock_once = true; mock_ros::log_line("INFO", rclcpp::mock_format(__VA_ARGS__)); } } while (0)
 #define RCLCPP_INFO_THROTTLE(logger, clock, ms, ...) mock_ros::log_line("INFO", rclcpp::mock_format(__VA_ARGS__))
 #define RCLCPP_WARN_THROTTLE(logger, clock, ms, ...) mock_ros::log_line("WARN", rclcpp::mock_format(__VA_ARGS__))
 
@@ -232,10 +240,18 @@ public:
             throw tf2::LookupException("\"" + target + "\" passed to lookupTransform argument target_frame does not exist (mock)");
         return t;
     }
+    geometry_msgs::msg::TransformStamped lookupTransform(const std::string& target, const std::string& source, tf2::TimePoint t) const {
+        return lookupTransform(target, source, t, tf2::Duration(0));
+    }
     bool canTransform(const std::string& target, const std::string& source, tf2::TimePoint, tf2::Duration) const {
         geometry_msgs::msg::TransformStamped t;
         return mock_ros::lookup_tf(target, source, &t);
     }
 };
 class TransformListener { public: explicit TransformListener(Buffer&) {} };
+class TransformBroadcaster {       // the broadcast is recorded, not fed back into lookupTransform: the script owns the TF tree
+public:
+    template <class NodeT> explicit TransformBroadcaster(NodeT&&) {}
+    void sendTransform(const geometry_msgs::msg::TransformStamped& t) { mock_ros::dump("/tf", t); }
+};
 }

@@ -34,6 +34,12 @@ def filter_scans():
 FILTER_PARAMS = {"voxel_leaf_size": 0.2, "robot_front_range": 12.0, "backhoe_height_range": 6.0}
 
 
+# pointcloud_merger: its inputs are the filter fixture's outputs; map <- */velodyne_link as the scripted TF tree answers
+MERGER_NAMES = {"robot": "four_wheel_robot", "backhoe": "zx120"}
+MERGER_TF = {"robot": (np.array([9.25, -3.0, 2.0]), quat_zyx(2.6, 0.1245)), "backhoe": (np.array([0.55, 0.4, 3.5]), quat_zyx(0.0, 0.4363))}
+MERGER_RGB = {"robot": (255, 0, 0), "backhoe": (0, 0, 255)}
+
+
 def drivable_scan():
     """A filtered robot scan in the sensor frame (point_step 16) and the two transforms the node looks up."""
     rng = np.random.Generator(np.random.PCG64(33))

@@ -6,7 +6,8 @@ cells, the candidate poses, the per-cell colours after the sweep (the six flags 
 pose, the fixed-sensor and best totals, the colour statistics.  Everything the reference wrote itself is therefore pinned
 by its own code; only the third-party arithmetic (FLANN's float32 radius search, PCL's normal estimation, fromROSMsg) is
 restated in the stand-ins.  PCA normals differ between restatements in the last bits, so totals are compared as the
-reference logs them (two decimals) and everything discrete exactly."""
+reference logs them (two decimals) and everything discrete exactly.  Further down: the same for pointcloud_filter.cpp,
+pointcloud_merger.cpp, calc_drivable_area.cpp and excavated_surface_generator.cpp (tests/refsrc_inputs.py)."""
 import subprocess
 from pathlib import Path
 
@@ -285,3 +286,51 @@ def test_cuda_generator_reproduces_the_reference_generator_node(ctx, shape):
     z, rec, bt, bq, prm = generator_reference(shape)
     terrain, area, info = ctx.excavate(rec, bt, bq, prm)
     check_generator(z, terrain, area, int(info.n_kept))
+
+
+def merger_reference():
+    """The reference's pointcloud_merger.cpp on what its pointcloud_filter.cpp published (refsrc_filter.npz)."""
+    z, f = np.load(GOLDEN / "refsrc_merger.npz"), np.load(GOLDEN / "refsrc_filter.npz")
+    clouds = {who: f[f"{who}_records"] for who in ("robot", "backhoe")}
+    for who in clouds:
+        assert R.digest(clouds[who]) == str(z[f"{who}_input_sha256"])
+    return z, clouds
+
+
+def check_merger(z, robot_only, merged, each):
+    """All 32 bytes of every published PointXYZRGB record: x y z, 1.0f, b g r 255, padding (:354-394, :316-351)."""
+    n_r, n_b = z["robot_colored"].shape[0], z["backhoe_colored"].shape[0]
+    assert merged.shape == (n_r + n_b, 32) and n_r > 1000 and n_b > 1000
+    assert np.array_equal(robot_only, z["robot_only"]) and np.array_equal(merged, z["merged"])
+    assert np.array_equal(each[0], z["robot_colored"]) and np.array_equal(each[1], z["backhoe_colored"])
+    assert np.array_equal(z["merged"][:n_r], z["robot_colored"]) and np.array_equal(z["merged"][n_r:], z["backhoe_colored"])   # robot first
+    metas, topics = json.loads(str(z["metas"])), json.loads(str(z["topics"]))
+    assert topics[:7] == ["/matched_point_cloud", "/robot_colored_point_cloud"] * 2 + ["/matched_point_cloud", "/robot_colored_point_cloud", "/backhoe_colored_point_cloud"]
+    for m in metas[:7]:
+        assert (m["frame_id"], m["point_step"], m["height"]) == ("map", 32, 1) and m["fields"] == [["x", 0, 7, 1], ["y", 4, 7, 1], ["z", 8, 7, 1], ["rgb", 16, 7, 1]]
+    assert z["same_again"].all()                                  # the same cloud is re-published on every timer tick
+    assert "Could not transform point cloud for zx120" in str(z["log"])
+
+
+def xyzrgb(xyz, rgb):
+    rec = np.zeros((xyz.shape[0], 32), np.uint8)
+    rec[:, :12] = np.ascontiguousarray(xyz, np.float32).view(np.uint8).reshape(-1, 12)
+    rec[:, 12:16] = np.frombuffer(np.float32(1.0).tobytes(), np.uint8)
+    rec[:, 16:20] = (rgb[2], rgb[1], rgb[0], 255)
+    return rec
+
+
+def test_oracle_reproduces_the_reference_merger_node():
+    z, clouds = merger_reference()
+    each = [xyzrgb(O.transform(clouds[who][:, :3], *R.MERGER_TF[who]), R.MERGER_RGB[who]) for who in ("robot", "backhoe")]
+    check_merger(z, each[0], np.concatenate(each), each)
+
+
+@pytest.mark.gpu
+def test_cuda_merge_reproduces_the_reference_merger_node(ctx):
+    z, clouds = merger_reference()
+    src = lambda who, present=True: dict(cloud=clouds[who], point_step=16, t=R.MERGER_TF[who][0], q=R.MERGER_TF[who][1],
+                                         rgb=R.MERGER_RGB[who], present=present)
+    robot_only, _ = ctx.merge([src("robot"), src("backhoe", present=False)])          # the TF of the backhoe's cloud is missing
+    merged, each = ctx.merge([src("robot"), src("backhoe")])
+    check_merger(z, robot_only, merged, each)
