@@ -38,6 +38,26 @@ FILTER_PARAMS = {"voxel_leaf_size": 0.2, "robot_front_range": 12.0, "backhoe_hei
 MERGER_NAMES = {"robot": "four_wheel_robot", "backhoe": "zx120"}
 MERGER_TF = {"robot": (np.array([9.25, -3.0, 2.0]), quat_zyx(2.6, 0.1245)), "backhoe": (np.array([0.55, 0.4, 3.5]), quat_zyx(0.0, 0.4363))}
 MERGER_RGB = {"robot": (255, 0, 0), "backhoe": (0, 0, 255)}
+MERGER_TOPICS = ["/matched_point_cloud", "/robot_colored_point_cloud"] * 2 + ["/matched_point_cloud", "/robot_colored_point_cloud",
+                                                                             "/backhoe_colored_point_cloud", "/tf", "/tf", "/tf"]
+
+
+def merger_script(tmp, clouds, cloud_line, tf_line):
+    """The message / TF / timer script both the reference's pointcloud_merger.cpp and ros2/src/pointcloud_merger_node.cpp
+    are played: ticks before the GNSS origin, with one source, with a source whose TF is missing, with both; then the
+    GNSS half (fix + heading -> map -> base_link broadcasts for both vehicles)."""
+    cl = lambda who: cloud_line(tmp, f"/{MERGER_NAMES[who]}/filtered_points", clouds[who], f"{MERGER_NAMES[who]}/velodyne", (100, 7), "x:0 y:4 z:8")
+    tfl = lambda who: tf_line("map", f"{MERGER_NAMES[who]}/velodyne_link", *MERGER_TF[who])
+    return [cl("robot"), tfl("robot"), "timers",                                 # no GNSS origin yet (:309): nothing
+            "fix /zx120/gnss_compass_front/fix 35.0 139.0 40.0 0", "timers",     # origin set; robot cloud only
+            cl("backhoe"), "timers",                                             # no TF for the backhoe's cloud: robot only + a warning (:389-393)
+            tfl("backhoe"), "timers",                                            # both
+            "heading /four_wheel_robot/gnss_compass/calc_heading 0 0 0.6 0.8",
+            tf_line("four_wheel_robot/gnss_link", "four_wheel_robot/base_link", (-0.5, 0, 0), (0, 0, 0, 1)),
+            "fix /four_wheel_robot/gnss_compass_front/fix 35.00005 139.00008 41.0 0",      # map -> four_wheel_robot/base_link, no backhoe heading
+            tf_line("zx120/base_link", "zx120/gnss_link", (2.0, 0, 3.8), (0, 0, 0, 1)),
+            "heading /zx120/gnss_compass/calc_heading 0 0 0.1 0.99498743710662",           # map -> zx120/base_link: identity
+            "fix /four_wheel_robot/gnss_compass_front/fix 35.00006 139.00007 41.5 0"]      # relative heading + antenna offset
 
 
 def drivable_scan():

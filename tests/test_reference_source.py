@@ -334,3 +334,29 @@ def test_cuda_merge_reproduces_the_reference_merger_node(ctx):
     robot_only, _ = ctx.merge([src("robot"), src("backhoe", present=False)])          # the TF of the backhoe's cloud is missing
     merged, each = ctx.merge([src("robot"), src("backhoe")])
     check_merger(z, robot_only, merged, each)
+
+
+def test_drop_in_merger_host_half_without_a_gpu(tmp_path):
+    """The wrapper's host half alone (libplc.so's three entry points stubbed, tests/mock_ros2/plc_stub_merger.cpp): which
+    ticks publish what, sizes, headers, stamps, the map -> base_link broadcasts to the last bit, the log text."""
+    from test_ros2_wrappers import cloud_line, play, tf_line
+    z, clouds = merger_reference()
+    msgs, log = play("pointcloud_merger", R.merger_script(tmp_path, clouds, cloud_line, tf_line), tmp_path, stub="plc_stub_merger.cpp")
+    assert [m for m, _ in msgs] == json.loads(str(z["metas"])) and log == str(z["log"]).splitlines()
+    assert [m["topic"] for m, _ in msgs[7:]] == ["/tf"] * 3 and msgs[8][0]["translation"] == [0, 0, 0] and msgs[9][0]["rotation"][2] != 0.6
+
+
+@pytest.mark.gpu
+def test_drop_in_merger_publishes_what_the_reference_merger_publishes(tmp_path):
+    """ros2/src/pointcloud_merger_node.cpp (on libplc.so, built against the mock ROS2) on the script the reference's own
+    pointcloud_merger.cpp was played: the same messages in the same order — every cloud byte, every header and stamp,
+    the three map -> base_link broadcasts of the GNSS half to the last bit — and the same log text."""
+    from test_ros2_wrappers import cloud_line, play, tf_line
+    z, clouds = merger_reference()
+    msgs, log = play("pointcloud_merger", R.merger_script(tmp_path, clouds, cloud_line, tf_line), tmp_path)
+    assert [m["topic"] for m, _ in msgs] == R.MERGER_TOPICS
+    assert [m for m, _ in msgs] == json.loads(str(z["metas"]))
+    want = {0: "robot_only", 1: "robot_only", 2: "robot_only", 3: "robot_only", 4: "merged", 5: "robot_colored", 6: "backhoe_colored"}
+    for k, name in want.items():
+        assert msgs[k][1] == z[name].tobytes(), (k, name)
+    assert log == str(z["log"]).splitlines()

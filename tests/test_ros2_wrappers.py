@@ -1,6 +1,6 @@
 """The rclcpp wrappers in ros2/src, compiled and driven without ROS2.
 
-There is no ROS2 in this image, so the four node executables a maintainer drops into the reference package are built
+There is no ROS2 in this image, so the five node executables a maintainer drops into the reference package are built
 against tests/mock_ros2 (rclcpp / tf2_ros / message types reduced to what the wrappers use, an in-process bus and a
 script player behind rclcpp::spin) and linked with libplc.so.  The CPU test checks that they compile and link; the GPU
 tests play message / TF / timer / parameter scripts through them and compare what they publish with the same calls made
@@ -17,20 +17,28 @@ import pytest
 ROOT = Path(__file__).resolve().parent.parent
 MOCK = ROOT / "tests" / "mock_ros2"
 BUILD = ROOT / "tests" / "_build"
-NODES = ["virtual_lidar", "pointcloud_filter", "excavated_surface_generator", "calc_drivable_area"]
+NODES = ["virtual_lidar", "pointcloud_filter", "pointcloud_merger", "excavated_surface_generator", "calc_drivable_area"]
+GEO = ROOT / "oracle" / "ref_shim" / "GeographicLib"       # stand-in LocalCartesian.hpp: the only header pointcloud_merger needs beyond the mock
 
 
-def build(name: str) -> Path:
-    exe = BUILD / f"ros2_{name}"
-    srcs = [ROOT / "ros2" / "src" / f"{name}_node.cpp", MOCK / "mock_ros2.cpp"]
+def build(name: str, stub: str | None = None) -> Path:
+    """stub: a tests/mock_ros2/plc_stub_*.cpp whose definitions shadow libplc.so's (host-logic tests on a box without a GPU)."""
+    exe = BUILD / (f"ros2_{name}" + ("_stub" if stub else ""))
+    srcs = [ROOT / "ros2" / "src" / f"{name}_node.cpp", MOCK / "mock_ros2.cpp"] + ([MOCK / stub] if stub else [])
     deps = srcs + [MOCK / "mock_ros2.hpp", ROOT / "ros2" / "src" / "cloud_msg.hpp", ROOT / "include" / "plc.h",
                    ROOT / "include" / "plc_node.h"]
     if exe.exists() and all(exe.stat().st_mtime >= d.stat().st_mtime for d in deps):
         return exe
     BUILD.mkdir(exist_ok=True)
     lib = ROOT / "pointcloud_processor_b200" / "lib"
+    geo = []
+    if name == "pointcloud_merger":                        # <GeographicLib/LocalCartesian.hpp> without the rest of oracle/ref_shim
+        (BUILD / "geo").mkdir(exist_ok=True)
+        if not (BUILD / "geo" / "GeographicLib").exists():
+            (BUILD / "geo" / "GeographicLib").symlink_to(GEO)
+        geo = [f"-I{BUILD / 'geo'}"]
     cmd = ["g++", "-O1", "-std=c++17", "-Wall", "-Wextra", "-Werror", f"-I{MOCK}", f"-I{ROOT / 'include'}",
-           f"-I{ROOT / 'ros2' / 'src'}", *map(str, srcs), "-o", str(exe), f"-L{lib}", "-lplc", f"-Wl,-rpath,{lib}"]
+           f"-I{ROOT / 'ros2' / 'src'}", *geo, *map(str, srcs), "-o", str(exe), f"-L{lib}", "-lplc", f"-Wl,-rpath,{lib}"]
     subprocess.run(cmd, check=True, capture_output=True, text=True)
     return exe
 
@@ -44,13 +52,13 @@ def test_wrapper_compiles_against_mock_ros2(name):
     assert exe.exists()
 
 
-def play(name: str, script: list[str], tmp: Path):
+def play(name: str, script: list[str], tmp: Path, stub: str | None = None):
     """Runs one wrapper executable over a script; returns (published messages as (meta, bytes), log lines)."""
     out = tmp / f"out_{name}_{len(list(tmp.glob('out_*')))}"
     out.mkdir()
     (out / "script.txt").write_text("\n".join(script) + "\n")
     env = dict(os.environ, MOCK_ROS_SCRIPT=str(out / "script.txt"), MOCK_ROS_OUT=str(out))
-    r = subprocess.run([str(build(name))], env=env, capture_output=True, text=True, timeout=300)
+    r = subprocess.run([str(build(name, stub))], env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     msgs = []
     for j in sorted(out.glob("[0-9][0-9][0-9].json")):

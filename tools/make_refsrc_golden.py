@@ -98,24 +98,15 @@ def other_nodes():
     print("filter", {k: v.shape for k, v in out.items() if hasattr(v, "shape") and v.ndim == 2})
     # ---- pointcloud_merger (src/pointcloud_merger.cpp) on what the filter node just published
     filt = {who: out[f"{who}_records"] for who in ("robot", "backhoe")}
-    cl = lambda tmp, who: cloud_line(tmp, f"/{R.MERGER_NAMES[who]}/filtered_points", filt[who], f"{R.MERGER_NAMES[who]}/velodyne", (100, 7), "x:0 y:4 z:8")
-    tfl = lambda who: tf_line("map", f"{R.MERGER_NAMES[who]}/velodyne_link", *R.MERGER_TF[who])
-    msgs, log = play("pointcloud_merger", lambda tmp: [
-        cl(tmp, "robot"), tfl("robot"), "timers",                            # no GNSS origin yet (:309): nothing
-        "fix /zx120/gnss_compass_front/fix 35.0 139.0 40.0 0", "timers",     # origin set; robot cloud only
-        cl(tmp, "backhoe"), "timers",                                        # no TF for the backhoe's cloud: robot only + a warning (:389-393)
-        tfl("backhoe"), "timers",                                            # both
-        "heading /four_wheel_robot/gnss_compass/calc_heading 0 0 0.6 0.8",
-        tf_line("four_wheel_robot/gnss_link", "four_wheel_robot/base_link", (-0.5, 0, 0), (0, 0, 0, 1)),
-        "fix /four_wheel_robot/gnss_compass_front/fix 35.00005 139.00008 41.0 0"])      # the GNSS half broadcasts map -> base_link
+    msgs, log = play("pointcloud_merger", lambda tmp: R.merger_script(tmp, filt, cloud_line, tf_line))
     topics = [m["topic"] for m, _ in msgs]
-    assert topics == ["/matched_point_cloud", "/robot_colored_point_cloud"] * 2 + ["/matched_point_cloud", "/robot_colored_point_cloud", "/backhoe_colored_point_cloud", "/tf"], topics
+    assert topics == R.MERGER_TOPICS, topics
     np.savez_compressed(gold / "refsrc_merger.npz", topics=json.dumps(topics), metas=json.dumps([m for m, _ in msgs]), log=log,
                         robot_only=np.frombuffer(msgs[0][1], np.uint8).reshape(-1, 32).copy(), merged=np.frombuffer(msgs[4][1], np.uint8).reshape(-1, 32).copy(),
                         robot_colored=np.frombuffer(msgs[5][1], np.uint8).reshape(-1, 32).copy(), backhoe_colored=np.frombuffer(msgs[6][1], np.uint8).reshape(-1, 32).copy(),
                         same_again=np.array([msgs[2][1] == msgs[0][1], msgs[3][1] == msgs[1][1], msgs[1][1] == msgs[0][1]]),
                         robot_input_sha256=R.digest(filt["robot"]), backhoe_input_sha256=R.digest(filt["backhoe"]))
-    print("merger", topics, msgs[4][0]["width"], msgs[-1][0])
+    print("merger", topics, msgs[4][0]["width"], [m for m, _ in msgs[7:]])
     # ---- calc_drivable_area (src/calc_drivable_area.cpp)
     scan, (t, q), robot = R.drivable_scan()
     line = lambda tmp: cloud_line(tmp, "/four_wheel_robot/filtered_points", scan, "four_wheel_robot/velodyne", (5, 6), "x:0 y:4 z:8 intensity:12")
