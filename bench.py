@@ -218,6 +218,57 @@ def cpu_reference_sample(scene, budget_s: float, threads: int, seed: int = 1234)
     return n * M / dt, n, dt
 
 
+def reference_source_sample(scene, res: float, layers: int, k_small: int = 9, k_large: int = 49) -> dict:
+    """Times the reference's OWN virtual_lidar.cpp — oracle/_ref/virtual_lidar_ref, compiled unmodified against the
+    stand-in PCL / ROS2 headers where /root/reference exists (`make -C oracle ref`; the binary travels, its sources do
+    not) — on this workload's terrain and area clouds: the node builds its own lattices (grid_resolution, vertical_layers
+    as the scene's) and runs one optimisation cycle per process; two runs with different num_candidates are differenced,
+    so that start-up, PCA normals and lattice generation cancel.  One thread, as upstream.  Informational: its radius
+    search is the stand-in's grid index, not FLANN's kd-tree."""
+    import tempfile
+    exe = ROOT / "oracle" / "_ref" / "virtual_lidar_ref"
+    if not exe.exists():
+        return {"unavailable": "oracle/_ref/virtual_lidar_ref not built (needs /root/reference at build time)"}
+
+    def records(xyz):
+        r = np.zeros((xyz.shape[0], 8), np.float32)
+        r[:, :3] = xyz[:, :3]
+        return r
+
+    def run(tmp, k):
+        out = tmp / f"k{k}"
+        out.mkdir()
+        lines = [f"param num_candidates int {k}", f"param vertical_layers int {layers}", f"param grid_resolution double {res!r}"]
+        for topic, cloud in (("/excavation_area", scene.area), ("/excavated_terrain", scene.terrain)):
+            f = out / (topic.strip("/") + ".bin")
+            records(cloud).tofile(f)
+            lines.append(f"cloud {topic} {f} {cloud.shape[0]} 32 map 1 0 x:0 y:4 z:8 rgb:16")
+        lines += ["tf map zx120/base_link 0 0 0 0 0 0 1", "timers"]
+        (out / "script.txt").write_text("\n".join(lines) + "\n")
+        env = dict(os.environ, MOCK_ROS_SCRIPT=str(out / "script.txt"), MOCK_ROS_OUT=str(out))
+        t0 = time.perf_counter()
+        subprocess.run([str(exe)], env=env, check=True, capture_output=True, timeout=600)
+        dt = time.perf_counter() - t0
+        n = {}
+        for j in sorted(out.glob("[0-9][0-9][0-9].json")):
+            m = json.loads(j.read_text())
+            n[m["topic"]] = m.get("markers", 0)
+        # candidate array: delete-all + fixed sensor + candidates + optimum; grid array: delete-all + cells
+        return dt, n["/mobile_lidar_candidate_positions"] - 3, n["/excavation_grid_visualization"] - 1
+
+    try:
+        with tempfile.TemporaryDirectory() as tmp:
+            t1, c1, m1 = run(Path(tmp), k_small)
+            t2, c2, m2 = run(Path(tmp), k_large)
+    except Exception as e:  # noqa: BLE001 — informational leg: report, do not fail the arm
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+    if c2 <= c1 or t2 <= t1 or m1 != m2:
+        return {"unavailable": f"differencing failed: {c1} poses in {t1:.2f} s, {c2} in {t2:.2f} s"}
+    return {"value": (c2 - c1) * m2 / (t2 - t1), "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": f"({c2} - {c1}) poses x {m2} rays of the node's own lattices in ({t2:.1f} - {t1:.1f}) s, one optimisation cycle per run",
+            "note": "virtual_lidar.cpp unmodified; KdTreeFLANN / NormalEstimation are the stand-ins of oracle/ref_shim (grid index, not FLANN)"}
+
+
 class Rig:
     """One rank's context, stream and collectives."""
 
@@ -800,10 +851,12 @@ def measure_setup(ctx, scene, peak, best) -> dict:
 
 
 def run_reference(args) -> dict | None:
-    """The reference's own CPU implementation of the path, on the box's host cores.  The reference
-    cannot be built here (ROS2/PCL/FLANN absent), so this times the oracle's restatement
-    with the reference's loop structure (KD-tree radius searches, per-candidate fixed-sensor
-    re-evaluation), all host threads, on a bounded seeded sample of the same workload."""
+    """The reference's own CPU implementation of the path, on the box's host cores.  The reference's
+    build cannot run here (ROS2/PCL/FLANN absent), so the line's value times the oracle's
+    restatement with the reference's loop structure (KD-tree radius searches, per-candidate fixed-sensor
+    re-evaluation), all host threads, on a bounded seeded sample of the same workload — the harder
+    baseline.  Beside it, `reference_source` times the reference's own virtual_lidar.cpp compiled against
+    the stand-in headers (oracle/_ref): one thread, as upstream runs, on the stand-in's grid index."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
@@ -826,6 +879,9 @@ def run_reference(args) -> dict | None:
         ns.append(n)
         total += dt
     value = float(np.mean(vals))
+    refsrc = None
+    if world == 1 and not args.no_reference_source:
+        refsrc = reference_source_sample(scene, float(scene.meta["res"]), int(scene.meta["layers_found"]))
     sample = f"{int(np.mean(ns))} seeded poses x {M} rays per step (~{total / steps:.1f} s/step) of {C} poses"
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps,
@@ -838,6 +894,7 @@ def run_reference(args) -> dict | None:
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        **({"reference_source": refsrc} if refsrc is not None else {}),
     }
 
 
@@ -847,6 +904,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-reference-source", action="store_true",
+                    help="reference arm: skip the single-threaded run of the reference's own virtual_lidar.cpp (oracle/_ref)")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default=None,
                     help="default: cfg2 (BASELINE.json configs[1]) on one GPU, cfg3 (configs[2]) strong-scaled on N > 1")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
