@@ -104,6 +104,14 @@ def main():
                   and got.counters["rays_gated_in"] == ref["counters"]["rays_gated_in"]
                   and np.array_equal(got.cell_flags, ref["flags"])
                   and np.allclose(got.fixed_scores, ref["fixed_scores"], rtol=1e-12, atol=1e-15))
+            # the any-hit traversal (the default of the library) on the same scene: every output but the sample counter
+            ctx.count_samples(False)
+            fast = ctx.sweep(prm, fixed, poses, mask=True, flags=True, fixed_scores=True)
+            ctx.count_samples(True)
+            ok = ok and (np.array_equal(fast.mask, got.mask) and np.array_equal(fast.covered, got.covered)
+                         and np.array_equal(fast.scores, got.scores, equal_nan=True) and np.array_equal(fast.cell_flags, got.cell_flags)
+                         and np.array_equal(fast.fixed_scores, got.fixed_scores, equal_nan=True) and fast.best_index == got.best_index
+                         and fast.counters["rays_visible"] == got.counters["rays_visible"])
             tot["rays"] += got.counters["rays"]; tot["gated"] += got.counters["rays_gated_in"]
             tot["visible"] += got.counters["rays_visible"]; tot["samples"] += got.counters["samples"]
             tot["exact"] += got.counters["exact_tests"]
@@ -112,7 +120,7 @@ def main():
                 print("MISMATCH it", it, "seed", seed, "mask", mism, "rel", float(np.nanmax(rel, initial=0.0)),
                       "samples", got.counters["samples"], ref["counters"]["samples"], "gated", got.counters["rays_gated_in"],
                       ref["counters"]["rays_gated_in"], "cells", cells.size, "poses", poses.size, flush=True)
-    print(f"fuzz: {iters} scenes, {bad} mismatching, {time.time() - t0:.1f} s, totals {tot}")
+    print(f"fuzz: {iters} scenes (seed {seed}) in both traversal modes, {bad} mismatching, {time.time() - t0:.1f} s, totals {tot}")
     sys.exit(1 if bad else 0)
 
 
