@@ -40,14 +40,14 @@ def layout(rng):
     step = int(rng.choice([12, 16, 19, 22, 32, 48]))
     if step == 12:
         return 12, (0, 4, 8)
-    slots = rng.permutation(np.arange(0, step - 3, 4 if step % 4 == 0 and rng.random() < 0.7 else 1))
-    chosen = []
-    for s in slots:
-        if all(abs(int(s) - c) >= 4 for c in chosen):
-            chosen.append(int(s))
-        if len(chosen) == 3:
-            break
-    return step, tuple(chosen)
+    while True:        # a greedy pick of byte offsets can leave no room for the third field in a short record: draw again
+        slots = rng.permutation(np.arange(0, step - 3, 4 if step % 4 == 0 and rng.random() < 0.7 else 1))
+        chosen = []
+        for s in slots:
+            if all(abs(int(s) - c) >= 4 for c in chosen):
+                chosen.append(int(s))
+            if len(chosen) == 3:
+                return step, tuple(chosen)
 
 
 def one_drivable(ctx, rng):
