@@ -167,7 +167,11 @@ private:
     // One source of the tick: the latest cloud and map <- <name>/velodyne_link (:362-366; failure: warn and skip, :389-393)
     plc_merger_input input_of(const Vehicle& v) {
         plc_merger_input in{};
-        if (!v.cloud || !plc_ros::view_of(*v.cloud, &in.cloud)) return in;
+        if (!v.cloud) return in;
+        if (!plc_ros::view_of(*v.cloud, &in.cloud)) {                       // upstream: fromROSMsg warns and reads zeros
+            RCLCPP_WARN_THROTTLE(get_logger(), *get_clock(), 1000, "cloud of %s has no FLOAT32 x, y, z fields: skipped", v.name.c_str());
+            return in;
+        }
         in.has_cloud = 1;
         try {
             const auto tf = tf_buffer_->lookupTransform("map", v.name + "/velodyne_link", tf2::TimePointZero, tf2::durationFromSec(0.1)).transform;
