@@ -84,3 +84,43 @@ def generator_cloud(shape):
     r[:, 4] = np.where(rng.random(n) < 0.5, np.uint32(0xFFFF0000), np.uint32(0xFF0000FF)).astype(np.uint32).view(np.float32)
     base = (np.array([0.3, -0.2, 0.0]), np.array([0.0, 0.0, np.sin(0.2), np.cos(0.2)]) if shape == "rect" else np.array([0.0, 0.0, 0.0, 1.0]))
     return r, base
+
+
+# ---- virtual_lidar over several cycles of one process (tests/golden/refsrc_cycles.npz) -------------------------------
+CYCLES_BASES = [(0.0, 0.0, 0.1), (0.3, 0.2, 0.05)]
+# parameters in force DURING each cycle's sweep (re-read at the top of runOptimization, :457) and the ones the cell
+# lattice was generated with (the area callback uses the values of the LAST re-read, :172 -> :236-287)
+CYCLES_PARAMS = [dict(num_candidates=36, vertical_layers=6, grid_resolution=0.1, sensor_height=1.1, search_radius=3.0, max_distance=15.0),
+                 dict(num_candidates=25, vertical_layers=6, grid_resolution=0.1, sensor_height=1.6, search_radius=2.0, max_distance=4.5),
+                 dict(num_candidates=25, vertical_layers=6, grid_resolution=0.1, sensor_height=1.6, search_radius=2.0, max_distance=4.5),
+                 dict(num_candidates=25, vertical_layers=4, grid_resolution=0.2, sensor_height=1.6, search_radius=2.0, max_distance=9.0),
+                 dict(num_candidates=25, vertical_layers=4, grid_resolution=0.2, sensor_height=1.6, search_radius=2.0, max_distance=9.0)]
+CYCLES_LATTICE = [(0.1, 6), (0.1, 6), (0.1, 6), (0.1, 6), (0.2, 4)]       # (grid_resolution, vertical_layers) behind each cycle's cells
+CYCLES_FRESH_CELLS = [True, False, False, True, True]                      # an area message arrived before this cycle: flags start from zero
+
+
+def cycles_inputs(scenes):
+    def rec(xyz):
+        r = np.zeros((xyz.shape[0], 8), np.float32)
+        r[:, :3] = xyz[:, :3]
+        return r
+    area = rec(scenes.excavation_area("rect", 0.05)[0])
+    return dict(area=area, terrain_a=rec(scenes.terrain("rect", 30_000, seed=7, side=24.0)),
+                terrain_b=rec(scenes.terrain("rect", 24_000, seed=8, side=24.0)), observed=rec(area[::7, :3].copy()))
+
+
+def cycles_script(tmp, C, cloud_line, tf_line):
+    cl = lambda topic, key: cloud_line(tmp, topic, C[key], "map", (10, 20), "x:0 y:4 z:8 rgb:16")
+    sp = lambda name, kind, v: f"setparam {name} {kind} {v!r}"
+    return ["param num_candidates int 36", "param vertical_layers int 6",
+            cl("/excavation_area", "area"), cl("/excavated_terrain", "terrain_a"), tf_line("map", "zx120/base_link", CYCLES_BASES[0], (0, 0, 0, 1)),
+            "timers",                                                                                    # cycle 0
+            sp("max_distance", "double", 4.5), sp("sensor_height", "double", 1.6), sp("search_radius", "double", 2.0), sp("num_candidates", "int", 25),
+            "timers",                                                                                    # cycle 1: new parameters, same data, flags carried over
+            cl("/excavated_terrain", "terrain_b"), cl("/zx120/filtered_points", "observed"), tf_line("map", "zx120/base_link", CYCLES_BASES[1], (0, 0, 0, 1)),
+            "timers",                                                                                    # cycle 2: new terrain, an observed cloud, the base moved
+            sp("grid_resolution", "double", 0.2), sp("vertical_layers", "int", 4), sp("max_distance", "double", 9.0),
+            cl("/excavation_area", "area"),                                                              # lattice still at 0.1 x 6: the re-read comes with the cycle
+            "timers",                                                                                    # cycle 3
+            cl("/excavation_area", "area"),                                                              # now 0.2 x 4
+            "timers"]                                                                                    # cycle 4

@@ -7,7 +7,8 @@ pose, the fixed-sensor and best totals, the colour statistics.  Everything the r
 by its own code; only the third-party arithmetic (FLANN's float32 radius search, PCL's normal estimation, fromROSMsg) is
 restated in the stand-ins.  PCA normals differ between restatements in the last bits, so totals are compared as the
 reference logs them (two decimals) and everything discrete exactly.  Further down: the same for pointcloud_filter.cpp,
-pointcloud_merger.cpp, calc_drivable_area.cpp and excavated_surface_generator.cpp (tests/refsrc_inputs.py)."""
+pointcloud_merger.cpp, calc_drivable_area.cpp and excavated_surface_generator.cpp (tests/refsrc_inputs.py), and five
+optimisation cycles of one virtual_lidar process (refsrc_cycles.npz)."""
 import subprocess
 from pathlib import Path
 
@@ -360,3 +361,99 @@ def test_drop_in_merger_publishes_what_the_reference_merger_publishes(tmp_path):
     for k, name in want.items():
         assert msgs[k][1] == z[name].tobytes(), (k, name)
     assert log == str(z["log"]).splitlines()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Five optimisation cycles of ONE virtual_lidar process (tests/golden/refsrc_cycles.npz): what carries over between
+# cycles — the per-cell flags (stale-flag rule), the cells until the next area message, and parameters that take effect
+# at the next cycle's re-read (:457), so that an area message BEFORE that re-read still builds the old lattice (:172).
+def cycles_reference():
+    from pointcloud_processor_b200 import scenes
+    z = np.load(GOLDEN / "refsrc_cycles.npz")
+    C = R.cycles_inputs(scenes)
+    for k, v in C.items():
+        assert R.digest(v) == str(z[f"{k}_sha256"]), k
+    assert int(z["n_cycles"]) == len(R.CYCLES_PARAMS) == 5
+    return z, C
+
+
+def cycle_view(z, k):
+    return {name: z[f"c{k}_{name}"] for name in ("cells_xyz", "cell_rgb", "cands_xyz", "fixed_xyz", "best_xyz", "fixed_total_2dp", "best_score_2dp", "colour_counts")}
+
+
+def test_oracle_reproduces_five_cycles_of_the_reference_node():
+    z, C = cycles_reference()
+    area = C["area"][:, :3]
+    normals = O.compute_normals(area, 1.5)
+    tix = {"a": O.Index(C["terrain_a"][:, :3], O.GRID), "b": O.Index(C["terrain_b"][:, :3], O.GRID)}
+    oix = O.Index(C["observed"][:, :3], O.GRID)
+    cells = bounds = flags = None
+    seen = []
+    for k, P in enumerate(R.CYCLES_PARAMS):
+        if R.CYCLES_FRESH_CELLS[k]:                                       # an area message since the last cycle: new cells, cleared flags
+            res, layers = R.CYCLES_LATTICE[k]
+            cells, bounds = O.generate_cells(area, normals, res, layers, 1.5)
+            flags = np.zeros(cells.size, np.uint8)
+        base = np.array(R.CYCLES_BASES[0 if k < 2 else 1])
+        fixed = np.zeros(1, A.POSE_DTYPE)
+        fixed["x"], fixed["y"], fixed["z"], fixed["pitch"] = *(base + np.array([0.4, 0.5, 3.5])), -np.pi / 6
+        terrain = tix["a" if k < 2 else "b"]
+        cands = O.generate_candidates(terrain, bounds, fixed, P["num_candidates"], P["search_radius"], P["sensor_height"])
+        prm = A.default_params()
+        prm.max_distance = P["max_distance"]
+        ref = O.sweep(terrain, oix if k >= 2 else None, cells, prm, fixed, cands, flags_inout=flags)
+        b = cands[ref["best_index"]]
+        check_against_fixture(cycle_view(z, k), cells, cands, (b["x"], b["y"], b["z"]), ref["best_score"], ref["fixed_total"], flags)
+        seen.append((cells.size, cands.size))
+    assert seen[3][0] == seen[2][0] and seen[4][0] < seen[3][0]           # the lattice follows the parameters one cycle late
+
+
+@pytest.mark.gpu
+def test_cuda_node_reproduces_five_cycles_of_the_reference_node(ctx):
+    from pointcloud_processor_b200.nodes import VirtualLidarNode
+    z, C = cycles_reference()
+    node = VirtualLidarNode(ctx)
+
+    def cycle(k):
+        res = node.run_optimization()
+        assert res.ran == 1
+        cells, flags = node.cells()
+        check_against_fixture(cycle_view(z, k), cells, node.candidates(), (res.best.x, res.best.y, res.best.z), res.best_score, res.fixed_total, flags)
+
+    node.set_parameter("num_candidates", 36)
+    node.set_parameter("vertical_layers", 6)
+    node.update_parameters()
+    node.excavation_area_callback(C["area"])
+    node.terrain_callback(C["terrain_a"])
+    node.set_base_transform(R.CYCLES_BASES[0])
+    cycle(0)
+    for name, v in (("max_distance", 4.5), ("sensor_height", 1.6), ("search_radius", 2.0), ("num_candidates", 25)):
+        node.set_parameter(name, v)
+    cycle(1)
+    node.terrain_callback(C["terrain_b"])
+    node.zx120_points_callback(C["observed"])
+    node.set_base_transform(R.CYCLES_BASES[1])
+    cycle(2)
+    for name, v in (("grid_resolution", 0.2), ("vertical_layers", 4), ("max_distance", 9.0)):
+        node.set_parameter(name, v)
+    node.excavation_area_callback(C["area"])          # before the re-read: the lattice is still 0.1 x 6
+    cycle(3)
+    node.excavation_area_callback(C["area"])          # after it: 0.2 x 4
+    cycle(4)
+
+
+@pytest.mark.gpu
+def test_drop_in_executable_reproduces_five_cycles_of_the_reference_node(tmp_path):
+    import sys
+    from test_ros2_wrappers import cloud_line, play, tf_line
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent / "tools"))
+    from make_refsrc_golden import parse_cycles
+    z, C = cycles_reference()
+    msgs, log = play("virtual_lidar", R.cycles_script(tmp_path, C, cloud_line, tf_line), tmp_path)
+    got = parse_cycles(msgs, "\n".join(log) + "\n")
+    assert len(got) == 5
+    for k, g in enumerate(got):
+        want = cycle_view(z, k)
+        for name in ("cells_xyz", "cell_rgb", "cands_xyz", "fixed_xyz", "best_xyz", "colour_counts"):
+            assert np.array_equal(g[name], want[name]), (k, name)
+        assert (g["fixed_total_2dp"], g["best_score_2dp"]) == (float(want["fixed_total_2dp"]), float(want["best_score_2dp"])), k

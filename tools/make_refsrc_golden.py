@@ -151,6 +151,44 @@ def parse(msgs, log):
                 log=log)
 
 
+def parse_cycles(msgs, log):
+    """One dict per optimisation cycle of a script with several `timers` lines: a cycle publishes optimum, candidates
+    and grid, in that order, and logs both statistics blocks once (an area message publishes a grid of its own)."""
+    rows = lambda b: np.frombuffer(b, np.float64).reshape(-1, 14)
+    topics = [m["topic"] for m, _ in msgs]
+    at = [i for i, t in enumerate(topics) if t == "/optimal_mobile_lidar_position"]
+    assert all(topics[i + 1] == "/mobile_lidar_candidate_positions" and topics[i + 2] == "/excavation_grid_visualization" for i in at), topics
+    blocks = log.split("INFO ZX120 LiDAR Only Evaluation")[1:]
+    assert len(blocks) == len(at)
+    out = []
+    for i, text in zip(at, blocks):
+        grid, cand = rows(msgs[i + 2][1])[1:], rows(msgs[i + 1][1])
+        num = lambda pat: [float(x) for x in re.findall(pat, text)]
+        counts = {c: [int(v) for v in re.findall(rf"{c} \([^)]*\): (\d+) cells", text)] for c in ("Green", "Red", "Blue", "Yellow")}
+        out.append(dict(cells_xyz=grid[:, 3:6].copy(), cell_rgb=grid[:, 9:12].copy(), cands_xyz=cand[2:-1, 3:6].copy(),
+                        fixed_xyz=cand[1, 3:6].copy(), best_xyz=np.array(msgs[i][0]["point"]),
+                        fixed_total_2dp=num(r"Total Score \(ZX120 only\): ([-\d.]+)")[-1], best_score_2dp=num(r"\nINFO Total Score: ([-\d.]+)")[-1],
+                        colour_counts=np.array([[counts[c][i] for c in ("Green", "Red", "Blue", "Yellow")] for i in (0, 1)])))
+    return out
+
+
+def cycles_case():
+    """tests/golden/refsrc_cycles.npz: five optimisation cycles of ONE node process — what carries over between cycles
+    (the per-cell flags, the cells until the next area message, parameters as of the last cycle's re-read)."""
+    sys.path.insert(0, os.fspath(ROOT / "tests"))
+    import refsrc_inputs as R
+    C = R.cycles_inputs(scenes)
+    msgs, log = play("virtual_lidar", lambda tmp: R.cycles_script(tmp, C, cloud_line, tf_line))
+    cyc = parse_cycles(msgs, log)
+    flat = {f"c{k}_{name}": v for k, c in enumerate(cyc) for name, v in c.items()}
+    path = ROOT / "tests" / "golden" / "refsrc_cycles.npz"
+    np.savez_compressed(path, n_cycles=len(cyc), log=log, **{f"{k}_sha256": R.digest(v) for k, v in C.items()}, **flat)
+    for k, c in enumerate(cyc):
+        print("cycle", k, "cells", c["cells_xyz"].shape[0], "candidates", c["cands_xyz"].shape[0], "best", c["best_xyz"], "score", c["best_score_2dp"],
+              "fixed", c["fixed_total_2dp"], "colours", c["colour_counts"].tolist())
+    print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
+
+
 def main():
     if not Path("/root/reference/src/virtual_lidar.cpp").exists():
         raise SystemExit("needs /root/reference")
@@ -170,4 +208,5 @@ def main():
 
 if __name__ == "__main__":
     main()
+    cycles_case()
     other_nodes()
