@@ -124,3 +124,57 @@ def cycles_script(tmp, C, cloud_line, tf_line):
             "timers",                                                                                    # cycle 3
             cl("/excavation_area", "area"),                                                              # now 0.2 x 4
             "timers"]                                                                                    # cycle 4
+
+
+# ---- edge rules of the nodes around the sweep (tests/golden/refsrc_edges.npz): the scripts tests/test_ros2_wrappers.py
+# plays through the drop-in executables, played through the reference's own nodes -----------------------------------
+def edges_inputs(scenes):
+    rng = np.random.Generator(np.random.PCG64(5))
+    robot = np.zeros((60_000, 4), np.float32)                       # x y z intensity, the velodyne driver's layout
+    robot[:, :3] = rng.uniform(-20, 20, (robot.shape[0], 3))
+    robot[::97, 1] = np.nan
+    back = np.zeros((40_000, 6), np.float32)                        # x, y, z NOT at 0/4/8: the fields are looked up by name
+    back[:, 1:4] = rng.uniform(-18, 18, (back.shape[0], 3))
+    far = np.zeros((3_000, 4), np.float32)                          # nothing inside the crop box: an empty cloud goes out
+    far[:, :3] = rng.uniform(-20, -1, (far.shape[0], 3))
+    rng = np.random.Generator(np.random.PCG64(6))
+    n = 80_000
+    pts = np.zeros((n, 4), np.float32)
+    pts[:, :2] = rng.uniform(-25, 25, (n, 2))
+    pts[:, 2] = 0.2 * np.sin(0.3 * pts[:, 0]) - 2.0 + np.where(rng.random(n) < 0.15, rng.uniform(0, 2.5, n), 0.0)
+    xyz = scenes.terrain("L", 20_000, seed=3, side=24.0)
+    rec = np.zeros((xyz.shape[0], 8), np.float32)                   # PointXYZRGB: rgb (bit-cast) at byte 16
+    rec[:, :3] = xyz
+    rec[:, 4] = np.full(xyz.shape[0], 0xFFFF0000, np.uint32).view(np.float32)
+    return dict(robot=robot, back=back, far=far, pts=pts, rec=rec)
+
+
+EDGES_DRIVABLE_TF = (np.array([9.25, -3.0, 2.0]), quat_zyx(2.6, 0.1245))
+EDGES_GENERATOR_TF = ((0.5, -0.25, 0.1), quat_zyx(0.3, 0.0))
+EDGES_FILTER_PARAMS = {"voxel_leaf_size": 0.1, "robot_front_range": 12.0, "backhoe_height_range": 6.0}
+EDGES_DRIVABLE_PARAMS = {"grid_resolution": 0.5, "map_width": 60.0, "map_height": 50.0, "min_points_per_cell": 4}
+
+
+def edges_scripts(tmp, E, cloud_line, tf_line):
+    empty = np.zeros((0, 4), np.float32)
+    scan = lambda a=None: cloud_line(tmp, "/four_wheel_robot/filtered_points", E["pts"] if a is None else a, "four_wheel_robot/velodyne", (12, 34), "x:0 y:4 z:8")
+    line = cloud_line(tmp, "/matched_point_cloud", E["rec"], "map", (55, 66), "x:0 y:4 z:8 rgb:16")
+    t, q = EDGES_DRIVABLE_TF
+    gt, gq = EDGES_GENERATOR_TF
+    prm = lambda d: [f"param {k} {'int' if isinstance(v, int) else 'double'} {v!r}" for k, v in d.items()]
+    return {
+        "pointcloud_filter": prm(EDGES_FILTER_PARAMS) + [
+            cloud_line(tmp, "/four_wheel_robot/velodyne_points", E["robot"], "four_wheel_robot/velodyne", (100, 7), "x:0 y:4 z:8"),
+            cloud_line(tmp, "/zx120/velodyne_points", E["back"], "zx120/velodyne", (101, 8), "x:4 y:8 z:12"),
+            cloud_line(tmp, "/zx120/velodyne_points", empty, "zx120/velodyne", (102, 9), "x:0 y:4 z:8"),      # an empty scan
+            cloud_line(tmp, "/four_wheel_robot/velodyne_points", E["far"], "four_wheel_robot/velodyne", (103, 10), "x:0 y:4 z:8")],
+        "calc_drivable_area": prm(EDGES_DRIVABLE_PARAMS) + [
+            scan(),                                                                      # no TF yet: skipped with a warning
+            tf_line("map", "four_wheel_robot/velodyne", t, q), tf_line("map", "four_wheel_robot/base_link", (9.0, -3.0, 0.0), (0, 0, 0, 1)),
+            scan(), scan(empty),
+            tf_line("map", "four_wheel_robot/base_link", (11.0, -2.0, 0.0), (0, 0, 0, 1)),    # the robot moved: the start stays
+            scan()],
+        "excavated_surface_generator_disabled": ["param excavation.enabled bool false", line],
+        "excavated_surface_generator": ["param excavation.depth double 2.5", line, tf_line("map", "zx120/base_link", gt, gq), line,
+                                        "setparam excavation.depth double 1.5", line, "timers", line],
+    }

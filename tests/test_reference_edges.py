@@ -1,0 +1,124 @@
+"""The skip / republish / empty-cloud / parameter-timing rules of the nodes around the sweep, pinned on the reference's
+own sources: tests/golden/refsrc_edges.npz holds what /root/reference/src/{pointcloud_filter, calc_drivable_area,
+excavated_surface_generator}.cpp — unmodified, compiled against the stand-in headers (`make -C oracle ref`,
+tools/make_refsrc_golden.py) — publish and log for the scripts of tests/refsrc_inputs.edges_scripts (fields looked up by
+name, an empty scan, a scan with nothing inside the crop box, no transform yet, the robot moving after the start position
+was set, the generator disabled, a parameter changed between two ticks of the generator's 1 s timer).  CPU: the oracle
+reproduces the payloads.  GPU: the drop-in executables of ros2/src publish the same messages."""
+import hashlib
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import refsrc_inputs as R
+from oracle import binding as O
+from pointcloud_processor_b200 import _abi as A, scenes
+
+GOLDEN = Path(__file__).resolve().parent / "golden"
+EMPTY = hashlib.sha256(b"").hexdigest()
+
+
+def sha(a) -> str:
+    return hashlib.sha256(a if isinstance(a, bytes) else np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def reference():
+    z = np.load(GOLDEN / "refsrc_edges.npz")
+    E = R.edges_inputs(scenes)
+    for k, v in E.items():
+        assert R.digest(v) == str(z[f"{k}_sha256"]), k
+    return {k: json.loads(str(z[k])) for k in ("pointcloud_filter", "calc_drivable_area", "excavated_surface_generator_disabled",
+                                               "excavated_surface_generator")}, E
+
+
+def xyz1(xyz):
+    rec = np.ones((xyz.shape[0], 4), np.float32)          # pcl::PointXYZ on the wire: x y z and 1.0f
+    rec[:, :3] = xyz
+    return rec
+
+
+def test_reference_filter_edges_against_oracle():
+    ref, E = reference()
+    f = ref["pointcloud_filter"]
+    metas, shas = f["metas"], f["payload_sha256"]
+    assert [(m["topic"], m["frame_id"], m["stamp"]) for m in metas] == [
+        ("/four_wheel_robot/filtered_points", "four_wheel_robot/velodyne", [100, 7]), ("/zx120/filtered_points", "zx120/velodyne", [101, 8]),
+        ("/zx120/filtered_points", "zx120/velodyne", [102, 9]), ("/four_wheel_robot/filtered_points", "four_wheel_robot/velodyne", [103, 10])]
+    P = R.EDGES_FILTER_PARAMS
+    robot = O.voxel_grid(O.crop(E["robot"], A.CropBox(0.0, P["robot_front_range"], -10.0, 10.0, -1.5, 10.0))[0], P["voxel_leaf_size"])[0]
+    back_xyz = np.ascontiguousarray(E["back"][:, 1:4])     # the fields are looked up by name: x y z at 4 / 8 / 12
+    back = O.voxel_grid(O.crop(back_xyz, A.CropBox(0.0, 15.0, -10.0, 10.0, -1.5, P["backhoe_height_range"]))[0], P["voxel_leaf_size"])[0]
+    assert (metas[0]["width"], metas[1]["width"]) == (robot.shape[0], back.shape[0]) and robot.shape[0] > 1000 and back.shape[0] > 1000
+    assert shas[0] == sha(xyz1(robot)) and shas[1] == sha(xyz1(back))
+    for k in (2, 3):                                        # an empty scan, and a scan with nothing in the box: an empty cloud IS published
+        assert (metas[k]["width"], metas[k]["height"], metas[k]["bytes"], metas[k]["point_step"]) == (0, 1, 0, 16) and shas[k] == EMPTY
+    assert all(m["fields"] == [["x", 0, 7, 1], ["y", 4, 7, 1], ["z", 8, 7, 1]] for m in metas)
+
+
+def test_reference_drivable_edges_against_oracle():
+    ref, E = reference()
+    d = ref["calc_drivable_area"]
+    t, q = R.EDGES_DRIVABLE_TF
+    P = R.EDGES_DRIVABLE_PARAMS
+    assert [m["topic"] for m in d["metas"]] == ["/occupancy_grid"] * 2            # no TF: nothing; empty scan: nothing
+    for m, s, robot in zip(d["metas"], d["payload_sha256"], ((9.0, -3.0), (11.0, -2.0))):
+        grid = O.drivable_area(E["pts"], t, q, robot, (9.0, -3.0), grid_resolution=P["grid_resolution"], map_width=P["map_width"],
+                               map_height=P["map_height"], min_points_per_cell=P["min_points_per_cell"])      # the start stays where it was set
+        assert s == sha(grid) and (m["width"], m["height"], m["frame_id"]) == (120, 100, "map")
+        assert m["origin"] == [robot[0] - 30.0, robot[1] - 25.0, 0.0] and m["resolution"] == 0.5
+    text = "\n".join(d["log"])
+    assert "Transform from four_wheel_robot/velodyne to map not available yet" in text and "Received empty point cloud" in text
+    assert text.count("Start position set at (9.00, -3.00)") == 1 and "Start position set at (11.00" not in text
+
+
+def test_reference_generator_edges_against_oracle():
+    ref, E = reference()
+    rec = E["rec"]
+    off = ref["excavated_surface_generator_disabled"]
+    assert [m["topic"] for m in off["metas"]] == ["/excavated_terrain"] and off["payload_sha256"] == [sha(rec)]     # republished untouched (:264-267)
+    assert off["metas"][0]["stamp"] == [55, 66]
+    g = ref["excavated_surface_generator"]
+    clouds = [(m, s) for m, s in zip(g["metas"], g["payload_sha256"]) if m["topic"] != "/excavation_markers"]
+    assert [m["topic"] for m, _ in clouds] == ["/excavated_terrain"] + ["/excavated_terrain", "/excavation_area"] * 3
+    assert clouds[0][1] == sha(rec) and any("Could not get zx120 transform" in l for l in g["log"])                  # no TF: republished with a warning
+    t, q = R.EDGES_GENERATOR_TF
+    for depth, k in ((2.5, 1), (2.5, 3), (1.5, 5)):          # the changed depth shows only after the 1 s timer has fired (:69-71)
+        prm = A.excavation_params(depth=depth)
+        ns, na = A.excavation_counts(prm)
+        terrain, area, info = O.excavate(rec[:, :3], np.ascontiguousarray(rec[:, 4]).view(np.uint32), np.array(t), np.array(q), prm, ns, na)
+        (mt, _), (ma, _) = clouds[k], clouds[k + 1]
+        assert (mt["width"], ma["width"]) == (terrain.shape[0], area.shape[0]) and int(info.n_kept) < rec.shape[0]
+        assert (mt["frame_id"], mt["stamp"], ma["frame_id"], ma["stamp"], mt["point_step"]) == ("map", [55, 66], "map", [55, 66], 32)
+    assert clouds[1][1] == clouds[3][1] and clouds[3][1] != clouds[5][1]
+
+
+def comparable(m):
+    return {k: v for k, v in m.items() if k != "is_dense"}     # the stand-in's fromROSMsg carries the input's flag through
+
+
+@pytest.mark.gpu
+def test_drop_in_executables_apply_the_reference_edge_rules(tmp_path):
+    """One assertion at the end lists every difference found."""
+    from test_ros2_wrappers import cloud_line, play, tf_line
+    ref, E = reference()
+    diffs = []
+    scripts = R.edges_scripts(tmp_path, E, cloud_line, tf_line)
+    for name in ("pointcloud_filter", "calc_drivable_area", "excavated_surface_generator_disabled", "excavated_surface_generator"):
+        msgs, log = play(name.replace("_disabled", ""), scripts[name], tmp_path)
+        want = [(m, s) for m, s in zip(ref[name]["metas"], ref[name]["payload_sha256"]) if m["topic"] != "/excavation_markers"]
+        got = [(m, sha(b)) for m, b in msgs if m["topic"] != "/excavation_markers"]
+        if [m["topic"] for m, _ in got] != [m["topic"] for m, _ in want]:
+            diffs.append((name, "topics", [m["topic"] for m, _ in got]))
+            continue
+        for k, ((gm, gs), (wm, ws)) in enumerate(zip(got, want)):
+            if comparable(gm) != comparable(wm):
+                diffs.append((name, k, "meta", gm, wm))
+            generated = name == "excavated_surface_generator" and k >= 1      # generated heights: one ulp apart at most, compared elsewhere
+            if gs != ws and not generated:
+                diffs.append((name, k, "payload"))
+        for line in ref[name]["log"]:
+            if line.startswith(("WARN", "INFO Start position", "INFO Excavation processed")) and line not in log:
+                diffs.append((name, "log", line))
+    assert not diffs, diffs

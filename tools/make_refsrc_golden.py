@@ -189,6 +189,24 @@ def cycles_case():
     print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
 
 
+def edges_case():
+    """tests/golden/refsrc_edges.npz: the skip / republish / empty-cloud / parameter-timing rules of the nodes around the
+    sweep, as the reference's own sources apply them to the scripts of tests/refsrc_inputs.edges_scripts: per script the
+    published messages' metadata, a SHA-256 of every payload, and the log."""
+    import hashlib
+    sys.path.insert(0, os.fspath(ROOT / "tests"))
+    import refsrc_inputs as R
+    E = R.edges_inputs(scenes)
+    out = {f"{k}_sha256": R.digest(v) for k, v in E.items()}
+    for name in ("pointcloud_filter", "calc_drivable_area", "excavated_surface_generator_disabled", "excavated_surface_generator"):
+        msgs, log = play(name.replace("_disabled", ""), lambda tmp: R.edges_scripts(tmp, E, cloud_line, tf_line)[name])
+        out[name] = json.dumps(dict(metas=[m for m, _ in msgs], payload_sha256=[hashlib.sha256(b).hexdigest() for _, b in msgs], log=log.splitlines()))
+        print(name, [(m["topic"], m.get("width")) for m, _ in msgs])
+    path = ROOT / "tests" / "golden" / "refsrc_edges.npz"
+    np.savez_compressed(path, **out)
+    print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
+
+
 def main():
     if not Path("/root/reference/src/virtual_lidar.cpp").exists():
         raise SystemExit("needs /root/reference")
@@ -209,4 +227,5 @@ def main():
 if __name__ == "__main__":
     main()
     cycles_case()
+    edges_case()
     other_nodes()
