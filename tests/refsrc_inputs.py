@@ -178,3 +178,28 @@ def edges_scripts(tmp, E, cloud_line, tf_line):
         "excavated_surface_generator": ["param excavation.depth double 2.5", line, tf_line("map", "zx120/base_link", gt, gq), line,
                                         "setparam excavation.depth double 1.5", line, "timers", line],
     }
+
+
+# ---- virtual_lidar's guards (tests/golden/refsrc_vl_edges.npz): empty messages, stale trees, a missing transform -----
+def vl_edges_inputs(scenes):
+    def rec(xyz):
+        r = np.zeros((xyz.shape[0], 8), np.float32)
+        r[:, :3] = xyz[:, :3]
+        return r
+    area = rec(scenes.excavation_area("rect", 0.05)[0])
+    return dict(area=area, terrain=rec(scenes.terrain("rect", 30_000, seed=23, side=24.0)), observed=rec(area[::7, :3].copy()))
+
+
+def vl_edges_script(tmp, V, cloud_line, tf_line):
+    empty = np.zeros((0, 8), np.float32)
+    cl = lambda topic, a: cloud_line(tmp, topic, a, "map", (10, 20), "x:0 y:4 z:8 rgb:16")
+    return ["param num_candidates int 49", "param vertical_layers int 5",
+            cl("/excavation_area", V["area"]), tf_line("map", "zx120/base_link", (0.0, 0.0, 0.0), (0, 0, 0, 1)),
+            "timers",                                              # no terrain message at all: the guard holds (:455), nothing
+            cl("/excavated_terrain", empty), "timers",             # cycle 0: a cloud but no tree: every gated ray visible, ground height 0
+            cl("/excavated_terrain", V["terrain"]), "timers",      # cycle 1
+            cl("/excavated_terrain", empty), "timers",             # cycle 2: the tree stays, ground heights go to 0
+            cl("/zx120/filtered_points", V["observed"]), "timers", # cycle 3: the observed-cloud branch of the fixed sensor
+            cl("/zx120/filtered_points", empty), "timers",         # cycle 4: an empty observed cloud: back to the ray path
+            cl("/excavation_area", empty), "timers",               # cycle 5: an empty area message leaves the grid in place (:168)
+            "notf map zx120/base_link", "timers"]                  # no transform: nothing

@@ -140,10 +140,45 @@ def test_edge_and_cycle_fixtures_are_what_the_reference_source_produces_today():
         strip = lambda metas: [{k: v for k, v in m.items() if k != "stamp" or m["topic"] != "/excavation_markers"} for m in metas]
         assert strip([m for m, _ in msgs]) == strip(want["metas"]) and [sha(b) for _, b in msgs] == want["payload_sha256"], name
         assert log.splitlines() == want["log"], name
-    z = np.load(GOLDEN / "refsrc_cycles.npz")
-    C = R.cycles_inputs(scenes)
-    cyc = G.parse_cycles(*G.play("virtual_lidar", lambda tmp: R.cycles_script(tmp, C, G.cloud_line, G.tf_line)))
-    assert len(cyc) == int(z["n_cycles"])
-    for k, c in enumerate(cyc):
-        for key, v in c.items():
-            assert np.array_equal(np.asarray(v), z[f"c{k}_{key}"]), (k, key)
+    for fixture, inputs, script in (("refsrc_cycles.npz", R.cycles_inputs, R.cycles_script), ("refsrc_vl_edges.npz", R.vl_edges_inputs, R.vl_edges_script)):
+        z = np.load(GOLDEN / fixture)
+        C = inputs(scenes)
+        cyc = G.parse_cycles(*G.play("virtual_lidar", lambda tmp: script(tmp, C, G.cloud_line, G.tf_line)))
+        assert len(cyc) == int(z["n_cycles"])
+        for k, c in enumerate(cyc):
+            for key, v in c.items():
+                assert np.array_equal(np.asarray(v), z[f"c{k}_{key}"]), (fixture, k, key)
+
+
+def test_oracle_reproduces_the_reference_nodes_guards():
+    """tests/golden/refsrc_vl_edges.npz, six cycles of the reference's virtual_lidar.cpp around its guards: an empty terrain
+    message satisfies `!terrain_cloud_` (:455) while no tree exists (every gated ray visible, :721 / :727; ground height 0,
+    :601); a later empty one keeps the tree but zeroes the heights; an empty observed cloud sends the fixed sensor back to
+    the ray path (:719); an empty area message leaves the grid in place (:168); no terrain message or no transform: no
+    cycle.  tests/test_nodes_gpu.py holds the CUDA node core to the same rules."""
+    from test_reference_source import check_against_fixture, cycle_view
+    z = np.load(GOLDEN / "refsrc_vl_edges.npz")
+    V = R.vl_edges_inputs(scenes)
+    for k, v in V.items():
+        assert R.digest(v) == str(z[f"{k}_sha256"]), k
+    topics = json.loads(str(z["topics"]))
+    assert int(z["n_cycles"]) == 6 and topics.count("/optimal_mobile_lidar_position") == 6      # eight timer ticks, six cycles
+    assert topics[0] == "/excavation_grid_visualization" and topics[1] == "/optimal_mobile_lidar_position"   # the first tick published nothing
+    area = V["area"][:, :3]
+    cells, bounds = O.generate_cells(area, O.compute_normals(area, 1.5), 0.1, 5, 1.5)
+    flags = np.zeros(cells.size, np.uint8)
+    fixed = np.zeros(1, A.POSE_DTYPE)
+    fixed["x"], fixed["y"], fixed["z"], fixed["pitch"] = 0.4, 0.5, 3.5, -np.pi / 6
+    tree, no_cloud = O.Index(V["terrain"][:, :3], O.GRID), O.Index(np.zeros((0, 3), np.float32), O.GRID)
+    observed = O.Index(V["observed"][:, :3], O.GRID)
+    #        tree the rays are tested against, cloud the ground heights come from, observed cloud
+    plan = [(None, no_cloud, None), (tree, tree, None), (tree, no_cloud, None), (tree, no_cloud, observed), (tree, no_cloud, None), (tree, no_cloud, None)]
+    for k, (rays, ground, obs) in enumerate(plan):
+        cands = O.generate_candidates(ground, bounds, fixed, 49, 3.0, 1.1)
+        ref = O.sweep(rays, obs, cells, A.default_params(), fixed, cands, flags_inout=flags)
+        b = cands[ref["best_index"]]
+        check_against_fixture(cycle_view(z, k), cells, cands, (b["x"], b["y"], b["z"]), ref["best_score"], ref["fixed_total"], flags)
+        if ground is no_cloud:
+            assert np.all(cands["z"] == 1.1)
+        if rays is None:
+            assert ref["counters"]["rays_visible"] == ref["counters"]["rays_gated_in"] > 0

@@ -189,6 +189,25 @@ def cycles_case():
     print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
 
 
+def vl_edges_case():
+    """tests/golden/refsrc_vl_edges.npz: virtual_lidar's guards — empty terrain / observed / area messages, the tree that
+    outlives its cloud, a missing transform — as six cycles of one process (and two timer ticks that publish nothing)."""
+    sys.path.insert(0, os.fspath(ROOT / "tests"))
+    import refsrc_inputs as R
+    V = R.vl_edges_inputs(scenes)
+    msgs, log = play("virtual_lidar", lambda tmp: R.vl_edges_script(tmp, V, cloud_line, tf_line))
+    cyc = parse_cycles(msgs, log)
+    assert len(cyc) == 6, len(cyc)
+    flat = {f"c{k}_{name}": v for k, c in enumerate(cyc) for name, v in c.items()}
+    path = ROOT / "tests" / "golden" / "refsrc_vl_edges.npz"
+    np.savez_compressed(path, n_cycles=len(cyc), log=log, topics=json.dumps([m["topic"] for m, _ in msgs]),
+                        **{f"{k}_sha256": R.digest(v) for k, v in V.items()}, **flat)
+    for k, c in enumerate(cyc):
+        print("vl edge cycle", k, "cells", c["cells_xyz"].shape[0], "candidates", c["cands_xyz"].shape[0], "cand z", np.unique(c["cands_xyz"][:, 2])[:3],
+              "score", c["best_score_2dp"], "fixed", c["fixed_total_2dp"], "colours", c["colour_counts"].tolist())
+    print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
+
+
 def edges_case():
     """tests/golden/refsrc_edges.npz: the skip / republish / empty-cloud / parameter-timing rules of the nodes around the
     sweep, as the reference's own sources apply them to the scripts of tests/refsrc_inputs.edges_scripts: per script the
@@ -227,5 +246,6 @@ def main():
 if __name__ == "__main__":
     main()
     cycles_case()
+    vl_edges_case()
     edges_case()
     other_nodes()
