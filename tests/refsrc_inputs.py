@@ -203,3 +203,46 @@ def vl_edges_script(tmp, V, cloud_line, tf_line):
             cl("/zx120/filtered_points", empty), "timers",         # cycle 4: an empty observed cloud: back to the ray path
             cl("/excavation_area", empty), "timers",               # cycle 5: an empty area message leaves the grid in place (:168)
             "notf map zx120/base_link", "timers"]                  # no transform: nothing
+
+
+# ---- non-default parameters of the nodes around the sweep (tests/golden/refsrc_variants.npz) -------------------------
+VARIANT_GENERATORS = {
+    "L": (dict(depth=0.7, slope_angle=60.0, offset_x=3.5, offset_y=0.5, point_density=0.08, terrain_search_radius=0.6, l_shape_enabled=True,
+               arm1_length=2.4, arm1_width=1.0, arm2_length=1.6, arm2_width=1.4),
+          ((0.2, 0.3, 0.05), (0.0, 0.0, float(np.sin(0.2)), float(np.cos(0.2))))),
+    "rect": (dict(depth=1.3, slope_angle=82.0, offset_x=4.5, offset_y=-0.5, point_density=0.06, l_shape_enabled=False, width=1.5, length=2.2),
+             ((-0.3, 0.1, 0.0), (0.0, 0.0, float(np.sin(-0.15)), float(np.cos(-0.15))))),
+}
+VARIANT_DRIVABLE = dict(grid_resolution=0.25, map_width=40.0, map_height=30.0, max_gradient=0.5, min_points_per_cell=2, start_clear_radius=5.0)
+VARIANT_FILTER = dict(voxel_leaf_size=0.05, robot_front_range=8.0, robot_side_range=6.0, robot_height_range=4.0,
+                      backhoe_front_range=10.0, backhoe_side_range=7.0, backhoe_height_range=3.0)
+
+
+def variant_cloud(name):
+    """Rolling ground over the place the pit of VARIANT_GENERATORS[name] will be carved, PointXYZRGB records."""
+    rng = np.random.Generator(np.random.PCG64(41 if name == "L" else 42))
+    n = 7_000
+    r = np.zeros((n, 8), np.float32)
+    r[:, :2] = rng.uniform(-1.0, 8.0, (n, 2)) + np.array([0.0, -3.5])
+    r[:, 2] = 0.15 * np.sin(0.4 * r[:, 0]) * np.cos(0.3 * r[:, 1]) + rng.normal(0, 0.01, n) - rng.uniform(0, 1.5, n) * (rng.random(n) < 0.3)
+    r[:, 4] = np.where(rng.random(n) < 0.5, np.uint32(0xFFFF0000), np.uint32(0xFF0000FF)).astype(np.uint32).view(np.float32)
+    return r
+
+
+def variants_scripts(tmp, cloud_line, tf_line):
+    prm = lambda d, pre="": [f"param {pre}{k} {'bool' if isinstance(v, bool) else 'int' if isinstance(v, int) else 'double'} "
+                             f"{str(v).lower() if isinstance(v, bool) else repr(v)}" for k, v in d.items()]
+    scans = filter_scans()
+    scan, (t, q), robot = drivable_scan()
+    out = {
+        "pointcloud_filter": prm(VARIANT_FILTER) + [
+            cloud_line(tmp, "/four_wheel_robot/velodyne_points", scans["robot"], "four_wheel_robot/velodyne", (100, 7), "x:0 y:4 z:8 intensity:12"),
+            cloud_line(tmp, "/zx120/velodyne_points", scans["backhoe"], "zx120/velodyne", (101, 8), "x:0 y:4 z:8 intensity:12")],
+        "calc_drivable_area": prm(VARIANT_DRIVABLE) + [
+            tf_line("map", "four_wheel_robot/velodyne", t, q), tf_line("map", "four_wheel_robot/base_link", (*robot, 0.0), (0, 0, 0, 1)),
+            cloud_line(tmp, "/four_wheel_robot/filtered_points", scan, "four_wheel_robot/velodyne", (5, 6), "x:0 y:4 z:8 intensity:12")],
+    }
+    for name, (p, (bt, bq)) in VARIANT_GENERATORS.items():
+        out[f"excavated_surface_generator_{name}"] = prm(p, "excavation.") + [
+            tf_line("map", "zx120/base_link", bt, bq), cloud_line(tmp, "/matched_point_cloud", variant_cloud(name), "map", (55, 66), "x:0 y:4 z:8 rgb:16")]
+    return out

@@ -182,3 +182,47 @@ def test_oracle_reproduces_the_reference_nodes_guards():
             assert np.all(cands["z"] == 1.1)
         if rays is None:
             assert ref["counters"]["rays_visible"] == ref["counters"]["rays_gated_in"] > 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Non-default parameters (tests/golden/refsrc_variants.npz): the reference's own nodes with other ranges, leaves,
+# resolutions, gradients, pit shapes and dimensions, a rotated base — against the oracle.
+def variants():
+    return np.load(GOLDEN / "refsrc_variants.npz")
+
+
+def test_oracle_reproduces_the_reference_filter_with_other_parameters():
+    z, scans, P = variants(), R.filter_scans(), R.VARIANT_FILTER
+    for who, topic in (("robot", "four_wheel_robot"), ("backhoe", "zx120")):
+        box = A.CropBox(0.0, P[f"{who}_front_range"], -P[f"{who}_side_range"], P[f"{who}_side_range"], -1.5, P[f"{who}_height_range"])
+        got = O.voxel_grid(O.crop(scans[who], box)[0], P["voxel_leaf_size"])[0]
+        key = f"pointcloud_filter__{topic}__filtered_points"
+        meta = json.loads(str(z[key + "__meta"]))
+        assert meta["width"] == got.shape[0] > 300 and z[key].tobytes() == xyz1(got).tobytes(), who
+
+
+def test_oracle_reproduces_the_reference_drivable_grid_with_other_parameters():
+    z, P = variants(), R.VARIANT_DRIVABLE
+    scan, (t, q), robot = R.drivable_scan()
+    grid = O.drivable_area(scan, t, q, robot, robot, grid_resolution=P["grid_resolution"], map_width=P["map_width"], map_height=P["map_height"],
+                           max_gradient=P["max_gradient"], min_points_per_cell=P["min_points_per_cell"], start_clear_radius=P["start_clear_radius"])
+    meta = json.loads(str(z["calc_drivable_area__occupancy_grid__meta"]))
+    assert grid.shape == (meta["height"], meta["width"]) == (120, 160) and meta["resolution"] == 0.25
+    assert np.array_equal(grid.ravel(), z["calc_drivable_area__occupancy_grid"].view(np.int8)) and set(np.unique(grid)) == {-1, 0, 100}
+
+
+@pytest.mark.parametrize("name", ["L", "rect"])
+def test_oracle_reproduces_the_reference_generator_with_other_parameters(name):
+    from test_reference_source import check_generator
+    z = variants()
+    P, (bt, bq) = R.VARIANT_GENERATORS[name]
+    rec = R.variant_cloud(name)
+    kw = {("slope_angle_deg" if k == "slope_angle" else k): (int(v) if isinstance(v, bool) else v) for k, v in P.items()}
+    prm = A.excavation_params(**kw)
+    ns, na = A.excavation_counts(prm)
+    terrain, area, info = O.excavate(rec[:, :3], np.ascontiguousarray(rec[:, 4]).view(np.uint32), np.array(bt), np.array(bq), prm, ns, na)
+    pre = f"excavated_surface_generator_{name}__"
+    view = {"terrain": z[pre + "excavated_terrain"].reshape(-1, 32), "area": z[pre + "excavation_area"].reshape(-1, 32),
+            "terrain_meta": z[pre + "excavated_terrain__meta"], "area_meta": z[pre + "excavation_area__meta"]}
+    check_generator(view, terrain, area, int(info.n_kept))
+    assert int(info.n_kept) < rec.shape[0] - 50               # the pit lies inside the cloud: points were carved

@@ -208,6 +208,30 @@ def vl_edges_case():
     print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
 
 
+def variants_case():
+    """tests/golden/refsrc_variants.npz: the nodes around the sweep with non-default parameters (tests/refsrc_inputs.py
+    VARIANT_*): filter ranges and leaf, drivable grid resolution / gradient / clear radius, both pit shapes with other
+    dimensions, slopes, densities, offsets and a rotated base."""
+    sys.path.insert(0, os.fspath(ROOT / "tests"))
+    import refsrc_inputs as R
+    out = {}
+    names = ["pointcloud_filter", "calc_drivable_area", "excavated_surface_generator_L", "excavated_surface_generator_rect"]
+    for name in names:
+        node = name if not name.startswith("excavated") else "excavated_surface_generator"
+        msgs, log = play(node, lambda tmp: R.variants_scripts(tmp, cloud_line, tf_line)[name])
+        for m, b in msgs:
+            if m["topic"] == "/excavation_markers":
+                continue
+            key = f"{name}{m['topic'].replace('/', '__')}"
+            assert key not in out, key
+            out[key] = np.frombuffer(b, np.uint8).copy()
+            out[key + "__meta"] = json.dumps(m)
+        print(name, [(m["topic"], m.get("width")) for m, _ in msgs])
+    path = ROOT / "tests" / "golden" / "refsrc_variants.npz"
+    np.savez_compressed(path, **out)
+    print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
+
+
 def edges_case():
     """tests/golden/refsrc_edges.npz: the skip / republish / empty-cloud / parameter-timing rules of the nodes around the
     sweep, as the reference's own sources apply them to the scripts of tests/refsrc_inputs.edges_scripts: per script the
@@ -247,5 +271,6 @@ if __name__ == "__main__":
     main()
     cycles_case()
     vl_edges_case()
+    variants_case()
     edges_case()
     other_nodes()
