@@ -226,3 +226,31 @@ def test_oracle_reproduces_the_reference_generator_with_other_parameters(name):
             "terrain_meta": z[pre + "excavated_terrain__meta"], "area_meta": z[pre + "excavation_area__meta"]}
     check_generator(view, terrain, area, int(info.n_kept))
     assert int(info.n_kept) < rec.shape[0] - 50               # the pit lies inside the cloud: points were carved
+
+
+def test_oracle_reproduces_the_reference_source_on_baseline_config_1():
+    """BASELINE.json configs[0] — the reference's own CPU-runnable case — through the reference's own virtual_lidar.cpp
+    (tests/golden/refsrc_cfg1.npz: 50 k terrain points, 228 poses of the 16 x 16 lattice, 14 449 cells = 3.3 M rays): the
+    oracle reproduces every cell, pose and colour, the optimum and both totals.  tests/test_sweep_gpu.py compares the CUDA
+    sweep with the oracle on this configuration in full (test_parity_config1_full)."""
+    from test_reference_source import colours_of, counts_of
+    z = np.load(GOLDEN / "refsrc_cfg1.npz")
+    cfg = scenes.CONFIGS["cfg1"]
+    terrain, area = scenes.terrain(cfg["shape"], cfg["n"], cfg["seed"], cfg["side"]), scenes.excavation_area(cfg["shape"], 0.05)[0]
+    rec = lambda a: np.concatenate([a[:, :3], np.zeros((a.shape[0], 5), np.float32)], axis=1)
+    assert R.digest(rec(terrain)) == str(z["terrain_sha256"]) and R.digest(rec(area)) == str(z["area_sha256"])
+    cells, bounds = O.generate_cells(area, O.compute_normals(area, 1.5), float(z["grid_resolution"]), int(z["vertical_layers"]), 1.5)
+    fixed = np.zeros(1, A.POSE_DTYPE)
+    fixed["x"], fixed["y"], fixed["z"], fixed["pitch"] = 0.4, 0.5, 3.5, -np.pi / 6
+    tix = O.Index(terrain, O.GRID)
+    cands = O.generate_candidates(tix, bounds, fixed, int(z["num_candidates"]), 3.0, 1.1)
+    assert cells.size == z["cells_xyz"].shape[0] == 14449 and cands.size == z["cands_xyz"].shape[0] == 228
+    for a, k in enumerate("xyz"):
+        assert np.array_equal(cells[k], z["cells_xyz"][:, a]) and np.array_equal(cands[k], z["cands_xyz"][:, a]), k
+    ref = O.sweep(tix, None, cells, A.default_params(), fixed, cands, want_mask=False)        # one thread: the stale-flag rule is sequential
+    b = cands[ref["best_index"]]
+    assert [b["x"], b["y"], b["z"]] == list(z["best_xyz"])
+    assert f"{ref['best_score']:.2f}" == f"{float(z['best_score_2dp']):.2f}" and f"{ref['fixed_total']:.2f}" == f"{float(z['fixed_total_2dp']):.2f}"
+    assert np.array_equal((colours_of(ref["flags"]) @ np.array([4, 2, 1])).astype(np.uint8), z["cell_rgb_code"])
+    assert [counts_of(ref["flags"], False), counts_of(ref["flags"], True)] == z["colour_counts"].tolist()
+    assert ref["counters"]["rays"] == 14449 * 228

@@ -63,9 +63,11 @@ def tf_line(target, source, t, q):
     return f"tf {target} {source} " + " ".join(repr(float(v)) for v in (*t, *q))
 
 
-def run_reference(area, terrain, observed, num_candidates, layers, base):
+def run_reference(area, terrain, observed, num_candidates, layers, base, res=None):
     def lines(tmp):
         out = [f"param num_candidates int {num_candidates}", f"param vertical_layers int {layers}"]
+        if res is not None:
+            out.append(f"param grid_resolution double {res!r}")
         for topic, cloud in (("/excavation_area", area), ("/excavated_terrain", terrain), ("/zx120/filtered_points", observed)):
             if cloud is not None:
                 out.append(cloud_line(tmp, topic, cloud, "map", (10, 20), "x:0 y:4 z:8 rgb:16"))
@@ -232,6 +234,27 @@ def variants_case():
     print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
 
 
+def cfg1_case():
+    """tests/golden/refsrc_cfg1.npz: BASELINE.json configs[0] — the reference's own CPU-runnable case (L-shaped pit, 50 k
+    terrain points, 16 x 16 requested poses, 16 x 900 rays per pose) — through the reference's own virtual_lidar.cpp: the
+    scene of scenes.CONFIGS["cfg1"], the node's own lattices (grid_resolution 0.05, vertical_layers 18: every valid cell,
+    where bench scenes truncate to exactly 14 400)."""
+    cfg = scenes.CONFIGS["cfg1"]
+    layers = scenes.LAYERS_FOUND["cfg1"]
+    terrain = records(scenes.terrain(cfg["shape"], cfg["n"], cfg["seed"], cfg["side"]))
+    area = records(scenes.excavation_area(cfg["shape"], 0.05)[0])
+    out = parse(*run_reference(area, terrain, None, cfg["px"] * cfg["px"], layers, (0.0, 0.0, 0.0), res=cfg["res"]))
+    out.pop("log")
+    path = ROOT / "tests" / "golden" / "refsrc_cfg1.npz"
+    sys.path.insert(0, os.fspath(ROOT / "tests"))
+    import refsrc_inputs as R
+    np.savez_compressed(path, num_candidates=cfg["px"] * cfg["px"], vertical_layers=layers, grid_resolution=cfg["res"],
+                        terrain_sha256=R.digest(terrain), area_sha256=R.digest(area),
+                        cell_rgb_code=(out.pop("cell_rgb") @ np.array([4, 2, 1])).astype(np.uint8), cells_xyz=out.pop("cells_xyz").astype(np.float64), **out)
+    print("cfg1 cells", np.load(path)["cells_xyz"].shape[0], "candidates", out["cands_xyz"].shape[0], "best", out["best_xyz"], "score", out["best_score_2dp"],
+          "fixed", out["fixed_total_2dp"], "colours", out["colour_counts"].tolist(), "->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
+
+
 def edges_case():
     """tests/golden/refsrc_edges.npz: the skip / republish / empty-cloud / parameter-timing rules of the nodes around the
     sweep, as the reference's own sources apply them to the scripts of tests/refsrc_inputs.edges_scripts: per script the
@@ -271,6 +294,7 @@ if __name__ == "__main__":
     main()
     cycles_case()
     vl_edges_case()
+    cfg1_case()
     variants_case()
     edges_case()
     other_nodes()
