@@ -4,7 +4,9 @@ excavated_surface_generator}.cpp — unmodified, compiled against the stand-in h
 tools/make_refsrc_golden.py) — publish and log for the scripts of tests/refsrc_inputs.edges_scripts (fields looked up by
 name, an empty scan, a scan with nothing inside the crop box, no transform yet, the robot moving after the start position
 was set, the generator disabled, a parameter changed between two ticks of the generator's 1 s timer).  CPU: the oracle
-reproduces the payloads.  GPU: the drop-in executables of ros2/src publish the same messages."""
+reproduces the payloads.  GPU: the drop-in executables of ros2/src publish the same messages.  Further down, CPU only:
+virtual_lidar.cpp around its guards (refsrc_vl_edges.npz), the nodes with non-default parameters (refsrc_variants.npz)
+and BASELINE.json's configs[0] and configs[1] through the reference's own virtual_lidar.cpp (refsrc_cfg1.npz, refsrc_cfg2.npz)."""
 import hashlib
 import json
 from pathlib import Path
@@ -228,23 +230,27 @@ def test_oracle_reproduces_the_reference_generator_with_other_parameters(name):
     assert int(info.n_kept) < rec.shape[0] - 50               # the pit lies inside the cloud: points were carved
 
 
-def test_oracle_reproduces_the_reference_source_on_baseline_config_1():
-    """BASELINE.json configs[0] — the reference's own CPU-runnable case — through the reference's own virtual_lidar.cpp
-    (tests/golden/refsrc_cfg1.npz: 50 k terrain points, 228 poses of the 16 x 16 lattice, 14 449 cells = 3.3 M rays): the
-    oracle reproduces every cell, pose and colour, the optimum and both totals.  tests/test_sweep_gpu.py compares the CUDA
-    sweep with the oracle on this configuration in full (test_parity_config1_full)."""
+@pytest.mark.parametrize("name,n_cells,n_cands", [("cfg1", 14449, 228), ("cfg2", 57685, 32)])
+def test_oracle_reproduces_the_reference_source_on_baseline_configs(name, n_cells, n_cands):
+    """BASELINE.json configurations through the reference's own virtual_lidar.cpp (tests/golden/refsrc_cfg{1,2}.npz).
+    cfg1 = configs[0], the reference's own CPU-runnable case, in full: 50 k terrain points, 228 poses of the 16 x 16
+    lattice, 14 449 cells = 3.3 M rays.  cfg2 = configs[1], the configuration the metric is quoted on: 200 k points, its
+    57 685-cell lattice (0.025 m x 74 layers), 32 poses of a 6 x 6 lattice = 1.8 M rays.  The oracle reproduces every cell,
+    pose and colour, the optimum and both totals; tests/test_sweep_gpu.py compares the CUDA sweep with the oracle on both
+    configurations in full (test_parity_config1_full, test_parity_config2_full)."""
     from test_reference_source import colours_of, counts_of
-    z = np.load(GOLDEN / "refsrc_cfg1.npz")
-    cfg = scenes.CONFIGS["cfg1"]
+    z = np.load(GOLDEN / f"refsrc_{name}.npz")
+    cfg = scenes.CONFIGS[name]
     terrain, area = scenes.terrain(cfg["shape"], cfg["n"], cfg["seed"], cfg["side"]), scenes.excavation_area(cfg["shape"], 0.05)[0]
     rec = lambda a: np.concatenate([a[:, :3], np.zeros((a.shape[0], 5), np.float32)], axis=1)
     assert R.digest(rec(terrain)) == str(z["terrain_sha256"]) and R.digest(rec(area)) == str(z["area_sha256"])
+    assert (float(z["grid_resolution"]), int(z["vertical_layers"])) == (cfg["res"], scenes.LAYERS_FOUND[name])
     cells, bounds = O.generate_cells(area, O.compute_normals(area, 1.5), float(z["grid_resolution"]), int(z["vertical_layers"]), 1.5)
     fixed = np.zeros(1, A.POSE_DTYPE)
     fixed["x"], fixed["y"], fixed["z"], fixed["pitch"] = 0.4, 0.5, 3.5, -np.pi / 6
     tix = O.Index(terrain, O.GRID)
     cands = O.generate_candidates(tix, bounds, fixed, int(z["num_candidates"]), 3.0, 1.1)
-    assert cells.size == z["cells_xyz"].shape[0] == 14449 and cands.size == z["cands_xyz"].shape[0] == 228
+    assert cells.size == z["cells_xyz"].shape[0] == n_cells and cands.size == z["cands_xyz"].shape[0] == n_cands
     for a, k in enumerate("xyz"):
         assert np.array_equal(cells[k], z["cells_xyz"][:, a]) and np.array_equal(cands[k], z["cands_xyz"][:, a]), k
     ref = O.sweep(tix, None, cells, A.default_params(), fixed, cands, want_mask=False)        # one thread: the stale-flag rule is sequential
@@ -253,4 +259,4 @@ def test_oracle_reproduces_the_reference_source_on_baseline_config_1():
     assert f"{ref['best_score']:.2f}" == f"{float(z['best_score_2dp']):.2f}" and f"{ref['fixed_total']:.2f}" == f"{float(z['fixed_total_2dp']):.2f}"
     assert np.array_equal((colours_of(ref["flags"]) @ np.array([4, 2, 1])).astype(np.uint8), z["cell_rgb_code"])
     assert [counts_of(ref["flags"], False), counts_of(ref["flags"], True)] == z["colour_counts"].tolist()
-    assert ref["counters"]["rays"] == 14449 * 228
+    assert ref["counters"]["rays"] == n_cells * n_cands

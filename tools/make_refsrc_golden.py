@@ -234,24 +234,26 @@ def variants_case():
     print("->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
 
 
-def cfg1_case():
-    """tests/golden/refsrc_cfg1.npz: BASELINE.json configs[0] — the reference's own CPU-runnable case (L-shaped pit, 50 k
-    terrain points, 16 x 16 requested poses, 16 x 900 rays per pose) — through the reference's own virtual_lidar.cpp: the
-    scene of scenes.CONFIGS["cfg1"], the node's own lattices (grid_resolution 0.05, vertical_layers 18: every valid cell,
-    where bench scenes truncate to exactly 14 400)."""
-    cfg = scenes.CONFIGS["cfg1"]
-    layers = scenes.LAYERS_FOUND["cfg1"]
+def config_case(name, num_candidates=None):
+    """tests/golden/refsrc_<name>.npz: a BASELINE.json configuration through the reference's own virtual_lidar.cpp — the
+    scene of scenes.CONFIGS[name] with the node's own lattices (every valid cell, where bench scenes truncate to exactly
+    V x H).  cfg1 (configs[0], the reference's own CPU-runnable case: L-shaped pit, 50 k points, 16 x 16 requested poses,
+    16 x 900 rays per pose) runs in full; cfg2 (configs[1], the configuration the metric is quoted on: rectangular pit,
+    200 k points, 32 x 1800 rays per pose) with 36 requested poses of its first height layer."""
+    cfg = scenes.CONFIGS[name]
+    layers = scenes.LAYERS_FOUND[name]
+    num = num_candidates or cfg["px"] * cfg["px"]
     terrain = records(scenes.terrain(cfg["shape"], cfg["n"], cfg["seed"], cfg["side"]))
     area = records(scenes.excavation_area(cfg["shape"], 0.05)[0])
-    out = parse(*run_reference(area, terrain, None, cfg["px"] * cfg["px"], layers, (0.0, 0.0, 0.0), res=cfg["res"]))
+    out = parse(*run_reference(area, terrain, None, num, layers, (0.0, 0.0, 0.0), res=cfg["res"]))
     out.pop("log")
-    path = ROOT / "tests" / "golden" / "refsrc_cfg1.npz"
+    path = ROOT / "tests" / "golden" / f"refsrc_{name}.npz"
     sys.path.insert(0, os.fspath(ROOT / "tests"))
     import refsrc_inputs as R
-    np.savez_compressed(path, num_candidates=cfg["px"] * cfg["px"], vertical_layers=layers, grid_resolution=cfg["res"],
+    np.savez_compressed(path, num_candidates=num, vertical_layers=layers, grid_resolution=cfg["res"],
                         terrain_sha256=R.digest(terrain), area_sha256=R.digest(area),
                         cell_rgb_code=(out.pop("cell_rgb") @ np.array([4, 2, 1])).astype(np.uint8), cells_xyz=out.pop("cells_xyz").astype(np.float64), **out)
-    print("cfg1 cells", np.load(path)["cells_xyz"].shape[0], "candidates", out["cands_xyz"].shape[0], "best", out["best_xyz"], "score", out["best_score_2dp"],
+    print(name, "cells", np.load(path)["cells_xyz"].shape[0], "candidates", out["cands_xyz"].shape[0], "best", out["best_xyz"], "score", out["best_score_2dp"],
           "fixed", out["fixed_total_2dp"], "colours", out["colour_counts"].tolist(), "->", path.relative_to(ROOT), f"{path.stat().st_size / 1e3:.0f} kB")
 
 
@@ -294,7 +296,8 @@ if __name__ == "__main__":
     main()
     cycles_case()
     vl_edges_case()
-    cfg1_case()
+    config_case("cfg1")
+    config_case("cfg2", 36)
     variants_case()
     edges_case()
     other_nodes()
