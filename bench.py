@@ -269,6 +269,62 @@ def reference_source_sample(scene, res: float, layers: int, k_small: int = 9, k_
             "note": "virtual_lidar.cpp unmodified; KdTreeFLANN / NormalEstimation are the stand-ins of oracle/ref_shim (grid index, not FLANN)"}
 
 
+def feeders_cpu_reference(n_scan: int = 1_000_000) -> dict:
+    """SURVEY D5's CPU baseline of the filter and merger stages on BASELINE config 4's scans (two synthetic 1 M-point
+    32-ring scans, crop 15/10/10, leaf 0.2, the launch files' transforms): the oracle port on one thread, and the
+    reference's own pointcloud_filter.cpp (oracle/_ref, stand-in VoxelGrid) per message — the same scan delivered once and
+    four times to one process, differenced.  The GPU figures beside them are `feeders.filter_*` / `feeders.merge` of the
+    other arm's line."""
+    import tempfile
+    try:
+        from oracle import binding as O
+        from pointcloud_processor_b200 import _abi as A, scenes
+        zt, zq = scenes.sensor_in_map(dict(xyz=(0.0, 0.0, 0.0), yaw=0.0), scenes.ZX120_VELODYNE)
+        rt, rq = scenes.sensor_in_map(scenes.ROBOT_BASE, scenes.ROBOT_VELODYNE)
+        scans = {"robot": scenes.lidar_scan(rt, rq, n_scan, 4, "rect"), "zx120": scenes.lidar_scan(zt, zq, n_scan, 5, "rect")}
+        tfs = {"robot": (rt, rq), "zx120": (zt, zq)}
+        box = A.CropBox(0.0, 15.0, -10.0, 10.0, -1.5, 10.0)
+        out = {"config": f"cfg4: two {n_scan}-point 32-ring scans -> crop 15/10/10 -> voxel 0.2 -> merge", "cores": 1}
+        cent = {}
+        for who, scan in scans.items():
+            best = float("inf")
+            for _ in range(3):
+                t0 = time.perf_counter()
+                cropped = O.crop(scan, box)[0]
+                cent[who] = O.voxel_grid(cropped, 0.2)[0]
+                best = min(best, time.perf_counter() - t0)
+            out[f"filter_{who}_port_ms"] = 1e3 * best
+            out[f"filter_{who}_points"] = [int(scan.shape[0]), int(cropped.shape[0]), int(cent[who].shape[0])]
+        t0 = time.perf_counter()
+        for _ in range(20):
+            merged = np.concatenate([O.transform(cent[w], *tfs[w]) for w in ("robot", "zx120")])
+        out["merge_port_ms"] = 1e3 * (time.perf_counter() - t0) / 20
+        out["merge_points"] = int(merged.shape[0])
+        exe = ROOT / "oracle" / "_ref" / "pointcloud_filter_ref"
+        if exe.exists():
+            with tempfile.TemporaryDirectory() as tmp:
+                tmp = Path(tmp)
+                scans["robot"].tofile(tmp / "scan.bin")
+                line = f"cloud /four_wheel_robot/velodyne_points {tmp / 'scan.bin'} {n_scan} 16 four_wheel_robot/velodyne 1 0 x:0 y:4 z:8"
+                wall = {}
+                for k in (1, 4):
+                    d = tmp / f"k{k}"
+                    d.mkdir()
+                    (d / "script.txt").write_text("\n".join([line] * k) + "\n")
+                    env = dict(os.environ, MOCK_ROS_SCRIPT=str(d / "script.txt"), MOCK_ROS_OUT=str(d))
+                    t0 = time.perf_counter()
+                    subprocess.run([str(exe)], env=env, check=True, capture_output=True, timeout=300)
+                    wall[k] = time.perf_counter() - t0
+                    n_out = json.loads(sorted(d.glob("[0-9][0-9][0-9].json"))[-1].read_text())["width"]
+            out["filter_robot_reference_source_ms"] = 1e3 * (wall[4] - wall[1]) / 3
+            out["filter_robot_reference_source_voxels"] = int(n_out)
+            out["note"] = ("reference_source: pointcloud_filter.cpp unmodified per message (fromROSMsg + crop + VoxelGrid + toROSMsg; the mock's "
+                           "read of the scan file included), pcl::VoxelGrid = the stand-in of oracle/ref_shim")
+        return out
+    except Exception as e:  # noqa: BLE001 — informational leg
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+
+
 class Rig:
     """One rank's context, stream and collectives."""
 
@@ -895,6 +951,7 @@ def run_reference(args) -> dict | None:
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         **({"reference_source": refsrc} if refsrc is not None else {}),
+        **({"feeders_cpu": feeders_cpu_reference()} if world == 1 and not args.no_reference_source else {}),
     }
 
 
@@ -905,7 +962,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-reference-source", action="store_true",
-                    help="reference arm: skip the single-threaded run of the reference's own virtual_lidar.cpp (oracle/_ref)")
+                    help="reference arm: skip the single-threaded run of the reference's own virtual_lidar.cpp (oracle/_ref) and the feeders' CPU baseline")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default=None,
                     help="default: cfg2 (BASELINE.json configs[1]) on one GPU, cfg3 (configs[2]) strong-scaled on N > 1")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
